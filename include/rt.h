@@ -1,0 +1,230 @@
+/*
+ * rt.h — C ABI of the B200 render core for simple-raytracer scenes.
+ *
+ * This is the drop-in boundary for the reference's one hot path. The reference
+ * has no FFI of its own: the seam is the single call
+ *
+ *     Mat3D matt = create_view_window_and_ray_trace(view_origin,
+ *                      view_direction.norm(), view_up.norm(), fov_h,
+ *                      height, width, background_color);      (main.cpp:607)
+ *
+ * whose callee reads everything else from the mutable global `Globals
+ * environment` (main.cpp:58, src/definitions.h:304-311).  The structs below
+ * carry exactly that state as plain-old-data, the functions replace that call.
+ *
+ * Conventions
+ *  - plain C, no exceptions; every int-returning function returns RT_OK (0) or
+ *    a negative RT_E_* code and leaves a message in rt_last_error().
+ *  - all pointers inside RtSceneDesc are HOST pointers, caller-owned, and may
+ *    be released as soon as rt_upload_scene() returns.
+ *  - one RtScene lives on the CUDA device that was current when it was
+ *    uploaded.  A handle is not thread-safe; distinct handles are independent.
+ *  - there is no CPU fallback: without a CUDA device every call fails with
+ *    RT_E_CUDA.
+ */
+#ifndef RT_B200_RT_H
+#define RT_B200_RT_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+#define RT_OK            0
+#define RT_E_INVALID    -1   /* bad argument / malformed scene description   */
+#define RT_E_CUDA       -2   /* CUDA runtime error (see rt_last_error)        */
+#define RT_E_NOMEM      -3   /* host or device allocation failed              */
+#define RT_E_STATE      -4   /* call order (e.g. download before render)      */
+#define RT_E_PARSE      -5   /* scene / texture file could not be parsed      */
+#define RT_E_IO         -6   /* file could not be opened / written            */
+
+/* ---- scene description (what `environment` + main()'s locals hold) ------ */
+
+/* Phong material, src/definitions.h:249-254, filled by `mtlcolor`
+ * (main.cpp:272-308).  opacity is already clamped to [0,1]; opacity = eta = 1
+ * when the scene line had no alpha/eta pair. */
+typedef struct RtMaterial {
+    float od[3];     /* diffuse colour   Od  */
+    float os[3];     /* specular colour  Os  */
+    float ka, kd, ks;
+    float n;         /* specular exponent */
+    float opacity;   /* alpha */
+    float eta;       /* refraction index */
+} RtMaterial;
+
+/* 8-bit RGB texture, row-major [y][x][3]; the reference keeps it as
+ * Mat3D[x][y][c] of size_t (src/definitions.h:197-237, utility.h:59-139). */
+typedef struct RtTexture {
+    int32_t width, height;
+    const uint8_t* rgb;
+} RtTexture;
+
+/* src/definitions.h:265-270 + the SceneObjectInfo it points to (256-263). */
+typedef struct RtSphere {
+    float   center[3];
+    float   radius;
+    int32_t material;   /* index into RtSceneDesc.materials               */
+    int32_t texture;    /* index into RtSceneDesc.textures, -1 = none     */
+    int32_t id;         /* reference object id: 1-based creation order over
+                           spheres and faces together (main.cpp:329, 476)  */
+} RtSphere;
+
+/* src/definitions.h:272-281.  The surface normal is NOT passed: the library
+ * recomputes it with the expression of main.cpp:537-539. */
+typedef struct RtFace {
+    float   v[3][3];    /* vertex positions                                */
+    float   vn[3][3];   /* per-vertex normals (raw, un-normalised)         */
+    float   vt[3][2];   /* per-vertex texture coordinates                  */
+    int32_t smooth;     /* Face::smooth_shading                            */
+    int32_t material;
+    int32_t texture;    /* -1 = none                                       */
+    int32_t id;
+} RtFace;
+
+/* src/definitions.h:283-289; w == 0 -> directional with direction xyz
+ * (un-normalised!), otherwise point light at xyz (main.cpp:383-396). */
+typedef struct RtLight {
+    float xyz[3];
+    float w;
+    float rgb[3];
+} RtLight;
+
+typedef struct RtSceneDesc {
+    int32_t width, height;        /* imsize                                  */
+    float   eye[3];
+    float   viewdir[3];           /* raw; normalised inside like main.cpp:607 */
+    float   updir[3];             /* raw; normalised inside like main.cpp:607 */
+    float   hfov_deg;
+    float   bkg[3];               /* NOT clamped (main.cpp:721)               */
+    float   bkg_eta;              /* 0.0f when bkgcolor had no 4th argument
+                                     (main.cpp:260-264, 751)                  */
+    int32_t n_materials;  const RtMaterial* materials;
+    int32_t n_textures;   const RtTexture*  textures;
+    int32_t n_spheres;    const RtSphere*   spheres;   /* file order */
+    int32_t n_faces;      const RtFace*     faces;     /* file order */
+    int32_t n_lights;     const RtLight*    lights;    /* file order */
+} RtSceneDesc;
+
+/* ---- render parameters (environment.other, main.cpp:100-101) ------------ */
+#define RT_ACCEL_AUTO   0   /* brute force for small scenes, LBVH otherwise */
+#define RT_ACCEL_BRUTE  1
+#define RT_ACCEL_LBVH   2
+
+typedef struct RtRenderParams {
+    int32_t max_depth;     /* environment.other["recursion_depth"], default 4 */
+    float   epsilon;       /* environment.other["epsilon"], default 1.0e-3f   */
+    int32_t accel;         /* RT_ACCEL_*                                      */
+    int32_t rank;          /* row-tile sharding: this process renders tiles   */
+    int32_t world_size;    /*   t with t % world_size == rank; default 0 / 1  */
+    int32_t tile_rows;     /* rows per tile (default 8)                       */
+    int32_t instrument;    /* 1: count rays / nodes / BVH work (slower)       */
+    int32_t reserved;
+} RtRenderParams;
+
+/* Filled by rt_render when a non-NULL pointer is passed.  The ray counts
+ * follow the reference's unit "one TraceRay call" (main.cpp:729, 896, 928,
+ * 992, 1113); they are only counted when params.instrument != 0, the node
+ * counts always. */
+typedef struct RtStats {
+    double   render_ms;          /* device time of this rt_render (CUDA events) */
+    uint64_t nodes_total;        /* ShadeRay invocations                       */
+    uint64_t nodes_per_level[8]; /* by generation (0 = primary hits)           */
+    uint64_t rays_primary, rays_shadow, rays_transmit, rays_reflect;
+    uint64_t bvh_nodes_visited, prim_tests;
+    uint64_t texel_fetches;
+    int32_t  accel_used;         /* RT_ACCEL_BRUTE or RT_ACCEL_LBVH            */
+    int32_t  kernel_launches;    /* launches of our kernels in this render     */
+    int32_t  queue_regrows;      /* wavefront queues re-sized and frame redone */
+    int32_t  reserved;
+} RtStats;
+
+typedef struct RtScene RtScene;   /* opaque: all device state of one scene */
+
+/* ---- the three calls named by the north star ---------------------------- */
+
+/* Packs the scene into structure-of-arrays device buffers, uploads textures,
+ * builds the LBVH when the scene is large.  Replaces the parser's writes into
+ * `environment` (main.cpp:328-552). */
+int rt_upload_scene(const RtSceneDesc* desc, RtScene** out);
+
+/* Renders this rank's row tiles.  Replaces create_view_window_and_ray_trace
+ * (main.cpp:670-767) and everything below it (ShadeRay 783-1207, TraceRay
+ * 1215-1407).  Synchronous.  `params` may be NULL (defaults). */
+int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats_or_null);
+
+/* Copies the last rendered frame to host memory.
+ *   rgb   : height*width*3 bytes, row-major, top row first (= matt(i,j,c),
+ *           main.cpp:760-762).
+ *   flags : height*width bytes or NULL. bit0..2: channel r/g/b was NaN (the
+ *           reference prints 18446744071562067968 there); bit3:
+ *           primary ray missed (pixel = un-clamped bkgcolor); rgb holds the
+ *           value clamped to 0..255 in that case.
+ * With world_size > 1 only the rows of this rank's tiles are written; other
+ * rows of the host buffers are left untouched. */
+int rt_download_framebuffer(RtScene* scene, uint8_t* rgb, uint8_t* flags);
+
+void        rt_free_scene(RtScene* scene);
+const char* rt_last_error(void);
+int         rt_abi_version(void);
+
+/* ---- device-side entry points used by the multi-GPU / re-render plumbing - */
+
+/* Number of bytes of this rank's tile buffer ([local_tile][row][col] RGBA8,
+ * A = flags) for the given sharding. */
+size_t rt_tile_buffer_bytes(const RtScene* scene, int32_t world_size, int32_t tile_rows);
+
+/* Like rt_render, but asynchronous on `cuda_stream` (a cudaStream_t, may be
+ * NULL for the default stream) and with the RGBA8 tile buffer written to
+ * caller-provided DEVICE memory (e.g. the send buffer of an NCCL allgather).
+ * dev_tiles may be NULL to render into the scene's own buffer only. */
+int rt_render_async(RtScene* scene, const RtRenderParams* params,
+                    void* dev_tiles, void* cuda_stream);
+
+/* After an allgather of every rank's tile buffer ([rank][local_tile][row][col]
+ * RGBA8, device memory) puts the pixels in scanline order:
+ * dev_rgba_out[height][width] RGBA8. Asynchronous on cuda_stream. */
+int rt_deinterleave_tiles(const RtScene* scene, const void* dev_gathered,
+                          void* dev_rgba_out, int32_t world_size,
+                          int32_t tile_rows, void* cuda_stream);
+
+/* Re-render API: replace the camera without re-uploading. */
+int rt_set_camera(RtScene* scene, const float eye[3], const float viewdir[3],
+                  const float updir[3], float hfov_deg);
+
+/* ---- parity probes (the reference's TraceRay + closest-hit loops) -------- */
+
+/* Closest hit of n rays against the scene (HOST arrays): the loop of
+ * main.cpp:730-742 / 1109-1124 applied to TraceRay (1215-1407) with the tie
+ * rule "faces before spheres, file order, strict <" and t > tmin.
+ *   origins, dirs : n*3 floats
+ *   out_id        : reference object id of the hit, 0 = miss
+ *   out_t         : hit distance (bit pattern of the reference's float)
+ *   out_normal    : n*3 floats, may be NULL
+ *   out_bary      : n*3 floats (a,b,g of a face hit), may be NULL */
+int rt_trace_closest(RtScene* scene, int32_t accel, int32_t n,
+                     const float* origins, const float* dirs, float tmin,
+                     int32_t* out_id, float* out_t,
+                     float* out_normal, float* out_bary);
+
+/* Shadow attenuation of n rays (HOST arrays): product of (1 - opacity) over
+ * all hits with tmin < t (< tmax[i] when tmax != NULL) of all objects whose id
+ * differs from self_id[i] (main.cpp:896-912, 928-949).  out_hits = number of
+ * qualifying hits. */
+int rt_trace_shadow(RtScene* scene, int32_t accel, int32_t n,
+                    const float* origins, const float* dirs,
+                    const int32_t* self_id, float tmin, const float* tmax,
+                    float* out_mask, int32_t* out_hits);
+
+/* Primary-hit object id per pixel of the last render (height*width int32,
+ * 0 = miss); available when the last render had instrument != 0. */
+int rt_download_primary_ids(RtScene* scene, int32_t* ids);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_B200_RT_H */

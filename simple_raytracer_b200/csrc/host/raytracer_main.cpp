@@ -1,0 +1,90 @@
+// raytracer_main.cpp — `raytracer scene.txt` -> scene.ppm, the reference CLI
+// (main.cpp:60-99, 604-656) around the CUDA render core.
+//
+//   parser output -> rt_upload_scene -> rt_render -> rt_download_framebuffer -> P3 writer
+//
+// Exit status: the reference returns 0 on every path it survives and dies with
+// SIGABRT (uncaught exception) on malformed input; we print the same messages
+// and return 0 / 1 respectively.  There is no CPU fallback: without a CUDA
+// device the render call fails and so does the program.
+#include "rt.h"
+#include "rt_host.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+static double now_s()
+{
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+int main(int argc, char* argv[])
+{
+    if (argc <= 1) {
+        // main.cpp:653
+        std::printf("Error: Incorrect number of arguments in input file. Please follow this formate: imsize width height\n");
+        return 0;
+    }
+    bool verbose = false;
+    int max_depth = 4;
+    const char* scene_path = nullptr;
+    for (int i = 1; i < argc; i++) {
+        if (!std::strcmp(argv[i], "--stats")) verbose = true;
+        else if (!std::strcmp(argv[i], "--depth") && i + 1 < argc) max_depth = std::atoi(argv[++i]);
+        else if (!scene_path) scene_path = argv[i];
+    }
+    if (!scene_path) return 0;
+
+    double t0 = now_s();
+    RtSceneDesc* desc = nullptr;
+    int rc = rt_host_parse_scene_file(scene_path, nullptr, &desc);
+    if (rc == RT_E_IO) { std::printf("%s\n", rt_host_last_error()); return 0; }   // main.cpp:567-568
+    if (rc != RT_OK) {
+        const char* msg = rt_host_last_error();
+        if (!std::strncmp(msg, "Error: Requires command", 23)) { std::printf("%s\n", msg); return 0; }   // 574-602
+        std::fprintf(stderr, "%s\n", msg);
+        return 1;
+    }
+    double t1 = now_s();
+
+    RtScene* scene = nullptr;
+    rc = rt_upload_scene(desc, &scene);
+    if (rc != RT_OK) { std::fprintf(stderr, "rt_upload_scene: %s\n", rt_last_error()); return 1; }
+    double t2 = now_s();
+
+    RtRenderParams params{};
+    params.max_depth = max_depth; params.epsilon = 1.0e-3f; params.accel = RT_ACCEL_AUTO;
+    params.rank = 0; params.world_size = 1; params.tile_rows = 8;
+    RtStats stats{};
+    rc = rt_render(scene, &params, &stats);
+    if (rc != RT_OK) { std::fprintf(stderr, "rt_render: %s\n", rt_last_error()); return 1; }
+    double t3 = now_s();
+
+    const size_t npx = (size_t)desc->width * (size_t)desc->height;
+    std::vector<uint8_t> rgb(npx * 3), flags(npx);
+    rc = rt_download_framebuffer(scene, rgb.data(), flags.data());
+    if (rc != RT_OK) { std::fprintf(stderr, "rt_download_framebuffer: %s\n", rt_last_error()); return 1; }
+    double t4 = now_s();
+
+    char out_path[4096];
+    if (rt_host_output_path(scene_path, out_path, sizeof out_path) != RT_OK) return 1;
+    rc = rt_host_write_ppm(out_path, desc->width, desc->height, rgb.data(), flags.data(), desc->bkg);
+    if (rc != RT_OK) { std::printf("ERROR: failed to create ppm image\n"); return 0; }   // main.cpp:621
+    double t5 = now_s();
+
+    if (verbose) {
+        std::fprintf(stderr,
+                     "parse %.3f ms | upload %.3f ms | render %.3f ms (device %.3f ms, %llu nodes, accel %s) | "
+                     "download %.3f ms | write %.3f ms\n",
+                     (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, stats.render_ms,
+                     (unsigned long long)stats.nodes_total, stats.accel_used == RT_ACCEL_LBVH ? "lbvh" : "brute",
+                     (t4 - t3) * 1e3, (t5 - t4) * 1e3);
+    }
+    rt_free_scene(scene);
+    rt_host_free_scene_desc(desc);
+    return 0;
+}
