@@ -122,8 +122,10 @@ typedef struct RtRenderParams {
     int32_t rank;          /* row-tile sharding: this process renders tiles   */
     int32_t world_size;    /*   t with t % world_size == rank; default 0 / 1  */
     int32_t tile_rows;     /* rows per tile (default 8)                       */
-    int32_t instrument;    /* 1: count rays / nodes / BVH work (slower)       */
-    int32_t reserved;
+    int32_t instrument;    /* 1: count BVH work / texels, keep primary hit ids
+                              (slower; never use for timing)                  */
+    int32_t profile;       /* 1: CUDA events around every generation's kernel;
+                              rt_render reports RtStats.level_ms / combine_ms */
 } RtRenderParams;
 
 /* Filled by rt_render when a non-NULL pointer is passed.  The ray counts
@@ -141,6 +143,9 @@ typedef struct RtStats {
     int32_t  kernel_launches;    /* launches of our kernels in this render     */
     int32_t  queue_regrows;      /* wavefront queues re-sized and frame redone */
     int32_t  reserved;
+    double   level_ms[8];        /* params.profile: device time of the trace+shade+spawn
+                                    kernel of each generation                   */
+    double   combine_ms;         /* params.profile: all bottom-up combine passes  */
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

@@ -66,7 +66,7 @@ class RtSceneDesc(C.Structure):
 class RtRenderParams(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("epsilon", C.c_float), ("accel", C.c_int32),
                 ("rank", C.c_int32), ("world_size", C.c_int32), ("tile_rows", C.c_int32),
-                ("instrument", C.c_int32), ("reserved", C.c_int32)]
+                ("instrument", C.c_int32), ("profile", C.c_int32)]
 
 
 class RtStats(C.Structure):
@@ -74,7 +74,8 @@ class RtStats(C.Structure):
                 ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_transmit", C.c_uint64),
                 ("rays_reflect", C.c_uint64), ("bvh_nodes_visited", C.c_uint64), ("prim_tests", C.c_uint64),
                 ("texel_fetches", C.c_uint64), ("accel_used", C.c_int32), ("kernel_launches", C.c_int32),
-                ("queue_regrows", C.c_int32), ("reserved", C.c_int32)]
+                ("queue_regrows", C.c_int32), ("reserved", C.c_int32),
+                ("level_ms", C.c_double * 8), ("combine_ms", C.c_double)]
 
     def as_dict(self) -> dict:
         d = {}

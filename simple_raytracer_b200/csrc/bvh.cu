@@ -1,0 +1,378 @@
+// bvh.cu — on-device LBVH build: padded primitive bounds -> 30-bit Morton codes ->
+// LSD radix sort (4 x 8 bits, hand-written) -> Karras hierarchy -> bottom-up refit
+// -> traversal nodes with both child boxes + primitive records in Morton order.
+//
+// The reference has no acceleration structure (TraceRay is O(N) per ray,
+// main.cpp:1215-1407); this one only decides WHICH primitives get the reference's
+// exact tests.  Bounds are padded so that every hit the reference's float
+// arithmetic accepts lies inside:
+//   triangle: the accepted point o + ray*t passes the float barycentric test, i.e.
+//             lies within rounding error of the triangle: pad = 1e-4 * extent +
+//             4e-6 * (largest coordinate magnitude in play);
+//   sphere  : B*B - 4*C >= 0 in mixed precision with a ray that is unit only up to
+//             rounding accepts rho^2 <= r^2 + c*eps*D^2 (D = distance from the ray
+//             origin to the centre): r_eff^2 = r^2 + 2e-6 * Dmax^2.
+#include "bvh.cuh"
+#include "host_scene.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+namespace rt {
+
+namespace {
+
+struct BuildBounds {
+    float lo[3], hi[3];      // bounds of all primitives and the eye
+    float scale;             // largest |coordinate|
+};
+
+RT_DEV unsigned expand_bits10(unsigned v)
+{
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+// one thread per primitive (order index): padded box + Morton code of its centre
+__global__ void prim_bounds_kernel(const float4* __restrict__ tri, const float4* __restrict__ sph, int nf, int ns,
+                                   BuildBounds bb, float4* __restrict__ box_lo, float4* __restrict__ box_hi,
+                                   unsigned* __restrict__ keys, unsigned* __restrict__ vals)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nf + ns) return;
+    float lo[3], hi[3];
+    if (i < nf) {
+        const float4* w = tri + (size_t)i * kTriWords;
+        const float4 v0 = w[1], e1 = w[2], e2 = w[3];
+        const float p[3][3] = { { v0.x, v0.y, v0.z }, { v0.x + e1.x, v0.y + e1.y, v0.z + e1.z }, { v0.x + e2.x, v0.y + e2.y, v0.z + e2.z } };
+        float ext = 0.0f;
+        for (int c = 0; c < 3; c++) {
+            lo[c] = fminf(p[0][c], fminf(p[1][c], p[2][c]));
+            hi[c] = fmaxf(p[0][c], fmaxf(p[1][c], p[2][c]));
+            ext = fmaxf(ext, hi[c] - lo[c]);
+        }
+        const float pad = 1.0e-4f * ext + 4.0e-6f * bb.scale;
+        for (int c = 0; c < 3; c++) { lo[c] -= pad; hi[c] += pad; }
+    } else {
+        const float4 s = sph[(size_t)(i - nf) * kSphWords];
+        const float c3[3] = { s.x, s.y, s.z };
+        float d2 = 0.0f;
+        for (int c = 0; c < 3; c++) {
+            const float d = fmaxf(fabsf(c3[c] - bb.lo[c]), fabsf(c3[c] - bb.hi[c]));
+            d2 += d * d;
+        }
+        const float r = fabsf(s.w);
+        const float reff = sqrtf(r * r + 2.0e-6f * d2) * 1.00001f + 4.0e-6f * bb.scale;
+        for (int c = 0; c < 3; c++) { lo[c] = c3[c] - reff; hi[c] = c3[c] + reff; }
+    }
+    // NaN / inf primitives (degenerate input) never hit anything: give them an empty box
+    bool ok = true;
+    for (int c = 0; c < 3; c++) ok = ok && isfinite(lo[c]) && isfinite(hi[c]);
+    if (!ok) { for (int c = 0; c < 3; c++) { lo[c] = FLT_MAX; hi[c] = -FLT_MAX; } }
+    box_lo[i] = make_float4(lo[0], lo[1], lo[2], 0.0f);
+    box_hi[i] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+    unsigned code = 0;
+    if (ok) {
+        unsigned q[3];
+        for (int c = 0; c < 3; c++) {
+            const float extent = bb.hi[c] - bb.lo[c];
+            float u = extent > 0.0f ? (0.5f * (lo[c] + hi[c]) - bb.lo[c]) / extent : 0.5f;
+            u = fminf(fmaxf(u * 1024.0f, 0.0f), 1023.0f);
+            q[c] = (unsigned)u;
+        }
+        code = (expand_bits10(q[0]) << 2) | (expand_bits10(q[1]) << 1) | expand_bits10(q[2]);
+    }
+    keys[i] = code;
+    vals[i] = (unsigned)i;
+}
+
+// ---- LSD radix sort, 8 bits per pass -------------------------------------------
+constexpr int kSortThreads = 256;
+constexpr int kSortRounds = 8;                       // items per thread
+constexpr int kSortTile = kSortThreads * kSortRounds;
+
+__global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const unsigned* __restrict__ keys, int n, int shift,
+                                                                  unsigned* __restrict__ hist, int nblocks)
+{
+    __shared__ unsigned h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * kSortTile;
+    for (int r = 0; r < kSortRounds; r++) {
+        const int i = base + r * kSortThreads + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];   // digit-major: a scan gives global offsets
+}
+
+// exclusive scan of `count` values by one block
+__global__ void __launch_bounds__(1024) scan_kernel(unsigned* __restrict__ data, int count)
+{
+    __shared__ unsigned warp_sums[32];
+    __shared__ unsigned carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < count; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned v = i < count ? data[i] : 0u;
+        unsigned x = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+            if ((threadIdx.x & 31) >= o) x += y;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            unsigned s = warp_sums[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned y = __shfl_up_sync(0xffffffffu, s, o);
+                if (threadIdx.x >= o) s += y;
+            }
+            warp_sums[threadIdx.x] = s;
+        }
+        __syncthreads();
+        const unsigned before = (threadIdx.x >> 5) ? warp_sums[(threadIdx.x >> 5) - 1] : 0u;
+        const unsigned c = carry;
+        if (i < count) data[i] = c + before + x - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + before + x;
+        __syncthreads();
+    }
+}
+
+// stable scatter: ranks inside a block come from warp match + per-warp digit counts
+__global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(const unsigned* __restrict__ keys_in,
+                                                                     const unsigned* __restrict__ vals_in, int n, int shift,
+                                                                     const unsigned* __restrict__ offsets, int nblocks,
+                                                                     unsigned* __restrict__ keys_out, unsigned* __restrict__ vals_out)
+{
+    constexpr int kWarps = kSortThreads / 32;
+    __shared__ unsigned digit_base[256];
+    __shared__ unsigned warp_cnt[kWarps][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    digit_base[threadIdx.x] = offsets[threadIdx.x * nblocks + blockIdx.x];
+    for (int w = 0; w < kWarps; w++) warp_cnt[w][threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * kSortTile;
+    for (int r = 0; r < kSortRounds; r++) {
+        const int i = base + r * kSortThreads + threadIdx.x;
+        const bool valid = i < n;
+        unsigned key = 0, val = 0, digit = 256;   // 256: invalid lanes match only each other
+        if (valid) { key = keys_in[i]; val = vals_in[i]; digit = (key >> shift) & 255u; }
+        const unsigned peers = __match_any_sync(0xffffffffu, digit);
+        const unsigned rank = __popc(peers & ((1u << lane) - 1u));
+        if (valid && rank == 0) warp_cnt[warp][digit] = __popc(peers);
+        __syncthreads();
+        if (valid) {
+            unsigned off = digit_base[digit] + rank;
+            for (int w = 0; w < warp; w++) off += warp_cnt[w][digit];
+            keys_out[off] = key; vals_out[off] = val;
+        }
+        __syncthreads();
+        unsigned total = 0;
+        for (int w = 0; w < kWarps; w++) { total += warp_cnt[w][threadIdx.x]; warp_cnt[w][threadIdx.x] = 0; }
+        digit_base[threadIdx.x] += total;
+        __syncthreads();
+    }
+}
+
+// ---- Karras 2012 -------------------------------------------------------------------
+RT_DEV int delta(const unsigned* keys, int n, int i, int j)
+{
+    if (j < 0 || j >= n) return -1;
+    const unsigned a = keys[i], b = keys[j];
+    if (a == b) return 32 + __clz((unsigned)i ^ (unsigned)j);   // duplicate codes: fall back to the index
+    return __clz(a ^ b);
+}
+
+// internal node i: children + covered range; child < 0 encodes leaf ~child
+__global__ void hierarchy_kernel(const unsigned* __restrict__ keys, int n, int2* __restrict__ children,
+                                 int2* __restrict__ range, int* __restrict__ parent_internal, int* __restrict__ parent_leaf)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) / 2;; t = (t + 1) / 2) {
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int left = (lo == gamma) ? ~gamma : gamma;
+    const int right = (hi == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    children[i] = make_int2(left, right);
+    range[i] = make_int2(lo, hi);
+    if (left < 0) parent_leaf[gamma] = i; else parent_internal[gamma] = i;
+    if (right < 0) parent_leaf[gamma + 1] = i; else parent_internal[gamma + 1] = i;
+    if (i == 0) parent_internal[0] = -1;
+}
+
+RT_DEV void box_union(float4& lo, float4& hi, const float4 a_lo, const float4 a_hi)
+{
+    lo.x = fminf(lo.x, a_lo.x); lo.y = fminf(lo.y, a_lo.y); lo.z = fminf(lo.z, a_lo.z);
+    hi.x = fmaxf(hi.x, a_hi.x); hi.y = fmaxf(hi.y, a_hi.y); hi.z = fmaxf(hi.z, a_hi.z);
+}
+
+// one thread per leaf climbs; the second arrival at a node computes its box
+__global__ void refit_kernel(int n, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ prim_lo,
+                             const float4* __restrict__ prim_hi, const int2* __restrict__ children,
+                             const int* __restrict__ parent_internal, const int* __restrict__ parent_leaf,
+                             float4* __restrict__ node_lo, float4* __restrict__ node_hi, unsigned* __restrict__ arrivals)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int node = parent_leaf[k];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&arrivals[node], 1u) == 0u) return;   // first child to arrive: the sibling finishes the node
+        const int2 ch = children[node];
+        float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
+        const int c2[2] = { ch.x, ch.y };
+        for (int c = 0; c < 2; c++) {
+            if (c2[c] < 0) {
+                const unsigned p = sorted_vals[~c2[c]];
+                box_union(lo, hi, prim_lo[p], prim_hi[p]);
+            } else {
+                box_union(lo, hi, __ldcg(&node_lo[c2[c]]), __ldcg(&node_hi[c2[c]]));
+            }
+        }
+        node_lo[node] = lo; node_hi[node] = hi;
+        node = parent_internal[node];
+    }
+}
+
+// traversal nodes: both child boxes + child codes; subtrees of <= kLeafMax primitives collapse into a leaf
+__global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ prim_lo,
+                                  const float4* __restrict__ prim_hi, const int2* __restrict__ children,
+                                  const int2* __restrict__ range, const float4* __restrict__ node_lo,
+                                  const float4* __restrict__ node_hi, float4* __restrict__ nodes)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int2 ch = children[i];
+    const int c2[2] = { ch.x, ch.y };
+    float4 lo[2], hi[2];
+    int code[2], count[2];
+    for (int c = 0; c < 2; c++) {
+        if (c2[c] < 0) {
+            const int slot = ~c2[c];
+            const unsigned p = sorted_vals[slot];
+            lo[c] = prim_lo[p]; hi[c] = prim_hi[p];
+            code[c] = slot; count[c] = 1;
+        } else {
+            lo[c] = node_lo[c2[c]]; hi[c] = node_hi[c2[c]];
+            const int2 r = range[c2[c]];
+            const int size = r.y - r.x + 1;
+            if (size <= kLeafMax) { code[c] = r.x; count[c] = size; }
+            else { code[c] = c2[c]; count[c] = 0; }
+        }
+    }
+    float4* w = nodes + (size_t)i * 4;
+    w[0] = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
+    w[1] = make_float4(hi[0].y, hi[0].z, lo[1].x, lo[1].y);
+    w[2] = make_float4(lo[1].z, hi[1].x, hi[1].y, hi[1].z);
+    w[3] = make_float4(__int_as_float(code[0]), __int_as_float(code[1]), __int_as_float(count[0]), __int_as_float(count[1]));
+}
+
+// scenes of <= kLeafMax primitives: a single node whose left child is the only leaf
+__global__ void emit_tiny_kernel(int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
+                                 float4* __restrict__ nodes)
+{
+    if (blockIdx.x || threadIdx.x) return;
+    float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
+    for (int p = 0; p < n; p++) box_union(lo, hi, prim_lo[p], prim_hi[p]);
+    nodes[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
+    nodes[1] = make_float4(hi.y, hi.z, FLT_MAX, FLT_MAX);
+    nodes[2] = make_float4(FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX);
+    nodes[3] = make_float4(__int_as_float(0), __int_as_float(0), __int_as_float(n), __int_as_float(0));
+}
+
+// primitive records in Morton order (spheres widened to the triangle record size)
+__global__ void emit_prims_kernel(int n, int nf, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ tri,
+                                  const float4* __restrict__ sph, float4* __restrict__ out)
+{
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int p = (int)sorted_vals[k];
+    float4* o = out + (size_t)k * kTriWords;
+    if (p < nf) {
+        const float4* w = tri + (size_t)p * kTriWords;
+        for (int q = 0; q < kTriWords; q++) o[q] = w[q];
+    } else {
+        const float4* w = sph + (size_t)(p - nf) * kSphWords;
+        o[0] = w[0];
+        o[1] = o[2] = o[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+        o[4] = make_float4(0.0f, w[1].x, w[1].y, __int_as_float(1));
+    }
+}
+
+}  // namespace
+
+int build_bvh(SceneHost* s)
+{
+    const int n = s->nf + s->ns;
+    if (n <= 0) { s->bvh_built = true; s->bvh_n_nodes = 0; return RT_OK; }
+    cudaStream_t st = s->stream;
+    BuildBounds bb;
+    float scale = 0.0f;
+    for (int c = 0; c < 3; c++) {
+        bb.lo[c] = std::fmin(s->scene_lo[c], s->cam.eye[c]);
+        bb.hi[c] = std::fmax(s->scene_hi[c], s->cam.eye[c]);
+        scale = std::fmax(scale, std::fmax(std::fabs(bb.lo[c]), std::fabs(bb.hi[c])));
+    }
+    bb.scale = scale;
+
+    const int n_internal = n > kLeafMax ? n - 1 : 1;
+    const int nblocks = (n + kSortTile - 1) / kSortTile;
+    DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals;
+    const size_t N = (size_t)n;
+    if (!box_lo.reserve(N * 16) || !box_hi.reserve(N * 16) || !keys_a.reserve(N * 4) || !keys_b.reserve(N * 4) ||
+        !vals_a.reserve(N * 4) || !vals_b.reserve(N * 4) || !hist.reserve((size_t)256 * nblocks * 4) ||
+        !children.reserve(N * 8) || !range.reserve(N * 8) || !par_i.reserve(N * 4) || !par_l.reserve(N * 4) ||
+        !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4))
+        return RT_E_NOMEM;
+    if (!s->bvh_nodes.reserve((size_t)n_internal * 64) || !s->bvh_tri.reserve(N * kTriWords * 16)) return RT_E_NOMEM;
+
+    const int B = 256, G = (n + B - 1) / B;
+    prim_bounds_kernel<<<G, B, 0, st>>>(s->tri.as<float4>(), s->sph.as<float4>(), s->nf, s->ns, bb, box_lo.as<float4>(),
+                                        box_hi.as<float4>(), keys_a.as<unsigned>(), vals_a.as<unsigned>());
+    unsigned *kin = keys_a.as<unsigned>(), *kout = keys_b.as<unsigned>(), *vin = vals_a.as<unsigned>(), *vout = vals_b.as<unsigned>();
+    for (int shift = 0; shift < 32; shift += 8) {
+        radix_hist_kernel<<<nblocks, kSortThreads, 0, st>>>(kin, n, shift, hist.as<unsigned>(), nblocks);
+        scan_kernel<<<1, 1024, 0, st>>>(hist.as<unsigned>(), 256 * nblocks);
+        radix_scatter_kernel<<<nblocks, kSortThreads, 0, st>>>(kin, vin, n, shift, hist.as<unsigned>(), nblocks, kout, vout);
+        std::swap(kin, kout); std::swap(vin, vout);
+    }
+    // 4 passes: the sorted data is back in keys_a / vals_a
+    if (n > kLeafMax) {
+        RT_CUDA(cudaMemsetAsync(arrivals.p, 0, N * 4, st));
+        hierarchy_kernel<<<G, B, 0, st>>>(kin, n, children.as<int2>(), range.as<int2>(), par_i.as<int>(), par_l.as<int>());
+        refit_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(), par_i.as<int>(),
+                                      par_l.as<int>(), node_lo.as<float4>(), node_hi.as<float4>(), arrivals.as<unsigned>());
+        emit_nodes_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
+                                           range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(), s->bvh_nodes.as<float4>());
+    } else {
+        emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), s->bvh_nodes.as<float4>());
+    }
+    emit_prims_kernel<<<G, B, 0, st>>>(n, s->nf, vin, s->tri.as<float4>(), s->sph.as<float4>(), s->bvh_tri.as<float4>());
+    RT_CUDA(cudaGetLastError());
+    RT_CUDA(cudaStreamSynchronize(st));
+    s->bvh_n_nodes = n_internal; s->bvh_root = 0; s->bvh_built = true;
+    return RT_OK;
+}
+
+}  // namespace rt

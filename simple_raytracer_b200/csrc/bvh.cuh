@@ -1,0 +1,271 @@
+// bvh.cuh — LBVH traversal that returns what the reference's brute-force loops
+// return.
+//
+// Node = 4 float4 words holding BOTH children's boxes, so one 64-byte fetch decides
+// two subtrees:
+//   w0 = L.lo.xyz, L.hi.x     w1 = L.hi.yz, R.lo.xy     w2 = R.lo.z, R.hi.xyz
+//   w3 = as_float{ left, right, left_count, right_count }
+//        count == 0: child is an internal node index; count > 0: child is a leaf
+//        covering `count` consecutive slots of the Morton-ordered primitive array
+//        starting at slot `left` / `right`.
+// Leaf slots are 5-word records (kTriWords) for triangles AND spheres:
+//   triangle: the record of scene_device.h, w4 = d12, kshadow, as_float(order), 0
+//   sphere  : w0 = centre, radius ; w4 = 0, kshadow, as_float(order), as_float(1)
+//
+// Boxes are padded at build time (bvh.cu) so that every point the reference's float
+// arithmetic accepts lies inside; the slab test itself only culls and may use any
+// arithmetic.  Exact-rounding tests (trace.cuh) run at the leaves, so a hit's t, b, g
+// are bit-identical to the brute-force walk; ties in t are broken by the iteration
+// order of the reference (smaller `order` wins).
+#pragma once
+
+#include "trace.cuh"
+
+namespace rt {
+
+constexpr int kBvhStack = 64;
+constexpr int kLeafMax = 4;
+
+template <bool kCount>
+struct BvhAccelT {
+    const float4* nodes;
+    const float4* prims;   // Morton order, kTriWords words per slot
+    const float4* tri;     // file order (direct tests of one known object)
+    const float4* sph;
+    int nf, ns;
+    int root;              // node index; n_nodes == 0 means empty scene
+    int n_nodes;
+    bool count_all = false;   // shadow(): keep counting hits after an opaque occluder (parity probes)
+    // instrumented variant only (kCount): child boxes tested / primitives tested by this thread
+    mutable unsigned long long cnt_boxes = 0, cnt_prims = 0;
+
+    RT_DEV static bool finite3(V3 v) { return isfinite(v.x) && isfinite(v.y) && isfinite(v.z); }
+
+    // conservative slab test; returns entry distance in tn
+    RT_DEV static bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, V3 o, V3 inv,
+                            float tmin, float tmax, float& tn)
+    {
+        const float x0 = (lox - o.x) * inv.x, x1 = (hix - o.x) * inv.x;
+        const float y0 = (loy - o.y) * inv.y, y1 = (hiy - o.y) * inv.y;
+        const float z0 = (loz - o.z) * inv.z, z1 = (hiz - o.z) * inv.z;
+        // fminf / fmaxf drop NaN (0 * inf when the origin sits on a slab plane): conservative
+        tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
+        const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+        return tn <= tf * 1.0000005f;
+    }
+
+    // Generic traversal.  `visit(slot_words, tcur)` tests one primitive and returns the
+    // new upper bound for culling (or a negative value to stop the whole walk).
+    template <class Visit>
+    RT_DEV void walk(V3 o, V3 ray, float tmin, float tmax, Visit& visit) const
+    {
+        if (n_nodes == 0 || !finite3(ray) || !finite3(o)) return;   // NaN/inf rays hit nothing in the reference either
+        const V3 inv = mk3(1.0f / ray.x, 1.0f / ray.y, 1.0f / ray.z);
+        int stack[kBvhStack];
+        int sp = 0;
+        int node = root;
+        while (true) {
+            const float4* w = nodes + (size_t)node * 4;
+            const float4 w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+            const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
+            const int ln = __float_as_int(w3.z), rn = __float_as_int(w3.w);
+            float tl, tr;
+            bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, o, inv, tmin, tmax, tl);
+            bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, o, inv, tmin, tmax, tr);
+            if (kCount) cnt_boxes += 2;
+            // leaves are tested right away
+            if (hl && ln > 0) {
+                for (int k = 0; k < ln; k++) {
+                    if (kCount) cnt_prims++;
+                    tmax = visit(prims + (size_t)(lc + k) * kTriWords, tmax);
+                    if (tmax < 0.0f) return;
+                }
+                hl = false;
+            }
+            if (hr && rn > 0) {
+                if (tr <= tmax * 1.0000005f) {
+                    for (int k = 0; k < rn; k++) {
+                        if (kCount) cnt_prims++;
+                        tmax = visit(prims + (size_t)(rc + k) * kTriWords, tmax);
+                        if (tmax < 0.0f) return;
+                    }
+                }
+                hr = false;
+            }
+            if (hl && hr) {
+                // near child first, far child on the stack
+                const bool left_first = tl <= tr;
+                if (sp < kBvhStack) stack[sp++] = left_first ? rc : lc;
+                node = left_first ? lc : rc;
+            } else if (hl) {
+                node = lc;
+            } else if (hr) {
+                node = rc;
+            } else {
+                if (sp == 0) return;
+                node = stack[--sp];
+            }
+        }
+    }
+
+    struct ClosestVisit {
+        V3 o, ray; float tmin; Hit best; int best_order;
+        RT_DEV float operator()(const float4* w, float tmax)
+        {
+            const float4 w4 = w[4];
+            const int order = __float_as_int(w4.z);
+            if (__float_as_int(w4.w) == 0) {
+                float t;
+                if (tri_distance(w[0], o, ray, t) && t > tmin && (t < best.t || (t == best.t && order < best_order))) {
+                    float b, g;
+                    if (tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g)) { best.t = t; best.obj = order; best.b = b; best.g = g; best_order = order; }
+                }
+            } else {
+                float tf, tn;
+                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                if (n >= 1 && tf > tmin && (tf < best.t || (tf == best.t && order < best_order))) { best.t = tf; best.obj = order; best_order = order; }
+                if (n == 2 && tn > tmin && (tn < best.t || (tn == best.t && order < best_order))) { best.t = tn; best.obj = order; best_order = order; }
+            }
+            return fminf(tmax, best.t);
+        }
+    };
+
+    RT_DEV Hit closest(V3 o, V3 ray, float tmin) const
+    {
+        ClosestVisit v; v.o = o; v.ray = ray; v.tmin = tmin;
+        v.best.t = 3.402823466e+38f; v.best.obj = -1; v.best.b = v.best.g = 0.0f; v.best_order = 0x7fffffff;
+        walk(o, ray, tmin, 3.402823466e+38f, v);
+        return v.best;
+    }
+
+    // Face-incidence transmission (main.cpp:992-1011) in its order-free form:
+    //   abort  <=>  some hit h of an object != B has t(h) > eps and
+    //               ( order(h) < order(B)  or  t(h) < tB ),
+    // tB = smallest t > eps among B's own hits on this ray (FLT_MAX if none).
+    struct FaceRuleVisit {
+        V3 o, ray; float tmin, tB; int back; bool aborted;
+        RT_DEV float operator()(const float4* w, float tmax)
+        {
+            const float4 w4 = w[4];
+            const int order = __float_as_int(w4.z);
+            if (order == back) return tmax;
+            const float limit = order < back ? 3.402823466e+38f : tB;
+            bool bad = false;
+            if (__float_as_int(w4.w) == 0) {
+                float t, b, g;
+                if (tri_distance(w[0], o, ray, t) && t > tmin && t < limit) bad = tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g);
+            } else {
+                float tf, tn;
+                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                bad = (n >= 1 && tf > tmin && tf < limit) || (n == 2 && tn > tmin && tn < limit);
+            }
+            if (bad) { aborted = true; return -1.0f; }
+            return tmax;
+        }
+    };
+
+    RT_DEV Hit closest_face_rule(V3 o, V3 ray, float tmin, int back, bool& aborted) const
+    {
+        // B's own hit by a direct test of its file-order record
+        Hit hb; hb.t = 3.402823466e+38f; hb.obj = -1; hb.b = hb.g = 0.0f;
+        if (back < nf) {
+            const float4* w = tri + (size_t)back * kTriWords;
+            float t, b, g;
+            if (tri_distance(w[0], o, ray, t) && t > tmin && tri_inside(w[1], w[2], w[3], w[4], o, ray, t, b, g)) { hb.t = t; hb.obj = back; hb.b = b; hb.g = g; }
+        } else {
+            float tf, tn;
+            const int n = sphere_roots(sph[(size_t)(back - nf) * kSphWords], o, ray, tf, tn);
+            if (n >= 1 && tf > tmin && tf < hb.t) { hb.t = tf; hb.obj = back; }
+            if (n == 2 && tn > tmin && tn < hb.t) { hb.t = tn; hb.obj = back; }
+        }
+        FaceRuleVisit v; v.o = o; v.ray = ray; v.tmin = tmin; v.tB = hb.t; v.back = back; v.aborted = false;
+        // objects before B in iteration order abort at ANY distance: no upper bound for culling
+        walk(o, ray, tmin, 3.402823466e+38f, v);
+        aborted = v.aborted;
+        return hb;
+    }
+
+    // Shadow product.  An opaque occluder (k == 0) makes the product exactly 0 whatever
+    // the order, so the walk stops there.  Partial factors are multiplied in the
+    // reference's iteration order (float products are not associative): they are
+    // collected, sorted by order, then applied.
+    static constexpr int kMaxPartial = 12;
+    struct ShadowVisit {
+        V3 o, ray; float tmin, tmax_hit; bool use_tmax, skip_spheres, count_all; int self; int hits;
+        int n_partial; int p_order[kMaxPartial]; float p_k[kMaxPartial];
+        float overflow_mask; bool opaque;
+        RT_DEV void add(int order, float k)
+        {
+            hits++;
+            if (k == 0.0f) { opaque = true; return; }
+            if (n_partial < kMaxPartial) { p_order[n_partial] = order; p_k[n_partial] = k; n_partial++; }
+            else overflow_mask = clamp01(fmul(k, overflow_mask));
+        }
+        RT_DEV float operator()(const float4* w, float tmax)
+        {
+            const float4 w4 = w[4];
+            const int order = __float_as_int(w4.z);
+            if (order == self) return tmax;
+            if (__float_as_int(w4.w) == 0) {
+                float t, b, g;
+                if (tri_distance(w[0], o, ray, t) && t > tmin && (!use_tmax || t < tmax_hit) &&
+                    tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g))
+                    add(order, w4.y);
+            } else if (!skip_spheres) {
+                float tf, tn;
+                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                if (n >= 1 && tf > tmin && (!use_tmax || tf < tmax_hit)) add(order, w4.y);
+                if (n == 2 && tn > tmin && (!use_tmax || tn < tmax_hit)) add(order, w4.y);
+            }
+            return (opaque && !count_all) ? -1.0f : tmax;
+        }
+    };
+
+    RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask) const
+    {
+        ShadowVisit v; v.o = o; v.ray = ray; v.tmin = tmin; v.tmax_hit = tmax; v.use_tmax = use_tmax; v.self = self;
+        v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false; v.count_all = count_all;
+        // The sphere quadratic assumes a unit ray (A == 1, main.cpp:1232).  For a ray of
+        // length s != 1 (un-normalised directional lights, main.cpp:895) the accepted set is
+        // rho^2 <= r^2 + (s^2 - 1) p^2 — unbounded for s > 1, so no box bounds it:
+        // such rays test every sphere directly and use the tree for the triangles only.
+        const float s2 = ray.x * ray.x + ray.y * ray.y + ray.z * ray.z;
+        v.skip_spheres = ns > 0 && fabsf(s2 - 1.0f) > 1.0e-4f;
+        walk(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
+        if (v.skip_spheres && !(v.opaque && !count_all)) {
+            for (int i = 0; i < ns; i++) {
+                if (nf + i == self) continue;
+                const float4* w = sph + (size_t)i * kSphWords;
+                float tf, tn;
+                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                if (n >= 1 && tf > tmin && (!use_tmax || tf < tmax)) v.add(nf + i, w[1].x);
+                if (n == 2 && tn > tmin && (!use_tmax || tn < tmax)) v.add(nf + i, w[1].x);
+                if (v.opaque && !count_all) break;
+            }
+        }
+        if (v.opaque) { mask = clamp01(fmul(0.0f, mask)); return v.hits; }
+        // insertion sort by order (stable: the two roots of one sphere share k)
+        for (int i = 1; i < v.n_partial; i++) {
+            const int ko = v.p_order[i]; const float kk = v.p_k[i];
+            int j = i - 1;
+            while (j >= 0 && v.p_order[j] > ko) { v.p_order[j + 1] = v.p_order[j]; v.p_k[j + 1] = v.p_k[j]; j--; }
+            v.p_order[j + 1] = ko; v.p_k[j + 1] = kk;
+        }
+        for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
+        if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
+        return v.hits;
+    }
+};
+
+using BvhAccel = BvhAccelT<false>;
+
+template <bool kCount>
+RT_DEV BvhAccelT<kCount> make_bvh_accel(const SceneView& S)
+{
+    BvhAccelT<kCount> a;
+    a.nodes = S.bvh.nodes; a.prims = S.bvh_tri; a.tri = S.tri; a.sph = S.sph;
+    a.nf = S.nf; a.ns = S.ns; a.root = S.bvh.root; a.n_nodes = S.bvh.n_nodes; a.count_all = false;
+    return a;
+}
+
+}  // namespace rt

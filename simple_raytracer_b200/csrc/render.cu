@@ -1,0 +1,273 @@
+// render.cu — frame scheduling: workspace sizing, the launch sequence of one frame
+// (generations 0..D forward, D-1..0 backward), and the framebuffer plumbing.
+#include "bvh.cuh"
+#include "host_scene.h"
+#include "wavefront.cuh"
+
+#include <algorithm>
+#include <cstring>
+#include <mutex>
+
+namespace rt {
+
+namespace {
+
+int g_sm_count[64] = { 0 };
+
+int sm_count(int device)
+{
+    if (device < 0 || device >= 64) return 148;
+    if (!g_sm_count[device]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n <= 0) n = 148;
+        g_sm_count[device] = n;
+    }
+    return g_sm_count[device];
+}
+
+struct BruteSmemFactory {
+    static RT_DEV BruteAccel make(const SceneView& S, float4* smem) { return make_brute<true>(S, smem); }
+    static RT_DEV void flush(const BruteAccel&, Counters*) {}
+};
+struct BruteGlobalFactory {
+    static RT_DEV BruteAccel make(const SceneView& S, float4* smem) { return make_brute<false>(S, smem); }
+    static RT_DEV void flush(const BruteAccel&, Counters*) {}
+};
+struct BvhFactory {
+    static RT_DEV BvhAccel make(const SceneView& S, float4*) { return make_bvh_accel<false>(S); }
+    static RT_DEV void flush(const BvhAccel&, Counters*) {}
+};
+// instrumented variant: per-thread work counters, one warp-reduced atomic at the end of the kernel
+struct BvhCountFactory {
+    static RT_DEV BvhAccelT<true> make(const SceneView& S, float4*) { return make_bvh_accel<true>(S); }
+    static RT_DEV void flush(const BvhAccelT<true>& a, Counters* c)
+    {
+        unsigned long long b = a.cnt_boxes, p = a.cnt_prims;
+        for (int o = 16; o > 0; o >>= 1) {
+            b += __shfl_down_sync(0xffffffffu, b, o);
+            p += __shfl_down_sync(0xffffffffu, p, o);
+        }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&c->bvh_nodes, b); atomicAdd(&c->prim_tests, p); }
+    }
+};
+
+// scanline-order planes for rt_download_framebuffer: tiles RGBA8 -> rgb24 + flags8
+__global__ void split_planes_kernel(const uchar4* __restrict__ tiles, int n, unsigned char* __restrict__ rgb,
+                                    unsigned char* __restrict__ flags)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uchar4 p = tiles[i];
+    rgb[3 * (size_t)i] = p.x; rgb[3 * (size_t)i + 1] = p.y; rgb[3 * (size_t)i + 2] = p.z;
+    flags[i] = p.w;
+}
+
+// [rank][local_tile][row][col] -> [row][col] after the allgather
+__global__ void deinterleave_kernel(const uchar4* __restrict__ gathered, uchar4* __restrict__ out, int width, int height,
+                                    int world, int tile_rows, int n_local_rows)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)width * height) return;
+    const int row = (int)(i / width), col = (int)(i - (size_t)row * width);
+    const int tile = row / tile_rows, in_tile = row - tile * tile_rows;
+    const int rank = tile % world, local_tile = tile / world;
+    const size_t src = ((size_t)rank * n_local_rows + (size_t)local_tile * tile_rows + in_tile) * width + col;
+    out[i] = gathered[src];
+}
+
+std::mutex g_cache_mutex;
+Workspace g_ws_cache;   // one retired workspace, reused by the next scene on the same device
+bool g_ws_cache_valid = false;
+
+}  // namespace
+
+TileLayout tile_layout(int height, int width, int world, int tile_rows)
+{
+    TileLayout t;
+    t.n_tiles_total = (height + tile_rows - 1) / tile_rows;
+    t.n_local_tiles = (t.n_tiles_total + world - 1) / world;   // equal per rank: allgather needs equal counts
+    t.n_local_rows = t.n_local_tiles * tile_rows;
+    t.n_local_pixels = t.n_local_rows * width;
+    return t;
+}
+
+void stash_workspace(Workspace&& ws)
+{
+    std::lock_guard<std::mutex> lock(g_cache_mutex);
+    g_ws_cache = std::move(ws);
+    g_ws_cache_valid = true;
+}
+
+static size_t level_bytes(int level, size_t cap)
+{
+    // level 0 has no ray queue (primary rays are generated in place)
+    const size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16;
+    return cap * per_slot + 256;
+}
+
+// Sizes the queues.  demand == nullptr: first guess from the pixel count (or what a
+// retired workspace already holds); otherwise grow to the observed demand.
+int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* demand)
+{
+    Workspace& ws = s->ws;
+    if (ws.device < 0) {
+        std::lock_guard<std::mutex> lock(g_cache_mutex);
+        if (g_ws_cache_valid && g_ws_cache.device == s->device) {
+            ws = std::move(g_ws_cache);
+            g_ws_cache_valid = false;
+        }
+        ws.device = s->device;
+    }
+    const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
+    const size_t npx = (size_t)tl.n_local_pixels;
+    if (!ws.counters.reserve(sizeof(Counters)) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
+    if (p.instrument && !ws.primary_ids.reserve(npx * sizeof(int))) return RT_E_NOMEM;
+    for (int l = 0; l <= p.max_depth; l++) {
+        size_t want;
+        if (l == 0) want = npx;
+        else if (demand) want = std::max<size_t>((size_t)ws.capacity[l], (size_t)(demand[l] * 1.25) + 1024);
+        else {
+            // rays of generation l per pixel seen on the example scenes: <= ~1.2, 0.5, 0.25, ...
+            static const double guess[kMaxLevels] = { 1.0, 1.25, 0.75, 0.5, 0.5, 0.5, 0.5, 0.5 };
+            want = std::max<size_t>((size_t)ws.capacity[l], (size_t)(npx * guess[l]) + 1024);
+        }
+        if (want > 0x7ffffff0u) { set_error("wavefront queue would exceed 2^31 slots"); return RT_E_NOMEM; }
+        if ((size_t)ws.capacity[l] < want || ws.level_mem[l].bytes < level_bytes(l, want)) {
+            if (!ws.level_mem[l].reserve(level_bytes(l, want))) return RT_E_NOMEM;
+            ws.capacity[l] = (int)want;
+        }
+    }
+    return RT_OK;
+}
+
+static void fill_levels(const SceneHost* s, int max_depth, FrameParams* P)
+{
+    const Workspace& ws = s->ws;
+    for (int l = 0; l < kMaxLevels; l++) {
+        LevelBuffers& L = P->level[l];
+        std::memset(&L, 0, sizeof L);
+        if (l > max_depth) continue;
+        const size_t cap = (size_t)ws.capacity[l];
+        char* base = ws.level_mem[l].as<char>();
+        L.capacity = (int)cap;
+        if (l > 0) {
+            L.rq_o = (float4*)base; base += cap * 16;
+            L.rq_d = (float4*)base; base += cap * 16;
+            L.rq_m = (int4*)base;   base += cap * 16;
+            L.rq_s = (int4*)base;   base += cap * 16;
+        }
+        L.nr_a = (float4*)base; base += cap * 16;
+        L.nr_b = (float4*)base; base += cap * 16;
+        L.res = (float4*)base;
+    }
+}
+
+static int pick_accel(const SceneHost* s, int requested)
+{
+    if (requested == RT_ACCEL_BRUTE || requested == RT_ACCEL_LBVH) return requested;
+    return (s->nf + s->ns) > 48 ? RT_ACCEL_LBVH : RT_ACCEL_BRUTE;
+}
+
+template <class Factory>
+static void launch_level(const FrameParams& P, int level, int grid, size_t smem, cudaStream_t st)
+{
+    level_kernel<Factory><<<grid, kBlock, smem, st>>>(P, level);
+}
+
+// Enqueues one frame on `stream`.  The queues must already be sized (ensure_workspace).
+int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cudaStream_t stream, int* launches)
+{
+    const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
+    int accel = pick_accel(s, p.accel);
+    if (accel == RT_ACCEL_LBVH) {
+        if (s->nf + s->ns == 0) accel = RT_ACCEL_BRUTE;
+        else if (!s->bvh_built) {
+            const int rc = build_bvh(s);
+            if (rc != RT_OK) return rc;
+        }
+    }
+    FrameParams P;
+    std::memset(&P, 0, sizeof P);
+    P.scene = scene_view(s);
+    P.cam = s->cam;
+    fill_levels(s, p.max_depth, &P);
+    P.counters = s->ws.counters.as<Counters>();
+    P.tiles = tiles_out ? tiles_out : s->ws.tiles.as<uchar4>();
+    P.primary_ids = p.instrument ? s->ws.primary_ids.as<int>() : nullptr;
+    P.max_depth = p.max_depth; P.epsilon = p.epsilon;
+    P.rank = p.rank; P.world = p.world_size; P.tile_rows = p.tile_rows;
+    P.n_local_rows = tl.n_local_rows; P.n_local_pixels = tl.n_local_pixels;
+
+    RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters), stream));
+    const int sms = sm_count(s->device);
+    const size_t smem = (size_t)(s->nf * kTriWords + s->ns * kSphWords) * sizeof(float4);
+    const bool stage = accel == RT_ACCEL_BRUTE && smem <= 48 * 1024;
+    int n = 0;
+    s->prof_levels = 0;
+    if (p.profile) {
+        for (int k = 0; k < kMaxLevels + 2; k++)
+            if (!s->prof_ev[k]) RT_CUDA(cudaEventCreate(&s->prof_ev[k]));
+    }
+    for (int l = 0; l <= p.max_depth; l++) {
+        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
+        // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
+        const long long work = l == 0 ? tl.n_local_pixels : s->ws.capacity[l];
+        int grid = (int)std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * 16);
+        if (grid < 1) grid = 1;
+        if (accel == RT_ACCEL_LBVH && p.instrument) launch_level<BvhCountFactory>(P, l, grid, 0, stream);
+        else if (accel == RT_ACCEL_LBVH) launch_level<BvhFactory>(P, l, grid, 0, stream);
+        else if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
+        else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
+        n++;
+    }
+    if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 1], stream));
+    for (int l = p.max_depth - 1; l >= 0; l--) {
+        const long long work = l == 0 ? tl.n_local_pixels : s->ws.capacity[l];
+        int grid = (int)std::min<long long>((work + 255) / 256, (long long)sms * 8);
+        if (grid < 1) grid = 1;
+        combine_kernel<<<grid, 256, 0, stream>>>(P, l);
+        n++;
+    }
+    if (p.max_depth == 0) {   // no backward pass above: generation 0 still has to be quantised
+        int grid = (int)std::min<long long>((tl.n_local_pixels + 255) / 256, (long long)sms * 8);
+        combine_kernel<<<grid, 256, 0, stream>>>(P, 0);
+        n++;
+    }
+    RT_CUDA(cudaGetLastError());
+    if (p.profile) {
+        RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 2], stream));
+        s->prof_levels = p.max_depth + 1;
+    }
+    if (tiles_out && tiles_out != s->ws.tiles.as<uchar4>())
+        RT_CUDA(cudaMemcpyAsync(s->ws.tiles.p, tiles_out, (size_t)tl.n_local_pixels * sizeof(uchar4),
+                                cudaMemcpyDeviceToDevice, stream));
+    s->rendered = true;
+    s->last = p;
+    s->last_local_rows = tl.n_local_rows; s->last_local_pixels = tl.n_local_pixels;
+    s->last_accel = accel; s->last_launches = n + 1;
+    s->have_primary_ids = p.instrument != 0;
+    if (launches) *launches = n + 1;
+    return RT_OK;
+}
+
+int launch_split_planes(SceneHost* s, cudaStream_t st)
+{
+    const int n = s->last_local_pixels;
+    if (!s->ws.rgb24.reserve((size_t)n * 3) || !s->ws.flags8.reserve((size_t)n)) return RT_E_NOMEM;
+    split_planes_kernel<<<(n + 255) / 256, 256, 0, st>>>(s->ws.tiles.as<uchar4>(), n, s->ws.rgb24.as<unsigned char>(),
+                                                        s->ws.flags8.as<unsigned char>());
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+int launch_deinterleave(const SceneHost* s, const void* gathered, void* out, int world, int tile_rows, cudaStream_t st)
+{
+    const TileLayout tl = tile_layout(s->height, s->width, world, tile_rows);
+    const size_t n = (size_t)s->width * s->height;
+    deinterleave_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const uchar4*)gathered, (uchar4*)out, s->width,
+                                                                    s->height, world, tile_rows, tl.n_local_rows);
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
+
+}  // namespace rt

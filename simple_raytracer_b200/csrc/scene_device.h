@@ -1,0 +1,130 @@
+// scene_device.h — how a scene lives in HBM, and the wavefront work buffers.
+//
+// The reference keeps a pointer-linked, std::map-indexed AoS scene
+// (src/definitions.h:249-311).  Here every table is a flat array of 16-byte
+// words.  Hot intersection data and cold shading attributes are split into
+// separate arrays; inside the intersection tables one primitive's words are
+// contiguous (80 B per triangle, 32 B per sphere) because a BVH leaf visit is a
+// single thread reading one whole primitive: contiguity makes that 3 sectors
+// instead of 5 cache lines.  In the brute-force path all lanes of a warp read the
+// same primitive at the same time (a broadcast), from a shared-memory copy.
+//
+// Objects are named by their position in the reference's TraceRay iteration
+// order ("order"): faces 0..nf-1 in file order, then spheres nf..nf+ns-1
+// (std::map key order "face" < "sphere", main.cpp:1218).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rt {
+
+constexpr int kTriWords = 5;     // float4 words per triangle intersection record
+constexpr int kSphWords = 2;     // float4 words per sphere intersection record
+constexpr int kFaceAttrWords = 4;
+constexpr int kMaxLevels = 8;    // generations of ShadeRay: max_depth + 1 <= 8
+constexpr int kMaxStack = 8;     // medium stack entries carried per ray
+
+// Triangle intersection record (ray-independent constants hoisted, bit-identical
+// to recomputing them per ray: main.cpp:1280-1282, 1301, 1361-1366):
+//   w0 = surface_normal.xyz, D            D   = -(n . v0)
+//   w1 = v0.xyz,             det          det = d11*d22 - d12*d12
+//   w2 = e1.xyz,             d11
+//   w3 = e2.xyz,             d22
+//   w4 = d12, kshadow, as_float(order), 0      kshadow = (float)(1.0 - opacity)
+// Sphere intersection record:
+//   w0 = center.xyz, radius
+//   w1 = kshadow, as_float(order), 0, 0
+//
+// Face shading attributes (4 words): normalised vertex normals and clamped-later
+// texture coordinates:
+//   a0 = vnn0.xyz, vt0.x   a1 = vnn1.xyz, vt0.y   a2 = vnn2.xyz, vt1.x   a3 = vt1.y, vt2.x, vt2.y, 0
+// Object table (one int4 per order): material index, texture index (-1), reference id, flags
+constexpr int kObjSmooth = 1;
+
+// Material (3 words): {od.rgb, ka} {os.rgb, kd} {ks, n, opacity, eta}
+// Light    (3 words): {xyz, w} {rgb, 0} {L.xyz for directional lights = -norm(dir), 0}
+// Texture descriptor (int4): texel offset, width, height, 0 ; texels are RGBA8 (A unused)
+
+struct BvhView {
+    const float4* nodes;     // 4 words per node, see bvh.cuh
+    int n_nodes;
+    int root;
+};
+
+struct SceneView {
+    int nf, ns, nl, ntex;
+    const float4* tri;        // nf * kTriWords, file order
+    const float4* sph;        // ns * kSphWords, file order
+    const float4* face_attr;  // nf * kFaceAttrWords
+    const int4*   obj;        // nf + ns
+    const float4* mat;        // n_materials * 3
+    const float4* light;      // nl * 3
+    const int4*   tex_desc;   // ntex
+    const uchar4* texels;
+    // LBVH over all primitives (bvh.cuh); prim records re-ordered along the Morton curve
+    BvhView bvh;
+    const float4* bvh_tri;    // triangles in leaf order (same 5-word records)
+    const float4* bvh_sph;    // spheres in leaf order
+    float bkg[3];
+    float bkg_eta;
+};
+
+struct CameraView {          // main.cpp:677-710, computed on the host in rt_upload_scene / rt_set_camera
+    float eye[3];
+    float ul[3];
+    float delta_h[3];
+    float delta_v[3];
+    int width, height;
+};
+
+// Result status of a ray / node slot (stored in the w component of `res`)
+constexpr float kResFinal = 0.0f;     // rgb is what the parent multiplies by its weights
+constexpr float kResZeroTerm = 1.0f;  // `goto SKIP_TRANS`: the parent's term stays (0,0,0)
+constexpr float kResPending = 2.0f;   // node shaded, children outstanding: combine pass finishes it
+constexpr float kResPrimaryMiss = 3.0f;
+
+// One generation of the wavefront.  Slot i of level d is both "ray i of the queue"
+// and "the ShadeRay node that ray produced, if it hit anything".
+struct LevelBuffers {
+    // ray queue written by level d-1 (unused for level 0: primary rays are generated)
+    float4* rq_o;   // origin.xyz, incidence_refraction_index of the PARENT call
+    float4* rq_d;   // direction.xyz, transmission_refraction_index of the PARENT call
+    int4*   rq_m;   // parent slot, incidence object (order), flags, stack[0]
+    int4*   rq_s;   // stack[1..4]
+    // node record written by the shade step, read by the combine pass
+    float4* nr_a;   // base.rgb (= diffuse*ka + tmp_specular), tw1 = (float)(1.0 - F_t)
+    float4* nr_b;   // tw2 = (float)(1.0 - opacity), F_r, as_float(childT), as_float(childR)
+    float4* res;    // rgb, status
+    int capacity;
+};
+
+// flags word of rq_m.z
+constexpr int kRayKindReflect = 1;   // bit0: 0 = transmission ray, 1 = reflection ray
+constexpr int kRayStateExiting = 2;  // bit1: previous_ray_state == EXITING
+constexpr int kRayNStackShift = 2;   // bits 2..5: medium stack length
+
+struct Counters {
+    unsigned int rays[kMaxLevels];        // rays queued for level d (level 0: unused)
+    unsigned int nodes[kMaxLevels];       // hits shaded at level d
+    unsigned int rays_reflect[kMaxLevels];
+    unsigned int overflow;                // some queue was too small: frame must be redone
+    unsigned int pad;
+    unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only
+};
+
+struct FrameParams {
+    SceneView scene;
+    CameraView cam;
+    LevelBuffers level[kMaxLevels];
+    Counters* counters;
+    uchar4* tiles;        // this rank's tile buffer [local_tile][row][col], A = flags
+    int* primary_ids;     // instrumented variant: reference id of the primary hit per local pixel
+    int max_depth;
+    float epsilon;
+    int rank, world, tile_rows;
+    int n_local_rows;     // rows of the tile buffer (padded to whole tiles)
+    int n_local_pixels;   // n_local_rows * width
+};
+
+}  // namespace rt

@@ -1,0 +1,268 @@
+// wavefront.cuh — the per-generation kernels of the render.
+//
+//   level_kernel<Accel>(d) : for every ray queued for generation d (d = 0: one
+//       primary ray per pixel, generated in place, main.cpp:718-728) find the
+//       closest hit, run the medium state machine, shade the hit (shade.cuh) and
+//       append the transmission / reflection rays it spawns to the queue of
+//       generation d+1.  Queue slots are handed out with one atomicAdd per warp
+//       (ballot + popc), so the queue of the next generation is dense: lanes of
+//       later generations are all busy however sparse the glass pixels are.
+//   combine_kernel(d)      : bottom-up, finishes the nodes of generation d from
+//       the finished results of d+1 with the reference's clamped operators
+//       (main.cpp:1083, 1087, 1194, 1198, 1206); generation 0 also quantises to
+//       8 bits (760-762) and writes this rank's row tiles.
+//
+// Grids are persistent (a multiple of the SM count) and stride over the device-side
+// queue count, so a frame needs no host synchronisation between generations.
+#pragma once
+
+#include "shade.cuh"
+
+namespace rt {
+
+constexpr int kBlock = 128;
+
+RT_DEV unsigned lanemask_lt()
+{
+    unsigned m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// Global row of local row r under interleaved row-tile sharding.
+RT_DEV int global_row(const FrameParams& P, int local_row)
+{
+    const int tile = local_row / P.tile_rows, in_tile = local_row - tile * P.tile_rows;
+    return (tile * P.world + P.rank) * P.tile_rows + in_tile;
+}
+
+// Shared-memory staging of the primitive tables for small scenes: every lane of a
+// warp walks the same primitive at the same time, so the reads are broadcasts.
+template <bool kStage>
+RT_DEV BruteAccel make_brute(const SceneView& S, float4* smem)
+{
+    BruteAccel a;
+    a.nf = S.nf; a.ns = S.ns;
+    if (kStage) {
+        const int ntw = S.nf * kTriWords, nsw = S.ns * kSphWords;
+        for (int i = threadIdx.x; i < ntw; i += blockDim.x) smem[i] = S.tri[i];
+        for (int i = threadIdx.x; i < nsw; i += blockDim.x) smem[ntw + i] = S.sph[i];
+        __syncthreads();
+        a.tri = smem; a.sph = smem + ntw;
+    } else {
+        a.tri = S.tri; a.sph = S.sph;
+    }
+    return a;
+}
+
+template <class Accel>
+RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsigned slot, bool active)
+{
+    const SceneView& S = P.scene;
+    const LevelBuffers& LB = P.level[level];
+    const Col bkg = mkc(S.bkg[0], S.bkg[1], S.bkg[2]);
+
+    // ---- the ray of this slot -------------------------------------------------
+    V3 o = mk3(0.f, 0.f, 0.f), ray = mk3(0.f, 0.f, 0.f);
+    float n_i = 0.f, n_t = 0.f;
+    int inc = -1, ns = 0;
+    bool reflect = false, exiting = false;
+    int stack[kMaxStack];
+    if (active) {
+        if (level == 0) {
+            const int lrow = slot / P.cam.width, col = slot - lrow * P.cam.width;
+            const int row = global_row(P, lrow);
+            if (row >= P.cam.height) {
+                active = false;                     // padding rows of the last tile
+                LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPrimaryMiss);
+            } else {
+                const V3 ul = mk3(P.cam.ul[0], P.cam.ul[1], P.cam.ul[2]);
+                const V3 dh = mk3(P.cam.delta_h[0], P.cam.delta_h[1], P.cam.delta_h[2]);
+                const V3 dv = mk3(P.cam.delta_v[0], P.cam.delta_v[1], P.cam.delta_v[2]);
+                o = mk3(P.cam.eye[0], P.cam.eye[1], P.cam.eye[2]);
+                const V3 p = vadd(vadd(ul, vmulf(dh, (float)col)), vmulf(dv, (float)row));   // 720
+                ray = vnorm(vsub(p, o));                                                    // 728
+            }
+        } else {
+            const float4 qo = LB.rq_o[slot], qd = LB.rq_d[slot];
+            const int4 qm = LB.rq_m[slot], qs = LB.rq_s[slot];
+            o = mk3(qo.x, qo.y, qo.z); n_i = qo.w;
+            ray = mk3(qd.x, qd.y, qd.z); n_t = qd.w;
+            inc = qm.y;
+            reflect = (qm.z & kRayKindReflect) != 0;
+            exiting = (qm.z & kRayStateExiting) != 0;
+            ns = (qm.z >> kRayNStackShift) & 15;
+            stack[0] = qm.w; stack[1] = qs.x; stack[2] = qs.y; stack[3] = qs.z; stack[4] = qs.w;
+        }
+    }
+
+    // ---- closest hit --------------------------------------------------------------
+    Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
+    bool aborted = false;
+    if (active) {
+        if (level == 0) {
+            h = acc.closest(o, ray, 0.0f);                                       // 729-742: t > 0.0f
+        } else if (!reflect && inc < S.nf && ns > 0) {
+            h = acc.closest_face_rule(o, ray, P.epsilon, stack[ns - 1], aborted);   // 992-1011
+        } else {
+            h = acc.closest(o, ray, P.epsilon);                                  // 1113-1124
+        }
+    }
+    const bool hit = active && !aborted && h.obj >= 0;
+
+    // nodes[level] counts ShadeRay invocations: one atomic per warp
+    {
+        const unsigned hm = __ballot_sync(0xffffffffu, hit);
+        if ((threadIdx.x & 31) == 0 && hm) atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
+    }
+    if (active && level == 0 && P.primary_ids) P.primary_ids[slot] = hit ? S.obj[h.obj].z : 0;
+    if (P.primary_ids) {   // instrumented frame: one texel per shaded hit on a textured object
+        const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[h.obj].y >= 0);
+        if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
+    }
+
+    // ---- shade -----------------------------------------------------------------
+    Spawn sp; sp.want_t = sp.want_r = false;
+    float tw1 = 0.f, tw2 = 0.f, fr = 0.f, c_ni = 0.f, c_nt = 0.f;
+    bool c_exiting = false;
+    Col base = mkc(0.f, 0.f, 0.f);
+    Surface sf;
+    if (hit) {
+        sf = finish_hit(S, o, ray, h);
+        if (level == 0) {                                                        // 746-757
+            c_ni = S.bkg_eta; c_nt = material_eta(S, h.obj); c_exiting = false;
+            stack[0] = h.obj; ns = 1;
+        } else {
+            medium_update(S, reflect, exiting, inc, h.obj, n_i, n_t, stack, ns, c_ni, c_nt, c_exiting);
+        }
+        base = shade_node(S, acc, ray, h.obj, sf, c_ni, c_nt, P.max_depth - level, P.epsilon, tw1, tw2, fr, sp);
+    }
+
+    // ---- spawn: warp-aggregated slot allocation in the next generation's queue -----
+    const unsigned mt = __ballot_sync(0xffffffffu, sp.want_t);
+    const unsigned mr = __ballot_sync(0xffffffffu, sp.want_r);
+    int child_t = -1, child_r = -1;
+    if (mt | mr) {                                   // warp-uniform
+        const LevelBuffers& NB = P.level[level + 1];
+        const int nt = __popc(mt), nr = __popc(mr);
+        unsigned basei = 0;
+        if ((threadIdx.x & 31) == 0) {
+            basei = atomicAdd(&P.counters->rays[level + 1], (unsigned)(nt + nr));
+            if (nr) atomicAdd(&P.counters->rays_reflect[level + 1], (unsigned)nr);
+        }
+        basei = __shfl_sync(0xffffffffu, basei, 0);
+        const unsigned lt = lanemask_lt();
+        const int flags_common = (c_exiting ? kRayStateExiting : 0) | (ns << kRayNStackShift);
+        if (sp.want_t) {
+            const unsigned s = basei + (unsigned)__popc(mt & lt);
+            if (s < (unsigned)NB.capacity) {
+                child_t = (int)s;
+                NB.rq_o[s] = make_float4(sf.p.x, sf.p.y, sf.p.z, c_ni);
+                NB.rq_d[s] = make_float4(sp.T.x, sp.T.y, sp.T.z, c_nt);
+                NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common, stack[0]);
+                NB.rq_s[s] = make_int4(stack[1], stack[2], stack[3], stack[4]);
+            } else {
+                P.counters->overflow = 1;
+            }
+        }
+        if (sp.want_r) {
+            const unsigned s = basei + (unsigned)nt + (unsigned)__popc(mr & lt);
+            if (s < (unsigned)NB.capacity) {
+                child_r = (int)s;
+                NB.rq_o[s] = make_float4(sf.p.x, sf.p.y, sf.p.z, c_ni);
+                NB.rq_d[s] = make_float4(sp.R.x, sp.R.y, sp.R.z, c_nt);
+                NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common | kRayKindReflect, stack[0]);
+                NB.rq_s[s] = make_int4(stack[1], stack[2], stack[3], stack[4]);
+            } else {
+                P.counters->overflow = 1;
+            }
+        }
+    }
+
+    // ---- the slot's record ------------------------------------------------------------
+    if (!active) return;
+    if (hit) {
+        if (child_t < 0 && child_r < 0 && !sp.want_t && !sp.want_r) {
+            // leaf node: both child terms are exactly (0,0,0); x + 0 leaves a clamped x unchanged
+            LB.res[slot] = make_float4(base.r, base.g, base.b, kResFinal);
+        } else {
+            LB.nr_a[slot] = make_float4(base.r, base.g, base.b, tw1);
+            LB.nr_b[slot] = make_float4(tw2, fr, __int_as_float(child_t), __int_as_float(child_r));
+            LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
+        }
+    } else if (level == 0) {
+        LB.res[slot] = make_float4(bkg.r, bkg.g, bkg.b, kResPrimaryMiss);       // 721
+    } else if (aborted) {
+        LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResZeroTerm);                // SKIP_TRANS
+    } else {
+        LB.res[slot] = make_float4(bkg.r, bkg.g, bkg.b, kResFinal);             // 1087 / 1198: bkg takes the child's place
+    }
+}
+
+// AccelFactory builds the per-block accelerator view (stages shared memory if any).
+template <class AccelFactory>
+__global__ void __launch_bounds__(kBlock) level_kernel(const __grid_constant__ FrameParams P, int level)
+{
+    extern __shared__ float4 smem[];
+    const auto acc = AccelFactory::make(P.scene, smem);
+    const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
+                                      : min(P.counters->rays[level], (unsigned)P.level[level].capacity);
+    const unsigned stride = gridDim.x * blockDim.x;
+    // all lanes of a warp run the same number of iterations (full-mask ballots inside)
+    const unsigned rounded = (count + 31u) & ~31u;
+    for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < rounded; slot += stride)
+        process_slot(P, acc, level, slot, slot < count);
+    AccelFactory::flush(acc, P.counters);
+}
+
+RT_DEV Col child_term(const LevelBuffers& NB, int child, bool& zero)
+{
+    const float4 r = NB.res[child];
+    zero = (r.w == kResZeroTerm);
+    return mkc(r.x, r.y, r.z);
+}
+
+__global__ void __launch_bounds__(256) combine_kernel(const __grid_constant__ FrameParams P, int level)
+{
+    const LevelBuffers& LB = P.level[level];
+    const LevelBuffers& NB = P.level[level + 1 < kMaxLevels ? level + 1 : level];
+    const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
+                                      : min(P.counters->rays[level], (unsigned)LB.capacity);
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < count; slot += stride) {
+        float4 r = LB.res[slot];
+        if (r.w == kResPending) {
+            const float4 a = LB.nr_a[slot], b = LB.nr_b[slot];
+            const int ct = __float_as_int(b.z), cr = __float_as_int(b.w);
+            Col acc = mkc(a.x, a.y, a.z);
+            Col tt = mkc(0.f, 0.f, 0.f), tr = mkc(0.f, 0.f, 0.f);
+            if (ct >= 0) {
+                bool zero;
+                const Col c = child_term(NB, ct, zero);
+                if (!zero) tt = cmulf(cmulf(c, a.w), b.x);                       // 1083 / 1087
+            }
+            if (cr >= 0) {
+                bool zero;
+                const Col c = child_term(NB, cr, zero);
+                tr = cmulf(c, b.y);                                              // 1194 / 1198
+            }
+            acc = cadd(cadd(acc, tt), tr);                                       // 1206
+            r = make_float4(acc.r, acc.g, acc.b, kResFinal);
+            if (level != 0) LB.res[slot] = r;
+        }
+        if (level == 0) {
+            // quantise, main.cpp:760-762: (int) map(c, 0, 1, 0, 255)
+            const float c[3] = { r.x, r.y, r.z };
+            unsigned char out[3]; unsigned flags = (r.w == kResPrimaryMiss) ? 8u : 0u;
+            #pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const int q = ref_f2i(mapf(c[k], 0.0f, 1.0f, 0.0f, 255.0f));
+                if (q == (int)0x80000000) { flags |= 1u << k; out[k] = 0; }
+                else out[k] = (unsigned char)min(max(q, 0), 255);
+            }
+            P.tiles[slot] = make_uchar4(out[0], out[1], out[2], (unsigned char)flags);
+        }
+    }
+}
+
+}  // namespace rt

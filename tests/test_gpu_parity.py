@@ -1,0 +1,197 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle.
+
+Bars (BASELINE.json north_star):
+  * hit primitive ids and shadow occlusion identical (grazing ties would be stated;
+    on these inputs there are none, so the tests demand zero mismatches);
+  * pixels within +-1 LSB per channel on >= 99.9 % of pixels, max error reported,
+    NaN pixel set identical.
+Integer / index work (hit ids, t bit patterns, node counts, hit counts) is held to
+bit-exactness.
+"""
+import numpy as np
+import pytest
+
+from simple_raytracer_b200 import abi, scenegen
+from simple_raytracer_b200.renderer import DeviceScene
+from tests import common
+from tests import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+
+PIXEL_BAR = 0.999
+
+
+def _render_and_compare(scene, raw, ids, ost, accel, depth=4):
+    with DeviceScene(scene) as ds:
+        st = ds.render(max_depth=depth, accel=accel, instrument=True)
+        rgb, flags = ds.download()
+        pid = ds.download_primary_ids()
+    cmp = common.compare_frames(raw, rgb, flags)
+    assert int((pid.reshape(-1) != ids).sum()) == 0, "primary hit ids differ"
+    assert st.nodes_total == ost.nodes_total, (list(st.nodes_per_level), list(ost.nodes_per_level))
+    assert list(st.nodes_per_level)[: depth + 1] == list(ost.nodes_per_level)[: depth + 1]
+    assert st.rays_transmit == ost.rays_transmit and st.rays_reflect == ost.rays_reflect
+    assert st.rays_shadow == ost.rays_shadow and st.rays_primary == ost.rays_primary
+    assert cmp["nan_mismatch"] == 0, cmp
+    assert cmp["frac_within_1"] >= PIXEL_BAR, cmp
+    assert st.kernel_launches > 0
+    return cmp, st
+
+
+@pytest.mark.parametrize("accel", [abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH])
+@pytest.mark.parametrize("name", common.ALL_SCENES)
+def test_example_scenes_match_reference_frames(name, accel):
+    """Committed frames of the unmodified reference program (reduced imsize)."""
+    scene, ref_raw = common.golden_frame(name)
+    if scene.n_prims == 0 and accel == abi.RT_ACCEL_LBVH:
+        pytest.skip("empty scene")
+    raw, ids, ost = O.oracle_render(scene)
+    assert np.array_equal(raw, ref_raw)
+    cmp, _ = _render_and_compare(scene, raw, ids, ost, accel)
+    assert cmp["max_err"] <= 2, cmp
+
+
+@pytest.mark.parametrize("name", ["reflection_transparency_tests/Test1", "reflection_transparency_tests/test7"])
+def test_full_size_goldens(name):
+    """The two 1080x1080 frames pinned by the reference repository's own screenshots."""
+    scene, ref_raw = common.golden_frame(name + "@full")
+    with DeviceScene(scene) as ds:
+        st = ds.render()
+        rgb, flags = ds.download()
+    cmp = common.compare_frames(ref_raw, rgb, flags)
+    assert cmp["nan_mismatch"] == 0 and cmp["nan_ref"] == common.frame_meta(name + "@full")["nan_pixels"], cmp
+    assert cmp["frac_within_1"] >= PIXEL_BAR and cmp["max_err"] <= 2, cmp
+
+
+@pytest.mark.parametrize("depth", [0, 1, 2, 3, 5])
+def test_other_recursion_depths(depth):
+    scene, _ = common.golden_frame("reflection_transparency_tests/test7")
+    raw, ids, ost = O.oracle_render(scene, max_depth=depth)
+    _render_and_compare(scene, raw, ids, ost, abi.RT_ACCEL_BRUTE, depth=depth)
+
+
+@pytest.mark.parametrize("accel", [abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH])
+@pytest.mark.parametrize("make", [
+    lambda: scenegen.coverage_scene(200, 150),
+    lambda: scenegen.random_soup(300, 20, 1, 96, 72),
+    lambda: scenegen.random_soup(60, 6, 5, 96, 72),
+    lambda: scenegen.random_soup(1500, 40, 2, 64, 48),
+    lambda: scenegen.mesh_earth(24, 12, 128, 72, tex_scale=1),
+])
+def test_generated_scenes(make, accel):
+    scene = make()
+    raw, ids, ost = O.oracle_render(scene)
+    _render_and_compare(scene, raw, ids, ost, accel)
+
+
+def _random_rays(n, extent, seed):
+    rng = np.random.default_rng(seed)
+    o = rng.uniform(-extent, extent, (n, 3)).astype(np.float32)
+    d = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    d[: n // 2] /= np.linalg.norm(d[: n // 2], axis=1, keepdims=True)   # half unit, half deliberately not (A3.2)
+    return o, d, rng
+
+
+@pytest.mark.parametrize("accel", [abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH])
+def test_closest_hit_probe_is_bit_exact(accel):
+    scene = scenegen.random_soup(400, 40, 9, 32, 24)
+    o, d, _ = _random_rays(20000, 12, 0)
+    ids, t, nrm, bary = O.oracle_trace_closest(scene, o, d, 1.0e-3)
+    with DeviceScene(scene) as ds:
+        gid, gt, gn, gb = ds.trace_closest(o, d, 1.0e-3, accel=accel)
+    assert (ids > 0).sum() > 1000
+    assert np.array_equal(gid, ids)
+    assert np.array_equal(gt.view(np.uint32), t.view(np.uint32))
+    hit = ids > 0
+    assert np.array_equal(gn[hit].view(np.uint32), nrm[hit].view(np.uint32))
+    assert np.array_equal(gb[hit].view(np.uint32), bary[hit].view(np.uint32))
+
+
+@pytest.mark.parametrize("accel", [abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH])
+def test_shadow_probe_is_bit_exact(accel):
+    scene = scenegen.random_soup(400, 40, 9, 32, 24)
+    o, d, rng = _random_rays(20000, 12, 1)
+    self_id = rng.integers(1, scene.n_prims + 1, len(o)).astype(np.int32)
+    tmax = rng.uniform(1, 30, len(o)).astype(np.float32)
+    with DeviceScene(scene) as ds:
+        for tm in (None, tmax):
+            m, h = O.oracle_trace_shadow(scene, o, d, self_id, 1.0e-3, tm)
+            gm, gh = ds.trace_shadow(o, d, self_id, 1.0e-3, tm, accel=accel)
+            assert (h > 0).sum() > 1000
+            assert np.array_equal(gh, h), f"{int((gh != h).sum())} rays with a different occluder count"
+            assert np.array_equal(gm.view(np.uint32), m.view(np.uint32))
+
+
+def test_lbvh_equals_brute_force_on_a_large_scene():
+    """Transitive parity for scenes the CPU cannot trace: on 200k
+    triangles + 500 spheres the LBVH returns the brute-force answer bit for bit."""
+    scene = scenegen.stress_scene(200_000, 500, 64, 48, seed=77, tex_size=32)
+    rng = np.random.default_rng(5)
+    n = 8192
+    o = rng.uniform(-60, 60, (n, 3)).astype(np.float32)
+    d = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    self_id = rng.integers(1, scene.n_prims + 1, n).astype(np.int32)
+    with DeviceScene(scene) as ds:
+        a = ds.trace_closest(o, d, 1.0e-3, accel=abi.RT_ACCEL_BRUTE)
+        b = ds.trace_closest(o, d, 1.0e-3, accel=abi.RT_ACCEL_LBVH)
+        sa = ds.trace_shadow(o, d, self_id, 1.0e-3, None, accel=abi.RT_ACCEL_BRUTE)
+        sb = ds.trace_shadow(o, d, self_id, 1.0e-3, None, accel=abi.RT_ACCEL_LBVH)
+    assert (a[0] > 0).sum() > 1000
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+    assert np.array_equal(a[3].view(np.uint32), b[3].view(np.uint32))
+    assert np.array_equal(sa[1], sb[1]) and np.array_equal(sa[0].view(np.uint32), sb[0].view(np.uint32))
+
+
+def test_row_tile_sharding_is_byte_identical():
+    """Every (rank, world) renders exactly the pixels the single-GPU frame has."""
+    scene = scenegen.coverage_scene(160, 101)          # height not a multiple of the tile size
+    with DeviceScene(scene) as ds:
+        ds.render()
+        full_rgb, full_flags = ds.download()
+        for world, tile_rows in ((2, 8), (4, 5), (8, 10)):
+            rgb = np.zeros_like(full_rgb); flags = np.zeros_like(full_flags)
+            for rank in range(world):
+                ds.render(rank=rank, world_size=world, tile_rows=tile_rows)
+                ds.download(rgb, flags)
+            assert np.array_equal(rgb, full_rgb) and np.array_equal(flags, full_flags), (world, tile_rows)
+
+
+def test_render_is_deterministic():
+    scene, _ = common.golden_frame("reflection_transparency_tests/Test1")
+    with DeviceScene(scene) as ds:
+        ds.render()
+        a = ds.download()
+        ds.render()
+        b = ds.download()
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+
+
+def test_set_camera_rerender_matches_fresh_upload():
+    base = scenegen.coverage_scene(120, 90)
+    moved = base.copy(eye=(1.0, 2.5, -3.0), viewdir=(-0.1, -0.2, 1.0), hfov_deg=50.0)
+    with DeviceScene(moved) as ds:
+        ds.render()
+        want = ds.download()
+    with DeviceScene(base) as ds:
+        ds.render()
+        ds.set_camera(moved.eye, moved.viewdir, moved.updir, moved.hfov_deg)
+        ds.render()
+        got = ds.download()
+    assert np.array_equal(want[0], got[0]) and np.array_equal(want[1], got[1])
+
+
+def test_invalid_arguments_are_reported():
+    scene = scenegen.coverage_scene(32, 24)
+    with DeviceScene(scene) as ds:
+        with pytest.raises(abi.RtError) as e:
+            ds.render(max_depth=9)
+        assert e.value.code == abi.RT_E_INVALID
+        with pytest.raises(abi.RtError) as e:
+            ds.download()
+        assert e.value.code == abi.RT_E_STATE
+    bad = scene.copy()
+    bad.faces["material"][0] = 99
+    with pytest.raises(abi.RtError) as e:
+        DeviceScene(bad)
+    assert e.value.code == abi.RT_E_INVALID

@@ -1,0 +1,180 @@
+"""CPU-only tests of the host front-end (parser, P3 reader / writer) and of the
+C-ABI libraries' export tables.  No compute call touches a GPU here."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from simple_raytracer_b200 import abi, ppm, scenegen
+from simple_raytracer_b200.scene import Scene
+from tests import common
+from tests import oracle_lib as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "raytracer_ref")
+
+
+def _declared(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rt_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_every_declared_symbol_is_exported():
+    rt, host = abi.load_rt(), abi.load_host()
+    names_rt, names_host = _declared("rt.h"), [n for n in _declared("rt_host.h") if n.startswith("rt_host_")]
+    assert set(names_rt) == set(abi.RT_SYMBOLS)
+    assert set(names_host) == set(abi.RT_HOST_SYMBOLS)
+    for n in names_rt:
+        assert getattr(rt, n) is not None
+    for n in names_host:
+        assert getattr(host, n) is not None
+    assert rt.rt_abi_version() == 1
+
+
+def test_struct_layouts_match_the_header():
+    # sizes implied by include/rt.h on LP64
+    assert C.sizeof(abi.RtMaterial) == 48 and C.sizeof(abi.RtSphere) == 28
+    assert C.sizeof(abi.RtFace) == 112 and C.sizeof(abi.RtLight) == 28 and C.sizeof(abi.RtTexture) == 16
+    assert C.sizeof(abi.RtRenderParams) == 32
+    assert C.sizeof(abi.RtSceneDesc) == 8 + 12 * 3 + 4 + 12 + 4 + 5 * 16
+
+
+def _write(tmp_path, text, name="s.txt"):
+    p = tmp_path / name
+    p.write_text(text)
+    return str(p)
+
+
+BASE = "eye 0 0 5\nviewdir 0 0 -1\nupdir 0 1 0\nhfov 60\nimsize 8 6\nbkgcolor 0.1 0.2 0.3\n"
+
+
+def test_parser_reads_the_example_scenes():
+    s = common.example_scene("basic_geometry_tests/four_spheres")
+    assert (s.width, s.height) == (512, 512) and len(s.spheres) == 4 and len(s.lights) == 1
+    assert s.spheres["radius"][3] == 1.0                       # "sphere 0 0 -6 1git": stof accepts trailing junk (A10.2)
+    assert s.bkg_eta == 0.0                                     # bkgcolor without eta (A10.3)
+    assert list(s.spheres["id"]) == [1, 2, 3, 4]
+    t1 = common.example_scene("reflection_transparency_tests/Test1")
+    assert t1.bkg_eta == 1.0 and len(t1.faces) == 2 and len(t1.spheres) == 4
+    assert list(t1.faces["id"]) == [5, 6]                      # ids count spheres and faces together (main.cpp:329,476)
+    assert np.allclose(t1.materials["opacity"][:2], [0.2, 1.0]) and t1.materials["eta"][1] == 0.0
+    h = common.example_scene("showcases/house")
+    assert len(h.textures) == 4 and h.faces["texture"].max() == 2 and h.spheres["texture"][0] == 3
+    assert h.faces["vt"].max() == 4.0                          # UVs beyond 1 are kept; the renderer clamps (A8.5)
+    ep = common.example_scene("showcases/earth_pyramid")
+    assert (ep.faces["vt"][2:] == 0).all() or (ep.faces["vt"] == 0).any()   # missing vt index reads as zeros (A10.5)
+
+
+def test_parser_quirks(tmp_path):
+    # mtlcolor alpha/eta only with exactly 12 arguments (A10.3)
+    s = Scene.from_file(_write(tmp_path, BASE + "mtlcolor 1 0 0 1 1 1 0.1 0.2 0.3 4 0.5\nsphere 0 0 0 1\n"))
+    assert s.materials["opacity"][0] == 1.0 and s.materials["eta"][0] == 1.0
+    s = Scene.from_file(_write(tmp_path, BASE + "mtlcolor 1 0 0 1 1 1 0.1 0.2 0.3 4 7.5 1.5\nsphere 0 0 0 1\n"))
+    assert s.materials["opacity"][0] == 1.0 and s.materials["eta"][0] == 1.5       # alpha clamped to [0,1]
+    # comment lines and unknown commands are skipped; a command without arguments too
+    s = Scene.from_file(_write(tmp_path, BASE + "# a comment here\nfoo 1 2 3\nsphere\nlight 0 -1 0 0 1 1 1\n"))
+    assert len(s.spheres) == 0 and len(s.lights) == 1 and s.lights["w"][0] == 0
+    # face format sniffing per vertex; the last vertex decides smooth shading (A10.6)
+    txt = BASE + "mtlcolor 1 1 1 1 1 1 0 1 0 1\nv 0 0 0\nv 1 0 0\nv 0 1 0\nvn 0 0 1\nvt 0.5 0.25\n"
+    s = Scene.from_file(_write(tmp_path, txt + "f 1//1 2//1 3\nf 1 2 3//1\nf 1/1 2/1 3/1\nf 1/1/1 2/1/1 3/1/1\n"))
+    assert list(s.faces["smooth"]) == [0, 1, 0, 1]
+    assert s.faces["texture"].tolist() == [-1, -1, -1, -1]      # has_texture comes from the parser state (A8.6)
+    assert s.faces["vn"][0][2].tolist() == [0, 0, 0] and s.faces["vn"][0][0].tolist() == [0, 0, 1]
+    assert s.faces["vt"][2][1].tolist() == [0.5, 0.25]
+    # a face that references a missing vertex silently gets zeros (A10.5)
+    s = Scene.from_file(_write(tmp_path, txt + "f 1 2 9\n"))
+    assert s.faces["v"][0][2].tolist() == [0, 0, 0]
+
+
+@pytest.mark.parametrize("text,needle", [
+    (BASE.replace("eye 0 0 5", "eye  0 0 5"), "empty token"),                    # double space aborts (A10.1)
+    (BASE + " sphere 0 0 0 1\n", "empty token"),                                  # leading space aborts
+    (BASE.replace("imsize 8 6", "imsize 1 6"), "Invalid image dimensions"),       # main.cpp:242
+    (BASE + "sphere 0 0 0 1\n", "Must define a 'mtlcolor'"),                      # main.cpp:360
+    (BASE.replace("hfov 60\n", ""), "Requires command 'hfov'"),                   # main.cpp:594
+    (BASE.replace("bkgcolor 0.1 0.2 0.3\n", ""), "Requires command 'bkgcolor'"),
+    (BASE + "mtlcolor 1 1 1\n", "material"),
+    (BASE + "mtlcolor 1 1 1 1 1 1 0 1 0 1\ntexture nope.ppm\n", "texture"),
+])
+def test_parser_errors(tmp_path, text, needle):
+    with pytest.raises(abi.RtError) as e:
+        Scene.from_file(_write(tmp_path, text))
+    assert e.value.code == abi.RT_E_PARSE and needle in e.value.message
+
+
+def test_parser_missing_file(tmp_path):
+    with pytest.raises(abi.RtError) as e:
+        Scene.from_file(str(tmp_path / "absent.txt"))
+    assert e.value.code == abi.RT_E_IO and "Issue reading input file" in e.value.message
+
+
+def test_texture_loader(tmp_path):
+    img = scenegen.make_texture("checker", 7, 5, 3)
+    p = tmp_path / "t.ppm"
+    p.write_text("P3\n# comment line\n7 5\n255\n" + "\n".join(" ".join(map(str, r.reshape(-1))) for r in img) + "\n")
+    got = ppm.read_texture_p3(str(p))
+    assert np.array_equal(got, img)
+    # header tokens on one line, several spaces between values
+    p.write_text("P3 7 5 255\n" + "  ".join(map(str, img.reshape(-1))) + "\n")
+    assert np.array_equal(ppm.read_texture_p3(str(p)), img)
+    for bad, needle in [("P6 7 5 255\n1 2 3\n", "P3"), ("P3 7 5 65535\n1 2 3\n", "255"), ("P3\n\n7 5\n255\n", "empty line"),
+                        ("P3 2 2 255\n1 2 3\n", "too few"), ("P3 1 1 255\n1 2 300\n", "outside")]:
+        p.write_text(bad)
+        with pytest.raises(abi.RtError) as e:
+            ppm.read_texture_p3(str(p))
+        assert needle in e.value.message
+
+
+def test_ppm_writer_text_is_the_reference_dialect():
+    rgb = np.array([[[0, 7, 255], [12, 100, 99]], [[1, 2, 3], [0, 0, 0]]], dtype=np.uint8)
+    flags = np.array([[0, 0], [7, 8]], dtype=np.uint8)
+    text = ppm.format_ppm(rgb, flags, bkg=(2.0, -0.5, 0.25))
+    nan = "18446744071562067968"
+    neg = str((1 << 64) - 127)                    # (size_t)(int)(-0.5 * 255)
+    assert text == f"P3 \n2 2 \n255 \n0 7 255 \n12 100 99 \n{nan} {nan} {nan} \n510 {neg} 63 \n"
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/raytracer_ref not built")
+@pytest.mark.parametrize("name", ["reflection_transparency_tests/Test1", "basic_geometry_tests/purple_pyramid"])
+def test_ppm_writer_is_byte_identical_to_the_reference_program(tmp_path, name):
+    """parser -> oracle frame -> our writer  ==  the reference program's own file."""
+    scene, _ = common.golden_frame(name)
+    text = common.scene_text(name)
+    text = "\n".join(f"imsize {scene.width} {scene.height}" if l.startswith("imsize ") else l for l in text.split("\n"))
+    sp = _write(tmp_path, text, "scene.txt")
+    subprocess.run([REF_BIN, "scene.txt"], cwd=str(tmp_path), check=True, capture_output=True)
+    ref_bytes = (tmp_path / "scene.ppm").read_bytes()
+    parsed = Scene.from_file(sp)
+    raw, ids, _ = O.oracle_render(parsed)
+    rgb, flags = O.raw_to_rgb8(raw, ids)
+    out = tmp_path / "ours.ppm"
+    ppm.write_ppm(str(out), rgb.reshape(parsed.height, parsed.width, 3), flags.reshape(parsed.height, parsed.width), parsed.bkg)
+    assert out.read_bytes() == ref_bytes
+    assert ppm.output_path("dir.v2/scene.txt") == "dir.v2/scene.ppm"
+
+
+def test_scene_text_round_trip(tmp_path):
+    sc = scenegen.coverage_scene(32, 24)
+    paths = []
+    for i, t in enumerate(sc.textures):
+        p = tmp_path / f"tex{i}.ppm"
+        p.write_text(scenegen.p3_text(t))
+        paths.append(str(p))
+    back = Scene.from_file(_write(tmp_path, sc.to_text(paths)))
+    raw_a, _, _ = O.oracle_render(sc)
+    raw_b, _, _ = O.oracle_render(back)
+    assert np.array_equal(raw_a, raw_b)
+
+
+def test_render_without_gpu_fails_loudly():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from simple_raytracer_b200.renderer import DeviceScene
+    with pytest.raises(abi.RtError) as e:
+        DeviceScene(scenegen.coverage_scene(16, 12))
+    assert e.value.code == abi.RT_E_CUDA and "no CPU fallback" in e.value.message
