@@ -115,8 +115,12 @@ class ClockSampler:
 
 
 # ---- CPU reference (the reference's own ShadeRay / TraceRay from oracle/_ref) -------------------
+_CPU_SCENE = None      # inherited by the forked workers (a Scene caches ctypes pointers: not picklable)
+
+
 def _cpu_worker(args):
-    scene, pixels, kind = args
+    pixels, kind = args
+    scene = _CPU_SCENE
     from tests import oracle_lib as O
     if kind == "reference":
         raw, ids, secs = O.ref_render_pixels(scene, pixels)
@@ -156,13 +160,16 @@ def cpu_reference(scene: Scene, budget_s: float, procs: int) -> dict:
     n = int(max(procs, min(scene.n_pixels, budget_s * procs / per_pixel)))
     pixels = cpu_sample_pixels(scene, n)
     _, _, st = O.oracle_render(scene, pixels=pixels) if kind == "reference" else (None, None, None)
-    parts = [p for p in np.array_split(pixels, procs) if len(p)]
+    # interleave the sample over the workers so that every process sees the same mix of pixels
+    parts = [pixels[k::procs] for k in range(procs) if len(pixels[k::procs])]
+    global _CPU_SCENE
+    _CPU_SCENE = scene
     t0 = time.perf_counter()
     if len(parts) == 1:
-        secs = [_cpu_worker((scene, parts[0], kind))]
+        secs = [_cpu_worker((parts[0], kind))]
     else:
         with mp.get_context("fork").Pool(len(parts)) as pool:
-            secs = pool.map(_cpu_worker, [(scene, p, kind) for p in parts])
+            secs = pool.map(_cpu_worker, [(p, kind) for p in parts])
     wall = time.perf_counter() - t0
     if st is None:
         _, _, st = O.oracle_render(scene, pixels=pixels)
@@ -172,3 +179,265 @@ def cpu_reference(scene: Scene, budget_s: float, procs: int) -> dict:
             "sample": f"{len(pixels)} pixels on a regular grid of the {scene.width}x{scene.height} frame "
                       f"({rays} rays, {busy:.1f} s in the slowest of {len(parts)} processes, {wall:.1f} s wall incl. scene load)",
             "rays": int(rays), "seconds": busy}
+
+
+# ---- peaks -----------------------------------------------------------------------------------
+def measured_peaks() -> dict:
+    """HBM GB/s from the driver-written MEASURED_PEAKS.json, else the profiling guide's fallback."""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        return {"hbm_gbs": float(d["hbm_gbs"]), "sm_max_mhz": float(d.get("sm_max_mhz", 1965.0)), "source": "measured"}
+    except (OSError, KeyError, ValueError):
+        return {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "source": "fallback"}
+
+
+def fp32_peak_tflops(sm_mhz: float, sms: int = 148) -> float:
+    """FP32 FMA peak: SMs x 128 lanes x 2 flop x clock."""
+    return sms * 128 * 2 * sm_mhz * 1e6 / 1e12
+
+
+# ---- pinned host copies of the scene arrays (the e2e leg uploads from pinned memory) ---------------
+def pin_scene(scene: Scene):
+    import torch
+    keep = []
+
+    def pin(a: np.ndarray) -> np.ndarray:
+        if a.nbytes == 0:
+            return a
+        t = torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).pin_memory()
+        keep.append(t)
+        return t.numpy().view(a.dtype).reshape(a.shape)
+
+    sc = Scene(scene.width, scene.height, scene.eye, scene.viewdir, scene.updir, scene.hfov_deg, scene.bkg,
+               scene.bkg_eta, pin(scene.materials), pin(scene.spheres), pin(scene.faces), pin(scene.lights),
+               [pin(t) for t in scene.textures])
+    sc._pinned = keep
+    return sc
+
+
+def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
+    """algorithmic bytes (BVH) or flops (brute force) of one frame, from the
+    instrumented frame's device counters."""
+    nodes = int(st.nodes_total)
+    rays = int(st.rays_primary + st.rays_shadow + st.rays_transmit + st.rays_reflect)
+    L = len(scene.lights)
+    if accel_used == abi.RT_ACCEL_LBVH:
+        b = 32 * int(st.bvh_nodes_visited) + 48 * int(st.prim_tests) + 64 * nodes + 4 * int(st.texel_fetches)
+        return {"bound": "hbm", "per_frame": b, "unit": "GB/s",
+                "detail": {"child_boxes_tested": int(st.bvh_nodes_visited), "prim_tests": int(st.prim_tests),
+                           "nodes_shaded": nodes, "texels": int(st.texel_fetches)}}
+    fl = rays * (19 * len(scene.spheres) + 42 * len(scene.faces)) + nodes * (64 + 52 * L)
+    return {"bound": "fp32", "per_frame": fl, "unit": "TFLOP/s", "detail": {"rays": rays, "nodes_shaded": nodes}}
+
+
+# ---- our arm ---------------------------------------------------------------------------------
+def run_ours(args) -> dict:
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    scene = WORKLOADS[args.workload]()
+    W, H = scene.width, scene.height
+    ds = DeviceScene(scene)
+    stream = torch.cuda.current_stream()
+    sptr = stream.cuda_stream
+    prm = make_params(rank=rank, world_size=world, tile_rows=TILE_ROWS)
+
+    # one synchronous instrumented frame per rank: sizes the queues, counts rays and algorithmic work
+    st_i = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS, instrument=True)
+    accel_used = st_i.accel_used
+    rays_local = int(st_i.rays_primary + st_i.rays_shadow + st_i.rays_transmit + st_i.rays_reflect)
+    work = algorithmic_work(scene, st_i, accel_used)
+    # per-generation kernel times of a plain (un-instrumented) frame: roofline of the dominant kernel
+    ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS)
+    st_p = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS, profile=True)
+    level_ms = [float(x) for x in list(st_p.level_ms)[:5]]
+    launches_per_frame = int(st_p.kernel_launches)
+
+    tile_bytes = ds.tile_buffer_bytes(world, TILE_ROWS)
+    send = torch.empty(tile_bytes, dtype=torch.uint8, device="cuda")
+    gathered = torch.empty(tile_bytes * world, dtype=torch.uint8, device="cuda") if world > 1 else send
+    frame = torch.empty(H * W * 4, dtype=torch.uint8, device="cuda")
+    flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device="cuda")
+
+    def frame_step():
+        ds.render_async(prm, send.data_ptr(), sptr)
+        if world > 1:
+            dist.all_gather_into_tensor(gathered, send)
+        ds.deinterleave(gathered.data_ptr(), frame.data_ptr(), world, TILE_ROWS, sptr)
+
+    for _ in range(args.warmup):
+        flush.zero_()
+        frame_step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for a, b in ev:
+        flush.zero_()                 # L2 flush between timed iterations (outside the timed events)
+        a.record(stream)
+        frame_step()
+        b.record(stream)
+    barrier()
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([total_ms, float(rays_local)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        total_ms, rays_frame = float(tmax[0]), int(tsum[1])
+    else:
+        rays_frame = rays_local
+    ms_per_step = total_ms / args.steps
+    value = rays_frame / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e: the C ABI with host buffers, every step: upload (H2D from pinned memory, packing,
+    # LBVH build) + render of this rank's tiles + download (D2H) of the rows this rank rendered
+    e2e = None
+    if not args.no_e2e:
+        ds.close()
+        pinned = pin_scene(scene)
+        rgb_t = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory()
+        flg_t = torch.empty((H, W), dtype=torch.uint8).pin_memory()
+        rgb, flg = rgb_t.numpy(), flg_t.numpy()
+        n_e2e = max(1, min(args.steps, args.e2e_steps))
+
+        def e2e_step():
+            with DeviceScene(pinned) as d2:
+                d2.render(prm)
+                d2.download(rgb, flg)
+
+        e2e_step()      # warm-up (first-touch of the pinned buffers, workspace cache)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n_e2e):
+            e2e_step()
+        barrier()
+        dt = time.perf_counter() - t0
+        tt = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dt = float(tt[0])
+        e2e = {"value": rays_frame * n_e2e / dt / 1e6, "unit": "Mrays/s", "ms_per_step": dt / n_e2e * 1e3,
+               "steps": n_e2e, "h2d_bytes_per_step": pinned.h2d_bytes(),
+               "d2h_bytes_per_step": int(H * W * 4 / world),
+               "what": "rt_upload_scene(host RtSceneDesc, pinned) + rt_render + rt_download_framebuffer per step, "
+                       "host wall clock, max over ranks"}
+    else:
+        ds.close()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return {}
+
+    peaks = measured_peaks()
+    dom_ms = sum(level_ms)
+    n_levels = 5
+    if work["bound"] == "hbm":
+        achieved = work["per_frame"] / (dom_ms * 1e-3) / 1e9
+        peak = peaks["hbm_gbs"]
+        roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": peaks["source"]}
+    else:
+        clk = (clocks or {}).get("sm_mhz") or peaks["sm_max_mhz"]
+        peak = fp32_peak_tflops(clk)
+        achieved = work["per_frame"] / (dom_ms * 1e-3) / 1e12
+        roof = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": f"148 SM x 128 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)"}
+    roof.update({"kernel": "level_kernel (closest hit + shadow rays + shade + spawn), all generations of one frame",
+                 "launches_per_frame": n_levels, "ms_per_launch_avg": dom_ms / n_levels, "level_ms": level_ms,
+                 "algorithmic_per_frame": work["per_frame"], "counters": work["detail"],
+                 "share_of_frame": dom_ms / float(st_p.render_ms) if st_p.render_ms else None,
+                 "note": "rank 0's shard" if world > 1 else "whole frame"})
+
+    out = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": args.workload, "width": W, "height": H, "triangles": len(scene.faces),
+                      "spheres": len(scene.spheres), "lights": len(scene.lights), "max_depth": 4,
+                      "accel": "lbvh" if accel_used == abi.RT_ACCEL_LBVH else "brute",
+                      "rays_per_frame": rays_frame, "sharding": f"interleaved tiles of {TILE_ROWS} rows, "
+                      f"{'NCCL allgather of RGBA8 tiles + ' if world > 1 else ''}device de-interleave",
+                      "l2": "flushed between timed iterations (252 MiB memset, untimed)"},
+           "clocks": clocks, "gpu_launches": (launches_per_frame + 1) * args.steps, "roofline": roof}
+    if e2e:
+        out["e2e"] = e2e
+    if world == 1 and not args.no_cpu:
+        out["cpu_baseline"] = cpu_reference(scene, args.cpu_budget, os.cpu_count() or 1)
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+# ---- reference arm ----------------------------------------------------------------------------
+def run_reference(args) -> dict:
+    """The reference's own CPU code for the path (oracle/_ref/libref.so, compiled from the
+    unmodified sources; the plain-C port when that library is absent) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return {}
+    scene = WORKLOADS[args.workload]()
+    cores = os.cpu_count() or 1
+    steps = max(1, args.steps)
+    # the whole --steps/--warmup run is bounded to ~args.cpu_budget * 4 seconds of wall time
+    per_step = max(2.0, min(args.cpu_budget, 4.0 * args.cpu_budget / (steps + args.warmup)))
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference(scene, min(per_step, 3.0), cores)
+    runs = [cpu_reference(scene, per_step, cores) for _ in range(steps)]
+    rays = sum(r["rays"] for r in runs)
+    secs = sum(r["seconds"] for r in runs)
+    value = rays / secs / 1e6
+    base = runs[-1]
+    return {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": secs / steps * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "width": scene.width, "height": scene.height,
+                       "triangles": len(scene.faces), "spheres": len(scene.spheres), "lights": len(scene.lights),
+                       "max_depth": 4, "accel": "brute force (the reference has no acceleration structure)"},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": base["cores"], "kind": base["kind"],
+                             "sample": "each step: " + base["sample"]},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline sample")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if out:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()
