@@ -183,6 +183,14 @@ int         rt_abi_version(void);
  * A = flags) for the given sharding. */
 size_t rt_tile_buffer_bytes(const RtScene* scene, int32_t world_size, int32_t tile_rows);
 
+/* The sharding arithmetic itself (pure host code, no CUDA call): rows are cut into
+ * tiles of tile_rows rows, tile t belongs to rank t % world_size, every rank holds
+ * ceil(n_tiles / world_size) tiles (padded so that an allgather has equal counts).
+ *   out[0] = tiles in the image, out[1] = tiles per rank, out[2] = rows per rank
+ *   (padded), out[3] = pixels per rank (padded). */
+int rt_tile_layout(int32_t height, int32_t width, int32_t world_size,
+                   int32_t tile_rows, int32_t out[4]);
+
 /* Like rt_render, but asynchronous on `cuda_stream` (a cudaStream_t, may be
  * NULL for the default stream) and with the RGBA8 tile buffer written to
  * caller-provided DEVICE memory (e.g. the send buffer of an NCCL allgather).

@@ -89,7 +89,7 @@ class RtStats(C.Structure):
 RT_SYMBOLS = [
     "rt_upload_scene", "rt_render", "rt_download_framebuffer", "rt_free_scene", "rt_last_error",
     "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_deinterleave_tiles", "rt_set_camera",
-    "rt_trace_closest", "rt_trace_shadow", "rt_download_primary_ids",
+    "rt_trace_closest", "rt_trace_shadow", "rt_download_primary_ids", "rt_tile_layout",
 ]
 RT_HOST_SYMBOLS = [
     "rt_host_parse_scene_file", "rt_host_free_scene_desc", "rt_host_read_texture_p3", "rt_host_free",
@@ -130,6 +130,8 @@ def load_rt() -> C.CDLL:
     lib.rt_abi_version.restype = C.c_int
     lib.rt_tile_buffer_bytes.argtypes = [vp, i32, i32]
     lib.rt_tile_buffer_bytes.restype = C.c_size_t
+    lib.rt_tile_layout.argtypes = [i32, i32, i32, i32, _p(i32)]
+    lib.rt_tile_layout.restype = C.c_int
     lib.rt_render_async.argtypes = [vp, _p(RtRenderParams), vp, vp]
     lib.rt_render_async.restype = C.c_int
     lib.rt_deinterleave_tiles.argtypes = [vp, vp, vp, i32, i32, vp]

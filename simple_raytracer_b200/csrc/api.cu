@@ -170,6 +170,14 @@ size_t rt_tile_buffer_bytes(const RtScene* scene, int32_t world_size, int32_t ti
     return (size_t)tl.n_local_pixels * sizeof(uchar4);
 }
 
+int rt_tile_layout(int32_t height, int32_t width, int32_t world_size, int32_t tile_rows, int32_t out[4])
+{
+    if (height < 1 || width < 1 || world_size < 1 || tile_rows < 1 || !out) { set_error("rt_tile_layout: bad argument"); return RT_E_INVALID; }
+    const TileLayout tl = tile_layout(height, width, world_size, tile_rows);
+    out[0] = tl.n_tiles_total; out[1] = tl.n_local_tiles; out[2] = tl.n_local_rows; out[3] = tl.n_local_pixels;
+    return RT_OK;
+}
+
 int rt_render_async(RtScene* scene, const RtRenderParams* params, void* dev_tiles, void* cuda_stream)
 {
     if (!scene) { set_error("rt_render_async: null scene"); return RT_E_INVALID; }
