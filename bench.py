@@ -30,6 +30,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 from simple_raytracer_b200 import abi, scenegen  # noqa: E402
+from simple_raytracer_b200.multigpu import DistributedFrame  # noqa: E402
 from simple_raytracer_b200.renderer import DeviceScene, make_params  # noqa: E402
 from simple_raytracer_b200.scene import Scene  # noqa: E402
 
@@ -270,17 +271,11 @@ def run_ours(args) -> dict:
     level_ms = [float(x) for x in list(st_p.level_ms)[:5]]
     launches_per_frame = int(st_p.kernel_launches)
 
-    tile_bytes = ds.tile_buffer_bytes(world, TILE_ROWS)
-    send = torch.empty(tile_bytes, dtype=torch.uint8, device="cuda")
-    gathered = torch.empty(tile_bytes * world, dtype=torch.uint8, device="cuda") if world > 1 else send
-    frame = torch.empty(H * W * 4, dtype=torch.uint8, device="cuda")
+    df = DistributedFrame(ds, TILE_ROWS, rank, world)
     flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device="cuda")
 
     def frame_step():
-        ds.render_async(prm, send.data_ptr(), sptr)
-        if world > 1:
-            dist.all_gather_into_tensor(gathered, send)
-        ds.deinterleave(gathered.data_ptr(), frame.data_ptr(), world, TILE_ROWS, sptr)
+        df.step(sptr)       # rt_render_async -> one allgather (N > 1) -> rt_deinterleave_tiles
 
     for _ in range(args.warmup):
         flush.zero_()

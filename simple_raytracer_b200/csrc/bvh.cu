@@ -11,7 +11,8 @@
 //             4e-6 * (largest coordinate magnitude in play);
 //   sphere  : B*B - 4*C >= 0 in mixed precision with a ray that is unit only up to
 //             rounding accepts rho^2 <= r^2 + c*eps*D^2 (D = distance from the ray
-//             origin to the centre): r_eff^2 = r^2 + 2e-6 * Dmax^2.
+//             origin to the centre): r_eff^2 = r^2 + 1.2e-5 * Dmax^2
+//             (rays with | |ray|^2 - 1 | > 1e-5 never use the tree for spheres, bvh.cuh).
 #include "bvh.cuh"
 #include "host_scene.h"
 
@@ -66,7 +67,7 @@ __global__ void prim_bounds_kernel(const float4* __restrict__ tri, const float4*
             d2 += d * d;
         }
         const float r = fabsf(s.w);
-        const float reff = sqrtf(r * r + 2.0e-6f * d2) * 1.00001f + 4.0e-6f * bb.scale;
+        const float reff = sqrtf(r * r + 1.2e-5f * d2) * 1.00001f + 4.0e-6f * bb.scale;
         for (int c = 0; c < 3; c++) { lo[c] = c3[c] - reff; hi[c] = c3[c] + reff; }
     }
     // NaN / inf primitives (degenerate input) never hit anything: give them an empty box
@@ -288,7 +289,10 @@ __global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_val
     w[3] = make_float4(__int_as_float(code[0]), __int_as_float(code[1]), __int_as_float(count[0]), __int_as_float(count[1]));
 }
 
-// scenes of <= kLeafMax primitives: a single node whose left child is the only leaf
+// scenes of <= kLeafMax primitives: one node; the left child is the leaf holding all of them,
+// the right child is a leaf holding the DUMMY record at slot n (a triangle with a zero normal:
+// `dem == 0` rejects it for every ray, main.cpp:1297).  An inverted box would not do: the
+// min/max slab test reads it as unbounded and, marked as an inner node, it would loop for ever.
 __global__ void emit_tiny_kernel(int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
                                  float4* __restrict__ nodes)
 {
@@ -296,9 +300,9 @@ __global__ void emit_tiny_kernel(int n, const float4* __restrict__ prim_lo, cons
     float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
     for (int p = 0; p < n; p++) box_union(lo, hi, prim_lo[p], prim_hi[p]);
     nodes[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
-    nodes[1] = make_float4(hi.y, hi.z, FLT_MAX, FLT_MAX);
-    nodes[2] = make_float4(FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX);
-    nodes[3] = make_float4(__int_as_float(0), __int_as_float(0), __int_as_float(n), __int_as_float(0));
+    nodes[1] = make_float4(hi.y, hi.z, lo.x, lo.y);
+    nodes[2] = make_float4(lo.z, hi.x, hi.y, hi.z);
+    nodes[3] = make_float4(__int_as_float(0), __int_as_float(n), __int_as_float(n), __int_as_float(1));
 }
 
 // primitive records in Morton order (spheres widened to the triangle record size)
@@ -306,9 +310,14 @@ __global__ void emit_prims_kernel(int n, int nf, const unsigned* __restrict__ so
                                   const float4* __restrict__ sph, float4* __restrict__ out)
 {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n) return;
-    const int p = (int)sorted_vals[k];
+    if (k > n) return;
     float4* o = out + (size_t)k * kTriWords;
+    if (k == n) {   // the never-hit dummy record (see emit_tiny_kernel)
+        o[0] = o[1] = o[2] = o[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+        o[4] = make_float4(0.f, 1.0f, __int_as_float(0x7fffffff), __int_as_float(0));
+        return;
+    }
+    const int p = (int)sorted_vals[k];
     if (p < nf) {
         const float4* w = tri + (size_t)p * kTriWords;
         for (int q = 0; q < kTriWords; q++) o[q] = w[q];
@@ -345,7 +354,7 @@ int build_bvh(SceneHost* s)
         !children.reserve(N * 8) || !range.reserve(N * 8) || !par_i.reserve(N * 4) || !par_l.reserve(N * 4) ||
         !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4))
         return RT_E_NOMEM;
-    if (!s->bvh_nodes.reserve((size_t)n_internal * 64) || !s->bvh_tri.reserve(N * kTriWords * 16)) return RT_E_NOMEM;
+    if (!s->bvh_nodes.reserve((size_t)n_internal * 64) || !s->bvh_tri.reserve((N + 1) * kTriWords * 16)) return RT_E_NOMEM;
 
     const int B = 256, G = (n + B - 1) / B;
     prim_bounds_kernel<<<G, B, 0, st>>>(s->tri.as<float4>(), s->sph.as<float4>(), s->nf, s->ns, bb, box_lo.as<float4>(),
@@ -368,7 +377,7 @@ int build_bvh(SceneHost* s)
     } else {
         emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), s->bvh_nodes.as<float4>());
     }
-    emit_prims_kernel<<<G, B, 0, st>>>(n, s->nf, vin, s->tri.as<float4>(), s->sph.as<float4>(), s->bvh_tri.as<float4>());
+    emit_prims_kernel<<<(n + 1 + B - 1) / B, B, 0, st>>>(n, s->nf, vin, s->tri.as<float4>(), s->sph.as<float4>(), s->bvh_tri.as<float4>());
     RT_CUDA(cudaGetLastError());
     RT_CUDA(cudaStreamSynchronize(st));
     s->bvh_n_nodes = n_internal; s->bvh_root = 0; s->bvh_built = true;

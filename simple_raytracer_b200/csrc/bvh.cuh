@@ -109,7 +109,7 @@ struct BvhAccelT {
     }
 
     struct ClosestVisit {
-        V3 o, ray; float tmin; Hit best; int best_order;
+        V3 o, ray; float tmin; Hit best; int best_order; bool skip_spheres;
         RT_DEV float operator()(const float4* w, float tmax)
         {
             const float4 w4 = w[4];
@@ -120,7 +120,7 @@ struct BvhAccelT {
                     float b, g;
                     if (tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g)) { best.t = t; best.obj = order; best.b = b; best.g = g; best_order = order; }
                 }
-            } else {
+            } else if (!skip_spheres) {
                 float tf, tn;
                 const int n = sphere_roots(w[0], o, ray, tf, tn);
                 if (n >= 1 && tf > tmin && (tf < best.t || (tf == best.t && order < best_order))) { best.t = tf; best.obj = order; best_order = order; }
@@ -130,11 +130,28 @@ struct BvhAccelT {
         }
     };
 
+    // |ray|^2 far from 1: the sphere quadratic (A == 1, main.cpp:1232) accepts a region no box
+    // bounds.  Such rays test every sphere directly and use the tree for triangles only.
+    RT_DEV bool spheres_unbounded(V3 ray) const
+    {
+        const float s2 = ray.x * ray.x + ray.y * ray.y + ray.z * ray.z;
+        return ns > 0 && !(fabsf(s2 - 1.0f) <= 1.0e-5f);   // bvh.cu pads sphere boxes for 1.2e-5
+    }
+
     RT_DEV Hit closest(V3 o, V3 ray, float tmin) const
     {
-        ClosestVisit v; v.o = o; v.ray = ray; v.tmin = tmin;
+        ClosestVisit v; v.o = o; v.ray = ray; v.tmin = tmin; v.skip_spheres = spheres_unbounded(ray);
         v.best.t = 3.402823466e+38f; v.best.obj = -1; v.best.b = v.best.g = 0.0f; v.best_order = 0x7fffffff;
         walk(o, ray, tmin, 3.402823466e+38f, v);
+        if (v.skip_spheres) {
+            for (int i = 0; i < ns; i++) {
+                float tf, tn;
+                const int n = sphere_roots(sph[(size_t)i * kSphWords], o, ray, tf, tn);
+                const int order = nf + i;
+                if (n >= 1 && tf > tmin && (tf < v.best.t || (tf == v.best.t && order < v.best_order))) { v.best.t = tf; v.best.obj = order; v.best_order = order; }
+                if (n == 2 && tn > tmin && (tn < v.best.t || (tn == v.best.t && order < v.best_order))) { v.best.t = tn; v.best.obj = order; v.best_order = order; }
+            }
+        }
         return v.best;
     }
 
@@ -229,8 +246,7 @@ struct BvhAccelT {
         // length s != 1 (un-normalised directional lights, main.cpp:895) the accepted set is
         // rho^2 <= r^2 + (s^2 - 1) p^2 — unbounded for s > 1, so no box bounds it:
         // such rays test every sphere directly and use the tree for the triangles only.
-        const float s2 = ray.x * ray.x + ray.y * ray.y + ray.z * ray.z;
-        v.skip_spheres = ns > 0 && fabsf(s2 - 1.0f) > 1.0e-4f;
+        v.skip_spheres = spheres_unbounded(ray);
         walk(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
         if (v.skip_spheres && !(v.opaque && !count_all)) {
             for (int i = 0; i < ns; i++) {

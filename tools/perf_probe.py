@@ -1,0 +1,44 @@
+#!/usr/bin/env python
+"""Scratch perf probe: per-generation times and traversal counters of one workload."""
+import argparse, json, os, sys, time
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+from simple_raytracer_b200 import abi, scenegen
+from simple_raytracer_b200.renderer import DeviceScene
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tris", type=int, default=1_000_000)
+    ap.add_argument("--spheres", type=int, default=1000)
+    ap.add_argument("--w", type=int, default=1920)
+    ap.add_argument("--h", type=int, default=1080)
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--depth", type=int, default=4)
+    ap.add_argument("--no-instrument", action="store_true")
+    a = ap.parse_args()
+    sc = scenegen.stress_scene(a.tris, a.spheres, a.w, a.h)
+    t0 = time.time()
+    with DeviceScene(sc) as ds:
+        up = time.time() - t0
+        t0 = time.time()
+        st = ds.render(max_depth=a.depth)
+        first = time.time() - t0
+        rays = st.rays_primary + st.rays_shadow + st.rays_transmit + st.rays_reflect
+        best = None
+        for _ in range(a.reps):
+            s = ds.render(max_depth=a.depth, profile=True)
+            if best is None or s.render_ms < best.render_ms:
+                best = s
+        out = dict(upload_s=round(up, 3), first_render_s=round(first, 3), ms=round(best.render_ms, 3), rays=int(rays),
+                   mrays_s=round(rays / best.render_ms / 1e3, 1), nodes=list(best.nodes_per_level)[:a.depth + 1],
+                   level_ms=[round(x, 3) for x in list(best.level_ms)[:a.depth + 1]], combine_ms=round(best.combine_ms, 3),
+                   launches=best.kernel_launches)
+        if not a.no_instrument:
+            si = ds.render(max_depth=a.depth, instrument=True)
+            out.update(boxes_per_ray=round(si.bvh_nodes_visited / rays, 1), prims_per_ray=round(si.prim_tests / rays, 2),
+                       texels=int(si.texel_fetches), instr_ms=round(si.render_ms, 2))
+        print(json.dumps(out), flush=True)
+
+if __name__ == "__main__":
+    main()
