@@ -273,12 +273,12 @@ __global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_val
             const int slot = ~c2[c];
             const unsigned p = sorted_vals[slot];
             lo[c] = prim_lo[p]; hi[c] = prim_hi[p];
-            code[c] = slot; count[c] = 1;
+            code[c] = ~(slot << 3); count[c] = 1;
         } else {
             lo[c] = node_lo[c2[c]]; hi[c] = node_hi[c2[c]];
             const int2 r = range[c2[c]];
             const int size = r.y - r.x + 1;
-            if (size <= kLeafMax) { code[c] = r.x; count[c] = size; }
+            if (size <= kLeafMax) { code[c] = ~((r.x << 3) | (size - 1)); count[c] = size; }
             else { code[c] = c2[c]; count[c] = 0; }
         }
     }
@@ -286,7 +286,7 @@ __global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_val
     w[0] = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
     w[1] = make_float4(hi[0].y, hi[0].z, lo[1].x, lo[1].y);
     w[2] = make_float4(lo[1].z, hi[1].x, hi[1].y, hi[1].z);
-    w[3] = make_float4(__int_as_float(code[0]), __int_as_float(code[1]), __int_as_float(count[0]), __int_as_float(count[1]));
+    w[3] = make_float4(__int_as_float(code[0]), __int_as_float(code[1]), 0.0f, 0.0f);
 }
 
 // scenes of <= kLeafMax primitives: one node; the left child is the leaf holding all of them,
@@ -302,7 +302,7 @@ __global__ void emit_tiny_kernel(int n, const float4* __restrict__ prim_lo, cons
     nodes[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
     nodes[1] = make_float4(hi.y, hi.z, lo.x, lo.y);
     nodes[2] = make_float4(lo.z, hi.x, hi.y, hi.z);
-    nodes[3] = make_float4(__int_as_float(0), __int_as_float(n), __int_as_float(n), __int_as_float(1));
+    nodes[3] = make_float4(__int_as_float(~((0 << 3) | (n - 1))), __int_as_float(~(n << 3)), 0.0f, 0.0f);
 }
 
 // primitive records in Morton order (spheres widened to the triangle record size)

@@ -4,10 +4,10 @@
 // Node = 4 float4 words holding BOTH children's boxes, so one 64-byte fetch decides
 // two subtrees:
 //   w0 = L.lo.xyz, L.hi.x     w1 = L.hi.yz, R.lo.xy     w2 = R.lo.z, R.hi.xyz
-//   w3 = as_float{ left, right, left_count, right_count }
-//        count == 0: child is an internal node index; count > 0: child is a leaf
-//        covering `count` consecutive slots of the Morton-ordered primitive array
-//        starting at slot `left` / `right`.
+//   w3 = as_float{ left, right, 0, 0 }
+//        child >= 0: index of an inner node; child < 0: a leaf, ~child = (first << 3) |
+//        (count - 1): `count` (1..kLeafMax <= 8) consecutive slots of the Morton-ordered
+//        primitive array starting at slot `first`.
 // Leaf slots are 5-word records (kTriWords) for triangles AND spheres:
 //   triangle: the record of scene_device.h, w4 = d12, kshadow, as_float(order), 0
 //   sphere  : w0 = centre, radius ; w4 = 0, kshadow, as_float(order), as_float(1)
@@ -54,56 +54,62 @@ struct BvhAccelT {
         return tn <= tf * 1.0000005f;
     }
 
-    // Generic traversal.  `visit(slot_words, tcur)` tests one primitive and returns the
-    // new upper bound for culling (or a negative value to stop the whole walk).
+    // Generic traversal, "while-while" with one postponed leaf per lane (Aila & Laine 2009):
+    // lanes keep descending inner nodes until every lane of the warp holds a leaf, then all
+    // test primitives together; that keeps box tests and primitive tests in separate,
+    // mostly converged loops.  `visit(slot_words, tcur)` tests one primitive and returns the
+    // new upper bound for culling (or a negative value to stop the whole walk).  A postponed
+    // leaf is visited late, so boxes may be tested against a stale (larger) bound: that only
+    // costs work, never a hit.
     template <class Visit>
     RT_DEV void walk(V3 o, V3 ray, float tmin, float tmax, Visit& visit) const
     {
         if (n_nodes == 0 || !finite3(ray) || !finite3(o)) return;   // NaN/inf rays hit nothing in the reference either
         const V3 inv = mk3(1.0f / ray.x, 1.0f / ray.y, 1.0f / ray.z);
+        constexpr int kDone = 0x7fffffff;
         int stack[kBvhStack];
         int sp = 0;
-        int node = root;
-        while (true) {
-            const float4* w = nodes + (size_t)node * 4;
-            const float4 w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
-            const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
-            const int ln = __float_as_int(w3.z), rn = __float_as_int(w3.w);
-            float tl, tr;
-            bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, o, inv, tmin, tmax, tl);
-            bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, o, inv, tmin, tmax, tr);
-            if (kCount) cnt_boxes += 2;
-            // leaves are tested right away
-            if (hl && ln > 0) {
-                for (int k = 0; k < ln; k++) {
+        int node = root;      // >= 0: inner node index, < 0: leaf code, kDone: nothing left
+        int leaf = 0;         // postponed leaf code (< 0), 0 = none
+        while (node != kDone) {
+            while ((unsigned)node < (unsigned)kDone) {
+                const float4* w = nodes + (size_t)node * 4;
+                const float4 w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+                const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
+                float tl, tr;
+                const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, o, inv, tmin, tmax, tl);
+                const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, o, inv, tmin, tmax, tr);
+                if (kCount) cnt_boxes += 2;
+                if (hl && hr) {
+                    const bool left_first = tl <= tr;              // near child first, far child on the stack
+                    if (sp < kBvhStack) stack[sp++] = left_first ? rc : lc;
+                    node = left_first ? lc : rc;
+                } else if (hl) {
+                    node = lc;
+                } else if (hr) {
+                    node = rc;
+                } else {
+                    node = sp ? stack[--sp] : kDone;
+                }
+                if (node < 0 && leaf == 0) {                       // postpone the first leaf, keep descending
+                    leaf = node;
+                    node = sp ? stack[--sp] : kDone;
+                }
+                if (!__any_sync(__activemask(), leaf == 0)) break; // every lane has a leaf to test
+            }
+            while (leaf < 0) {
+                const int code = ~leaf;
+                const int first = code >> 3, count = (code & 7) + 1;
+                for (int k = 0; k < count; k++) {
                     if (kCount) cnt_prims++;
-                    tmax = visit(prims + (size_t)(lc + k) * kTriWords, tmax);
+                    tmax = visit(prims + (size_t)(first + k) * kTriWords, tmax);
                     if (tmax < 0.0f) return;
                 }
-                hl = false;
-            }
-            if (hr && rn > 0) {
-                if (tr <= tmax * 1.0000005f) {
-                    for (int k = 0; k < rn; k++) {
-                        if (kCount) cnt_prims++;
-                        tmax = visit(prims + (size_t)(rc + k) * kTriWords, tmax);
-                        if (tmax < 0.0f) return;
-                    }
+                leaf = 0;
+                if (node < 0) {                                    // the next node is a leaf too: take it now
+                    leaf = node;
+                    node = sp ? stack[--sp] : kDone;
                 }
-                hr = false;
-            }
-            if (hl && hr) {
-                // near child first, far child on the stack
-                const bool left_first = tl <= tr;
-                if (sp < kBvhStack) stack[sp++] = left_first ? rc : lc;
-                node = left_first ? lc : rc;
-            } else if (hl) {
-                node = lc;
-            } else if (hr) {
-                node = rc;
-            } else {
-                if (sp == 0) return;
-                node = stack[--sp];
             }
         }
     }
@@ -238,9 +244,11 @@ struct BvhAccelT {
         }
     };
 
-    RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask) const
+    // Walks the tree (and, for rays no box bounds, the sphere list) and leaves the partial
+    // factors sorted by iteration order in v.
+    RT_DEV void shadow_collect(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, ShadowVisit& v) const
     {
-        ShadowVisit v; v.o = o; v.ray = ray; v.tmin = tmin; v.tmax_hit = tmax; v.use_tmax = use_tmax; v.self = self;
+        v.o = o; v.ray = ray; v.tmin = tmin; v.tmax_hit = tmax; v.use_tmax = use_tmax; v.self = self;
         v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false; v.count_all = count_all;
         // The sphere quadratic assumes a unit ray (A == 1, main.cpp:1232).  For a ray of
         // length s != 1 (un-normalised directional lights, main.cpp:895) the accepted set is
@@ -259,7 +267,7 @@ struct BvhAccelT {
                 if (v.opaque && !count_all) break;
             }
         }
-        if (v.opaque) { mask = clamp01(fmul(0.0f, mask)); return v.hits; }
+        if (v.opaque) return;
         // insertion sort by order (stable: the two roots of one sphere share k)
         for (int i = 1; i < v.n_partial; i++) {
             const int ko = v.p_order[i]; const float kk = v.p_k[i];
@@ -267,9 +275,31 @@ struct BvhAccelT {
             while (j >= 0 && v.p_order[j] > ko) { v.p_order[j + 1] = v.p_order[j]; v.p_k[j + 1] = v.p_k[j]; j--; }
             v.p_order[j + 1] = ko; v.p_k[j + 1] = kk;
         }
+    }
+
+    RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask) const
+    {
+        ShadowVisit v;
+        shadow_collect(o, ray, self, tmin, tmax, use_tmax, v);
+        if (v.opaque) { mask = clamp01(fmul(0.0f, mask)); return v.hits; }
         for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
         if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
         return v.hits;
+    }
+
+    // The same product as a record for the wavefront shade kernel: up to four partial
+    // factors in iteration order (unused slots 1.0f: x * 1.0f == x), (0,1,1,1) for an opaque
+    // occluder, x < 0 when more than four partial factors were met (the shade kernel then
+    // re-traces this light itself; rare).
+    RT_DEV float4 shadow_factors(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax) const
+    {
+        ShadowVisit v;
+        shadow_collect(o, ray, self, tmin, tmax, use_tmax, v);
+        if (v.opaque) return make_float4(0.0f, 1.0f, 1.0f, 1.0f);
+        if (v.n_partial > 4 || v.overflow_mask != 1.0f) return make_float4(-1.0f, 1.0f, 1.0f, 1.0f);
+        float f[4] = { 1.0f, 1.0f, 1.0f, 1.0f };
+        for (int i = 0; i < 4; i++) if (i < v.n_partial) f[i] = v.p_k[i];
+        return make_float4(f[0], f[1], f[2], f[3]);
     }
 };
 

@@ -2,7 +2,7 @@
 // (generations 0..D forward, D-1..0 backward), and the framebuffer plumbing.
 #include "bvh.cuh"
 #include "host_scene.h"
-#include "wavefront.cuh"
+#include "wavefront_bvh.cuh"
 
 #include <algorithm>
 #include <cstring>
@@ -33,24 +33,6 @@ struct BruteGlobalFactory {
     static RT_DEV BruteAccel make(const SceneView& S, float4* smem) { return make_brute<false>(S, smem); }
     static RT_DEV void flush(const BruteAccel&, Counters*) {}
 };
-struct BvhFactory {
-    static RT_DEV BvhAccel make(const SceneView& S, float4*) { return make_bvh_accel<false>(S); }
-    static RT_DEV void flush(const BvhAccel&, Counters*) {}
-};
-// instrumented variant: per-thread work counters, one warp-reduced atomic at the end of the kernel
-struct BvhCountFactory {
-    static RT_DEV BvhAccelT<true> make(const SceneView& S, float4*) { return make_bvh_accel<true>(S); }
-    static RT_DEV void flush(const BvhAccelT<true>& a, Counters* c)
-    {
-        unsigned long long b = a.cnt_boxes, p = a.cnt_prims;
-        for (int o = 16; o > 0; o >>= 1) {
-            b += __shfl_down_sync(0xffffffffu, b, o);
-            p += __shfl_down_sync(0xffffffffu, p, o);
-        }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(&c->bvh_nodes, b); atomicAdd(&c->prim_tests, p); }
-    }
-};
-
 // scanline-order planes for rt_download_framebuffer: tiles RGBA8 -> rgb24 + flags8
 __global__ void split_planes_kernel(const uchar4* __restrict__ tiles, int n, unsigned char* __restrict__ rgb,
                                     unsigned char* __restrict__ flags)
@@ -98,11 +80,19 @@ void stash_workspace(Workspace&& ws)
     g_ws_cache_valid = true;
 }
 
-static size_t level_bytes(int level, size_t cap)
+static size_t level_bytes(int level, size_t cap, bool bvh, int nl)
 {
     // level 0 has no ray queue (primary rays are generated in place)
-    const size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16;
+    size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16;
+    if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 16;   // hp, hb, node_list, sh (wavefront_bvh.cuh)
     return cap * per_slot + 256;
+}
+
+static int pick_accel(const SceneHost* s, int requested)
+{
+    if (s->nf + s->ns == 0) return RT_ACCEL_BRUTE;
+    if (requested == RT_ACCEL_BRUTE || requested == RT_ACCEL_LBVH) return requested;
+    return (s->nf + s->ns) > 48 ? RT_ACCEL_LBVH : RT_ACCEL_BRUTE;
 }
 
 // Sizes the queues.  demand == nullptr: first guess from the pixel count (or what a
@@ -120,6 +110,7 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
     }
     const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
     const size_t npx = (size_t)tl.n_local_pixels;
+    const bool bvh = pick_accel(s, p.accel) == RT_ACCEL_LBVH;
     if (!ws.counters.reserve(sizeof(Counters)) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
     if (p.instrument && !ws.primary_ids.reserve(npx * sizeof(int))) return RT_E_NOMEM;
     for (int l = 0; l <= p.max_depth; l++) {
@@ -132,15 +123,16 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
             want = std::max<size_t>((size_t)ws.capacity[l], (size_t)(npx * guess[l]) + 1024);
         }
         if (want > 0x7ffffff0u) { set_error("wavefront queue would exceed 2^31 slots"); return RT_E_NOMEM; }
-        if ((size_t)ws.capacity[l] < want || ws.level_mem[l].bytes < level_bytes(l, want)) {
-            if (!ws.level_mem[l].reserve(level_bytes(l, want))) return RT_E_NOMEM;
+        want = std::max<size_t>(want, (size_t)ws.capacity[l]);
+        if ((size_t)ws.capacity[l] < want || ws.level_mem[l].bytes < level_bytes(l, want, bvh, s->nl)) {
+            if (!ws.level_mem[l].reserve(level_bytes(l, want, bvh, s->nl))) return RT_E_NOMEM;
             ws.capacity[l] = (int)want;
         }
     }
     return RT_OK;
 }
 
-static void fill_levels(const SceneHost* s, int max_depth, FrameParams* P)
+static void fill_levels(const SceneHost* s, int max_depth, bool bvh, FrameParams* P)
 {
     const Workspace& ws = s->ws;
     for (int l = 0; l < kMaxLevels; l++) {
@@ -158,14 +150,14 @@ static void fill_levels(const SceneHost* s, int max_depth, FrameParams* P)
         }
         L.nr_a = (float4*)base; base += cap * 16;
         L.nr_b = (float4*)base; base += cap * 16;
-        L.res = (float4*)base;
+        L.res = (float4*)base;  base += cap * 16;
+        if (bvh) {
+            L.hp = (float4*)base; base += cap * 16;
+            L.hb = (float4*)base; base += cap * 16;
+            L.sh = (float4*)base; base += cap * 16 * (size_t)s->nl;
+            L.node_list = (int*)base;
+        }
     }
-}
-
-static int pick_accel(const SceneHost* s, int requested)
-{
-    if (requested == RT_ACCEL_BRUTE || requested == RT_ACCEL_LBVH) return requested;
-    return (s->nf + s->ns) > 48 ? RT_ACCEL_LBVH : RT_ACCEL_BRUTE;
 }
 
 template <class Factory>
@@ -178,19 +170,16 @@ static void launch_level(const FrameParams& P, int level, int grid, size_t smem,
 int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cudaStream_t stream, int* launches)
 {
     const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
-    int accel = pick_accel(s, p.accel);
-    if (accel == RT_ACCEL_LBVH) {
-        if (s->nf + s->ns == 0) accel = RT_ACCEL_BRUTE;
-        else if (!s->bvh_built) {
-            const int rc = build_bvh(s);
-            if (rc != RT_OK) return rc;
-        }
+    const int accel = pick_accel(s, p.accel);
+    if (accel == RT_ACCEL_LBVH && !s->bvh_built) {
+        const int rc = build_bvh(s);
+        if (rc != RT_OK) return rc;
     }
     FrameParams P;
     std::memset(&P, 0, sizeof P);
     P.scene = scene_view(s);
     P.cam = s->cam;
-    fill_levels(s, p.max_depth, &P);
+    fill_levels(s, p.max_depth, accel == RT_ACCEL_LBVH, &P);
     P.counters = s->ws.counters.as<Counters>();
     P.tiles = tiles_out ? tiles_out : s->ws.tiles.as<uchar4>();
     P.primary_ids = p.instrument ? s->ws.primary_ids.as<int>() : nullptr;
@@ -214,11 +203,24 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         const long long work = l == 0 ? tl.n_local_pixels : s->ws.capacity[l];
         int grid = (int)std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * 16);
         if (grid < 1) grid = 1;
-        if (accel == RT_ACCEL_LBVH && p.instrument) launch_level<BvhCountFactory>(P, l, grid, 0, stream);
-        else if (accel == RT_ACCEL_LBVH) launch_level<BvhFactory>(P, l, grid, 0, stream);
-        else if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
-        else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
-        n++;
+        if (accel == RT_ACCEL_LBVH) {
+            // trace: one thread per ray; shadow: one per (node, light); shade: one per node
+            const long long sh_work = work * std::max(1, s->nl);
+            const int sh_grid = (int)std::max<long long>(1, std::min<long long>((sh_work + kBlock - 1) / kBlock, (long long)sms * 16));
+            if (p.instrument) {
+                bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
+                if (s->nl) bvh_shadow_kernel<true><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            } else {
+                bvh_trace_kernel<false><<<grid, kBlock, 0, stream>>>(P, l);
+                if (s->nl) bvh_shadow_kernel<false><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            }
+            bvh_shade_kernel<<<grid, kBlock, 0, stream>>>(P, l);
+            n += s->nl ? 3 : 2;
+        } else {
+            if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
+            else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
+            n++;
+        }
     }
     if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 1], stream));
     for (int l = p.max_depth - 1; l >= 0; l--) {

@@ -96,6 +96,13 @@ struct LevelBuffers {
     float4* nr_a;   // base.rgb (= diffuse*ka + tmp_specular), tw1 = (float)(1.0 - F_t)
     float4* nr_b;   // tw2 = (float)(1.0 - opacity), F_r, as_float(childT), as_float(childR)
     float4* res;    // rgb, status
+    // LBVH pipeline only (wavefront_bvh.cuh): the hit of slot i, the list of slots that hit
+    // something (= the ShadeRay nodes of this generation, in arrival order), and one shadow
+    // record per (node, light), light-major: sh[li * n_nodes + k] for node_list[k]
+    float4* hp;     // hit point.xyz, as_float(object order)
+    float4* hb;     // b, g, t, 0
+    int*    node_list;
+    float4* sh;     // <= 4 partial shadow factors in iteration order; see BvhAccelT::shadow_factors
     int capacity;
 };
 

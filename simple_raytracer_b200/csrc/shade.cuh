@@ -82,10 +82,22 @@ struct Spawn {
     V3 T, R;
 };
 
+// Where the shadow product of one light comes from.  DirectShadow traces the shadow ray
+// in this thread (brute-force path: all lanes walk the same primitive list);
+// RecordedShadow (wavefront_bvh.cuh) reads what the shadow kernel left.
+template <class Accel>
+struct DirectShadow {
+    const Accel& acc;
+    RT_DEV void operator()(int, V3 p, V3 dir, int self, float eps, float tmax, bool use_tmax, float& mask) const
+    {
+        acc.shadow(p, dir, self, eps, tmax, use_tmax, mask);
+    }
+};
+
 // The part of ShadeRay before the recursive calls.  Returns the node's base colour
 // (diffuse*ka + tmp_specular), the child weights, and the rays to spawn.
-template <class Accel>
-RT_DEV Col shade_node(const SceneView& S, const Accel& acc, V3 incidence_ray, int obj, const Surface& sf,
+template <class ShadowSrc>
+RT_DEV Col shade_node(const SceneView& S, const ShadowSrc& shadow, V3 incidence_ray, int obj, const Surface& sf,
                       float n_i, float n_t, int depth_left, float eps,
                       float& tw1, float& tw2, float& fr, Spawn& sp)
 {
@@ -105,12 +117,12 @@ RT_DEV Col shade_node(const SceneView& S, const Accel& acc, V3 incidence_ray, in
         V3 L;
         if (l0.w == 0.0f) {
             L = ld3(S.light[3 * li + 2]);                                        // 887 (hoisted)
-            acc.shadow(sf.p, vneg(ld3(l0)), obj, eps, 0.0f, false, shadow_mask); // 895-912: un-normalised ray
+            shadow(li, sf.p, vneg(ld3(l0)), obj, eps, 0.0f, false, shadow_mask);  // 895-912: un-normalised ray
         } else {
             L = vnorm(vsub(ld3(l0), sf.p));                                      // 921
             const V3 dp = vsub(sf.p, ld3(l0));
             const float dist = fsqrt(vsum3(fmul(dp.x, dp.x), fmul(dp.y, dp.y), fmul(dp.z, dp.z)));   // 922
-            acc.shadow(sf.p, L, obj, eps, dist, true, shadow_mask);              // 928-949
+            shadow(li, sf.p, L, obj, eps, dist, true, shadow_mask);               // 928-949
         }
         const V3 H = vnorm(vadd(L, I));                                          // 952
         const float mdl = max0(vdot(N, L)), mdh = max0(vdot(N, H));

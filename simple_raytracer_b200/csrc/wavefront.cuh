@@ -55,87 +55,94 @@ RT_DEV BruteAccel make_brute(const SceneView& S, float4* smem)
     return a;
 }
 
+// The ray of one queue slot, with the medium state its parent call left.
+struct RayIn {
+    V3 o, ray;
+    float n_i, n_t;        // indices of the PARENT call
+    int inc;               // incidence object of the parent call (order), -1 for primary rays
+    int ns;                // medium stack length
+    bool reflect, exiting;
+    int stack[kMaxStack];
+};
+
+// Level 0: generates the primary ray of local pixel `slot` (main.cpp:720, 728); deeper
+// levels: reads the queue entry.  Returns false for the padding rows of the last tile.
+RT_DEV bool load_ray(const FrameParams& P, int level, unsigned slot, RayIn& r)
+{
+    r.o = mk3(0.f, 0.f, 0.f); r.ray = mk3(0.f, 0.f, 0.f);
+    r.n_i = r.n_t = 0.f; r.inc = -1; r.ns = 0; r.reflect = r.exiting = false;
+    if (level == 0) {
+        const int lrow = slot / P.cam.width, col = slot - lrow * P.cam.width;
+        const int row = global_row(P, lrow);
+        if (row >= P.cam.height) return false;
+        const V3 ul = mk3(P.cam.ul[0], P.cam.ul[1], P.cam.ul[2]);
+        const V3 dh = mk3(P.cam.delta_h[0], P.cam.delta_h[1], P.cam.delta_h[2]);
+        const V3 dv = mk3(P.cam.delta_v[0], P.cam.delta_v[1], P.cam.delta_v[2]);
+        r.o = mk3(P.cam.eye[0], P.cam.eye[1], P.cam.eye[2]);
+        const V3 p = vadd(vadd(ul, vmulf(dh, (float)col)), vmulf(dv, (float)row));   // 720
+        r.ray = vnorm(vsub(p, r.o));                                                // 728
+        return true;
+    }
+    const LevelBuffers& LB = P.level[level];
+    const float4 qo = LB.rq_o[slot], qd = LB.rq_d[slot];
+    const int4 qm = LB.rq_m[slot], qs = LB.rq_s[slot];
+    r.o = mk3(qo.x, qo.y, qo.z); r.n_i = qo.w;
+    r.ray = mk3(qd.x, qd.y, qd.z); r.n_t = qd.w;
+    r.inc = qm.y;
+    r.reflect = (qm.z & kRayKindReflect) != 0;
+    r.exiting = (qm.z & kRayStateExiting) != 0;
+    r.ns = (qm.z >> kRayNStackShift) & 15;
+    r.stack[0] = qm.w; r.stack[1] = qs.x; r.stack[2] = qs.y; r.stack[3] = qs.z; r.stack[4] = qs.w;
+    return true;
+}
+
+// Closest hit of the slot's ray with the rule its kind asks for.
 template <class Accel>
-RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsigned slot, bool active)
+RT_DEV Hit trace_ray(const FrameParams& P, const Accel& acc, int level, const RayIn& r, bool& aborted)
+{
+    aborted = false;
+    if (level == 0) return acc.closest(r.o, r.ray, 0.0f);                            // 729-742: t > 0.0f
+    if (!r.reflect && r.inc < P.scene.nf && r.ns > 0)
+        return acc.closest_face_rule(r.o, r.ray, P.epsilon, r.stack[r.ns - 1], aborted);   // 992-1011
+    return acc.closest(r.o, r.ray, P.epsilon);                                       // 1113-1124
+}
+
+// The record of a slot whose ray found nothing to shade.
+RT_DEV void write_miss(const FrameParams& P, int level, unsigned slot, bool padding, bool aborted)
+{
+    const SceneView& S = P.scene;
+    float4 r;
+    if (padding) r = make_float4(0.f, 0.f, 0.f, kResPrimaryMiss);
+    else if (level == 0) r = make_float4(S.bkg[0], S.bkg[1], S.bkg[2], kResPrimaryMiss);   // 721
+    else if (aborted) r = make_float4(0.f, 0.f, 0.f, kResZeroTerm);                         // SKIP_TRANS
+    else r = make_float4(S.bkg[0], S.bkg[1], S.bkg[2], kResFinal);   // 1087 / 1198: bkg takes the child's place
+    P.level[level].res[slot] = r;
+}
+
+// ShadeRay for the hit `h` of slot `slot` (main.cpp:783-1207 up to the recursive calls),
+// then the spawn of its two child rays into the queue of generation level+1 and the node
+// record the combine pass reads.  Must be called by all 32 lanes of a warp (`hit` false
+// for idle lanes): queue slots are handed out with one atomicAdd per warp.
+template <class ShadowSrc>
+RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int level, unsigned slot, RayIn& r,
+                            const Hit& h, bool hit)
 {
     const SceneView& S = P.scene;
     const LevelBuffers& LB = P.level[level];
-    const Col bkg = mkc(S.bkg[0], S.bkg[1], S.bkg[2]);
-
-    // ---- the ray of this slot -------------------------------------------------
-    V3 o = mk3(0.f, 0.f, 0.f), ray = mk3(0.f, 0.f, 0.f);
-    float n_i = 0.f, n_t = 0.f;
-    int inc = -1, ns = 0;
-    bool reflect = false, exiting = false;
-    int stack[kMaxStack];
-    if (active) {
-        if (level == 0) {
-            const int lrow = slot / P.cam.width, col = slot - lrow * P.cam.width;
-            const int row = global_row(P, lrow);
-            if (row >= P.cam.height) {
-                active = false;                     // padding rows of the last tile
-                LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPrimaryMiss);
-            } else {
-                const V3 ul = mk3(P.cam.ul[0], P.cam.ul[1], P.cam.ul[2]);
-                const V3 dh = mk3(P.cam.delta_h[0], P.cam.delta_h[1], P.cam.delta_h[2]);
-                const V3 dv = mk3(P.cam.delta_v[0], P.cam.delta_v[1], P.cam.delta_v[2]);
-                o = mk3(P.cam.eye[0], P.cam.eye[1], P.cam.eye[2]);
-                const V3 p = vadd(vadd(ul, vmulf(dh, (float)col)), vmulf(dv, (float)row));   // 720
-                ray = vnorm(vsub(p, o));                                                    // 728
-            }
-        } else {
-            const float4 qo = LB.rq_o[slot], qd = LB.rq_d[slot];
-            const int4 qm = LB.rq_m[slot], qs = LB.rq_s[slot];
-            o = mk3(qo.x, qo.y, qo.z); n_i = qo.w;
-            ray = mk3(qd.x, qd.y, qd.z); n_t = qd.w;
-            inc = qm.y;
-            reflect = (qm.z & kRayKindReflect) != 0;
-            exiting = (qm.z & kRayStateExiting) != 0;
-            ns = (qm.z >> kRayNStackShift) & 15;
-            stack[0] = qm.w; stack[1] = qs.x; stack[2] = qs.y; stack[3] = qs.z; stack[4] = qs.w;
-        }
-    }
-
-    // ---- closest hit --------------------------------------------------------------
-    Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
-    bool aborted = false;
-    if (active) {
-        if (level == 0) {
-            h = acc.closest(o, ray, 0.0f);                                       // 729-742: t > 0.0f
-        } else if (!reflect && inc < S.nf && ns > 0) {
-            h = acc.closest_face_rule(o, ray, P.epsilon, stack[ns - 1], aborted);   // 992-1011
-        } else {
-            h = acc.closest(o, ray, P.epsilon);                                  // 1113-1124
-        }
-    }
-    const bool hit = active && !aborted && h.obj >= 0;
-
-    // nodes[level] counts ShadeRay invocations: one atomic per warp
-    {
-        const unsigned hm = __ballot_sync(0xffffffffu, hit);
-        if ((threadIdx.x & 31) == 0 && hm) atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
-    }
-    if (active && level == 0 && P.primary_ids) P.primary_ids[slot] = hit ? S.obj[h.obj].z : 0;
-    if (P.primary_ids) {   // instrumented frame: one texel per shaded hit on a textured object
-        const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[h.obj].y >= 0);
-        if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
-    }
-
-    // ---- shade -----------------------------------------------------------------
     Spawn sp; sp.want_t = sp.want_r = false;
     float tw1 = 0.f, tw2 = 0.f, fr = 0.f, c_ni = 0.f, c_nt = 0.f;
     bool c_exiting = false;
     Col base = mkc(0.f, 0.f, 0.f);
     Surface sf;
     if (hit) {
-        sf = finish_hit(S, o, ray, h);
+        sf = finish_hit(S, r.o, r.ray, h);
         if (level == 0) {                                                        // 746-757
             c_ni = S.bkg_eta; c_nt = material_eta(S, h.obj); c_exiting = false;
-            stack[0] = h.obj; ns = 1;
+            r.stack[0] = h.obj; r.ns = 1;
         } else {
-            medium_update(S, reflect, exiting, inc, h.obj, n_i, n_t, stack, ns, c_ni, c_nt, c_exiting);
+            medium_update(S, r.reflect, r.exiting, r.inc, h.obj, r.n_i, r.n_t, r.stack, r.ns, c_ni, c_nt, c_exiting);
         }
-        base = shade_node(S, acc, ray, h.obj, sf, c_ni, c_nt, P.max_depth - level, P.epsilon, tw1, tw2, fr, sp);
+        base = shade_node(S, shadow, r.ray, h.obj, sf, c_ni, c_nt, P.max_depth - level, P.epsilon, tw1, tw2, fr, sp);
     }
 
     // ---- spawn: warp-aggregated slot allocation in the next generation's queue -----
@@ -152,15 +159,15 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
         }
         basei = __shfl_sync(0xffffffffu, basei, 0);
         const unsigned lt = lanemask_lt();
-        const int flags_common = (c_exiting ? kRayStateExiting : 0) | (ns << kRayNStackShift);
+        const int flags_common = (c_exiting ? kRayStateExiting : 0) | (r.ns << kRayNStackShift);
         if (sp.want_t) {
             const unsigned s = basei + (unsigned)__popc(mt & lt);
             if (s < (unsigned)NB.capacity) {
                 child_t = (int)s;
                 NB.rq_o[s] = make_float4(sf.p.x, sf.p.y, sf.p.z, c_ni);
                 NB.rq_d[s] = make_float4(sp.T.x, sp.T.y, sp.T.z, c_nt);
-                NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common, stack[0]);
-                NB.rq_s[s] = make_int4(stack[1], stack[2], stack[3], stack[4]);
+                NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common, r.stack[0]);
+                NB.rq_s[s] = make_int4(r.stack[1], r.stack[2], r.stack[3], r.stack[4]);
             } else {
                 P.counters->overflow = 1;
             }
@@ -171,32 +178,50 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
                 child_r = (int)s;
                 NB.rq_o[s] = make_float4(sf.p.x, sf.p.y, sf.p.z, c_ni);
                 NB.rq_d[s] = make_float4(sp.R.x, sp.R.y, sp.R.z, c_nt);
-                NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common | kRayKindReflect, stack[0]);
-                NB.rq_s[s] = make_int4(stack[1], stack[2], stack[3], stack[4]);
+                NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common | kRayKindReflect, r.stack[0]);
+                NB.rq_s[s] = make_int4(r.stack[1], r.stack[2], r.stack[3], r.stack[4]);
             } else {
                 P.counters->overflow = 1;
             }
         }
     }
 
-    // ---- the slot's record ------------------------------------------------------------
-    if (!active) return;
-    if (hit) {
-        if (child_t < 0 && child_r < 0 && !sp.want_t && !sp.want_r) {
-            // leaf node: both child terms are exactly (0,0,0); x + 0 leaves a clamped x unchanged
-            LB.res[slot] = make_float4(base.r, base.g, base.b, kResFinal);
-        } else {
-            LB.nr_a[slot] = make_float4(base.r, base.g, base.b, tw1);
-            LB.nr_b[slot] = make_float4(tw2, fr, __int_as_float(child_t), __int_as_float(child_r));
-            LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
-        }
-    } else if (level == 0) {
-        LB.res[slot] = make_float4(bkg.r, bkg.g, bkg.b, kResPrimaryMiss);       // 721
-    } else if (aborted) {
-        LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResZeroTerm);                // SKIP_TRANS
+    if (!hit) return;
+    if (child_t < 0 && child_r < 0 && !sp.want_t && !sp.want_r) {
+        // leaf node: both child terms are exactly (0,0,0); x + 0 leaves a clamped x unchanged
+        LB.res[slot] = make_float4(base.r, base.g, base.b, kResFinal);
     } else {
-        LB.res[slot] = make_float4(bkg.r, bkg.g, bkg.b, kResFinal);             // 1087 / 1198: bkg takes the child's place
+        LB.nr_a[slot] = make_float4(base.r, base.g, base.b, tw1);
+        LB.nr_b[slot] = make_float4(tw2, fr, __int_as_float(child_t), __int_as_float(child_r));
+        LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
     }
+}
+
+// Fused path (brute force): trace + shadow rays + shade + spawn of one slot in one thread.
+template <class Accel>
+RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsigned slot, bool in_range)
+{
+    const SceneView& S = P.scene;
+    RayIn r;
+    const bool active = in_range && load_ray(P, level, slot, r);
+    Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
+    bool aborted = false;
+    if (active) h = trace_ray(P, acc, level, r, aborted);
+    const bool hit = active && !aborted && h.obj >= 0;
+
+    // nodes[level] counts ShadeRay invocations: one atomic per warp
+    {
+        const unsigned hm = __ballot_sync(0xffffffffu, hit);
+        if ((threadIdx.x & 31) == 0 && hm) atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
+    }
+    if (active && level == 0 && P.primary_ids) P.primary_ids[slot] = hit ? S.obj[h.obj].z : 0;
+    if (P.primary_ids) {   // instrumented frame: one texel per shaded hit on a textured object
+        const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[h.obj].y >= 0);
+        if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
+    }
+    const DirectShadow<Accel> direct{ acc };
+    shade_and_spawn(P, direct, level, slot, r, h, hit);
+    if (in_range && !hit) write_miss(P, level, slot, !active, aborted);
 }
 
 // AccelFactory builds the per-block accelerator view (stages shared memory if any).
