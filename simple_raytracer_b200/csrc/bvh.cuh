@@ -114,6 +114,98 @@ struct BvhAccelT {
         }
     }
 
+    // Persistent form of walk(): a warp keeps pulling jobs (rays) from a global counter and
+    // replaces lanes whose ray has finished, so a warp does not idle behind its longest ray
+    // (Aila & Laine's "persistent while-while" with dynamic fetch).  All 32 lanes must call it.
+    //   job.begin(j, o, ray, tmin, tmax) -> false when job j needs no tree walk
+    //   job.visit(words, tcur)           -> new culling bound, < 0 to stop this ray
+    //   job.retire(bool finishing)       -> called by ALL lanes whenever some lane finishes
+    //                                       (warp collectives allowed inside)
+    static constexpr int kRefillLanes = 8;    // refill when at least this many lanes are idle
+    template <class Job>
+    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job) const
+    {
+        constexpr int kDone = 0x7fffffff;
+        constexpr unsigned kFull = 0xffffffffu;
+        const unsigned lane = threadIdx.x & 31u;
+        const unsigned lt = (1u << lane) - 1u;
+        int stack[kBvhStack];
+        int sp = 0, node = kDone, leaf = 0;
+        bool alive = false, pool_empty = false;
+        V3 o = mk3(0.f, 0.f, 0.f), inv = mk3(0.f, 0.f, 0.f);
+        float tmin = 0.f, tmax = 0.f;
+        for (;;) {
+            const unsigned dead = __ballot_sync(kFull, !alive);
+            if (!pool_empty && (__popc(dead) >= kRefillLanes || dead == kFull)) {
+                unsigned base = 0;
+                if (lane == 0) base = atomicAdd(counter, (unsigned)__popc(dead));
+                base = __shfl_sync(kFull, base, 0);
+                if (base + (unsigned)__popc(dead) >= total) pool_empty = true;
+                if (!alive) {
+                    const unsigned j = base + (unsigned)__popc(dead & lt);
+                    if (j < total) {
+                        V3 ray;
+                        const bool need_walk = job.begin(j, o, ray, tmin, tmax);
+                        alive = true; sp = 0; leaf = 0;
+                        node = (need_walk && n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
+                        inv = mk3(1.0f / ray.x, 1.0f / ray.y, 1.0f / ray.z);
+                    }
+                }
+            }
+            if (!__any_sync(kFull, alive)) break;
+            // inner nodes, until every live lane holds a leaf (or has nothing left)
+            for (;;) {
+                if (alive && (unsigned)node < (unsigned)kDone) {
+                    const float4* w = nodes + (size_t)node * 4;
+                    const float4 w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+                    const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
+                    float tl, tr;
+                    const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, o, inv, tmin, tmax, tl);
+                    const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, o, inv, tmin, tmax, tr);
+                    if (kCount) cnt_boxes += 2;
+                    if (hl && hr) {
+                        const bool left_first = tl <= tr;
+                        if (sp < kBvhStack) stack[sp++] = left_first ? rc : lc;
+                        node = left_first ? lc : rc;
+                    } else if (hl) {
+                        node = lc;
+                    } else if (hr) {
+                        node = rc;
+                    } else {
+                        node = sp ? stack[--sp] : kDone;
+                    }
+                    if (node < 0 && leaf == 0) {
+                        leaf = node;
+                        node = sp ? stack[--sp] : kDone;
+                    }
+                }
+                if (!__any_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) break;
+            }
+            // pending leaves
+            while (__any_sync(kFull, alive && leaf < 0)) {
+                if (alive && leaf < 0) {
+                    const int code = ~leaf;
+                    const int first = code >> 3, count = (code & 7) + 1;
+                    leaf = 0;
+                    for (int k = 0; k < count; k++) {
+                        if (kCount) cnt_prims++;
+                        tmax = job.visit(prims + (size_t)(first + k) * kTriWords, tmax);
+                        if (tmax < 0.0f) { node = kDone; sp = 0; break; }
+                    }
+                    if (node < 0) {
+                        leaf = node;
+                        node = sp ? stack[--sp] : kDone;
+                    }
+                }
+            }
+            const bool fin = alive && node == kDone && leaf == 0;
+            if (__any_sync(kFull, fin)) {
+                job.retire(fin);
+                if (fin) alive = false;
+            }
+        }
+    }
+
     struct ClosestVisit {
         V3 o, ray; float tmin; Hit best; int best_order; bool skip_spheres;
         RT_DEV float operator()(const float4* w, float tmax)
@@ -246,7 +338,7 @@ struct BvhAccelT {
 
     // Walks the tree (and, for rays no box bounds, the sphere list) and leaves the partial
     // factors sorted by iteration order in v.
-    RT_DEV void shadow_collect(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, ShadowVisit& v) const
+    RT_DEV void shadow_begin(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, ShadowVisit& v) const
     {
         v.o = o; v.ray = ray; v.tmin = tmin; v.tmax_hit = tmax; v.use_tmax = use_tmax; v.self = self;
         v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false; v.count_all = count_all;
@@ -255,7 +347,15 @@ struct BvhAccelT {
         // rho^2 <= r^2 + (s^2 - 1) p^2 — unbounded for s > 1, so no box bounds it:
         // such rays test every sphere directly and use the tree for the triangles only.
         v.skip_spheres = spheres_unbounded(ray);
-        walk(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
+    }
+
+    // after the walk: spheres of rays no box bounds, then the sort by iteration order
+    RT_DEV void shadow_end(ShadowVisit& v) const
+    {
+        const V3 o = v.o, ray = v.ray;
+        const float tmin = v.tmin, tmax = v.tmax_hit;
+        const bool use_tmax = v.use_tmax;
+        const int self = v.self;
         if (v.skip_spheres && !(v.opaque && !count_all)) {
             for (int i = 0; i < ns; i++) {
                 if (nf + i == self) continue;
@@ -277,6 +377,22 @@ struct BvhAccelT {
         }
     }
 
+    RT_DEV void shadow_collect(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, ShadowVisit& v) const
+    {
+        shadow_begin(o, ray, self, tmin, tmax, use_tmax, v);
+        walk(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
+        shadow_end(v);
+    }
+
+    static RT_DEV float4 shadow_record(const ShadowVisit& v)
+    {
+        if (v.opaque) return make_float4(0.0f, 1.0f, 1.0f, 1.0f);
+        if (v.n_partial > 4 || v.overflow_mask != 1.0f) return make_float4(-1.0f, 1.0f, 1.0f, 1.0f);
+        float f[4] = { 1.0f, 1.0f, 1.0f, 1.0f };
+        for (int i = 0; i < 4; i++) if (i < v.n_partial) f[i] = v.p_k[i];
+        return make_float4(f[0], f[1], f[2], f[3]);
+    }
+
     RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask) const
     {
         ShadowVisit v;
@@ -295,11 +411,7 @@ struct BvhAccelT {
     {
         ShadowVisit v;
         shadow_collect(o, ray, self, tmin, tmax, use_tmax, v);
-        if (v.opaque) return make_float4(0.0f, 1.0f, 1.0f, 1.0f);
-        if (v.n_partial > 4 || v.overflow_mask != 1.0f) return make_float4(-1.0f, 1.0f, 1.0f, 1.0f);
-        float f[4] = { 1.0f, 1.0f, 1.0f, 1.0f };
-        for (int i = 0; i < 4; i++) if (i < v.n_partial) f[i] = v.p_k[i];
-        return make_float4(f[0], f[1], f[2], f[3]);
+        return shadow_record(v);
     }
 };
 

@@ -117,6 +117,8 @@ struct Counters {
     unsigned int rays_reflect[kMaxLevels];
     unsigned int overflow;                // some queue was too small: frame must be redone
     unsigned int pad;
+    unsigned int fetch_trace[kMaxLevels];   // LBVH pipeline: next job of the persistent trace / shadow kernels
+    unsigned int fetch_shadow[kMaxLevels];
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only
 };
 

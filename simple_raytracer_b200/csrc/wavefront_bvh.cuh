@@ -34,71 +34,184 @@ RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c)
     if ((threadIdx.x & 31) == 0) { atomicAdd(&c->bvh_nodes, b); atomicAdd(&c->prim_tests, p); }
 }
 
+// One closest-hit job of the persistent trace kernel: plain closest hit (primary, reflection,
+// sphere-incidence transmission) or the face-incidence rule (main.cpp:992-1011).
 template <bool kCount>
-__global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
-{
-    const SceneView& S = P.scene;
-    const LevelBuffers& LB = P.level[level];
-    const auto acc = make_bvh_accel<kCount>(S);
-    const unsigned count = level == 0 ? (unsigned)P.n_local_pixels : min(P.counters->rays[level], (unsigned)LB.capacity);
-    const unsigned stride = gridDim.x * blockDim.x;
-    const unsigned rounded = (count + 31u) & ~31u;
-    for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < rounded; slot += stride) {
-        const bool in_range = slot < count;
+struct TraceJob {
+    const FrameParams& P;
+    const BvhAccelT<kCount>& acc;
+    int level;
+    // per ray
+    unsigned slot;
+    V3 o, ray;
+    Hit best; int best_order;
+    int back;                 // >= 0: face rule with B = back (best = B's own hit, best.t = tB)
+    bool skip_spheres, aborted, padding;
+
+    RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
+    {
+        slot = j;
         RayIn r;
-        const bool active = in_range && load_ray(P, level, slot, r);
-        Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
-        bool aborted = false;
-        if (active) h = trace_ray(P, acc, level, r, aborted);
-        const bool hit = active && !aborted && h.obj >= 0;
+        padding = !load_ray(P, level, slot, r);
+        o = r.o; ray = r.ray; wo = o; wray = ray;
+        tmin = level == 0 ? 0.0f : P.epsilon;                                   // 736 / 997 / 1117
+        tmax = 3.402823466e+38f;
+        best.t = 3.402823466e+38f; best.obj = -1; best.b = best.g = 0.0f; best_order = 0x7fffffff;
+        aborted = false; back = -1;
+        skip_spheres = acc.spheres_unbounded(ray);
+        if (padding) return false;
+        if (level > 0 && !r.reflect && r.inc < P.scene.nf && r.ns > 0) {
+            // B's own hit by a direct test of its file-order record; the walk only looks for a reason to abort
+            back = r.stack[r.ns - 1];
+            if (back < acc.nf) {
+                const float4* w = acc.tri + (size_t)back * kTriWords;
+                float t, b, g;
+                if (tri_distance(w[0], o, ray, t) && t > tmin && tri_inside(w[1], w[2], w[3], w[4], o, ray, t, b, g)) { best.t = t; best.obj = back; best.b = b; best.g = g; }
+            } else {
+                float tf, tn;
+                const int n = sphere_roots(acc.sph[(size_t)(back - acc.nf) * kSphWords], o, ray, tf, tn);
+                if (n >= 1 && tf > tmin && tf < best.t) { best.t = tf; best.obj = back; }
+                if (n == 2 && tn > tmin && tn < best.t) { best.t = tn; best.obj = back; }
+            }
+        }
+        return true;
+    }
+
+    RT_DEV float visit(const float4* w, float tmax)
+    {
+        const float tmin = level == 0 ? 0.0f : P.epsilon;
+        const float4 w4 = w[4];
+        const int order = __float_as_int(w4.z);
+        const bool is_tri = __float_as_int(w4.w) == 0;
+        if (back >= 0) {
+            // abort <=> a hit of another object with t > eps and (order < order(B) or t < tB)
+            if (order == back) return tmax;
+            const float limit = order < back ? 3.402823466e+38f : best.t;
+            bool bad = false;
+            if (is_tri) {
+                float t, b, g;
+                if (tri_distance(w[0], o, ray, t) && t > tmin && t < limit) bad = tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g);
+            } else {
+                float tf, tn;
+                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                bad = (n >= 1 && tf > tmin && tf < limit) || (n == 2 && tn > tmin && tn < limit);
+            }
+            if (bad) { aborted = true; return -1.0f; }
+            return tmax;
+        }
+        if (is_tri) {
+            float t;
+            if (tri_distance(w[0], o, ray, t) && t > tmin && (t < best.t || (t == best.t && order < best_order))) {
+                float b, g;
+                if (tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g)) { best.t = t; best.obj = order; best.b = b; best.g = g; best_order = order; }
+            }
+        } else if (!skip_spheres) {
+            sphere_candidate(w[0], order, tmin);
+        }
+        return fminf(tmax, best.t);
+    }
+
+    RT_DEV void sphere_candidate(const float4& w0, int order, float tmin)
+    {
+        float tf, tn;
+        const int n = sphere_roots(w0, o, ray, tf, tn);
+        if (n >= 1 && tf > tmin && (tf < best.t || (tf == best.t && order < best_order))) { best.t = tf; best.obj = order; best_order = order; }
+        if (n == 2 && tn > tmin && (tn < best.t || (tn == best.t && order < best_order))) { best.t = tn; best.obj = order; best_order = order; }
+    }
+
+    RT_DEV void retire(bool fin)
+    {
+        const SceneView& S = P.scene;
+        const LevelBuffers& LB = P.level[level];
+        if (fin && !padding && back < 0 && skip_spheres) {
+            const float tmin = level == 0 ? 0.0f : P.epsilon;
+            for (int i = 0; i < acc.ns; i++) sphere_candidate(acc.sph[(size_t)i * kSphWords], acc.nf + i, tmin);
+        }
+        const bool hit = fin && !padding && !aborted && best.obj >= 0;
         // append to the node list: one atomic per warp
         const unsigned hm = __ballot_sync(0xffffffffu, hit);
         unsigned base = 0;
         if ((threadIdx.x & 31) == 0 && hm) base = atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
         base = __shfl_sync(0xffffffffu, base, 0);
         if (hit) {
-            const V3 p = vadd(r.o, vmulf(r.ray, h.t));                           // 1245 / 1303, same as finish_hit
-            LB.hp[slot] = make_float4(p.x, p.y, p.z, __int_as_float(h.obj));
-            LB.hb[slot] = make_float4(h.b, h.g, h.t, 0.0f);
+            const V3 p = vadd(o, vmulf(ray, best.t));                            // 1245 / 1303, same as finish_hit
+            LB.hp[slot] = make_float4(p.x, p.y, p.z, __int_as_float(best.obj));
+            LB.hb[slot] = make_float4(best.b, best.g, best.t, 0.0f);
             LB.node_list[base + __popc(hm & lanemask_lt())] = (int)slot;
-        } else if (in_range) {
-            write_miss(P, level, slot, !active, aborted);
+        } else if (fin) {
+            write_miss(P, level, slot, padding, aborted);
         }
-        if (active && level == 0 && P.primary_ids) P.primary_ids[slot] = hit ? S.obj[h.obj].z : 0;
-        if (P.primary_ids) {   // instrumented frame: one texel per shaded hit on a textured object
-            const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[h.obj].y >= 0);
+        if (P.primary_ids) {   // instrumented frame
+            if (fin && !padding && level == 0) P.primary_ids[slot] = hit ? S.obj[best.obj].z : 0;
+            const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[best.obj].y >= 0);
             if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
         }
     }
+};
+
+template <bool kCount>
+__global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
+{
+    const auto acc = make_bvh_accel<kCount>(P.scene);
+    const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
+                                      : min(P.counters->rays[level], (unsigned)P.level[level].capacity);
+    TraceJob<kCount> job{ P, acc, level };
+    acc.persistent_walk(count, &P.counters->fetch_trace[level], job);
     flush_bvh_counters(acc, P.counters);
 }
 
+// One shadow ray (main.cpp:896 / 928) of the persistent shadow kernel: job j = light-major
+// index li * n_nodes + k for node_list[k].
 template <bool kCount>
-__global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
-{
-    const SceneView& S = P.scene;
-    const LevelBuffers& LB = P.level[level];
-    const auto acc = make_bvh_accel<kCount>(S);
-    const unsigned n_nodes = P.counters->nodes[level];
-    const unsigned long long total = (unsigned long long)n_nodes * (unsigned)S.nl;
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        const unsigned li = (unsigned)(i / n_nodes), k = (unsigned)(i - (unsigned long long)li * n_nodes);
+struct ShadowJob {
+    const FrameParams& P;
+    const BvhAccelT<kCount>& acc;
+    int level;
+    unsigned n_nodes;
+    unsigned idx;
+    typename BvhAccelT<kCount>::ShadowVisit v;
+
+    RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
+    {
+        const SceneView& S = P.scene;
+        const LevelBuffers& LB = P.level[level];
+        idx = j;
+        const unsigned li = j / n_nodes, k = j - li * n_nodes;
         const float4 hp = LB.hp[LB.node_list[k]];
         const V3 p = mk3(hp.x, hp.y, hp.z);
         const int self = __float_as_int(hp.w);
         const float4 l0 = S.light[3 * li];
-        float4 rec;
+        tmin = P.epsilon;
         if (l0.w == 0.0f) {
-            rec = acc.shadow_factors(p, vneg(ld3(l0)), self, P.epsilon, 0.0f, false);       // 895-912: un-normalised ray
+            wray = vneg(ld3(l0));                                                // 895: un-normalised ray
+            tmax = 3.402823466e+38f;
+            acc.shadow_begin(p, wray, self, tmin, 0.0f, false, v);
         } else {
-            const V3 L = vnorm(vsub(ld3(l0), p));                                           // 921
+            wray = vnorm(vsub(ld3(l0), p));                                      // 921
             const V3 dp = vsub(p, ld3(l0));
-            const float dist = fsqrt(vsum3(fmul(dp.x, dp.x), fmul(dp.y, dp.y), fmul(dp.z, dp.z)));   // 922
-            rec = acc.shadow_factors(p, L, self, P.epsilon, dist, true);                    // 928-949
+            tmax = fsqrt(vsum3(fmul(dp.x, dp.x), fmul(dp.y, dp.y), fmul(dp.z, dp.z)));   // 922
+            acc.shadow_begin(p, wray, self, tmin, tmax, true, v);
         }
-        LB.sh[i] = rec;
+        wo = p;
+        return true;
     }
+    RT_DEV float visit(const float4* w, float tmax) { return v(w, tmax); }
+    RT_DEV void retire(bool fin)
+    {
+        if (!fin) return;
+        acc.shadow_end(v);
+        P.level[level].sh[idx] = BvhAccelT<kCount>::shadow_record(v);
+    }
+};
+
+template <bool kCount>
+__global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
+{
+    const auto acc = make_bvh_accel<kCount>(P.scene);
+    const unsigned n_nodes = P.counters->nodes[level];
+    const unsigned long long total = (unsigned long long)n_nodes * (unsigned)P.scene.nl;
+    ShadowJob<kCount> job{ P, acc, level, n_nodes };
+    acc.persistent_walk((unsigned)min(total, 0xffffffffull), &P.counters->fetch_shadow[level], job);
     flush_bvh_counters(acc, P.counters);
 }
 
