@@ -146,6 +146,11 @@ typedef struct RtStats {
     double   level_ms[8];        /* params.profile: device time of the trace+shade+spawn
                                     kernel of each generation                   */
     double   combine_ms;         /* params.profile: all bottom-up combine passes  */
+    uint64_t shadow_rays_walked; /* instrument, LBVH: shadow rays actually traced.  rays_shadow counts
+                                    the reference's TraceRay calls (one per light per node); the
+                                    LBVH pipeline skips the walks whose result cannot matter because
+                                    the carried shadow_mask is already exactly 0.  Equal
+                                    to rays_shadow on the brute-force path. */
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

@@ -242,6 +242,7 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->rays_primary = rows * (uint64_t)s->width;
         stats->rays_shadow = stats->nodes_total * (uint64_t)s->nl;   // one shadow TraceRay per light per node (896 / 928)
         stats->bvh_nodes_visited = c.bvh_nodes; stats->prim_tests = c.prim_tests; stats->texel_fetches = c.texels;
+        stats->shadow_rays_walked = (s->last_accel == RT_ACCEL_LBVH && p.instrument) ? c.shadow_walks : stats->rays_shadow;
         stats->accel_used = s->last_accel; stats->kernel_launches = launches; stats->queue_regrows = regrows;
         if (s->prof_levels > 0) {
             float t = 0.0f;

@@ -8,7 +8,7 @@
 // arithmetic accepts lies inside:
 //   triangle: the accepted point o + ray*t passes the float barycentric test, i.e.
 //             lies within rounding error of the triangle: pad = 1e-4 * extent +
-//             4e-6 * (largest coordinate magnitude in play);
+//             8e-6 * (largest coordinate magnitude in play; this also covers the FFMA slab test);
 //   sphere  : B*B - 4*C >= 0 in mixed precision with a ray that is unit only up to
 //             rounding accepts rho^2 <= r^2 + c*eps*D^2 (D = distance from the ray
 //             origin to the centre): r_eff^2 = r^2 + 1.2e-5 * Dmax^2
@@ -18,9 +18,18 @@
 
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace rt {
+
+int tuning_int(const char* name, int dflt, int lo, int hi)
+{
+    const char* v = std::getenv(name);
+    if (!v || !*v) return dflt;
+    const int x = std::atoi(v);
+    return x < lo ? lo : (x > hi ? hi : x);
+}
 
 namespace {
 
@@ -56,7 +65,7 @@ __global__ void prim_bounds_kernel(const float4* __restrict__ tri, const float4*
             hi[c] = fmaxf(p[0][c], fmaxf(p[1][c], p[2][c]));
             ext = fmaxf(ext, hi[c] - lo[c]);
         }
-        const float pad = 1.0e-4f * ext + 4.0e-6f * bb.scale;
+        const float pad = 1.0e-4f * ext + 8.0e-6f * bb.scale;
         for (int c = 0; c < 3; c++) { lo[c] -= pad; hi[c] += pad; }
     } else {
         const float4 s = sph[(size_t)(i - nf) * kSphWords];
@@ -67,7 +76,7 @@ __global__ void prim_bounds_kernel(const float4* __restrict__ tri, const float4*
             d2 += d * d;
         }
         const float r = fabsf(s.w);
-        const float reff = sqrtf(r * r + 1.2e-5f * d2) * 1.00001f + 4.0e-6f * bb.scale;
+        const float reff = sqrtf(r * r + 1.2e-5f * d2) * 1.00001f + 8.0e-6f * bb.scale;
         for (int c = 0; c < 3; c++) { lo[c] = c3[c] - reff; hi[c] = c3[c] + reff; }
     }
     // NaN / inf primitives (degenerate input) never hit anything: give them an empty box
@@ -260,7 +269,7 @@ __global__ void refit_kernel(int n, const unsigned* __restrict__ sorted_vals, co
 __global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ prim_lo,
                                   const float4* __restrict__ prim_hi, const int2* __restrict__ children,
                                   const int2* __restrict__ range, const float4* __restrict__ node_lo,
-                                  const float4* __restrict__ node_hi, float4* __restrict__ nodes)
+                                  const float4* __restrict__ node_hi, float4* __restrict__ nodes, int leaf_max)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
@@ -278,7 +287,7 @@ __global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_val
             lo[c] = node_lo[c2[c]]; hi[c] = node_hi[c2[c]];
             const int2 r = range[c2[c]];
             const int size = r.y - r.x + 1;
-            if (size <= kLeafMax) { code[c] = ~((r.x << 3) | (size - 1)); count[c] = size; }
+            if (size <= leaf_max) { code[c] = ~((r.x << 3) | (size - 1)); count[c] = size; }
             else { code[c] = c2[c]; count[c] = 0; }
         }
     }
@@ -345,6 +354,7 @@ int build_bvh(SceneHost* s)
     }
     bb.scale = scale;
 
+    const int leaf_max = tuning_int("RT_LEAF_MAX", kLeafDefault, 1, 8);
     const int n_internal = n > kLeafMax ? n - 1 : 1;
     const int nblocks = (n + kSortTile - 1) / kSortTile;
     DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals;
@@ -373,7 +383,7 @@ int build_bvh(SceneHost* s)
         refit_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(), par_i.as<int>(),
                                       par_l.as<int>(), node_lo.as<float4>(), node_hi.as<float4>(), arrivals.as<unsigned>());
         emit_nodes_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
-                                           range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(), s->bvh_nodes.as<float4>());
+                                           range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(), s->bvh_nodes.as<float4>(), leaf_max);
     } else {
         emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), s->bvh_nodes.as<float4>());
     }

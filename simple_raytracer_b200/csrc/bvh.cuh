@@ -24,7 +24,9 @@
 namespace rt {
 
 constexpr int kBvhStack = 64;
-constexpr int kLeafMax = 4;
+constexpr int kLeafMax = 4;       // scenes of <= kLeafMax primitives are a single leaf
+constexpr int kLeafDefault = 1;   // primitives per leaf otherwise: with one triangle per leaf the parent's box test
+                                  // rejects most of the 80-byte exact tests (measured: 32 -> 6.4 tests per ray)
 
 template <bool kCount>
 struct BvhAccelT {
@@ -41,18 +43,32 @@ struct BvhAccelT {
 
     RT_DEV static bool finite3(V3 v) { return isfinite(v.x) && isfinite(v.y) && isfinite(v.z); }
 
-    // conservative slab test; returns entry distance in tn
-    RT_DEV static bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, V3 o, V3 inv,
+    // Conservative slab test; returns the entry distance in tn.  t = lo * inv + (-o * inv) is one
+    // FFMA per plane; against (lo - o) * inv it is off by at most ~2 ulp of the coordinate
+    // magnitude when mapped back to a position, which the build-time padding of every box
+    // (bvh.cu: >= 8e-6 * scene scale) covers with a wide margin.  inv comes from safe_inv3().
+    RT_DEV static bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, V3 inv, V3 oinv,
                             float tmin, float tmax, float& tn)
     {
-        const float x0 = (lox - o.x) * inv.x, x1 = (hix - o.x) * inv.x;
-        const float y0 = (loy - o.y) * inv.y, y1 = (hiy - o.y) * inv.y;
-        const float z0 = (loz - o.z) * inv.z, z1 = (hiz - o.z) * inv.z;
-        // fminf / fmaxf drop NaN (0 * inf when the origin sits on a slab plane): conservative
+        const float x0 = fmaf(lox, inv.x, oinv.x), x1 = fmaf(hix, inv.x, oinv.x);
+        const float y0 = fmaf(loy, inv.y, oinv.y), y1 = fmaf(hiy, inv.y, oinv.y);
+        const float z0 = fmaf(loz, inv.z, oinv.z), z1 = fmaf(hiz, inv.z, oinv.z);
         tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
         const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
-        return tn <= tf * 1.0000005f;
+        return tn <= tf;
     }
+
+    RT_DEV static float4 ldn(const float4* p) { return __ldg(p); }
+
+    // 1 / d for the slab test.  A zero (or denormal-small) component would make lo * inv + oinv
+    // mix infinities of both signs (inf - inf = NaN on the far plane, which fminf/fmaxf then
+    // drop on the WRONG side), so it is replaced by +-1e-18: over any distance that matters
+    // the ray moves < 1e-15 along that axis, far inside the box padding.
+    RT_DEV static float safe_inv(float d)
+    {
+        return 1.0f / (fabsf(d) > 1.0e-18f ? d : copysignf(1.0e-18f, d));
+    }
+    RT_DEV static V3 safe_inv3(V3 d) { return mk3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)); }
 
     // Generic traversal, "while-while" with one postponed leaf per lane (Aila & Laine 2009):
     // lanes keep descending inner nodes until every lane of the warp holds a leaf, then all
@@ -65,7 +81,8 @@ struct BvhAccelT {
     RT_DEV void walk(V3 o, V3 ray, float tmin, float tmax, Visit& visit) const
     {
         if (n_nodes == 0 || !finite3(ray) || !finite3(o)) return;   // NaN/inf rays hit nothing in the reference either
-        const V3 inv = mk3(1.0f / ray.x, 1.0f / ray.y, 1.0f / ray.z);
+        const V3 inv = safe_inv3(ray);
+        const V3 oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
         constexpr int kDone = 0x7fffffff;
         int stack[kBvhStack];
         int sp = 0;
@@ -74,11 +91,11 @@ struct BvhAccelT {
         while (node != kDone) {
             while ((unsigned)node < (unsigned)kDone) {
                 const float4* w = nodes + (size_t)node * 4;
-                const float4 w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+                const float4 w0 = ldn(w), w1 = ldn(w + 1), w2 = ldn(w + 2), w3 = ldn(w + 3);
                 const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
                 float tl, tr;
-                const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, o, inv, tmin, tmax, tl);
-                const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, o, inv, tmin, tmax, tr);
+                const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, inv, oinv, tmin, tmax, tl);
+                const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, inv, oinv, tmin, tmax, tr);
                 if (kCount) cnt_boxes += 2;
                 if (hl && hr) {
                     const bool left_first = tl <= tr;              // near child first, far child on the stack
@@ -121,9 +138,9 @@ struct BvhAccelT {
     //   job.visit(words, tcur)           -> new culling bound, < 0 to stop this ray
     //   job.retire(bool finishing)       -> called by ALL lanes whenever some lane finishes
     //                                       (warp collectives allowed inside)
-    static constexpr int kRefillLanes = 8;    // refill when at least this many lanes are idle
+    //   job.next(o, ray, tmin, tmax)     -> true when the finished lane's job has another ray
     template <class Job>
-    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job) const
+    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes) const
     {
         constexpr int kDone = 0x7fffffff;
         constexpr unsigned kFull = 0xffffffffu;
@@ -132,11 +149,11 @@ struct BvhAccelT {
         int stack[kBvhStack];
         int sp = 0, node = kDone, leaf = 0;
         bool alive = false, pool_empty = false;
-        V3 o = mk3(0.f, 0.f, 0.f), inv = mk3(0.f, 0.f, 0.f);
+        V3 inv = mk3(0.f, 0.f, 0.f), oinv = mk3(0.f, 0.f, 0.f);
         float tmin = 0.f, tmax = 0.f;
         for (;;) {
             const unsigned dead = __ballot_sync(kFull, !alive);
-            if (!pool_empty && (__popc(dead) >= kRefillLanes || dead == kFull)) {
+            if (!pool_empty && (__popc(dead) >= refill_lanes || dead == kFull)) {
                 unsigned base = 0;
                 if (lane == 0) base = atomicAdd(counter, (unsigned)__popc(dead));
                 base = __shfl_sync(kFull, base, 0);
@@ -144,11 +161,12 @@ struct BvhAccelT {
                 if (!alive) {
                     const unsigned j = base + (unsigned)__popc(dead & lt);
                     if (j < total) {
-                        V3 ray;
+                        V3 o, ray;
                         const bool need_walk = job.begin(j, o, ray, tmin, tmax);
                         alive = true; sp = 0; leaf = 0;
                         node = (need_walk && n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
-                        inv = mk3(1.0f / ray.x, 1.0f / ray.y, 1.0f / ray.z);
+                        inv = safe_inv3(ray);
+                        oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
                     }
                 }
             }
@@ -157,11 +175,11 @@ struct BvhAccelT {
             for (;;) {
                 if (alive && (unsigned)node < (unsigned)kDone) {
                     const float4* w = nodes + (size_t)node * 4;
-                    const float4 w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3];
+                    const float4 w0 = ldn(w), w1 = ldn(w + 1), w2 = ldn(w + 2), w3 = ldn(w + 3);
                     const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
                     float tl, tr;
-                    const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, o, inv, tmin, tmax, tl);
-                    const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, o, inv, tmin, tmax, tr);
+                    const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, inv, oinv, tmin, tmax, tl);
+                    const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, inv, oinv, tmin, tmax, tr);
                     if (kCount) cnt_boxes += 2;
                     if (hl && hr) {
                         const bool left_first = tl <= tr;
@@ -201,7 +219,18 @@ struct BvhAccelT {
             const bool fin = alive && node == kDone && leaf == 0;
             if (__any_sync(kFull, fin)) {
                 job.retire(fin);
-                if (fin) alive = false;
+                if (fin) {
+                    // a job may be a chain of rays (the lights of one node): go on in this lane
+                    V3 o, ray;
+                    if (job.next(o, ray, tmin, tmax)) {
+                        sp = 0; leaf = 0;
+                        node = (n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
+                        inv = safe_inv3(ray);
+                        oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
+                    } else {
+                        alive = false;
+                    }
+                }
             }
         }
     }

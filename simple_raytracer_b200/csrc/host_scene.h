@@ -98,6 +98,7 @@ SceneView scene_view(const SceneHost* s);
 
 // bvh.cu
 int build_bvh(SceneHost* s);
+int tuning_int(const char* name, int dflt, int lo, int hi);   // internal tuning knobs (environment)
 
 // render.cu
 struct TileLayout {

@@ -186,6 +186,9 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     P.max_depth = p.max_depth; P.epsilon = p.epsilon;
     P.rank = p.rank; P.world = p.world_size; P.tile_rows = p.tile_rows;
     P.n_local_rows = tl.n_local_rows; P.n_local_pixels = tl.n_local_pixels;
+    static const int refill = tuning_int("RT_REFILL_LANES", 8, 1, 32);
+    static const int grid_mult = tuning_int("RT_GRID_MULT", 16, 1, 64);
+    P.refill_lanes = refill;
 
     RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters), stream));
     const int sms = sm_count(s->device);
@@ -201,12 +204,12 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
         // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
         const long long work = l == 0 ? tl.n_local_pixels : s->ws.capacity[l];
-        int grid = (int)std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * 16);
+        int grid = (int)std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * grid_mult);
         if (grid < 1) grid = 1;
         if (accel == RT_ACCEL_LBVH) {
             // trace: one thread per ray; shadow: one per (node, light); shade: one per node
             const long long sh_work = work * std::max(1, s->nl);
-            const int sh_grid = (int)std::max<long long>(1, std::min<long long>((sh_work + kBlock - 1) / kBlock, (long long)sms * 16));
+            const int sh_grid = (int)std::max<long long>(1, std::min<long long>((sh_work + kBlock - 1) / kBlock, (long long)sms * grid_mult));
             if (p.instrument) {
                 bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
                 if (s->nl) bvh_shadow_kernel<true><<<sh_grid, kBlock, 0, stream>>>(P, l);

@@ -120,6 +120,7 @@ struct Counters {
     unsigned int fetch_trace[kMaxLevels];   // LBVH pipeline: next job of the persistent trace / shadow kernels
     unsigned int fetch_shadow[kMaxLevels];
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only
+    unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
 };
 
 struct FrameParams {
@@ -134,6 +135,7 @@ struct FrameParams {
     int rank, world, tile_rows;
     int n_local_rows;     // rows of the tile buffer (padded to whole tiles)
     int n_local_pixels;   // n_local_rows * width
+    int refill_lanes;     // persistent kernels: fetch new rays when this many lanes of a warp are idle
 };
 
 }  // namespace rt

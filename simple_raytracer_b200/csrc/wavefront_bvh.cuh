@@ -111,6 +111,8 @@ struct TraceJob {
         return fminf(tmax, best.t);
     }
 
+    RT_DEV bool next(V3&, V3&, float&, float&) { return false; }
+
     RT_DEV void sphere_candidate(const float4& w0, int order, float tmin)
     {
         float tf, tn;
@@ -156,31 +158,33 @@ __global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant
     const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
                                       : min(P.counters->rays[level], (unsigned)P.level[level].capacity);
     TraceJob<kCount> job{ P, acc, level };
-    acc.persistent_walk(count, &P.counters->fetch_trace[level], job);
+    acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes);
     flush_bvh_counters(acc, P.counters);
 }
 
-// One shadow ray (main.cpp:896 / 928) of the persistent shadow kernel: job j = light-major
-// index li * n_nodes + k for node_list[k].
+// The shadow rays (main.cpp:896 / 928) of ONE node as a chain: job k = node_list[k], the lane
+// walks light 0, 1, ... in turn.  The reference never resets shadow_mask between lights
+// (main.cpp:788) and every factor lies in [0,1], so once the running product
+// is exactly 0 it stays 0 whatever the later lights meet: the chain stops there and the
+// remaining records are never read (RecordedShadow stops at the same point).  In a dense
+// scene that removes most shadow walks without changing a bit of the result.
 template <bool kCount>
 struct ShadowJob {
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
     unsigned n_nodes;
-    unsigned idx;
+    // per node
+    unsigned k;
+    int li;
+    V3 p; int self;
+    float mask;
+    unsigned long long walks = 0;      // instrumented variant: shadow rays actually walked by this thread
     typename BvhAccelT<kCount>::ShadowVisit v;
 
-    RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
+    RT_DEV void setup(V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        const SceneView& S = P.scene;
-        const LevelBuffers& LB = P.level[level];
-        idx = j;
-        const unsigned li = j / n_nodes, k = j - li * n_nodes;
-        const float4 hp = LB.hp[LB.node_list[k]];
-        const V3 p = mk3(hp.x, hp.y, hp.z);
-        const int self = __float_as_int(hp.w);
-        const float4 l0 = S.light[3 * li];
+        const float4 l0 = P.scene.light[3 * li];
         tmin = P.epsilon;
         if (l0.w == 0.0f) {
             wray = vneg(ld3(l0));                                                // 895: un-normalised ray
@@ -193,14 +197,40 @@ struct ShadowJob {
             acc.shadow_begin(p, wray, self, tmin, tmax, true, v);
         }
         wo = p;
+    }
+    RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
+    {
+        k = j; li = 0; mask = 1.0f;                                              // 788
+        const float4 hp = P.level[level].hp[P.level[level].node_list[k]];
+        p = mk3(hp.x, hp.y, hp.z);
+        self = __float_as_int(hp.w);
+        setup(wo, wray, tmin, tmax);
         return true;
     }
     RT_DEV float visit(const float4* w, float tmax) { return v(w, tmax); }
     RT_DEV void retire(bool fin)
     {
         if (!fin) return;
+        if (kCount) walks++;
         acc.shadow_end(v);
-        P.level[level].sh[idx] = BvhAccelT<kCount>::shadow_record(v);
+        const float4 f = BvhAccelT<kCount>::shadow_record(v);
+        P.level[level].sh[(size_t)li * n_nodes + k] = f;
+        if (f.x < 0.0f) {
+            // more than four partial occluders: the shade kernel re-traces this light; what its
+            // product is only matters here for the early-out, so carry on conservatively
+            if (mask == 0.0f) return;
+            mask = 1.0f;
+        } else {
+            mask = clamp01(fmul(f.x, mask)); mask = clamp01(fmul(f.y, mask));
+            mask = clamp01(fmul(f.z, mask)); mask = clamp01(fmul(f.w, mask));
+        }
+    }
+    RT_DEV bool next(V3& wo, V3& wray, float& tmin, float& tmax)
+    {
+        if (mask == 0.0f || li + 1 >= P.scene.nl) return false;
+        li++;
+        setup(wo, wray, tmin, tmax);
+        return true;
     }
 };
 
@@ -209,10 +239,14 @@ __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constan
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned n_nodes = P.counters->nodes[level];
-    const unsigned long long total = (unsigned long long)n_nodes * (unsigned)P.scene.nl;
     ShadowJob<kCount> job{ P, acc, level, n_nodes };
-    acc.persistent_walk((unsigned)min(total, 0xffffffffull), &P.counters->fetch_shadow[level], job);
+    acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes);
     flush_bvh_counters(acc, P.counters);
+    if (kCount) {
+        unsigned long long w = job.walks;
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_down_sync(0xffffffffu, w, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&P.counters->shadow_walks, w);
+    }
 }
 
 // Shadow source of the shade kernel: the records of bvh_shadow_kernel.
@@ -222,6 +256,7 @@ struct RecordedShadow {
     const BvhAccel& acc;        // only for the rare "more than four partial occluders" re-trace
     RT_DEV void operator()(int li, V3 p, V3 dir, int self, float eps, float tmax, bool use_tmax, float& mask) const
     {
+        if (mask == 0.0f) return;     // 0 * f == 0 for every later factor: those records were never written
         const float4 f = rec[(size_t)li * n_nodes];
         if (f.x < 0.0f) { acc.shadow(p, dir, self, eps, tmax, use_tmax, mask); return; }
         mask = clamp01(fmul(f.x, mask)); mask = clamp01(fmul(f.y, mask));                   // 909 / 946, in iteration order

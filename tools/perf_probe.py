@@ -37,7 +37,7 @@ def main():
         if not a.no_instrument:
             si = ds.render(max_depth=a.depth, instrument=True)
             out.update(boxes_per_ray=round(si.bvh_nodes_visited / rays, 1), prims_per_ray=round(si.prim_tests / rays, 2),
-                       texels=int(si.texel_fetches), instr_ms=round(si.render_ms, 2))
+                       texels=int(si.texel_fetches), shadow_walked=int(si.shadow_rays_walked), shadow_ref=int(si.rays_shadow), instr_ms=round(si.render_ms, 2))
         print(json.dumps(out), flush=True)
 
 if __name__ == "__main__":
