@@ -146,11 +146,20 @@ struct BvhAccelT {
         constexpr unsigned kFull = 0xffffffffu;
         const unsigned lane = threadIdx.x & 31u;
         const unsigned lt = (1u << lane) - 1u;
+        // (Carrying the entry distance on the stack to drop far children unfetched was tried:
+        // 2 % fewer box tests, but the doubled local-memory stack traffic cost more.)
         int stack[kBvhStack];
         int sp = 0, node = kDone, leaf = 0;
         bool alive = false, pool_empty = false;
         V3 inv = mk3(0.f, 0.f, 0.f), oinv = mk3(0.f, 0.f, 0.f);
         float tmin = 0.f, tmax = 0.f;
+        auto pop = [&]() { return sp ? stack[--sp] : kDone; };
+        auto start = [&](bool need_walk, V3 o, V3 ray) {
+            sp = 0; leaf = 0;
+            node = (need_walk && n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
+            inv = safe_inv3(ray);
+            oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
+        };
         for (;;) {
             const unsigned dead = __ballot_sync(kFull, !alive);
             if (!pool_empty && (__popc(dead) >= refill_lanes || dead == kFull)) {
@@ -163,10 +172,8 @@ struct BvhAccelT {
                     if (j < total) {
                         V3 o, ray;
                         const bool need_walk = job.begin(j, o, ray, tmin, tmax);
-                        alive = true; sp = 0; leaf = 0;
-                        node = (need_walk && n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
-                        inv = safe_inv3(ray);
-                        oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
+                        alive = true;
+                        start(need_walk, o, ray);
                     }
                 }
             }
@@ -190,11 +197,11 @@ struct BvhAccelT {
                     } else if (hr) {
                         node = rc;
                     } else {
-                        node = sp ? stack[--sp] : kDone;
+                        node = pop();
                     }
                     if (node < 0 && leaf == 0) {
                         leaf = node;
-                        node = sp ? stack[--sp] : kDone;
+                        node = pop();
                     }
                 }
                 if (!__any_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) break;
@@ -212,7 +219,7 @@ struct BvhAccelT {
                     }
                     if (node < 0) {
                         leaf = node;
-                        node = sp ? stack[--sp] : kDone;
+                        node = pop();
                     }
                 }
             }
@@ -222,14 +229,8 @@ struct BvhAccelT {
                 if (fin) {
                     // a job may be a chain of rays (the lights of one node): go on in this lane
                     V3 o, ray;
-                    if (job.next(o, ray, tmin, tmax)) {
-                        sp = 0; leaf = 0;
-                        node = (n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
-                        inv = safe_inv3(ray);
-                        oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
-                    } else {
-                        alive = false;
-                    }
+                    if (job.next(o, ray, tmin, tmax)) start(true, o, ray);
+                    else alive = false;
                 }
             }
         }

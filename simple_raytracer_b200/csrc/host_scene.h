@@ -67,6 +67,7 @@ struct SceneHost {
     float bkg[3] = { 0, 0, 0 };
     float bkg_eta = 0;
     float scene_lo[3] = { 0, 0, 0 }, scene_hi[3] = { 0, 0, 0 };   // bounds of all primitives
+    bool zero_mask_exit = false;        // all material / light values finite, exponents tame (shade.cuh)
     bool nonunit_directional = false;   // some directional light has |dir| != 1
 
     DevBuf tri, sph, face_attr, obj, mat, light, tex_desc, texels;

@@ -68,6 +68,7 @@ struct SceneView {
     const float4* bvh_sph;    // spheres in leaf order
     float bkg[3];
     float bkg_eta;
+    int zero_mask_exit;       // shade_node may leave the light loop once shadow_mask == 0 (see there)
 };
 
 struct CameraView {          // main.cpp:677-710, computed on the host in rt_upload_scene / rt_set_camera

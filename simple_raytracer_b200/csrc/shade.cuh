@@ -113,6 +113,11 @@ RT_DEV Col shade_node(const SceneView& S, const ShadowSrc& shadow, V3 incidence_
     Col tmp_specular = mkc(0.0f, 0.0f, 0.0f);
     float shadow_mask = 1.0f;                                                    // 788, never reset (A5.1)
     for (int li = 0; li < S.nl; li++) {                                          // 878
+        // Once the carried mask is exactly 0 it stays 0 (every factor is in [0,1]) and each
+        // remaining light adds light.color * 0 * (finite) = +0 to a clamped sum: nothing
+        // left to do.  Only taken when upload found all material / light values finite and
+        // the exponents small enough that powf cannot overflow (S.zero_mask_exit).
+        if (S.zero_mask_exit && shadow_mask == 0.0f) break;
         const float4 l0 = S.light[3 * li], l1 = S.light[3 * li + 1];
         V3 L;
         if (l0.w == 0.0f) {

@@ -193,6 +193,16 @@ int build_scene(const RtSceneDesc* d, SceneHost* s)
             if (std::fabs(s2 - 1.0) > 1.0e-5) s->nonunit_directional = true;
         }
     }
+    bool tame = true;
+    for (int i = 0; i < d->n_materials; i++) {
+        const RtMaterial& m = d->materials[i];
+        const float v[12] = { m.od[0], m.od[1], m.od[2], m.os[0], m.os[1], m.os[2], m.ka, m.kd, m.ks, m.n, m.opacity, m.eta };
+        for (float x : v) tame = tame && std::isfinite(x);
+        tame = tame && std::fabs(m.n) <= 1.0e6f;
+    }
+    for (int i = 0; i < d->n_lights; i++)
+        for (int c = 0; c < 3; c++) tame = tame && std::isfinite(d->lights[i].rgb[c]) && std::isfinite(d->lights[i].xyz[c]);
+    s->zero_mask_exit = tame;
     make_camera(d->eye, d->viewdir, d->updir, d->hfov_deg, d->width, d->height, &s->cam);
 
     cudaStream_t st = s->stream;
@@ -281,6 +291,7 @@ SceneView scene_view(const SceneHost* s)
     v.bvh_tri = s->bvh_tri.as<float4>(); v.bvh_sph = s->bvh_sph.as<float4>();
     for (int k = 0; k < 3; k++) v.bkg[k] = s->bkg[k];
     v.bkg_eta = s->bkg_eta;
+    v.zero_mask_exit = s->zero_mask_exit ? 1 : 0;
     return v;
 }
 
