@@ -151,6 +151,10 @@ typedef struct RtStats {
                                     LBVH pipeline skips the walks whose result cannot matter because
                                     the carried shadow_mask is already exactly 0.  Equal
                                     to rays_shadow on the brute-force path. */
+    /* LBVH pipeline detail.  params.profile: device time per generation of the three kernels;
+       params.instrument: the part of bvh_nodes_visited / prim_tests done by the shadow kernels. */
+    double   trace_ms[8], shadow_ms[8], shade_ms[8];
+    uint64_t shadow_boxes_tested, shadow_prim_tests;
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

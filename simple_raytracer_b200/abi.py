@@ -75,7 +75,9 @@ class RtStats(C.Structure):
                 ("rays_reflect", C.c_uint64), ("bvh_nodes_visited", C.c_uint64), ("prim_tests", C.c_uint64),
                 ("texel_fetches", C.c_uint64), ("accel_used", C.c_int32), ("kernel_launches", C.c_int32),
                 ("queue_regrows", C.c_int32), ("reserved", C.c_int32),
-                ("level_ms", C.c_double * 8), ("combine_ms", C.c_double), ("shadow_rays_walked", C.c_uint64)]
+                ("level_ms", C.c_double * 8), ("combine_ms", C.c_double), ("shadow_rays_walked", C.c_uint64),
+                ("trace_ms", C.c_double * 8), ("shadow_ms", C.c_double * 8), ("shade_ms", C.c_double * 8),
+                ("shadow_boxes_tested", C.c_uint64), ("shadow_prim_tests", C.c_uint64)]
 
     def as_dict(self) -> dict:
         d = {}

@@ -148,6 +148,9 @@ void rt_free_scene(RtScene* scene)
     if (s->ev1) cudaEventDestroy(s->ev1);
     for (int k = 0; k < kMaxLevels + 2; k++)
         if (s->prof_ev[k]) cudaEventDestroy(s->prof_ev[k]);
+    for (int k = 0; k < kMaxLevels; k++)
+        for (int j = 0; j < 2; j++)
+            if (s->prof_mid[k][j]) cudaEventDestroy(s->prof_mid[k][j]);
     if (s->h_counters) cudaFreeHost(s->h_counters);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete scene;
@@ -242,6 +245,7 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->rays_primary = rows * (uint64_t)s->width;
         stats->rays_shadow = stats->nodes_total * (uint64_t)s->nl;   // one shadow TraceRay per light per node (896 / 928)
         stats->bvh_nodes_visited = c.bvh_nodes; stats->prim_tests = c.prim_tests; stats->texel_fetches = c.texels;
+        stats->shadow_boxes_tested = c.shadow_boxes; stats->shadow_prim_tests = c.shadow_prims;
         stats->shadow_rays_walked = (s->last_accel == RT_ACCEL_LBVH && p.instrument) ? c.shadow_walks : stats->rays_shadow;
         stats->accel_used = s->last_accel; stats->kernel_launches = launches; stats->queue_regrows = regrows;
         if (s->prof_levels > 0) {
@@ -249,6 +253,11 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
             for (int l = 0; l < s->prof_levels; l++) {
                 RT_CUDA(cudaEventElapsedTime(&t, s->prof_ev[l], s->prof_ev[l + 1]));
                 stats->level_ms[l] = t;
+                if (s->prof_split) {
+                    RT_CUDA(cudaEventElapsedTime(&t, s->prof_ev[l], s->prof_mid[l][0]));      stats->trace_ms[l] = t;
+                    RT_CUDA(cudaEventElapsedTime(&t, s->prof_mid[l][0], s->prof_mid[l][1])); stats->shadow_ms[l] = t;
+                    RT_CUDA(cudaEventElapsedTime(&t, s->prof_mid[l][1], s->prof_ev[l + 1])); stats->shade_ms[l] = t;
+                }
             }
             RT_CUDA(cudaEventElapsedTime(&t, s->prof_ev[s->prof_levels], s->prof_ev[s->prof_levels + 1]));
             stats->combine_ms = t;

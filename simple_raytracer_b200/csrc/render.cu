@@ -199,7 +199,11 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     if (p.profile) {
         for (int k = 0; k < kMaxLevels + 2; k++)
             if (!s->prof_ev[k]) RT_CUDA(cudaEventCreate(&s->prof_ev[k]));
+        for (int k = 0; k < kMaxLevels; k++)
+            for (int j = 0; j < 2; j++)
+                if (!s->prof_mid[k][j]) RT_CUDA(cudaEventCreate(&s->prof_mid[k][j]));
     }
+    s->prof_split = p.profile && accel == RT_ACCEL_LBVH;
     for (int l = 0; l <= p.max_depth; l++) {
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
         // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
@@ -210,13 +214,12 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             // trace: one thread per ray; shadow: one per (node, light); shade: one per node
             const long long sh_work = work * std::max(1, s->nl);
             const int sh_grid = (int)std::max<long long>(1, std::min<long long>((sh_work + kBlock - 1) / kBlock, (long long)sms * grid_mult));
-            if (p.instrument) {
-                bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
-                if (s->nl) bvh_shadow_kernel<true><<<sh_grid, kBlock, 0, stream>>>(P, l);
-            } else {
-                bvh_trace_kernel<false><<<grid, kBlock, 0, stream>>>(P, l);
-                if (s->nl) bvh_shadow_kernel<false><<<sh_grid, kBlock, 0, stream>>>(P, l);
-            }
+            if (p.instrument) bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
+            else bvh_trace_kernel<false><<<grid, kBlock, 0, stream>>>(P, l);
+            if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
+            if (s->nl && p.instrument) bvh_shadow_kernel<true><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            else if (s->nl) bvh_shadow_kernel<false><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
             bvh_shade_kernel<<<grid, kBlock, 0, stream>>>(P, l);
             n += s->nl ? 3 : 2;
         } else {

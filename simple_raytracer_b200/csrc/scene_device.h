@@ -120,7 +120,8 @@ struct Counters {
     unsigned int pad;
     unsigned int fetch_trace[kMaxLevels];   // LBVH pipeline: next job of the persistent trace / shadow kernels
     unsigned int fetch_shadow[kMaxLevels];
-    unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only
+    unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
+    unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
 };
 

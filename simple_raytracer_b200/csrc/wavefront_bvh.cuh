@@ -23,7 +23,7 @@
 namespace rt {
 
 template <bool kCount>
-RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c)
+RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool shadow = false)
 {
     if (!kCount) return;
     unsigned long long b = a.cnt_boxes, p = a.cnt_prims;
@@ -31,7 +31,10 @@ RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c)
         b += __shfl_down_sync(0xffffffffu, b, o);
         p += __shfl_down_sync(0xffffffffu, p, o);
     }
-    if ((threadIdx.x & 31) == 0) { atomicAdd(&c->bvh_nodes, b); atomicAdd(&c->prim_tests, p); }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&c->bvh_nodes, b); atomicAdd(&c->prim_tests, p);
+        if (shadow) { atomicAdd(&c->shadow_boxes, b); atomicAdd(&c->shadow_prims, p); }
+    }
 }
 
 // One closest-hit job of the persistent trace kernel: plain closest hit (primary, reflection,
@@ -241,7 +244,7 @@ __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constan
     const unsigned n_nodes = P.counters->nodes[level];
     ShadowJob<kCount> job{ P, acc, level, n_nodes };
     acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes);
-    flush_bvh_counters(acc, P.counters);
+    flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
         unsigned long long w = job.walks;
         for (int o = 16; o > 0; o >>= 1) w += __shfl_down_sync(0xffffffffu, w, o);
