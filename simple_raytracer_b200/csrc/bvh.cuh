@@ -24,6 +24,8 @@
 namespace rt {
 
 constexpr int kBvhStack = 64;
+constexpr int kSmemStack = 24;    // shared-memory part of the persistent walk's stack (entries per thread)
+constexpr int kWalkBlock = 128;   // block size of the persistent walk kernels (= kBlock)
 constexpr int kLeafMax = 4;       // scenes of <= kLeafMax primitives are a single leaf
 constexpr int kLeafDefault = 1;   // primitives per leaf otherwise: with one triangle per leaf the parent's box test
                                   // rejects most of the 80-byte exact tests (measured: 32 -> 6.4 tests per ray)
@@ -144,19 +146,40 @@ struct BvhAccelT {
     {
         constexpr int kDone = 0x7fffffff;
         constexpr unsigned kFull = 0xffffffffu;
+        // loop invariants in registers (the accelerator object itself may sit in local memory)
+        const float4* __restrict__ const nd = nodes;
+        const float4* __restrict__ const pr = prims;
+        const int root_ = root;
+        const bool have_tree = n_nodes != 0;
         const unsigned lane = threadIdx.x & 31u;
         const unsigned lt = (1u << lane) - 1u;
+        // Traversal stack: the first kSmemStack entries live in shared memory, laid out
+        // [entry][thread] so that a warp's pushes and pops never conflict whatever the lanes'
+        // depths are (a local-memory stack costs one L1 wavefront per distinct depth, and L1 is
+        // what binds this loop); deeper entries overflow into local memory.
         // (Carrying the entry distance on the stack to drop far children unfetched was tried:
-        // 2 % fewer box tests, but the doubled local-memory stack traffic cost more.)
+        // 2 % fewer box tests, but the doubled stack traffic cost more.)
+        __shared__ int s_stack[kSmemStack][kWalkBlock];
         int stack[kBvhStack];
+        const int tid = threadIdx.x;
         int sp = 0, node = kDone, leaf = 0;
         bool alive = false, pool_empty = false;
         V3 inv = mk3(0.f, 0.f, 0.f), oinv = mk3(0.f, 0.f, 0.f);
         float tmin = 0.f, tmax = 0.f;
-        auto pop = [&]() { return sp ? stack[--sp] : kDone; };
+        auto pop = [&]() {
+            if (sp == 0) return kDone;
+            --sp;
+            return sp < kSmemStack ? s_stack[sp][tid] : stack[sp - kSmemStack];
+        };
+        auto push = [&](int v) {
+            if (sp < kSmemStack) s_stack[sp][tid] = v;
+            else if (sp < kSmemStack + kBvhStack) stack[sp - kSmemStack] = v;
+            else return;
+            sp++;
+        };
         auto start = [&](bool need_walk, V3 o, V3 ray) {
             sp = 0; leaf = 0;
-            node = (need_walk && n_nodes != 0 && finite3(ray) && finite3(o)) ? root : kDone;
+            node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
             inv = safe_inv3(ray);
             oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
         };
@@ -181,7 +204,7 @@ struct BvhAccelT {
             // inner nodes, until every live lane holds a leaf (or has nothing left)
             for (;;) {
                 if (alive && (unsigned)node < (unsigned)kDone) {
-                    const float4* w = nodes + (size_t)node * 4;
+                    const float4* w = nd + (size_t)node * 4;
                     const float4 w0 = ldn(w), w1 = ldn(w + 1), w2 = ldn(w + 2), w3 = ldn(w + 3);
                     const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
                     float tl, tr;
@@ -190,7 +213,7 @@ struct BvhAccelT {
                     if (kCount) cnt_boxes += 2;
                     if (hl && hr) {
                         const bool left_first = tl <= tr;
-                        if (sp < kBvhStack) stack[sp++] = left_first ? rc : lc;
+                        push(left_first ? rc : lc);
                         node = left_first ? lc : rc;
                     } else if (hl) {
                         node = lc;
@@ -214,7 +237,7 @@ struct BvhAccelT {
                     leaf = 0;
                     for (int k = 0; k < count; k++) {
                         if (kCount) cnt_prims++;
-                        tmax = job.visit(prims + (size_t)(first + k) * kTriWords, tmax);
+                        tmax = job.visit(pr + (size_t)(first + k) * kTriWords, tmax);
                         if (tmax < 0.0f) { node = kDone; sp = 0; break; }
                     }
                     if (node < 0) {

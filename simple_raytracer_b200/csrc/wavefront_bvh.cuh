@@ -22,6 +22,8 @@
 
 namespace rt {
 
+static_assert(kWalkBlock == kBlock, "the shared-memory stack is laid out for kBlock threads");
+
 template <bool kCount>
 RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool shadow = false)
 {
