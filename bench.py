@@ -258,6 +258,8 @@ def run_ours(args) -> dict:
     assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
     torch.cuda.set_device(local)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's banner out of stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -398,7 +400,10 @@ def run_ours(args) -> dict:
            "config": {"workload": args.workload, "width": W, "height": H, "triangles": len(scene.faces),
                       "spheres": len(scene.spheres), "lights": len(scene.lights), "max_depth": 4,
                       "accel": "lbvh" if accel_used == abi.RT_ACCEL_LBVH else "brute",
-                      "rays_per_frame": rays_frame, "sharding": f"interleaved tiles of {TILE_ROWS} rows, "
+                      "rays_per_frame": rays_frame,
+                      "rays_traced": (work["detail"].get("closest_hit_rays", 0) + work["detail"].get("shadow_rays_walked", 0))
+                      if world == 1 and "closest_hit_rays" in work["detail"] else None,
+                      "sharding": f"interleaved tiles of {TILE_ROWS} rows, "
                       f"{'NCCL allgather of RGBA8 tiles + ' if world > 1 else ''}device de-interleave",
                       "l2": "flushed between timed iterations (252 MiB memset, untimed)"},
            "clocks": clocks, "gpu_launches": (launches_per_frame + 1) * args.steps, "roofline": roof}

@@ -16,26 +16,30 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--depth", type=int, default=4)
     ap.add_argument("--no-instrument", action="store_true")
+    ap.add_argument("--world", type=int, default=1)
+    ap.add_argument("--rank", type=int, default=0)
+    ap.add_argument("--tile-rows", type=int, default=10)
     a = ap.parse_args()
     sc = scenegen.stress_scene(a.tris, a.spheres, a.w, a.h)
     t0 = time.time()
     with DeviceScene(sc) as ds:
         up = time.time() - t0
         t0 = time.time()
-        st = ds.render(max_depth=a.depth)
+        kw = dict(max_depth=a.depth, world_size=a.world, rank=a.rank, tile_rows=a.tile_rows)
+        st = ds.render(**kw)
         first = time.time() - t0
         rays = st.rays_primary + st.rays_shadow + st.rays_transmit + st.rays_reflect
         best = None
         for _ in range(a.reps):
-            s = ds.render(max_depth=a.depth, profile=True)
+            s = ds.render(profile=True, **kw)
             if best is None or s.render_ms < best.render_ms:
                 best = s
         out = dict(upload_s=round(up, 3), first_render_s=round(first, 3), ms=round(best.render_ms, 3), rays=int(rays),
                    mrays_s=round(rays / best.render_ms / 1e3, 1), nodes=list(best.nodes_per_level)[:a.depth + 1],
-                   level_ms=[round(x, 3) for x in list(best.level_ms)[:a.depth + 1]], combine_ms=round(best.combine_ms, 3),
+                   level_ms=[round(x, 3) for x in list(best.level_ms)[:a.depth + 1]], combine_ms=round(best.combine_ms, 3), trace_ms=[round(x, 3) for x in list(best.trace_ms)[:a.depth + 1]], shadow_ms=[round(x, 3) for x in list(best.shadow_ms)[:a.depth + 1]], shade_ms=[round(x, 3) for x in list(best.shade_ms)[:a.depth + 1]],
                    launches=best.kernel_launches)
         if not a.no_instrument:
-            si = ds.render(max_depth=a.depth, instrument=True)
+            si = ds.render(instrument=True, **kw)
             out.update(boxes_per_ray=round(si.bvh_nodes_visited / rays, 1), prims_per_ray=round(si.prim_tests / rays, 2),
                        texels=int(si.texel_fetches), shadow_walked=int(si.shadow_rays_walked), shadow_ref=int(si.rays_shadow), instr_ms=round(si.render_ms, 2))
         print(json.dumps(out), flush=True)
