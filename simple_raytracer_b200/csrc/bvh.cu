@@ -265,53 +265,129 @@ __global__ void refit_kernel(int n, const unsigned* __restrict__ sorted_vals, co
     }
 }
 
-// traversal nodes: both child boxes + child codes; subtrees of <= kLeafMax primitives collapse into a leaf
-__global__ void emit_nodes_kernel(int n, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ prim_lo,
-                                  const float4* __restrict__ prim_hi, const int2* __restrict__ children,
-                                  const int2* __restrict__ range, const float4* __restrict__ node_lo,
-                                  const float4* __restrict__ node_hi, float4* __restrict__ nodes, int leaf_max)
+// ---- 4-wide quantised traversal nodes (layout: bvh.cuh) ---------------------------------
+// depth of every binary inner node (root = 0): nodes of even depth become 4-wide nodes, nodes
+// of odd depth are absorbed by their parent
+__global__ void depth_kernel(int n, const int* __restrict__ parent_internal, unsigned char* __restrict__ odd)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
-    const int2 ch = children[i];
-    const int c2[2] = { ch.x, ch.y };
-    float4 lo[2], hi[2];
-    int code[2], count[2];
-    for (int c = 0; c < 2; c++) {
-        if (c2[c] < 0) {
-            const int slot = ~c2[c];
-            const unsigned p = sorted_vals[slot];
-            lo[c] = prim_lo[p]; hi[c] = prim_hi[p];
-            code[c] = ~(slot << 3); count[c] = 1;
-        } else {
-            lo[c] = node_lo[c2[c]]; hi[c] = node_hi[c2[c]];
-            const int2 r = range[c2[c]];
-            const int size = r.y - r.x + 1;
-            if (size <= leaf_max) { code[c] = ~((r.x << 3) | (size - 1)); count[c] = size; }
-            else { code[c] = c2[c]; count[c] = 0; }
-        }
-    }
-    float4* w = nodes + (size_t)i * 4;
-    w[0] = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
-    w[1] = make_float4(hi[0].y, hi[0].z, lo[1].x, lo[1].y);
-    w[2] = make_float4(lo[1].z, hi[1].x, hi[1].y, hi[1].z);
-    w[3] = make_float4(__int_as_float(code[0]), __int_as_float(code[1]), 0.0f, 0.0f);
+    int d = 0;
+    for (int p = parent_internal[i]; p >= 0; p = parent_internal[p]) d++;
+    odd[i] = (unsigned char)(d & 1);
 }
 
-// scenes of <= kLeafMax primitives: one node; the left child is the leaf holding all of them,
-// the right child is a leaf holding the DUMMY record at slot n (a triangle with a zero normal:
-// `dem == 0` rejects it for every ray, main.cpp:1297).  An inverted box would not do: the
-// min/max slab test reads it as unbounded and, marked as an inner node, it would loop for ever.
+// Writes one node from up to four (box, code) entries.  Per axis: quantum q = 2^e with e the
+// smallest exponent that spans the node box in 250 steps (but never below 64 ulp of the
+// coordinates, so that fp32 rounding in the decode stays far below one quantum); origin =
+// node.lo - 2q; child lo -> floor(..) - 1, child hi -> ceil(..) + 1: one quantum of slack on
+// both sides of every plane, which absorbs the <= 1/2 quantum rounding of the decode constant.
+__device__ void write_node4(float4* out, int n_e, const float4* lo, const float4* hi, const int* code, int dummy_code)
+{
+    float nlo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, nhi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    for (int k = 0; k < n_e; k++) {
+        const float l[3] = { lo[k].x, lo[k].y, lo[k].z }, h[3] = { hi[k].x, hi[k].y, hi[k].z };
+        for (int c = 0; c < 3; c++) { nlo[c] = fminf(nlo[c], l[c]); nhi[c] = fmaxf(nhi[c], h[c]); }
+    }
+    float origin[3], q[3];
+    unsigned eb[3];
+    for (int c = 0; c < 3; c++) {
+        float ext = nhi[c] - nlo[c];
+        if (!(ext >= 0.0f) || !isfinite(ext)) ext = 0.0f;
+        int e = -120;
+        if (ext > 0.0f) { int k; frexpf(ext / 250.0f, &k); e = k; }          // ext / 250 < 2^k
+        const float maxabs = fmaxf(fabsf(nlo[c]), fabsf(nhi[c]));
+        if (maxabs > 0.0f && isfinite(maxabs)) e = max(e, ilogbf(maxabs) - 17);   // >= 64 ulp
+        e = min(max(e, -120), 120);
+        q[c] = ldexpf(1.0f, e);
+        eb[c] = (unsigned)(e + 127);
+        origin[c] = nlo[c] - 2.0f * q[c];
+    }
+    unsigned bytes[4][2];
+    int codes[4];
+    for (int k = 0; k < 4; k++) {
+        if (k < n_e) {
+            const float l[3] = { lo[k].x, lo[k].y, lo[k].z }, h[3] = { hi[k].x, hi[k].y, hi[k].z };
+            unsigned ql[3], qh[3];
+            for (int c = 0; c < 3; c++) {
+                const float fl = floorf((l[c] - origin[c]) / q[c]) - 1.0f;
+                const float fh = ceilf((h[c] - origin[c]) / q[c]) + 1.0f;
+                // NaN / inf (degenerate primitives carry an inverted infinite box) clamp to the range ends
+                ql[c] = (unsigned)fminf(fmaxf(fl, 0.0f), 255.0f);
+                qh[c] = (unsigned)fminf(fmaxf(fh, 0.0f), 255.0f);
+            }
+            bytes[k][0] = ql[0] | (qh[0] << 8) | (ql[1] << 16) | (qh[1] << 24);
+            bytes[k][1] = ql[2] | (qh[2] << 8);
+            codes[k] = code[k];
+        } else {
+            bytes[k][0] = 0x00ff00ffu;      // lo = 255, hi = 0 on every axis: never hit ...
+            bytes[k][1] = 0x000000ffu;
+            codes[k] = dummy_code;          // ... and harmless if a degenerate ray gets through anyway
+        }
+    }
+    uint4* w = reinterpret_cast<uint4*>(out);
+    w[0] = make_uint4(__float_as_uint(origin[0]), __float_as_uint(origin[1]), __float_as_uint(origin[2]),
+                      eb[0] | (eb[1] << 8) | (eb[2] << 16));
+    w[1] = make_uint4((unsigned)codes[0], (unsigned)codes[1], (unsigned)codes[2], (unsigned)codes[3]);
+    w[2] = make_uint4(bytes[0][0], bytes[0][1], bytes[1][0], bytes[1][1]);
+    w[3] = make_uint4(bytes[2][0], bytes[2][1], bytes[3][0], bytes[3][1]);
+}
+
+// one thread per binary inner node of even depth: its (grand)children become the 4 entries;
+// subtrees of <= leaf_max primitives collapse into one leaf
+__global__ void emit_nodes4_kernel(int n, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ prim_lo,
+                                   const float4* __restrict__ prim_hi, const int2* __restrict__ children,
+                                   const int2* __restrict__ range, const float4* __restrict__ node_lo,
+                                   const float4* __restrict__ node_hi, const unsigned char* __restrict__ odd,
+                                   float4* __restrict__ nodes, int leaf_max)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1 || odd[i]) return;
+    float4 lo[4], hi[4];
+    int code[4];
+    int n_e = 0;
+    // returns true when child c became an entry, false when it is an inner node to be absorbed
+    auto entry = [&](int c, bool may_absorb) {
+        if (c < 0) {
+            const int slot = ~c;
+            const unsigned p = sorted_vals[slot];
+            lo[n_e] = prim_lo[p]; hi[n_e] = prim_hi[p]; code[n_e] = ~(slot << 3); n_e++;
+            return true;
+        }
+        const int2 r = range[c];
+        const int size = r.y - r.x + 1;
+        if (size <= leaf_max) {
+            lo[n_e] = node_lo[c]; hi[n_e] = node_hi[c]; code[n_e] = ~((r.x << 3) | (size - 1)); n_e++;
+            return true;
+        }
+        if (may_absorb) return false;
+        lo[n_e] = node_lo[c]; hi[n_e] = node_hi[c]; code[n_e] = c; n_e++;
+        return true;
+    };
+    const int2 ch = children[i];
+    const int c2[2] = { ch.x, ch.y };
+    for (int c = 0; c < 2; c++) {
+        if (!entry(c2[c], true)) {
+            const int2 g = children[c2[c]];
+            entry(g.x, false);
+            entry(g.y, false);
+        }
+    }
+    write_node4(nodes + (size_t)i * 4, n_e, lo, hi, code, ~(n << 3));
+}
+
+// scenes of <= kLeafMax (4) primitives: one node with one leaf per primitive
 __global__ void emit_tiny_kernel(int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
-                                 float4* __restrict__ nodes)
+                                 const unsigned* __restrict__ sorted_vals, float4* __restrict__ nodes)
 {
     if (blockIdx.x || threadIdx.x) return;
-    float4 lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.f), hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.f);
-    for (int p = 0; p < n; p++) box_union(lo, hi, prim_lo[p], prim_hi[p]);
-    nodes[0] = make_float4(lo.x, lo.y, lo.z, hi.x);
-    nodes[1] = make_float4(hi.y, hi.z, lo.x, lo.y);
-    nodes[2] = make_float4(lo.z, hi.x, hi.y, hi.z);
-    nodes[3] = make_float4(__int_as_float(~((0 << 3) | (n - 1))), __int_as_float(~(n << 3)), 0.0f, 0.0f);
+    float4 lo[4], hi[4];
+    int code[4];
+    for (int k = 0; k < n; k++) {
+        const unsigned p = sorted_vals[k];
+        lo[k] = prim_lo[p]; hi[k] = prim_hi[p]; code[k] = ~(k << 3);
+    }
+    write_node4(nodes, n, lo, hi, code, ~(n << 3));
 }
 
 // primitive records in Morton order (spheres widened to the triangle record size)
@@ -321,7 +397,7 @@ __global__ void emit_prims_kernel(int n, int nf, const unsigned* __restrict__ so
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k > n) return;
     float4* o = out + (size_t)k * kTriWords;
-    if (k == n) {   // the never-hit dummy record (see emit_tiny_kernel)
+    if (k == n) {   // the never-hit dummy record: a triangle with a zero normal, `dem == 0` rejects it (main.cpp:1297)
         o[0] = o[1] = o[2] = o[3] = make_float4(0.f, 0.f, 0.f, 0.f);
         o[4] = make_float4(0.f, 1.0f, __int_as_float(0x7fffffff), __int_as_float(0));
         return;
@@ -357,12 +433,12 @@ int build_bvh(SceneHost* s)
     const int leaf_max = tuning_int("RT_LEAF_MAX", kLeafDefault, 1, 8);
     const int n_internal = n > kLeafMax ? n - 1 : 1;
     const int nblocks = (n + kSortTile - 1) / kSortTile;
-    DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals;
+    DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals, odd;
     const size_t N = (size_t)n;
     if (!box_lo.reserve(N * 16) || !box_hi.reserve(N * 16) || !keys_a.reserve(N * 4) || !keys_b.reserve(N * 4) ||
         !vals_a.reserve(N * 4) || !vals_b.reserve(N * 4) || !hist.reserve((size_t)256 * nblocks * 4) ||
         !children.reserve(N * 8) || !range.reserve(N * 8) || !par_i.reserve(N * 4) || !par_l.reserve(N * 4) ||
-        !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4))
+        !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4) || !odd.reserve(N))
         return RT_E_NOMEM;
     if (!s->bvh_nodes.reserve((size_t)n_internal * 64) || !s->bvh_tri.reserve((N + 1) * kTriWords * 16)) return RT_E_NOMEM;
 
@@ -382,10 +458,12 @@ int build_bvh(SceneHost* s)
         hierarchy_kernel<<<G, B, 0, st>>>(kin, n, children.as<int2>(), range.as<int2>(), par_i.as<int>(), par_l.as<int>());
         refit_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(), par_i.as<int>(),
                                       par_l.as<int>(), node_lo.as<float4>(), node_hi.as<float4>(), arrivals.as<unsigned>());
-        emit_nodes_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
-                                           range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(), s->bvh_nodes.as<float4>(), leaf_max);
+        depth_kernel<<<G, B, 0, st>>>(n, par_i.as<int>(), odd.as<unsigned char>());
+        emit_nodes4_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
+                                            range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(),
+                                            odd.as<unsigned char>(), s->bvh_nodes.as<float4>(), leaf_max);
     } else {
-        emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), s->bvh_nodes.as<float4>());
+        emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), vin, s->bvh_nodes.as<float4>());
     }
     emit_prims_kernel<<<(n + 1 + B - 1) / B, B, 0, st>>>(n, s->nf, vin, s->tri.as<float4>(), s->sph.as<float4>(), s->bvh_tri.as<float4>());
     RT_CUDA(cudaGetLastError());

@@ -1,38 +1,55 @@
 // bvh.cuh — LBVH traversal that returns what the reference's brute-force loops
 // return.
 //
-// Node = 4 float4 words holding BOTH children's boxes, so one 64-byte fetch decides
-// two subtrees:
-//   w0 = L.lo.xyz, L.hi.x     w1 = L.hi.yz, R.lo.xy     w2 = R.lo.z, R.hi.xyz
-//   w3 = as_float{ left, right, 0, 0 }
-//        child >= 0: index of an inner node; child < 0: a leaf, ~child = (first << 3) |
-//        (count - 1): `count` (1..kLeafMax <= 8) consecutive slots of the Morton-ordered
-//        primitive array starting at slot `first`.
+// The tree is 4-wide with quantised child boxes: the binary LBVH of bvh.cu is collapsed
+// by skipping every other level, and each 64-byte node stores up to four children as
+// 8-bit boxes in the node's own frame (as in Ylitie et al. 2017, "Efficient Incoherent
+// Ray Traversal on GPUs Through Compressed Wide BVHs", 4- instead of 8-wide):
+//   w0 = origin.xyz (fp32), ex | ey << 8 | ez << 16     plane = origin + q * 2^(e - 127)
+//   w1 = child[0..3]   >= 0: index of an inner node; < 0: a leaf, ~child = (first << 3) |
+//                      (count - 1): `count` consecutive slots of the Morton-ordered
+//                      primitive array from slot `first`.  Unused slots hold an inverted
+//                      box and the code of the never-hit dummy record (bvh.cu).
+//   w2 = child 0 {lo.x, hi.x, lo.y, hi.y}{lo.z, hi.z, 0, 0}, child 1 likewise     (bytes)
+//   w3 = child 2, child 3
+// One fetch decides four subtrees: against the 2-wide fp32 node of the same size that halves
+// the node visits per ray, i.e. the L1 gather traffic (the binding unit) and
+// the length of the dependent-load chain that sets the tail latency of a launch.
+//
 // Leaf slots are 5-word records (kTriWords) for triangles AND spheres:
 //   triangle: the record of scene_device.h, w4 = d12, kshadow, as_float(order), 0
 //   sphere  : w0 = centre, radius ; w4 = 0, kshadow, as_float(order), as_float(1)
 //
-// Boxes are padded at build time (bvh.cu) so that every point the reference's float
-// arithmetic accepts lies inside; the slab test itself only culls and may use any
-// arithmetic.  Exact-rounding tests (trace.cuh) run at the leaves, so a hit's t, b, g
-// are bit-identical to the brute-force walk; ties in t are broken by the iteration
-// order of the reference (smaller `order` wins).
+// Conservativeness.  Primitive boxes are padded at build time (bvh.cu) so that every point
+// the reference's float arithmetic accepts lies inside.  Quantisation rounds lo down / hi up
+// and then moves each plane one further quantum outward; the decode below is exact except
+// for the rounding of the per-node constant c (<= half a quantum), so a decoded box always
+// contains the padded box.  The box test only culls; exact-rounding tests (trace.cuh) run
+// at the leaves, so a hit's t, b, g are bit-identical to the brute-force walk; ties in t
+// are broken by the iteration order of the reference (smaller `order` wins).
 #pragma once
 
 #include "trace.cuh"
 
 namespace rt {
 
-constexpr int kBvhStack = 64;
+constexpr int kBvhStack = 96;     // local-memory part of the traversal stack (entries)
 constexpr int kSmemStack = 24;    // shared-memory part of the persistent walk's stack (entries per thread)
 constexpr int kWalkBlock = 128;   // block size of the persistent walk kernels (= kBlock)
-constexpr int kLeafMax = 4;       // scenes of <= kLeafMax primitives are a single leaf
+constexpr int kLeafMax = 4;       // scenes of <= kLeafMax primitives are a single node
 constexpr int kLeafDefault = 1;   // primitives per leaf otherwise: with one triangle per leaf the parent's box test
                                   // rejects most of the 80-byte exact tests (measured: 32 -> 6.4 tests per ray)
+constexpr int kWalkDone = 0x7fffffff;
+
+// Ray-side constants of the quantised box test.
+struct RayQ {
+    V3 o, inv;               // origin; 1 / direction (safe_inv)
+    unsigned sn[3], sf[3];   // PRMT selectors of the near / far plane byte per axis
+};
 
 template <bool kCount>
 struct BvhAccelT {
-    const float4* nodes;
+    const float4* nodes;   // 4 words per node, layout above (bit patterns)
     const float4* prims;   // Morton order, kTriWords words per slot
     const float4* tri;     // file order (direct tests of one known object)
     const float4* sph;
@@ -40,37 +57,102 @@ struct BvhAccelT {
     int root;              // node index; n_nodes == 0 means empty scene
     int n_nodes;
     bool count_all = false;   // shadow(): keep counting hits after an opaque occluder (parity probes)
-    // instrumented variant only (kCount): child boxes tested / primitives tested by this thread
+    // instrumented variant only (kCount): nodes visited / primitives tested by this thread
     mutable unsigned long long cnt_boxes = 0, cnt_prims = 0;
 
     RT_DEV static bool finite3(V3 v) { return isfinite(v.x) && isfinite(v.y) && isfinite(v.z); }
 
-    // Conservative slab test; returns the entry distance in tn.  t = lo * inv + (-o * inv) is one
-    // FFMA per plane; against (lo - o) * inv it is off by at most ~2 ulp of the coordinate
-    // magnitude when mapped back to a position, which the build-time padding of every box
-    // (bvh.cu: >= 8e-6 * scene scale) covers with a wide margin.  inv comes from safe_inv3().
-    RT_DEV static bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, V3 inv, V3 oinv,
-                            float tmin, float tmax, float& tn)
-    {
-        const float x0 = fmaf(lox, inv.x, oinv.x), x1 = fmaf(hix, inv.x, oinv.x);
-        const float y0 = fmaf(loy, inv.y, oinv.y), y1 = fmaf(hiy, inv.y, oinv.y);
-        const float z0 = fmaf(loz, inv.z, oinv.z), z1 = fmaf(hiz, inv.z, oinv.z);
-        tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), tmin));
-        const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
-        return tn <= tf;
-    }
-
-    RT_DEV static float4 ldn(const float4* p) { return __ldg(p); }
-
-    // 1 / d for the slab test.  A zero (or denormal-small) component would make lo * inv + oinv
-    // mix infinities of both signs (inf - inf = NaN on the far plane, which fminf/fmaxf then
-    // drop on the WRONG side), so it is replaced by +-1e-18: over any distance that matters
-    // the ray moves < 1e-15 along that axis, far inside the box padding.
+    // 1 / d for the box test.  A zero (or denormal-small) component is replaced by +-1e-18:
+    // over any distance that matters the ray moves < 1e-15 along that axis, far inside the
+    // box padding, and the plane distances stay finite and correctly ordered.
     RT_DEV static float safe_inv(float d)
     {
         return 1.0f / (fabsf(d) > 1.0e-18f ? d : copysignf(1.0e-18f, d));
     }
-    RT_DEV static V3 safe_inv3(V3 d) { return mk3(safe_inv(d.x), safe_inv(d.y), safe_inv(d.z)); }
+
+    RT_DEV static RayQ make_rayq(V3 o, V3 ray)
+    {
+        RayQ r;
+        r.o = o;
+        r.inv = mk3(safe_inv(ray.x), safe_inv(ray.y), safe_inv(ray.z));
+        // result bytes [q, 0, 0, 0x4B] = the float 2^23 + q; q = byte 0/1 (x, z) or 2/3 (y) of the
+        // child word: lo for the near plane of a ray going up the axis, hi otherwise
+        const unsigned nx = signbit(r.inv.x) ? 1u : 0u, ny = signbit(r.inv.y) ? 1u : 0u, nz = signbit(r.inv.z) ? 1u : 0u;
+        r.sn[0] = 0x7540u | nx;        r.sf[0] = 0x7540u | (nx ^ 1u);
+        r.sn[1] = 0x7542u | ny;        r.sf[1] = 0x7542u | (ny ^ 1u);
+        r.sn[2] = 0x7540u | nz;        r.sf[2] = 0x7540u | (nz ^ 1u);
+        return r;
+    }
+
+    // Box test of the four children of one node.  t[k] = entry distance, mask bit k = hit.
+    RT_DEV void test_node(const float4* __restrict__ nd, int node, const RayQ& r, float tmin, float tmax,
+                          float t[4], int code[4], unsigned& mask) const
+    {
+        const uint4* w = reinterpret_cast<const uint4*>(nd) + (size_t)node * 4;
+        const uint4 h = __ldg(w), c = __ldg(w + 1), b01 = __ldg(w + 2), b23 = __ldg(w + 3);
+        if (kCount) cnt_boxes += 1;
+        // plane distance = (origin + q * 2^e - o) * inv = (2^23 + q) * s + c,
+        //   s = 2^e * inv,  c = (origin - o) * inv - 2^23 * s
+        const float sx = __uint_as_float((h.w & 0xffu) << 23) * r.inv.x;
+        const float sy = __uint_as_float(((h.w >> 8) & 0xffu) << 23) * r.inv.y;
+        const float sz = __uint_as_float(((h.w >> 16) & 0xffu) << 23) * r.inv.z;
+        const float cx = fmaf(-8388608.0f, sx, (__uint_as_float(h.x) - r.o.x) * r.inv.x);
+        const float cy = fmaf(-8388608.0f, sy, (__uint_as_float(h.y) - r.o.y) * r.inv.y);
+        const float cz = fmaf(-8388608.0f, sz, (__uint_as_float(h.z) - r.o.z) * r.inv.z);
+        const unsigned a[4] = { b01.x, b01.z, b23.x, b23.z }, b[4] = { b01.y, b01.w, b23.y, b23.w };
+        code[0] = (int)c.x; code[1] = (int)c.y; code[2] = (int)c.z; code[3] = (int)c.w;
+        mask = 0;
+        #pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const float nx = fmaf(__uint_as_float(__byte_perm(a[k], 0x4B000000u, r.sn[0])), sx, cx);
+            const float ny = fmaf(__uint_as_float(__byte_perm(a[k], 0x4B000000u, r.sn[1])), sy, cy);
+            const float nz = fmaf(__uint_as_float(__byte_perm(b[k], 0x4B000000u, r.sn[2])), sz, cz);
+            const float fx = fmaf(__uint_as_float(__byte_perm(a[k], 0x4B000000u, r.sf[0])), sx, cx);
+            const float fy = fmaf(__uint_as_float(__byte_perm(a[k], 0x4B000000u, r.sf[1])), sy, cy);
+            const float fz = fmaf(__uint_as_float(__byte_perm(b[k], 0x4B000000u, r.sf[2])), sz, cz);
+            // fminf / fmaxf drop NaN (overflowing products of degenerate rays): conservative
+            const float tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, tmin));
+            const float tf = fminf(fminf(fx, fy), fminf(fz, tmax));
+            t[k] = tn;
+            if (tn <= tf) mask |= 1u << k;
+        }
+    }
+
+    // One traversal step at inner node `node`: tests its children, pushes all hit children but
+    // the one to visit next and returns that one (a node index, a leaf code, or pop()'s result
+    // when nothing was hit).  kOrdered: nearest child next, the others pushed far-to-near.
+    template <bool kOrdered, class Push, class Pop>
+    RT_DEV int step(const float4* __restrict__ nd, int node, const RayQ& r, float tmin, float tmax, Push& push, Pop& pop) const
+    {
+        float t[4]; int code[4]; unsigned mask;
+        test_node(nd, node, r, tmin, tmax, t, code, mask);
+        if (mask == 0) return pop();
+        if (kOrdered) {
+            #pragma unroll
+            for (int k = 0; k < 4; k++) if (!((mask >> k) & 1u)) t[k] = 3.402823466e+38f;
+            // sorting network on 4 (t, code) pairs, ascending
+            auto cswap = [&](int i, int j) {
+                const bool sw = t[j] < t[i];
+                const float ti = sw ? t[j] : t[i], tj = sw ? t[i] : t[j];
+                const int ci = sw ? code[j] : code[i], cj = sw ? code[i] : code[j];
+                t[i] = ti; t[j] = tj; code[i] = ci; code[j] = cj;
+            };
+            cswap(0, 1); cswap(2, 3); cswap(0, 2); cswap(1, 3); cswap(1, 2);
+            const int n = __popc(mask);
+            if (n > 3) push(code[3]);
+            if (n > 2) push(code[2]);
+            if (n > 1) push(code[1]);
+            return code[0];
+        }
+        int next = kWalkDone;
+        #pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if ((mask >> k) & 1u) {
+                if (next == kWalkDone) next = code[k]; else push(code[k]);
+            }
+        }
+        return next;
+    }
 
     // Generic traversal, "while-while" with one postponed leaf per lane (Aila & Laine 2009):
     // lanes keep descending inner nodes until every lane of the warp holds a leaf, then all
@@ -83,36 +165,20 @@ struct BvhAccelT {
     RT_DEV void walk(V3 o, V3 ray, float tmin, float tmax, Visit& visit) const
     {
         if (n_nodes == 0 || !finite3(ray) || !finite3(o)) return;   // NaN/inf rays hit nothing in the reference either
-        const V3 inv = safe_inv3(ray);
-        const V3 oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
-        constexpr int kDone = 0x7fffffff;
+        const RayQ rq = make_rayq(o, ray);
+        constexpr int kDone = kWalkDone;
         int stack[kBvhStack];
         int sp = 0;
+        auto pop = [&]() { return sp ? stack[--sp] : kDone; };
+        auto push = [&](int v) { if (sp < kBvhStack) stack[sp++] = v; };
         int node = root;      // >= 0: inner node index, < 0: leaf code, kDone: nothing left
         int leaf = 0;         // postponed leaf code (< 0), 0 = none
         while (node != kDone) {
             while ((unsigned)node < (unsigned)kDone) {
-                const float4* w = nodes + (size_t)node * 4;
-                const float4 w0 = ldn(w), w1 = ldn(w + 1), w2 = ldn(w + 2), w3 = ldn(w + 3);
-                const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
-                float tl, tr;
-                const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, inv, oinv, tmin, tmax, tl);
-                const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, inv, oinv, tmin, tmax, tr);
-                if (kCount) cnt_boxes += 2;
-                if (hl && hr) {
-                    const bool left_first = tl <= tr;              // near child first, far child on the stack
-                    if (sp < kBvhStack) stack[sp++] = left_first ? rc : lc;
-                    node = left_first ? lc : rc;
-                } else if (hl) {
-                    node = lc;
-                } else if (hr) {
-                    node = rc;
-                } else {
-                    node = sp ? stack[--sp] : kDone;
-                }
+                node = step<true>(nodes, node, rq, tmin, tmax, push, pop);
                 if (node < 0 && leaf == 0) {                       // postpone the first leaf, keep descending
                     leaf = node;
-                    node = sp ? stack[--sp] : kDone;
+                    node = pop();
                 }
                 if (!__any_sync(__activemask(), leaf == 0)) break; // every lane has a leaf to test
             }
@@ -127,7 +193,7 @@ struct BvhAccelT {
                 leaf = 0;
                 if (node < 0) {                                    // the next node is a leaf too: take it now
                     leaf = node;
-                    node = sp ? stack[--sp] : kDone;
+                    node = pop();
                 }
             }
         }
@@ -141,10 +207,11 @@ struct BvhAccelT {
     //   job.retire(bool finishing)       -> called by ALL lanes whenever some lane finishes
     //                                       (warp collectives allowed inside)
     //   job.next(o, ray, tmin, tmax)     -> true when the finished lane's job has another ray
+    //   Job::kOrdered                    -> visit near children first (closest hit) or not (any hit)
     template <class Job>
     RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes) const
     {
-        constexpr int kDone = 0x7fffffff;
+        constexpr int kDone = kWalkDone;
         constexpr unsigned kFull = 0xffffffffu;
         // loop invariants in registers (the accelerator object itself may sit in local memory)
         const float4* __restrict__ const nd = nodes;
@@ -157,14 +224,12 @@ struct BvhAccelT {
         // [entry][thread] so that a warp's pushes and pops never conflict whatever the lanes'
         // depths are (a local-memory stack costs one L1 wavefront per distinct depth, and L1 is
         // what binds this loop); deeper entries overflow into local memory.
-        // (Carrying the entry distance on the stack to drop far children unfetched was tried:
-        // 2 % fewer box tests, but the doubled stack traffic cost more.)
         __shared__ int s_stack[kSmemStack][kWalkBlock];
         int stack[kBvhStack];
         const int tid = threadIdx.x;
         int sp = 0, node = kDone, leaf = 0;
         bool alive = false, pool_empty = false;
-        V3 inv = mk3(0.f, 0.f, 0.f), oinv = mk3(0.f, 0.f, 0.f);
+        RayQ rq = make_rayq(mk3(0.f, 0.f, 0.f), mk3(1.f, 1.f, 1.f));
         float tmin = 0.f, tmax = 0.f;
         auto pop = [&]() {
             if (sp == 0) return kDone;
@@ -180,8 +245,7 @@ struct BvhAccelT {
         auto start = [&](bool need_walk, V3 o, V3 ray) {
             sp = 0; leaf = 0;
             node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
-            inv = safe_inv3(ray);
-            oinv = mk3(-o.x * inv.x, -o.y * inv.y, -o.z * inv.z);
+            rq = make_rayq(o, ray);
         };
         for (;;) {
             const unsigned dead = __ballot_sync(kFull, !alive);
@@ -204,24 +268,7 @@ struct BvhAccelT {
             // inner nodes, until every live lane holds a leaf (or has nothing left)
             for (;;) {
                 if (alive && (unsigned)node < (unsigned)kDone) {
-                    const float4* w = nd + (size_t)node * 4;
-                    const float4 w0 = ldn(w), w1 = ldn(w + 1), w2 = ldn(w + 2), w3 = ldn(w + 3);
-                    const int lc = __float_as_int(w3.x), rc = __float_as_int(w3.y);
-                    float tl, tr;
-                    const bool hl = slab(w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, inv, oinv, tmin, tmax, tl);
-                    const bool hr = slab(w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, inv, oinv, tmin, tmax, tr);
-                    if (kCount) cnt_boxes += 2;
-                    if (hl && hr) {
-                        const bool left_first = tl <= tr;
-                        push(left_first ? rc : lc);
-                        node = left_first ? lc : rc;
-                    } else if (hl) {
-                        node = lc;
-                    } else if (hr) {
-                        node = rc;
-                    } else {
-                        node = pop();
-                    }
+                    node = step<Job::kOrdered>(nd, node, rq, tmin, tmax, push, pop);
                     if (node < 0 && leaf == 0) {
                         leaf = node;
                         node = pop();

@@ -43,6 +43,7 @@ RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool sha
 // sphere-incidence transmission) or the face-incidence rule (main.cpp:992-1011).
 template <bool kCount>
 struct TraceJob {
+    static constexpr bool kOrdered = true;       // closest hit: near children first, the bound shrinks
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
@@ -175,6 +176,7 @@ __global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant
 // scene that removes most shadow walks without changing a bit of the result.
 template <bool kCount>
 struct ShadowJob {
+    static constexpr bool kOrdered = false;      // any hit: the order is irrelevant, skip the sort
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
