@@ -484,15 +484,6 @@ struct BvhAccelT {
         shadow_end(v);
     }
 
-    static RT_DEV float4 shadow_record(const ShadowVisit& v)
-    {
-        if (v.opaque) return make_float4(0.0f, 1.0f, 1.0f, 1.0f);
-        if (v.n_partial > 4 || v.overflow_mask != 1.0f) return make_float4(-1.0f, 1.0f, 1.0f, 1.0f);
-        float f[4] = { 1.0f, 1.0f, 1.0f, 1.0f };
-        for (int i = 0; i < 4; i++) if (i < v.n_partial) f[i] = v.p_k[i];
-        return make_float4(f[0], f[1], f[2], f[3]);
-    }
-
     RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask) const
     {
         ShadowVisit v;
@@ -501,17 +492,6 @@ struct BvhAccelT {
         for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
         if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
         return v.hits;
-    }
-
-    // The same product as a record for the wavefront shade kernel: up to four partial
-    // factors in iteration order (unused slots 1.0f: x * 1.0f == x), (0,1,1,1) for an opaque
-    // occluder, x < 0 when more than four partial factors were met (the shade kernel then
-    // re-traces this light itself; rare).
-    RT_DEV float4 shadow_factors(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax) const
-    {
-        ShadowVisit v;
-        shadow_collect(o, ray, self, tmin, tmax, use_tmax, v);
-        return shadow_record(v);
     }
 };
 

@@ -84,7 +84,7 @@ static size_t level_bytes(int level, size_t cap, bool bvh, int nl)
 {
     // level 0 has no ray queue (primary rays are generated in place)
     size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16;
-    if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 16;   // hp, hb, node_list, sh (wavefront_bvh.cuh)
+    if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 4;    // hp, hb, node_list, sh (wavefront_bvh.cuh)
     return cap * per_slot + 256;
 }
 
@@ -154,7 +154,7 @@ static void fill_levels(const SceneHost* s, int max_depth, bool bvh, FrameParams
         if (bvh) {
             L.hp = (float4*)base; base += cap * 16;
             L.hb = (float4*)base; base += cap * 16;
-            L.sh = (float4*)base; base += cap * 16 * (size_t)s->nl;
+            L.sh = (float*)base;  base += cap * 4 * (size_t)s->nl;
             L.node_list = (int*)base;
         }
     }
@@ -217,8 +217,10 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             if (p.instrument) bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
             else bvh_trace_kernel<false><<<grid, kBlock, 0, stream>>>(P, l);
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
-            if (s->nl && p.instrument) bvh_shadow_kernel<true><<<sh_grid, kBlock, 0, stream>>>(P, l);
-            else if (s->nl) bvh_shadow_kernel<false><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
+            if (s->nl && p.instrument) bvh_shadow_kernel<true, false><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            else if (s->nl && near_first) bvh_shadow_kernel<false, true><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            else if (s->nl) bvh_shadow_kernel<false, false><<<sh_grid, kBlock, 0, stream>>>(P, l);
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
             bvh_shade_kernel<<<grid, kBlock, 0, stream>>>(P, l);
             n += s->nl ? 3 : 2;

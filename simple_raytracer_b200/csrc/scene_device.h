@@ -99,11 +99,12 @@ struct LevelBuffers {
     float4* res;    // rgb, status
     // LBVH pipeline only (wavefront_bvh.cuh): the hit of slot i, the list of slots that hit
     // something (= the ShadeRay nodes of this generation, in arrival order), and one shadow
-    // record per (node, light), light-major: sh[li * n_nodes + k] for node_list[k]
+    // record per (node, light), light-major: sh[li * n_nodes + k] for node_list[k] = the carried
+    // shadow_mask after light li
     float4* hp;     // hit point.xyz, as_float(object order)
     float4* hb;     // b, g, t, 0
     int*    node_list;
-    float4* sh;     // <= 4 partial shadow factors in iteration order; see BvhAccelT::shadow_factors
+    float*  sh;
     int capacity;
 };
 

@@ -174,9 +174,9 @@ __global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant
 // is exactly 0 it stays 0 whatever the later lights meet: the chain stops there and the
 // remaining records are never read (RecordedShadow stops at the same point).  In a dense
 // scene that removes most shadow walks without changing a bit of the result.
-template <bool kCount>
+template <bool kCount, bool kNearFirst>
 struct ShadowJob {
-    static constexpr bool kOrdered = false;      // any hit: the order is irrelevant, skip the sort
+    static constexpr bool kOrdered = kNearFirst; // any hit: order is only a heuristic (near boxes first finds occluders sooner?)
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
@@ -220,17 +220,15 @@ struct ShadowJob {
         if (!fin) return;
         if (kCount) walks++;
         acc.shadow_end(v);
-        const float4 f = BvhAccelT<kCount>::shadow_record(v);
-        P.level[level].sh[(size_t)li * n_nodes + k] = f;
-        if (f.x < 0.0f) {
-            // more than four partial occluders: the shade kernel re-traces this light; what its
-            // product is only matters here for the early-out, so carry on conservatively
-            if (mask == 0.0f) return;
-            mask = 1.0f;
+        // the carried product exactly as BvhAccelT::shadow applies it (main.cpp:909 / 946 in
+        // iteration order); the record is the mask AFTER this light
+        if (v.opaque) {
+            mask = clamp01(fmul(0.0f, mask));
         } else {
-            mask = clamp01(fmul(f.x, mask)); mask = clamp01(fmul(f.y, mask));
-            mask = clamp01(fmul(f.z, mask)); mask = clamp01(fmul(f.w, mask));
+            for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
+            if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
         }
+        P.level[level].sh[(size_t)li * n_nodes + k] = mask;
     }
     RT_DEV bool next(V3& wo, V3& wray, float& tmin, float& tmax)
     {
@@ -241,12 +239,12 @@ struct ShadowJob {
     }
 };
 
-template <bool kCount>
+template <bool kCount, bool kNearFirst>
 __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned n_nodes = P.counters->nodes[level];
-    ShadowJob<kCount> job{ P, acc, level, n_nodes };
+    ShadowJob<kCount, kNearFirst> job{ P, acc, level, n_nodes };
     acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
@@ -256,18 +254,15 @@ __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constan
     }
 }
 
-// Shadow source of the shade kernel: the records of bvh_shadow_kernel.
+// Shadow source of the shade kernel: the carried shadow_mask after each light, as left by
+// the node's chain in bvh_shadow_kernel.
 struct RecordedShadow {
-    const float4* rec;          // sh + k: record of light li at rec[li * n_nodes]
+    const float* rec;           // sh + k: mask after light li at rec[li * n_nodes]
     unsigned n_nodes;
-    const BvhAccel& acc;        // only for the rare "more than four partial occluders" re-trace
-    RT_DEV void operator()(int li, V3 p, V3 dir, int self, float eps, float tmax, bool use_tmax, float& mask) const
+    RT_DEV void operator()(int li, V3, V3, int, float, float, bool, float& mask) const
     {
-        if (mask == 0.0f) return;     // 0 * f == 0 for every later factor: those records were never written
-        const float4 f = rec[(size_t)li * n_nodes];
-        if (f.x < 0.0f) { acc.shadow(p, dir, self, eps, tmax, use_tmax, mask); return; }
-        mask = clamp01(fmul(f.x, mask)); mask = clamp01(fmul(f.y, mask));                   // 909 / 946, in iteration order
-        mask = clamp01(fmul(f.z, mask)); mask = clamp01(fmul(f.w, mask));
+        if (mask == 0.0f) return;     // the chain stopped here: later records were never written (and 0 stays 0)
+        mask = rec[(size_t)li * n_nodes];
     }
 };
 
@@ -275,7 +270,6 @@ __global__ void __launch_bounds__(kBlock) bvh_shade_kernel(const __grid_constant
 {
     const SceneView& S = P.scene;
     const LevelBuffers& LB = P.level[level];
-    const BvhAccel acc = make_bvh_accel<false>(S);
     const unsigned n_nodes = P.counters->nodes[level];
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned rounded = (n_nodes + 31u) & ~31u;
@@ -290,7 +284,7 @@ __global__ void __launch_bounds__(kBlock) bvh_shade_kernel(const __grid_constant
             const float4 hp = LB.hp[slot], hb = LB.hb[slot];
             h.obj = __float_as_int(hp.w); h.b = hb.x; h.g = hb.y; h.t = hb.z;
         }
-        const RecordedShadow shadow{ LB.sh + k, n_nodes, acc };
+        const RecordedShadow shadow{ LB.sh + k, n_nodes };
         shade_and_spawn(P, shadow, level, slot, r, h, hit);
     }
 }
