@@ -209,7 +209,7 @@ struct BvhAccelT {
     //   job.next(o, ray, tmin, tmax)     -> true when the finished lane's job has another ray
     //   Job::kOrdered                    -> visit near children first (closest hit) or not (any hit)
     template <class Job>
-    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes) const
+    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes, int inner_min = 1, int leaf_min = 1) const
     {
         constexpr int kDone = kWalkDone;
         constexpr unsigned kFull = 0xffffffffu;
@@ -274,10 +274,14 @@ struct BvhAccelT {
                         node = pop();
                     }
                 }
-                if (!__any_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) break;
+                if (__popc(__ballot_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) < inner_min) break;
             }
             // pending leaves
-            while (__any_sync(kFull, alive && leaf < 0)) {
+            for (bool first = true;; first = false) {
+                // always one pass when any lane holds a leaf (progress), further passes only while
+                // enough lanes still have one
+                const int holders = __popc(__ballot_sync(kFull, alive && leaf < 0));
+                if (holders == 0 || (!first && holders < leaf_min)) break;
                 if (alive && leaf < 0) {
                     const int code = ~leaf;
                     const int first = code >> 3, count = (code & 7) + 1;

@@ -186,9 +186,12 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     P.max_depth = p.max_depth; P.epsilon = p.epsilon;
     P.rank = p.rank; P.world = p.world_size; P.tile_rows = p.tile_rows;
     P.n_local_rows = tl.n_local_rows; P.n_local_pixels = tl.n_local_pixels;
-    static const int refill = tuning_int("RT_REFILL_LANES", 8, 1, 32);
+    static const int refill = tuning_int("RT_REFILL_LANES", 6, 1, 32);
     static const int grid_mult = tuning_int("RT_GRID_MULT", 16, 1, 64);
     P.refill_lanes = refill;
+    static const int inner_min = tuning_int("RT_INNER_MIN_LANES", 4, 1, 32);
+    static const int leaf_min = tuning_int("RT_LEAF_MIN_LANES", 1, 1, 32);
+    P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
 
     RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters), stream));
     const int sms = sm_count(s->device);

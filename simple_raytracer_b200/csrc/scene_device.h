@@ -139,6 +139,8 @@ struct FrameParams {
     int n_local_rows;     // rows of the tile buffer (padded to whole tiles)
     int n_local_pixels;   // n_local_rows * width
     int refill_lanes;     // persistent kernels: fetch new rays when this many lanes of a warp are idle
+    int inner_min_lanes;  // ... leave the inner-node loop when fewer lanes than this can still descend
+    int leaf_min_lanes;   // ... leave the leaf loop when fewer lanes than this hold a leaf
 };
 
 }  // namespace rt

@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant
     const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
                                       : min(P.counters->rays[level], (unsigned)P.level[level].capacity);
     TraceJob<kCount> job{ P, acc, level };
-    acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes);
+    acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes);
     flush_bvh_counters(acc, P.counters);
 }
 
@@ -245,7 +245,7 @@ __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constan
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned n_nodes = P.counters->nodes[level];
     ShadowJob<kCount, kNearFirst> job{ P, acc, level, n_nodes };
-    acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes);
+    acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
         unsigned long long w = job.walks;
