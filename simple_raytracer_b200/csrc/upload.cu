@@ -16,12 +16,52 @@ namespace rt {
 
 namespace {
 
-__global__ void pack_faces_kernel(const RtFace* __restrict__ in, const RtMaterial* __restrict__ mats, int nf,
-                                  float4* __restrict__ tri, float4* __restrict__ attr, int4* __restrict__ obj)
+// What the packing kernels report back: bounds of all primitives (for the BVH padding) and the
+// first primitive with a material / texture index out of range.  Floats are kept as order-
+// preserving ints so that atomicMin / atomicMax work on them.
+struct PackReport {
+    int lo[3], hi[3];
+    int bad_face, bad_sphere;
+};
+
+RT_DEV int ordered(float f) { const int i = __float_as_int(f); return i ^ ((i >> 31) & 0x7fffffff); }
+inline float unordered(int i) { i ^= (i >> 31) & 0x7fffffff; float f; std::memcpy(&f, &i, 4); return f; }
+
+// warp-reduced bounds -> one atomic pair per axis per warp; NaN coordinates are ignored (fminf / fmaxf)
+RT_DEV void report_bounds(PackReport* rep, bool valid, const float lo[3], const float hi[3])
+{
+    for (int c = 0; c < 3; c++) {
+        float l = valid ? lo[c] : 3.0e38f, h = valid ? hi[c] : -3.0e38f;
+        for (int o = 16; o > 0; o >>= 1) {
+            l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+            h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+        }
+        if ((threadIdx.x & 31) == 0) { atomicMin(&rep->lo[c], ordered(l)); atomicMax(&rep->hi[c], ordered(h)); }
+    }
+}
+
+__global__ void pack_faces_kernel(const RtFace* __restrict__ in, const RtMaterial* __restrict__ mats, int nf, int nmat,
+                                  int ntex, float4* __restrict__ tri, float4* __restrict__ attr, int4* __restrict__ obj,
+                                  PackReport* __restrict__ rep)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nf) return;
-    const RtFace f = in[i];
+    const bool valid = i < nf;
+    RtFace f;
+    if (valid) f = in[i];
+    {
+        float lo[3], hi[3];
+        for (int c = 0; c < 3; c++) {
+            lo[c] = valid ? fminf(f.v[0][c], fminf(f.v[1][c], f.v[2][c])) : 0.f;
+            hi[c] = valid ? fmaxf(f.v[0][c], fmaxf(f.v[1][c], f.v[2][c])) : 0.f;
+        }
+        report_bounds(rep, valid, lo, hi);
+    }
+    if (!valid) return;
+    if (f.material < 0 || f.material >= nmat || f.texture < -1 || f.texture >= ntex) {
+        atomicMin(&rep->bad_face, i);
+        f.material = 0; f.texture = -1;      // keep the kernel in bounds; the upload is rejected anyway
+        if (nmat == 0) return;
+    }
     const V3 p0 = mk3(f.v[0][0], f.v[0][1], f.v[0][2]);
     const V3 p1 = mk3(f.v[1][0], f.v[1][1], f.v[1][2]);
     const V3 p2 = mk3(f.v[2][0], f.v[2][1], f.v[2][2]);
@@ -48,11 +88,28 @@ __global__ void pack_faces_kernel(const RtFace* __restrict__ in, const RtMateria
 }
 
 __global__ void pack_spheres_kernel(const RtSphere* __restrict__ in, const RtMaterial* __restrict__ mats, int ns, int nf,
-                                    float4* __restrict__ sph, int4* __restrict__ obj)
+                                    int nmat, int ntex, float4* __restrict__ sph, int4* __restrict__ obj,
+                                    PackReport* __restrict__ rep)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= ns) return;
-    const RtSphere s = in[i];
+    const bool valid = i < ns;
+    RtSphere s;
+    if (valid) s = in[i];
+    {
+        float lo[3], hi[3];
+        for (int c = 0; c < 3; c++) {
+            const float r = valid ? fabsf(s.radius) : 0.f;
+            lo[c] = valid ? s.center[c] - r : 0.f;
+            hi[c] = valid ? s.center[c] + r : 0.f;
+        }
+        report_bounds(rep, valid, lo, hi);
+    }
+    if (!valid) return;
+    if (s.material < 0 || s.material >= nmat || s.texture < -1 || s.texture >= ntex) {
+        atomicMin(&rep->bad_sphere, i);
+        s.material = 0; s.texture = -1;
+        if (nmat == 0) return;
+    }
     const float kshadow = (float)dsub(1.0, (double)mats[s.material].opacity);
     sph[(size_t)i * kSphWords] = make_float4(s.center[0], s.center[1], s.center[2], s.radius);
     sph[(size_t)i * kSphWords + 1] = make_float4(kshadow, __int_as_float(nf + i), 0.0f, 0.0f);
@@ -166,21 +223,6 @@ int build_scene(const RtSceneDesc* d, SceneHost* s)
         set_error("null array in RtSceneDesc");
         return RT_E_INVALID;
     }
-    // index validation on the host (one pass; cheap next to the copy)
-    for (int i = 0; i < d->n_faces; i++) {
-        const RtFace& f = d->faces[i];
-        if (f.material < 0 || f.material >= d->n_materials || f.texture < -1 || f.texture >= d->n_textures) {
-            set_error("face " + std::to_string(i) + ": material / texture index out of range");
-            return RT_E_INVALID;
-        }
-    }
-    for (int i = 0; i < d->n_spheres; i++) {
-        const RtSphere& sp = d->spheres[i];
-        if (sp.material < 0 || sp.material >= d->n_materials || sp.texture < -1 || sp.texture >= d->n_textures) {
-            set_error("sphere " + std::to_string(i) + ": material / texture index out of range");
-            return RT_E_INVALID;
-        }
-    }
     s->width = d->width; s->height = d->height;
     s->nf = d->n_faces; s->ns = d->n_spheres; s->nl = d->n_lights; s->ntex = d->n_textures; s->nmat = d->n_materials;
     for (int k = 0; k < 3; k++) s->bkg[k] = d->bkg[k];
@@ -221,13 +263,23 @@ int build_scene(const RtSceneDesc* d, SceneHost* s)
         !s->light.reserve(sizeof(float4) * 3 * (size_t)s->nl + 16))
         return RT_E_NOMEM;
 
+    DevBuf report;
+    if (!report.reserve(sizeof(PackReport))) return RT_E_NOMEM;
+    {
+        PackReport init;
+        for (int c = 0; c < 3; c++) { init.lo[c] = 0x7f7fffff /* ordered(FLT_MAX) */; init.hi[c] = (int)0x80800000 /* ordered(-FLT_MAX) */; }
+        init.bad_face = 0x7fffffff; init.bad_sphere = 0x7fffffff;
+        RT_CUDA(cudaMemcpyAsync(report.p, &init, sizeof init, cudaMemcpyHostToDevice, st));
+    }
     const int B = 256;
     if (s->nf)
-        pack_faces_kernel<<<(s->nf + B - 1) / B, B, 0, st>>>(raw_faces.as<RtFace>(), raw_mats.as<RtMaterial>(), s->nf,
-                                                            s->tri.as<float4>(), s->face_attr.as<float4>(), s->obj.as<int4>());
+        pack_faces_kernel<<<(s->nf + B - 1) / B, B, 0, st>>>(raw_faces.as<RtFace>(), raw_mats.as<RtMaterial>(), s->nf, s->nmat,
+                                                            s->ntex, s->tri.as<float4>(), s->face_attr.as<float4>(),
+                                                            s->obj.as<int4>(), report.as<PackReport>());
     if (s->ns)
         pack_spheres_kernel<<<(s->ns + B - 1) / B, B, 0, st>>>(raw_spheres.as<RtSphere>(), raw_mats.as<RtMaterial>(), s->ns,
-                                                              s->nf, s->sph.as<float4>(), s->obj.as<int4>());
+                                                              s->nf, s->nmat, s->ntex, s->sph.as<float4>(), s->obj.as<int4>(),
+                                                              report.as<PackReport>());
     const int nmisc = s->nmat > s->nl ? s->nmat : s->nl;
     if (nmisc)
         pack_misc_kernel<<<(nmisc + B - 1) / B, B, 0, st>>>(raw_mats.as<RtMaterial>(), s->nmat, raw_lights.as<RtLight>(),
@@ -259,24 +311,19 @@ int build_scene(const RtSceneDesc* d, SceneHost* s)
         // raw_tex is reused by the next texture: stream order keeps this safe
     }
 
-    // scene bounds (for BVH padding) on the host from the raw arrays
-    float lo[3] = { 3.0e38f, 3.0e38f, 3.0e38f }, hi[3] = { -3.0e38f, -3.0e38f, -3.0e38f };
-    for (int i = 0; i < d->n_faces; i++)
-        for (int k = 0; k < 3; k++)
-            for (int c = 0; c < 3; c++) {
-                const float x = d->faces[i].v[k][c];
-                if (x < lo[c]) lo[c] = x;
-                if (x > hi[c]) hi[c] = x;
-            }
-    for (int i = 0; i < d->n_spheres; i++)
-        for (int c = 0; c < 3; c++) {
-            const float r = std::fabs(d->spheres[i].radius);
-            if (d->spheres[i].center[c] - r < lo[c]) lo[c] = d->spheres[i].center[c] - r;
-            if (d->spheres[i].center[c] + r > hi[c]) hi[c] = d->spheres[i].center[c] + r;
-        }
-    for (int c = 0; c < 3; c++) { s->scene_lo[c] = lo[c]; s->scene_hi[c] = hi[c]; }
-
+    PackReport h_rep;
+    RT_CUDA(cudaMemcpyAsync(&h_rep, report.p, sizeof h_rep, cudaMemcpyDeviceToHost, st));
     RT_CUDA(cudaStreamSynchronize(st));   // raw staging buffers die here
+    if (h_rep.bad_face < d->n_faces) {
+        set_error("face " + std::to_string(h_rep.bad_face) + ": material / texture index out of range");
+        return RT_E_INVALID;
+    }
+    if (h_rep.bad_sphere < d->n_spheres) {
+        set_error("sphere " + std::to_string(h_rep.bad_sphere) + ": material / texture index out of range");
+        return RT_E_INVALID;
+    }
+    // bounds of all primitives (for the BVH padding)
+    for (int c = 0; c < 3; c++) { s->scene_lo[c] = unordered(h_rep.lo[c]); s->scene_hi[c] = unordered(h_rep.hi[c]); }
     return RT_OK;
 }
 
