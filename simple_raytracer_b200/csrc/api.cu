@@ -143,6 +143,12 @@ void rt_free_scene(RtScene* scene)
     SceneHost* s = &scene->h;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
+    if (s->stream2) {
+        cudaStreamSynchronize(s->stream2);
+        for (int k = 0; k < kMaxLevels; k++) if (s->ev_fork[k]) cudaEventDestroy(s->ev_fork[k]);
+        if (s->ev_join) cudaEventDestroy(s->ev_join);
+        cudaStreamDestroy(s->stream2);
+    }
     if (s->ws.device >= 0) stash_workspace(std::move(s->ws));
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);

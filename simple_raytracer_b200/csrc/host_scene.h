@@ -79,6 +79,8 @@ struct SceneHost {
     Workspace ws;
 
     cudaStream_t stream = nullptr;      // owned
+    cudaStream_t stream2 = nullptr;     // owned: the shadow -> colour chain of the LBVH pipeline (render.cu)
+    cudaEvent_t ev_fork[kMaxLevels] = { nullptr }, ev_join = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t prof_ev[kMaxLevels + 2] = { nullptr };   // params.profile: boundaries of the generations
     cudaEvent_t prof_mid[kMaxLevels][2] = { { nullptr } };   // LBVH pipeline: after trace, after shadow

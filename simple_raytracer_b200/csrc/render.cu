@@ -83,7 +83,7 @@ void stash_workspace(Workspace&& ws)
 static size_t level_bytes(int level, size_t cap, bool bvh, int nl)
 {
     // level 0 has no ray queue (primary rays are generated in place)
-    size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16;
+    size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16 + 8;
     if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 4;    // hp, hb, node_list, sh (wavefront_bvh.cuh)
     return cap * per_slot + 256;
 }
@@ -154,6 +154,10 @@ static void fill_levels(const SceneHost* s, int max_depth, bool bvh, FrameParams
         if (bvh) {
             L.hp = (float4*)base; base += cap * 16;
             L.hb = (float4*)base; base += cap * 16;
+        }
+        // 8- and 4-byte arrays after all the 16-byte ones (cap may be odd)
+        L.nr_c = (int2*)base;   base += cap * 8;
+        if (bvh) {
             L.sh = (float*)base;  base += cap * 4 * (size_t)s->nl;
             L.node_list = (int*)base;
         }
@@ -207,6 +211,13 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 if (!s->prof_mid[k][j]) RT_CUDA(cudaEventCreate(&s->prof_mid[k][j]));
     }
     s->prof_split = p.profile && accel == RT_ACCEL_LBVH;
+    static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
+    const bool overlap = accel == RT_ACCEL_LBVH && overlap_knob && !p.profile && !p.instrument;
+    if (overlap && !s->stream2) {
+        RT_CUDA(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
+        for (int k = 0; k < kMaxLevels; k++) RT_CUDA(cudaEventCreateWithFlags(&s->ev_fork[k], cudaEventDisableTiming));
+        RT_CUDA(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+    }
     for (int l = 0; l <= p.max_depth; l++) {
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
         // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
@@ -214,24 +225,47 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         int grid = (int)std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * grid_mult);
         if (grid < 1) grid = 1;
         if (accel == RT_ACCEL_LBVH) {
-            // trace: one thread per ray; shadow: one per (node, light); shade: one per node
+            // trace: one thread per ray; shadow: one chain per node; colour / spawn: one thread per node
             const long long sh_work = work * std::max(1, s->nl);
             const int sh_grid = (int)std::max<long long>(1, std::min<long long>((sh_work + kBlock - 1) / kBlock, (long long)sms * grid_mult));
+            static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
             if (p.instrument) bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
             else bvh_trace_kernel<false><<<grid, kBlock, 0, stream>>>(P, l);
+            n++;
+            // shadow -> colour depends only on this generation's hits, spawn -> next trace too:
+            // two chains on two streams (profiled / instrumented frames stay serial)
+            cudaStream_t side = stream;
+            if (overlap) {
+                RT_CUDA(cudaEventRecord(s->ev_fork[l], stream));
+                RT_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork[l], 0));
+                side = s->stream2;
+                // the critical chain first: spawn feeds the next generation's trace
+                if (l < p.max_depth) { bvh_shade_kernel<false, true><<<grid, kBlock, 0, stream>>>(P, l); n++; }
+            }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
-            static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
-            if (s->nl && p.instrument) bvh_shadow_kernel<true, false><<<sh_grid, kBlock, 0, stream>>>(P, l);
-            else if (s->nl && near_first) bvh_shadow_kernel<false, true><<<sh_grid, kBlock, 0, stream>>>(P, l);
-            else if (s->nl) bvh_shadow_kernel<false, false><<<sh_grid, kBlock, 0, stream>>>(P, l);
+            if (s->nl) {
+                if (p.instrument) bvh_shadow_kernel<true, false><<<sh_grid, kBlock, 0, side>>>(P, l);
+                else if (near_first) bvh_shadow_kernel<false, true><<<sh_grid, kBlock, 0, side>>>(P, l);
+                else bvh_shadow_kernel<false, false><<<sh_grid, kBlock, 0, side>>>(P, l);
+                n++;
+            }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
-            bvh_shade_kernel<<<grid, kBlock, 0, stream>>>(P, l);
-            n += s->nl ? 3 : 2;
+            if (overlap) {
+                bvh_shade_kernel<true, false><<<grid, kBlock, 0, side>>>(P, l);
+                n++;
+            } else {
+                bvh_shade_kernel<true, true><<<grid, kBlock, 0, stream>>>(P, l);
+                n++;
+            }
         } else {
             if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
             else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
             n++;
         }
+    }
+    if (overlap) {
+        RT_CUDA(cudaEventRecord(s->ev_join, s->stream2));
+        RT_CUDA(cudaStreamWaitEvent(stream, s->ev_join, 0));
     }
     if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 1], stream));
     for (int l = p.max_depth - 1; l >= 0; l--) {

@@ -94,8 +94,9 @@ struct LevelBuffers {
     int4*   rq_m;   // parent slot, incidence object (order), flags, stack[0]
     int4*   rq_s;   // stack[1..4]
     // node record written by the shade step, read by the combine pass
-    float4* nr_a;   // base.rgb (= diffuse*ka + tmp_specular), tw1 = (float)(1.0 - F_t)
-    float4* nr_b;   // tw2 = (float)(1.0 - opacity), F_r, as_float(childT), as_float(childR)
+    float4* nr_a;   // base.rgb (= diffuse*ka + tmp_specular), 0
+    float4* nr_b;   // tw1 = (float)(1.0 - F_t), tw2 = (float)(1.0 - opacity), F_r, 0
+    int2*   nr_c;   // slots of the transmission / reflection child in generation d+1 (-1 = none)
     float4* res;    // rgb, status
     // LBVH pipeline only (wavefront_bvh.cuh): the hit of slot i, the list of slots that hit
     // something (= the ShadeRay nodes of this generation, in arrival order), and one shadow

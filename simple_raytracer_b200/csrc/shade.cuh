@@ -94,12 +94,17 @@ struct DirectShadow {
     }
 };
 
-// The part of ShadeRay before the recursive calls.  Returns the node's base colour
-// (diffuse*ka + tmp_specular), the child weights, and the rays to spawn.
+// ShadeRay before its recursive calls, in two independent halves (the LBVH pipeline runs them
+// as separate kernels so that the next generation's rays do not wait for this one's shadows):
+//
+//   shade_colour : texture, per-light shadows + Blinn-Phong -> diffuse*ka + tmp_specular
+//                  (main.cpp:800-958 and the first two terms of 1206)
+//   shade_spawn  : Fresnel terms, TIR test, the transmission and reflection rays and the
+//                  weights of their terms (main.cpp:961-987, 1083/1087, 1103-1108)
+//
+// Both flip the normal of a sphere hit from inside the same way (main.cpp:869-872).
 template <class ShadowSrc>
-RT_DEV Col shade_node(const SceneView& S, const ShadowSrc& shadow, V3 incidence_ray, int obj, const Surface& sf,
-                      float n_i, float n_t, int depth_left, float eps,
-                      float& tw1, float& tw2, float& fr, Spawn& sp)
+RT_DEV Col shade_colour(const SceneView& S, const ShadowSrc& shadow, V3 incidence_ray, int obj, const Surface& sf, float eps)
 {
     const int4 oi = S.obj[obj];
     const Material m = load_material(S, oi.x);
@@ -137,6 +142,19 @@ RT_DEV Col shade_node(const SceneView& S, const ShadowSrc& shadow, V3 incidence_
         const Col sm = mkc(shadow_mask, shadow_mask, shadow_mask);
         tmp_specular = cadd(tmp_specular, cmul(cmul(lc, sm), cadd(dc, sc)));     // 955-958
     }
+    return cadd(cmulf(diffuse, m.ka), tmp_specular);                             // first two terms of 1206
+}
+
+RT_DEV void shade_spawn(const SceneView& S, V3 incidence_ray, int obj, const Surface& sf, float n_i, float n_t,
+                        int depth_left, float& tw1, float& tw2, float& fr, Spawn& sp)
+{
+    const int4 oi = S.obj[obj];
+    const Material m = load_material(S, oi.x);
+    const bool is_sphere = obj >= S.nf;
+    V3 N = sf.n;                                                                 // 785
+    const V3 I = vneg(incidence_ray);                                            // 786
+    float cosi = vdot(N, I);                                                     // 794
+    if (cosi < 0.0f && is_sphere) { N = vneg(N); cosi = vdot(N, I); }            // 869-872
 
     const float snell = fdiv(n_i, n_t);                                          // 961
     const float critical = ref_asinf(fdiv(n_t, n_i));                            // 962
@@ -159,8 +177,6 @@ RT_DEV Col shade_node(const SceneView& S, const ShadowSrc& shadow, V3 incidence_
     fr = schlick(F0r, cosi);                                                     // 1104
     sp.want_r = depth_left > 0 && fr != 0.0f && m.ks > 0.0f;                     // 1105
     if (sp.want_r) sp.R = vsub(vmulf(N, fmul(2.0f, cosi)), I);                   // 1108
-
-    return cadd(cmulf(diffuse, m.ka), tmp_specular);                             // first two terms of 1206
 }
 
 // Medium-stack state machine run when a spawned ray has found its hit

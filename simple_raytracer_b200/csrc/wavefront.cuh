@@ -119,30 +119,41 @@ RT_DEV void write_miss(const FrameParams& P, int level, unsigned slot, bool padd
     P.level[level].res[slot] = r;
 }
 
-// ShadeRay for the hit `h` of slot `slot` (main.cpp:783-1207 up to the recursive calls),
-// then the spawn of its two child rays into the queue of generation level+1 and the node
-// record the combine pass reads.  Must be called by all 32 lanes of a warp (`hit` false
-// for idle lanes): queue slots are handed out with one atomicAdd per warp.
-template <class ShadowSrc>
+// ShadeRay for the hit `h` of slot `slot` (main.cpp:783-1207 up to the recursive calls).
+//   kColour: the node's base colour (shade_colour) -> nr_a, or the final result for the last
+//            generation (whose nodes have no children and no combine pass of their own);
+//   kSpawn : medium state machine, Fresnel weights (shade_spawn), the two child rays appended
+//            to the queue of generation level+1 -> nr_b, nr_c.
+// The fused brute-force kernel does both in one call, the LBVH pipeline in two kernels.
+// Must be called by all 32 lanes of a warp (`hit` false for idle lanes): queue slots are
+// handed out with one atomicAdd per warp.
+template <bool kColour, bool kSpawn, class ShadowSrc>
 RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int level, unsigned slot, RayIn& r,
                             const Hit& h, bool hit)
 {
     const SceneView& S = P.scene;
     const LevelBuffers& LB = P.level[level];
+    Surface sf;
+    if (hit) sf = finish_hit(S, r.o, r.ray, h);
+
+    if (kColour && hit) {
+        const Col base = shade_colour(S, shadow, r.ray, h.obj, sf, P.epsilon);
+        if (level == P.max_depth) LB.res[slot] = make_float4(base.r, base.g, base.b, kResFinal);
+        else LB.nr_a[slot] = make_float4(base.r, base.g, base.b, 0.0f);
+    }
+    if (!kSpawn) return;
+
     Spawn sp; sp.want_t = sp.want_r = false;
     float tw1 = 0.f, tw2 = 0.f, fr = 0.f, c_ni = 0.f, c_nt = 0.f;
     bool c_exiting = false;
-    Col base = mkc(0.f, 0.f, 0.f);
-    Surface sf;
     if (hit) {
-        sf = finish_hit(S, r.o, r.ray, h);
         if (level == 0) {                                                        // 746-757
             c_ni = S.bkg_eta; c_nt = material_eta(S, h.obj); c_exiting = false;
             r.stack[0] = h.obj; r.ns = 1;
         } else {
             medium_update(S, r.reflect, r.exiting, r.inc, h.obj, r.n_i, r.n_t, r.stack, r.ns, c_ni, c_nt, c_exiting);
         }
-        base = shade_node(S, shadow, r.ray, h.obj, sf, c_ni, c_nt, P.max_depth - level, P.epsilon, tw1, tw2, fr, sp);
+        shade_spawn(S, r.ray, h.obj, sf, c_ni, c_nt, P.max_depth - level, tw1, tw2, fr, sp);
     }
 
     // ---- spawn: warp-aggregated slot allocation in the next generation's queue -----
@@ -186,15 +197,12 @@ RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int l
         }
     }
 
-    if (!hit) return;
-    if (child_t < 0 && child_r < 0 && !sp.want_t && !sp.want_r) {
-        // leaf node: both child terms are exactly (0,0,0); x + 0 leaves a clamped x unchanged
-        LB.res[slot] = make_float4(base.r, base.g, base.b, kResFinal);
-    } else {
-        LB.nr_a[slot] = make_float4(base.r, base.g, base.b, tw1);
-        LB.nr_b[slot] = make_float4(tw2, fr, __int_as_float(child_t), __int_as_float(child_r));
-        LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
-    }
+    if (!hit || level == P.max_depth) return;
+    // a node without children is finished by the combine pass like any other: x + 0 leaves a
+    // clamped x unchanged
+    LB.nr_b[slot] = make_float4(tw1, tw2, fr, 0.0f);
+    LB.nr_c[slot] = make_int2(child_t, child_r);
+    if (kColour) LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);   // (LBVH pipeline: the trace kernel wrote it)
 }
 
 // Fused path (brute force): trace + shadow rays + shade + spawn of one slot in one thread.
@@ -220,7 +228,7 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
         if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
     }
     const DirectShadow<Accel> direct{ acc };
-    shade_and_spawn(P, direct, level, slot, r, h, hit);
+    shade_and_spawn<true, true>(P, direct, level, slot, r, h, hit);
     if (in_range && !hit) write_miss(P, level, slot, !active, aborted);
 }
 
@@ -257,19 +265,20 @@ __global__ void __launch_bounds__(256) combine_kernel(const __grid_constant__ Fr
     for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < count; slot += stride) {
         float4 r = LB.res[slot];
         if (r.w == kResPending) {
-            const float4 a = LB.nr_a[slot], b = LB.nr_b[slot];
-            const int ct = __float_as_int(b.z), cr = __float_as_int(b.w);
+            const float4 a = LB.nr_a[slot], b = LB.nr_b[slot];      // base colour | tw1, tw2, F_r
+            const int2 ch = LB.nr_c[slot];
+            const int ct = ch.x, cr = ch.y;
             Col acc = mkc(a.x, a.y, a.z);
             Col tt = mkc(0.f, 0.f, 0.f), tr = mkc(0.f, 0.f, 0.f);
             if (ct >= 0) {
                 bool zero;
                 const Col c = child_term(NB, ct, zero);
-                if (!zero) tt = cmulf(cmulf(c, a.w), b.x);                       // 1083 / 1087
+                if (!zero) tt = cmulf(cmulf(c, b.x), b.y);                       // 1083 / 1087
             }
             if (cr >= 0) {
                 bool zero;
                 const Col c = child_term(NB, cr, zero);
-                tr = cmulf(c, b.y);                                              // 1194 / 1198
+                tr = cmulf(c, b.z);                                              // 1194 / 1198
             }
             acc = cadd(cadd(acc, tt), tr);                                       // 1206
             r = make_float4(acc.r, acc.g, acc.b, kResFinal);

@@ -146,6 +146,8 @@ struct TraceJob {
             LB.hp[slot] = make_float4(p.x, p.y, p.z, __int_as_float(best.obj));
             LB.hb[slot] = make_float4(best.b, best.g, best.t, 0.0f);
             LB.node_list[base + __popc(hm & lanemask_lt())] = (int)slot;
+            // nodes of the last generation are finished by the colour kernel itself
+            if (level < P.max_depth) LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
         } else if (fin) {
             write_miss(P, level, slot, padding, aborted);
         }
@@ -266,9 +268,19 @@ struct RecordedShadow {
     }
 };
 
+// A dummy shadow source for the spawn half (it never asks).
+struct NoShadow {
+    RT_DEV void operator()(int, V3, V3, int, float, float, bool, float&) const {}
+};
+
+// kColour / kSpawn select the half of ShadeRay this launch does (wavefront.cuh:
+// shade_and_spawn).  The spawn half depends only on the hits, so the next generation's trace
+// kernel can start while this generation's shadow rays are still being walked: the frame
+// scheduler (render.cu) runs trace -> spawn -> trace -> ... on one stream and shadow -> colour
+// on a second one, which fills the tail of every persistent launch with the other chain's work.
+template <bool kColour, bool kSpawn>
 __global__ void __launch_bounds__(kBlock) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
 {
-    const SceneView& S = P.scene;
     const LevelBuffers& LB = P.level[level];
     const unsigned n_nodes = P.counters->nodes[level];
     const unsigned stride = gridDim.x * blockDim.x;
@@ -284,8 +296,13 @@ __global__ void __launch_bounds__(kBlock) bvh_shade_kernel(const __grid_constant
             const float4 hp = LB.hp[slot], hb = LB.hb[slot];
             h.obj = __float_as_int(hp.w); h.b = hb.x; h.g = hb.y; h.t = hb.z;
         }
-        const RecordedShadow shadow{ LB.sh + k, n_nodes };
-        shade_and_spawn(P, shadow, level, slot, r, h, hit);
+        if (kColour) {
+            const RecordedShadow shadow{ LB.sh + k, n_nodes };
+            shade_and_spawn<kColour, kSpawn>(P, shadow, level, slot, r, h, hit);
+        } else {
+            const NoShadow none;
+            shade_and_spawn<kColour, kSpawn>(P, none, level, slot, r, h, hit);
+        }
     }
 }
 

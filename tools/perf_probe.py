@@ -16,6 +16,7 @@ def main():
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--depth", type=int, default=4)
     ap.add_argument("--no-instrument", action="store_true")
+    ap.add_argument("--nop", action="store_true", help="no per-kernel profiling events (the frame then runs overlapped)")
     ap.add_argument("--world", type=int, default=1)
     ap.add_argument("--rank", type=int, default=0)
     ap.add_argument("--tile-rows", type=int, default=10)
@@ -31,7 +32,7 @@ def main():
         rays = st.rays_primary + st.rays_shadow + st.rays_transmit + st.rays_reflect
         best = None
         for _ in range(a.reps):
-            s = ds.render(profile=True, **kw)
+            s = ds.render(profile=not a.nop, **kw)
             if best is None or s.render_ms < best.render_ms:
                 best = s
         out = dict(upload_s=round(up, 3), first_render_s=round(first, 3), ms=round(best.render_ms, 3), rays=int(rays),
