@@ -530,6 +530,23 @@ int rto_render(const RtSceneDesc* desc, const RtoParams* params, int64_t n_pixel
     return RT_OK;
 }
 
+/* The primary rays of n pixels (main.cpp:720, 728): origin = eye, direction = (p - eye).norm(). */
+int rto_primary_rays(const RtSceneDesc* desc, int64_t n_pixels, const int64_t* pixel_index,
+                     float* out_origins, float* out_dirs)
+{
+    OCamera cam;
+    if (!desc || desc->width < 2 || desc->height < 2 || !pixel_index || !out_origins || !out_dirs) return RT_E_INVALID;
+    make_camera(desc, &cam);
+    for (int64_t k = 0; k < n_pixels; k++) {
+        int i = (int)(pixel_index[k] / desc->width), j = (int)(pixel_index[k] % desc->width);
+        V3 p = vadd(vadd(cam.ul, vmulf(cam.delta_h, (float)j)), vmulf(cam.delta_v, (float)i));   /* 720 */
+        V3 ray = vnorm(vsub(p, cam.eye));                                                        /* 728 */
+        out_origins[3 * k] = cam.eye.x; out_origins[3 * k + 1] = cam.eye.y; out_origins[3 * k + 2] = cam.eye.z;
+        out_dirs[3 * k] = ray.x; out_dirs[3 * k + 1] = ray.y; out_dirs[3 * k + 2] = ray.z;
+    }
+    return RT_OK;
+}
+
 int rto_trace_closest(const RtSceneDesc* desc, int32_t n, const float* origins, const float* dirs,
                       float tmin, int32_t* out_id, float* out_t, float* out_normal, float* out_bary)
 {

@@ -50,6 +50,10 @@ int rto_render(const RtSceneDesc* desc, const RtoParams* params,
                int64_t n_pixels, const int64_t* pixel_index,
                int32_t* out_raw, int32_t* out_primary_id, RtoStats* stats);
 
+/* Primary rays of the given pixels (main.cpp:677-728): n*3 floats each. */
+int rto_primary_rays(const RtSceneDesc* desc, int64_t n_pixels, const int64_t* pixel_index,
+                     float* out_origins, float* out_dirs);
+
 /* The closest-hit loop of main.cpp:1109-1124 over TraceRay's result. */
 int rto_trace_closest(const RtSceneDesc* desc, int32_t n,
                       const float* origins, const float* dirs, float tmin,

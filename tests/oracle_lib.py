@@ -53,6 +53,8 @@ def load_oracle() -> C.CDLL:
         lib.rto_render.argtypes = [C.POINTER(abi.RtSceneDesc), C.POINTER(RtoParams), C.c_int64, vp, vp, vp,
                                    C.POINTER(RtoStats)]
         lib.rto_render.restype = C.c_int
+        lib.rto_primary_rays.argtypes = [C.POINTER(abi.RtSceneDesc), C.c_int64, vp, vp, vp]
+        lib.rto_primary_rays.restype = C.c_int
         lib.rto_trace_closest.argtypes = [C.POINTER(abi.RtSceneDesc), C.c_int32, vp, vp, C.c_float, vp, vp, vp, vp]
         lib.rto_trace_closest.restype = C.c_int
         lib.rto_trace_shadow.argtypes = [C.POINTER(abi.RtSceneDesc), C.c_int32, vp, vp, vp, C.c_float, vp, vp, vp]
@@ -107,6 +109,16 @@ def oracle_render(scene: Scene, max_depth: int = 4, epsilon: float = 1.0e-3, pix
     if rc != 0:
         raise RuntimeError(f"rto_render failed: {rc}")
     return raw, ids, st
+
+
+def primary_rays(scene: Scene, rows):
+    """Primary rays of whole image rows -> (origins [n,3], dirs [n,3]) float32."""
+    lib = load_oracle()
+    px = np.concatenate([np.arange(scene.width, dtype=np.int64) + int(r) * scene.width for r in rows])
+    o = np.zeros((len(px), 3), np.float32); d = np.zeros((len(px), 3), np.float32)
+    rc = lib.rto_primary_rays(C.byref(scene.desc()), len(px), _ptr(px), _ptr(o), _ptr(d))
+    assert rc == 0
+    return o, d
 
 
 def oracle_trace_closest(scene: Scene, origins, dirs, tmin: float):

@@ -89,6 +89,11 @@ def _random_rays(n, extent, seed):
     o = rng.uniform(-extent, extent, (n, 3)).astype(np.float32)
     d = rng.normal(0, 1, (n, 3)).astype(np.float32)
     d[: n // 2] /= np.linalg.norm(d[: n // 2], axis=1, keepdims=True)   # half unit, half deliberately not (A3.2)
+    # axis-parallel rays (one or two zero components, both signs of zero): the box test's 1/d path
+    k = n // 10
+    d[:k, 0] = 0.0
+    d[k // 2:k, 1] = -0.0
+    d[:k] /= np.maximum(np.linalg.norm(d[:k], axis=1, keepdims=True), 1e-30)
     return o, d, rng
 
 
@@ -141,6 +146,79 @@ def test_lbvh_equals_brute_force_on_a_large_scene():
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
     assert np.array_equal(a[3].view(np.uint32), b[3].view(np.uint32))
     assert np.array_equal(sa[1], sb[1]) and np.array_equal(sa[0].view(np.uint32), sb[0].view(np.uint32))
+
+
+def test_lbvh_equals_brute_force_on_the_full_stress_scene():
+    """BASELINE configs[4] at its full primitive count (1 M triangles + 1 k spheres): closest
+    hits and shadow products of the 4-wide quantised LBVH against the brute-force walk."""
+    scene = scenegen.stress_scene(1_000_000, 1000, 64, 48)
+    rng = np.random.default_rng(11)
+    n = 2048
+    o = rng.uniform(-70, 70, (n, 3)).astype(np.float32)
+    d = rng.normal(0, 1, (n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    d[:64, 0] = 0.0                                        # some axis-parallel ones
+    d[:64] /= np.linalg.norm(d[:64], axis=1, keepdims=True)
+    self_id = rng.integers(1, scene.n_prims + 1, n).astype(np.int32)
+    with DeviceScene(scene) as ds:
+        a = ds.trace_closest(o, d, 1.0e-3, accel=abi.RT_ACCEL_BRUTE)
+        b = ds.trace_closest(o, d, 1.0e-3, accel=abi.RT_ACCEL_LBVH)
+        sa = ds.trace_shadow(o, d, self_id, 1.0e-3, None, accel=abi.RT_ACCEL_BRUTE)
+        sb = ds.trace_shadow(o, d, self_id, 1.0e-3, None, accel=abi.RT_ACCEL_LBVH)
+    assert (a[0] > 0).sum() > 1000
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+    assert np.array_equal(a[3].view(np.uint32), b[3].view(np.uint32))
+    assert np.array_equal(sa[1], sb[1]) and np.array_equal(sa[0].view(np.uint32), sb[0].view(np.uint32))
+
+
+def test_lbvh_with_outlier_primitives():
+    """A small soup inside a sky sphere of radius 1e6 over a huge floor: the node frames of the
+    quantised tree must cope with boxes 5 orders of magnitude apart (LBVH forced)."""
+    scene = scenegen.random_soup(200, 10, 21, 96, 72)
+    big = np.zeros(1, dtype=scene.spheres.dtype)
+    big["center"], big["radius"], big["material"], big["texture"] = (0, 0, 0), 1.0e6, 5, -1
+    floor = np.zeros(2, dtype=scene.faces.dtype)
+    q = [(-5e4, -12, -5e4), (5e4, -12, -5e4), (5e4, -12, 5e4), (-5e4, -12, 5e4)]
+    floor["v"][0] = [q[0], q[2], q[1]]; floor["v"][1] = [q[0], q[3], q[2]]
+    floor["vn"][:] = (0, 1, 0); floor["material"] = 6; floor["texture"] = -1
+    faces = np.concatenate([scene.faces, floor]); spheres = np.concatenate([scene.spheres, big])
+    spheres["id"] = np.arange(1, len(spheres) + 1)
+    faces["id"] = np.arange(len(spheres) + 1, len(spheres) + len(faces) + 1)
+    sc = scene.copy(faces=faces, spheres=spheres)
+    raw, ids, ost = O.oracle_render(sc)
+    for accel in (abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH):
+        _render_and_compare(sc, raw, ids, ost, accel)
+
+
+def test_full_size_frame_properties():
+    """BASELINE configs[4]'s scene at the north star's 4K: the frame is deterministic, every
+    (rank, 8) shard is byte-identical to the rows of the single-GPU frame, and the LBVH frame
+    equals the brute-force frame on a band of rows (the CPU cannot trace this scene)."""
+    scene = scenegen.stress_scene(1_000_000, 1000, 3840, 2160)
+    with DeviceScene(scene) as ds:
+        st = ds.render(tile_rows=10)
+        full_rgb, full_flags = ds.download()
+        ds.render(tile_rows=10)
+        again = ds.download()
+        assert np.array_equal(again[0], full_rgb) and np.array_equal(again[1], full_flags)
+        assert st.accel_used == abi.RT_ACCEL_LBVH and st.nodes_total > 2_000_000
+        for rank in (0, 5):
+            rgb = np.zeros_like(full_rgb); flags = np.full_like(full_flags, 255)
+            ds.render(rank=rank, world_size=8, tile_rows=10)
+            ds.download(rgb, flags)
+            rows = np.array([r for r in range(2160) if (r // 10) % 8 == rank])
+            assert np.array_equal(rgb[rows], full_rgb[rows]) and np.array_equal(flags[rows], full_flags[rows])
+    # brute force on a thin slice of the same camera: a 3840 x 4 image re-centred on row 1080
+    # is a different camera, so compare through the probes' primary rays instead: the ids of
+    # the LBVH frame's primary hits against brute-force closest hits of the same rays
+    small = scene.with_size(3840, 2160)
+    with DeviceScene(small) as ds:
+        ds.render(tile_rows=10, instrument=True)
+        pid = ds.download_primary_ids()
+        rows = [3, 1080, 2101]
+        o, d = O.primary_rays(small, rows)
+        ids, t, _, _ = ds.trace_closest(o, d, 0.0, accel=abi.RT_ACCEL_BRUTE)
+        assert np.array_equal(ids.reshape(len(rows), -1), pid[rows])
 
 
 def test_row_tile_sharding_is_byte_identical():
