@@ -230,14 +230,14 @@ def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
         closest_rays = int(st.rays_primary + st.rays_transmit + st.rays_reflect)
         walked = int(st.shadow_rays_walked)
         per_kernel = {
-            # 32 B per child box tested + 48 B per primitive tested + the ray read and the hit written
-            "bvh_trace_kernel": 32 * tb + 48 * tp + 64 * closest_rays,
-            "bvh_shadow_kernel": 32 * sb + 48 * sp + 32 * walked,
+            # 64 B per 4-wide node visited + 80 B per primitive record tested + the ray read and the hit written
+            "bvh_trace_kernel": 64 * tb + 80 * tp + 64 * closest_rays,
+            "bvh_shadow_kernel": 64 * sb + 80 * sp + 20 * walked,
             # 64 B per shaded hit + 4 B per texel
             "bvh_shade_kernel": 64 * nodes + 4 * int(st.texel_fetches),
         }
         return {"bound": "hbm", "per_frame": sum(per_kernel.values()), "per_kernel": per_kernel, "unit": "GB/s",
-                "detail": {"trace_boxes_tested": tb, "trace_prim_tests": tp, "shadow_boxes_tested": sb,
+                "detail": {"trace_nodes_visited": tb, "trace_prim_tests": tp, "shadow_nodes_visited": sb,
                            "shadow_prim_tests": sp, "closest_hit_rays": closest_rays, "shadow_rays_walked": walked,
                            "shadow_rays_reference": int(st.rays_shadow), "nodes_shaded": nodes,
                            "texels": int(st.texel_fetches)}}
@@ -372,15 +372,22 @@ def run_ours(args) -> dict:
         dom_ms = sum(kernel_ms[dom])
         achieved = work["per_kernel"][dom] / (dom_ms * 1e-3) / 1e9
         peak = peaks["hbm_gbs"]
+        traffic = None
+        try:      # dram__bytes_read + dram__bytes_write per launch from the committed ncu --set full capture
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                traffic = json.load(f)[dom]["dram_bytes_per_launch"] if args.workload == DEFAULT_WORKLOAD and world == 1 else None
+        except (OSError, KeyError, ValueError):
+            pass
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peaks["source"], "kernel": dom,
+                "traffic": traffic, "peak_source": peaks["source"], "kernel": dom,
                 "algorithmic_bytes_per_launch": work["per_kernel"][dom] / n_levels,
                 "kernels": {k: {"ms_per_frame": sum(v), "ms_by_generation": v,
                                 "algorithmic_bytes_per_frame": work["per_kernel"][k],
                                 "achieved_gbs": work["per_kernel"][k] / (sum(v) * 1e-3) / 1e9 if sum(v) else None}
                             for k, v in kernel_ms.items()},
-                "note": "algorithmic bytes are mostly served by L1/L2 (the tree's top levels are shared by all rays): "
-                        "see DESIGN.md; dram traffic from ncu is in profiles/"}
+                "note": "algorithmic bytes = 64 B per node visit + 80 B per primitive test; they are mostly served by "
+                        "L1/L2 (the tree is shared by all rays): the walk is bound by the L1/TEX gather pipe and SIMT "
+                        "divergence, not by HBM - see DESIGN.md 6 and profiles/"}
     else:
         dom_ms = sum(level_ms)
         clk = (clocks or {}).get("sm_mhz") or peaks["sm_max_mhz"]
