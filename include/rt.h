@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 1
+#define RT_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 #define RT_OK            0
@@ -126,6 +126,13 @@ typedef struct RtRenderParams {
                               (slower; never use for timing)                  */
     int32_t profile;       /* 1: CUDA events around every generation's kernel;
                               rt_render reports RtStats.level_ms / combine_ms */
+    int32_t subframes;     /* LBVH pipeline: independent launch chains the rank's
+                              tiles are dealt out to (1..8; 0 = choose).  Never
+                              changes a pixel, only how kernel tails overlap. */
+    int32_t work_sharing;  /* LBVH walk kernels: once a launch's ray queue is dry,
+                              idle lanes take subtrees off the stacks of the lanes
+                              still walking.  0 = for short launches (default),
+                              1 = always, 2 = never.  Never changes a pixel.   */
 } RtRenderParams;
 
 /* Filled by rt_render when a non-NULL pointer is passed.  The ray counts
@@ -155,6 +162,16 @@ typedef struct RtStats {
        params.instrument: the part of bvh_nodes_visited / prim_tests done by the shadow kernels. */
     double   trace_ms[8], shadow_ms[8], shade_ms[8];
     uint64_t shadow_boxes_tested, shadow_prim_tests;
+    /* params.instrument, LBVH: how each persistent walk kernel spent its time (device
+       %globaltimer): span = first warp's start .. last warp's end; drain = from the moment
+       the job queue ran dry (no lane can be refilled any more) to the last warp's end;
+       warp_drain = the same, averaged over warps. */
+    double   trace_span_ms[8], trace_drain_ms[8], trace_warp_drain_ms[8];
+    double   shadow_span_ms[8], shadow_drain_ms[8], shadow_warp_drain_ms[8];
+    /* ... and, per warp on average, the inner-node passes it still made after the queue ran
+       dry, the lanes active in such a pass, and the subtrees handed to idle lanes. */
+    double   trace_drain_steps[8], trace_drain_lanes[8], trace_drain_steals[8];
+    double   shadow_drain_steps[8], shadow_drain_lanes[8];
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */
@@ -206,6 +223,13 @@ int rt_tile_layout(int32_t height, int32_t width, int32_t world_size,
  * dev_tiles may be NULL to render into the scene's own buffer only. */
 int rt_render_async(RtScene* scene, const RtRenderParams* params,
                     void* dev_tiles, void* cuda_stream);
+
+/* rt_render_async cannot re-run a frame whose wavefront queues turned out too small
+ * (rt_render does; the reference's recursion has no such limit).  Call this once the
+ * frame's stream has been synchronised: RT_OK = the frame is complete; RT_E_NOMEM = a
+ * queue overflowed and the frame is truncated — the queues have been grown, render it
+ * again.  A synchronous rt_render of the same view beforehand sizes the queues exactly. */
+int rt_async_frame_status(RtScene* scene);
 
 /* After an allgather of every rank's tile buffer ([rank][local_tile][row][col]
  * RGBA8, device memory) puts the pixels in scanline order:

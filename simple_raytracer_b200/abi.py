@@ -66,7 +66,8 @@ class RtSceneDesc(C.Structure):
 class RtRenderParams(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("epsilon", C.c_float), ("accel", C.c_int32),
                 ("rank", C.c_int32), ("world_size", C.c_int32), ("tile_rows", C.c_int32),
-                ("instrument", C.c_int32), ("profile", C.c_int32)]
+                ("instrument", C.c_int32), ("profile", C.c_int32), ("subframes", C.c_int32),
+                ("work_sharing", C.c_int32)]
 
 
 class RtStats(C.Structure):
@@ -77,7 +78,13 @@ class RtStats(C.Structure):
                 ("queue_regrows", C.c_int32), ("reserved", C.c_int32),
                 ("level_ms", C.c_double * 8), ("combine_ms", C.c_double), ("shadow_rays_walked", C.c_uint64),
                 ("trace_ms", C.c_double * 8), ("shadow_ms", C.c_double * 8), ("shade_ms", C.c_double * 8),
-                ("shadow_boxes_tested", C.c_uint64), ("shadow_prim_tests", C.c_uint64)]
+                ("shadow_boxes_tested", C.c_uint64), ("shadow_prim_tests", C.c_uint64),
+                ("trace_span_ms", C.c_double * 8), ("trace_drain_ms", C.c_double * 8), ("trace_warp_drain_ms", C.c_double * 8),
+                ("shadow_span_ms", C.c_double * 8), ("shadow_drain_ms", C.c_double * 8),
+                ("shadow_warp_drain_ms", C.c_double * 8),
+                ("trace_drain_steps", C.c_double * 8), ("trace_drain_lanes", C.c_double * 8),
+                ("trace_drain_steals", C.c_double * 8), ("shadow_drain_steps", C.c_double * 8),
+                ("shadow_drain_lanes", C.c_double * 8)]
 
     def as_dict(self) -> dict:
         d = {}
@@ -90,7 +97,7 @@ class RtStats(C.Structure):
 # The exported symbols of each library — tests check that every one resolves.
 RT_SYMBOLS = [
     "rt_upload_scene", "rt_render", "rt_download_framebuffer", "rt_free_scene", "rt_last_error",
-    "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_deinterleave_tiles", "rt_set_camera",
+    "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_async_frame_status", "rt_deinterleave_tiles", "rt_set_camera",
     "rt_trace_closest", "rt_trace_shadow", "rt_download_primary_ids", "rt_tile_layout",
 ]
 RT_HOST_SYMBOLS = [
@@ -136,6 +143,8 @@ def load_rt() -> C.CDLL:
     lib.rt_tile_layout.restype = C.c_int
     lib.rt_render_async.argtypes = [vp, _p(RtRenderParams), vp, vp]
     lib.rt_render_async.restype = C.c_int
+    lib.rt_async_frame_status.argtypes = [vp]
+    lib.rt_async_frame_status.restype = C.c_int
     lib.rt_deinterleave_tiles.argtypes = [vp, vp, vp, i32, i32, vp]
     lib.rt_deinterleave_tiles.restype = C.c_int
     lib.rt_set_camera.argtypes = [vp, _p(f32), _p(f32), _p(f32), f32]

@@ -40,6 +40,8 @@ int check_params(const RtRenderParams* in, RtRenderParams* out)
     if (out->max_depth < 0 || out->max_depth > 5) { set_error("max_depth must be in 0..5"); return RT_E_INVALID; }
     if (out->world_size < 1 || out->rank < 0 || out->rank >= out->world_size) { set_error("bad rank / world_size"); return RT_E_INVALID; }
     if (out->tile_rows < 1) { set_error("tile_rows must be >= 1"); return RT_E_INVALID; }
+    if (out->subframes < 0 || out->subframes > kMaxSubframes) { set_error("subframes must be in 0..8"); return RT_E_INVALID; }
+    if (out->work_sharing < 0 || out->work_sharing > 2) { set_error("work_sharing must be 0, 1 or 2"); return RT_E_INVALID; }
     if (out->accel < RT_ACCEL_AUTO || out->accel > RT_ACCEL_LBVH) { set_error("bad accel"); return RT_E_INVALID; }
     return RT_OK;
 }
@@ -129,7 +131,7 @@ int rt_upload_scene(const RtSceneDesc* desc, RtScene** out)
     if (!cuda_ok(cudaGetDevice(&s->device), "cudaGetDevice") ||
         !cuda_ok(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
         !cuda_ok(cudaEventCreate(&s->ev0), "cudaEventCreate") || !cuda_ok(cudaEventCreate(&s->ev1), "cudaEventCreate") ||
-        !cuda_ok(cudaMallocHost((void**)&s->h_counters, sizeof(Counters)), "cudaMallocHost"))
+        !cuda_ok(cudaMallocHost((void**)&s->h_counters, sizeof(Counters) * kMaxSubframes), "cudaMallocHost"))
         rc = RT_E_CUDA;
     if (rc == RT_OK) rc = build_scene(desc, s);
     if (rc != RT_OK) { rt_free_scene(sc); return rc; }
@@ -143,12 +145,7 @@ void rt_free_scene(RtScene* scene)
     SceneHost* s = &scene->h;
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
-    if (s->stream2) {
-        cudaStreamSynchronize(s->stream2);
-        for (int k = 0; k < kMaxLevels; k++) if (s->ev_fork[k]) cudaEventDestroy(s->ev_fork[k]);
-        if (s->ev_join) cudaEventDestroy(s->ev_join);
-        cudaStreamDestroy(s->stream2);
-    }
+    s->ws.chains.sync();
     if (s->ws.device >= 0) stash_workspace(std::move(s->ws));
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -199,6 +196,21 @@ int rt_render_async(RtScene* scene, const RtRenderParams* params, void* dev_tile
     return enqueue_frame(s, p, (uchar4*)dev_tiles, cuda_stream ? (cudaStream_t)cuda_stream : s->stream, nullptr);
 }
 
+int rt_async_frame_status(RtScene* scene)
+{
+    if (!scene) { set_error("rt_async_frame_status: null scene"); return RT_E_INVALID; }
+    SceneHost* s = &scene->h;
+    if (!s->rendered) { set_error("rt_async_frame_status before a frame"); return RT_E_STATE; }
+    RT_CUDA(cudaSetDevice(s->device));
+    RT_CUDA(cudaMemcpy(s->h_counters, s->ws.counters.p, sizeof(Counters) * s->last_subframes, cudaMemcpyDeviceToHost));
+    unsigned demand[kMaxLevels];
+    if (!frame_overflowed(s, nullptr, demand)) return RT_OK;
+    const int rc = ensure_workspace(s, s->last, demand);
+    if (rc != RT_OK) return rc;
+    set_error("the last asynchronous frame overflowed a wavefront queue (queues grown: render it again)");
+    return RT_E_NOMEM;
+}
+
 int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
 {
     if (!scene) { set_error("rt_render: null scene"); return RT_E_INVALID; }
@@ -210,31 +222,23 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
     if ((rc = ensure_workspace(s, p, nullptr)) != RT_OK) return rc;
     int regrows = 0, launches = 0;
     float ms = 0.0f;
+    Counters total;
     for (;;) {
         RT_CUDA(cudaEventRecord(s->ev0, s->stream));
         if ((rc = enqueue_frame(s, p, nullptr, s->stream, &launches)) != RT_OK) return rc;
         RT_CUDA(cudaEventRecord(s->ev1, s->stream));
-        RT_CUDA(cudaMemcpyAsync(s->h_counters, s->ws.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, s->stream));
+        RT_CUDA(cudaMemcpyAsync(s->h_counters, s->ws.counters.p, sizeof(Counters) * s->last_subframes,
+                                cudaMemcpyDeviceToHost, s->stream));
         RT_CUDA(cudaStreamSynchronize(s->stream));
         RT_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
-        bool overflow = s->h_counters->overflow != 0;
-        for (int l = 1; l <= p.max_depth; l++) overflow = overflow || s->h_counters->rays[l] > (unsigned)s->ws.capacity[l];
-        if (!overflow) break;
-        if (++regrows > 16) { set_error("wavefront queues still overflow after 16 regrows"); return RT_E_NOMEM; }
-        // a truncated generation under-reports what the deeper ones need: scale those up with it
         unsigned demand[kMaxLevels];
-        double factor = 1.0;
-        for (int l = 0; l < kMaxLevels; l++) {
-            const unsigned seen = s->h_counters->rays[l];
-            const unsigned cap = (unsigned)s->ws.capacity[l];
-            if (l >= 1 && l <= p.max_depth && seen > cap) factor = std::max(factor, (double)seen / (double)cap);
-            demand[l] = (unsigned)std::min(2.0e9, seen * factor);
-        }
+        if (!frame_overflowed(s, &total, demand)) break;
+        if (++regrows > 16) { set_error("wavefront queues still overflow after 16 regrows"); return RT_E_NOMEM; }
         if ((rc = ensure_workspace(s, p, demand)) != RT_OK) return rc;
     }
     if (stats) {
         std::memset(stats, 0, sizeof *stats);
-        const Counters& c = *s->h_counters;
+        const Counters& c = total;
         stats->render_ms = ms;
         for (int l = 0; l <= p.max_depth; l++) {
             stats->nodes_per_level[l] = c.nodes[l];
@@ -254,6 +258,21 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->shadow_boxes_tested = c.shadow_boxes; stats->shadow_prim_tests = c.shadow_prims;
         stats->shadow_rays_walked = (s->last_accel == RT_ACCEL_LBVH && p.instrument) ? c.shadow_walks : stats->rays_shadow;
         stats->accel_used = s->last_accel; stats->kernel_launches = launches; stats->queue_regrows = regrows;
+        if (p.instrument && s->last_accel == RT_ACCEL_LBVH) {
+            for (int l = 0; l <= p.max_depth; l++)
+                for (int k = 0; k < 2; k++) {
+                    const WalkClock& w = c.clock[k][l];
+                    if (!w.warps) continue;
+                    const double first = (double)~w.inv_first, empty = (double)~w.inv_empty, last = (double)w.last;
+                    (k ? stats->shadow_span_ms : stats->trace_span_ms)[l] = (last - first) * 1e-6;
+                    (k ? stats->shadow_drain_ms : stats->trace_drain_ms)[l] = (last - empty) * 1e-6;
+                    (k ? stats->shadow_warp_drain_ms : stats->trace_warp_drain_ms)[l] = (double)w.drain_sum / w.warps * 1e-6;
+                    (k ? stats->shadow_drain_steps : stats->trace_drain_steps)[l] = (double)w.drain_steps / w.warps;
+                    (k ? stats->shadow_drain_lanes : stats->trace_drain_lanes)[l] =
+                        w.drain_steps ? (double)w.drain_lane_steps / (double)w.drain_steps : 0.0;
+                    if (!k) stats->trace_drain_steals[l] = (double)w.drain_steals / w.warps;
+                }
+        }
         if (s->prof_levels > 0) {
             float t = 0.0f;
             for (int l = 0; l < s->prof_levels; l++) {

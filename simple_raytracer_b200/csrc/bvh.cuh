@@ -208,8 +208,25 @@ struct BvhAccelT {
     //                                       (warp collectives allowed inside)
     //   job.next(o, ray, tmin, tmax)     -> true when the finished lane's job has another ray
     //   Job::kOrdered                    -> visit near children first (closest hit) or not (any hit)
+    //   Job::kSteal                      -> once the job queue is dry, lanes whose ray has finished take
+    //                                       subtrees off the stacks of the lanes still walking (a kernel
+    //                                       otherwise ends with ~0.3 ms in which a few long rays keep a few
+    //                                       lanes of every warp busy).  Needs a result that is a fold over
+    //                                       the primitives in any order:
+    //   job.adopt(src, take, o, ray)     -> ALL lanes; lanes with `take` copy the ray state of lane src
+    //   job.merge(src, mine)             -> ALL lanes; the lane with `mine` folds lane src's result into its own
+    //   job.share(group, tmax)           -> the lanes (mask `group`, >= 2) walking one ray: returns the culling
+    //                                       bound they should all use from now on, < 0 to stop
+    RT_DEV static unsigned long long globaltimer()
+    {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        return t;
+    }
+
     template <class Job>
-    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes, int inner_min = 1, int leaf_min = 1) const
+    RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes, int inner_min = 1, int leaf_min = 1,
+                                WalkClock* clock = nullptr, bool steal = true) const
     {
         constexpr int kDone = kWalkDone;
         constexpr unsigned kFull = 0xffffffffu;
@@ -228,11 +245,17 @@ struct BvhAccelT {
         int stack[kBvhStack];
         const int tid = threadIdx.x;
         int sp = 0, node = kDone, leaf = 0;
+        int bot = 0;                 // stack bottom: entries below it were given to helper lanes
+        unsigned owner = lane;       // != lane: this lane walks a subtree for lane `owner`
         bool alive = false, pool_empty = false;
         RayQ rq = make_rayq(mk3(0.f, 0.f, 0.f), mk3(1.f, 1.f, 1.f));
         float tmin = 0.f, tmax = 0.f;
+        unsigned long long t_empty = 0;
+        bool worked = false;
+        unsigned d_steps = 0, d_lanes = 0, d_steals = 0;
+        if (kCount && clock && lane == 0) atomicMax(&clock->inv_first, ~globaltimer());
         auto pop = [&]() {
-            if (sp == 0) return kDone;
+            if (sp == bot) return kDone;
             --sp;
             return sp < kSmemStack ? s_stack[sp][tid] : stack[sp - kSmemStack];
         };
@@ -243,7 +266,7 @@ struct BvhAccelT {
             sp++;
         };
         auto start = [&](bool need_walk, V3 o, V3 ray) {
-            sp = 0; leaf = 0;
+            sp = 0; bot = 0; leaf = 0; owner = lane;
             node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
             rq = make_rayq(o, ray);
         };
@@ -253,7 +276,10 @@ struct BvhAccelT {
                 unsigned base = 0;
                 if (lane == 0) base = atomicAdd(counter, (unsigned)__popc(dead));
                 base = __shfl_sync(kFull, base, 0);
-                if (base + (unsigned)__popc(dead) >= total) pool_empty = true;
+                if (base + (unsigned)__popc(dead) >= total) {
+                    pool_empty = true;
+                    if (kCount && clock) t_empty = globaltimer();
+                }
                 if (!alive) {
                     const unsigned j = base + (unsigned)__popc(dead & lt);
                     if (j < total) {
@@ -264,9 +290,56 @@ struct BvhAccelT {
                     }
                 }
             }
+            if constexpr (Job::kSteal) {
+                if (pool_empty && steal) {
+                    const unsigned idle = __ballot_sync(kFull, !alive);
+                    // (only the shared-memory part of a stack can be read by another lane)
+                    const int avail = alive ? min(sp, kSmemStack) - bot : 0;
+                    const unsigned donors = __ballot_sync(kFull, avail > 0);
+                    if (idle != 0u && donors != 0u) {
+                        // the r-th idle lane takes the lower half (the older entries: the farther,
+                        // larger subtrees) of the r-th donor's stack, order kept
+                        const int pairs = min(__popc(idle), __popc(donors));
+                        const int rank = __popc((alive ? donors : idle) & lt);
+                        const bool give = avail > 0 && rank < pairs;
+                        const bool take = !alive && rank < pairs;
+                        const int n_give = give ? (avail + 1) / 2 : 0;
+                        const int src = take ? (int)__fns(donors, 0, rank + 1) : (int)lane;
+                        const int from = __shfl_sync(kFull, bot, src), n_take = __shfl_sync(kFull, n_give, src);
+                        const float tmin_s = __shfl_sync(kFull, tmin, src), tmax_s = __shfl_sync(kFull, tmax, src);
+                        const unsigned owner_s = __shfl_sync(kFull, owner, src);
+                        V3 o, ray;
+                        job.adopt(src, take, o, ray);
+                        if (give) bot += n_give;
+                        if (kCount) d_steals += (unsigned)pairs;
+                        if (take) {
+                            alive = true; owner = owner_s;
+                            tmin = tmin_s; tmax = tmax_s;
+                            rq = make_rayq(o, ray);
+                            const int col = tid - (int)lane + src;
+                            for (int i = 0; i < n_take; i++) s_stack[i][tid] = s_stack[from + i][col];
+                            sp = n_take; bot = 0; leaf = 0;
+                            node = pop();
+                            if (node < 0) { leaf = node; node = pop(); }
+                        }
+                        __syncwarp();
+                    }
+                    // lanes on the same ray share what bounds / ends the walk
+                    const unsigned group = __match_any_sync(kFull, alive ? owner : 32u + lane);
+                    if (group & (group - 1u)) {
+                        tmax = job.share(group, tmax);
+                        if (tmax < 0.0f) { node = kDone; leaf = 0; sp = bot; }
+                    }
+                }
+            }
             if (!__any_sync(kFull, alive)) break;
+            if (kCount) worked = true;
             // inner nodes, until every live lane holds a leaf (or has nothing left)
             for (;;) {
+                if (kCount && pool_empty) {
+                    d_steps++;
+                    d_lanes += (unsigned)__popc(__ballot_sync(kFull, alive && (unsigned)node < (unsigned)kDone));
+                }
                 if (alive && (unsigned)node < (unsigned)kDone) {
                     node = step<Job::kOrdered>(nd, node, rq, tmin, tmax, push, pop);
                     if (node < 0 && leaf == 0) {
@@ -289,7 +362,7 @@ struct BvhAccelT {
                     for (int k = 0; k < count; k++) {
                         if (kCount) cnt_prims++;
                         tmax = job.visit(pr + (size_t)(first + k) * kTriWords, tmax);
-                        if (tmax < 0.0f) { node = kDone; sp = 0; break; }
+                        if (tmax < 0.0f) { node = kDone; sp = bot; break; }
                     }
                     if (node < 0) {
                         leaf = node;
@@ -297,7 +370,23 @@ struct BvhAccelT {
                     }
                 }
             }
-            const bool fin = alive && node == kDone && leaf == 0;
+            bool fin = alive && node == kDone && leaf == 0;
+            if constexpr (Job::kSteal) {
+                if (pool_empty) {
+                    // helpers that are done hand their result to the owner of the ray and go idle
+                    unsigned hf = __ballot_sync(kFull, fin && owner != lane);
+                    while (hf) {
+                        const int src = __ffs(hf) - 1;
+                        hf &= hf - 1u;
+                        const unsigned to = __shfl_sync(kFull, owner, src);
+                        job.merge(src, lane == to);
+                    }
+                    if (fin && owner != lane) { alive = false; owner = lane; fin = false; }
+                    // an owner retires once nobody walks for it any more
+                    const unsigned group = __match_any_sync(kFull, alive ? owner : 32u + lane);
+                    if (fin && (group & ~(1u << lane)) != 0u) fin = false;
+                }
+            }
             if (__any_sync(kFull, fin)) {
                 job.retire(fin);
                 if (fin) {
@@ -306,6 +395,18 @@ struct BvhAccelT {
                     if (job.next(o, ray, tmin, tmax)) start(true, o, ray);
                     else alive = false;
                 }
+            }
+        }
+        if (kCount && clock && lane == 0) {
+            const unsigned long long t = globaltimer();
+            atomicMax(&clock->last, t);
+            if (worked) {
+                atomicMax(&clock->inv_empty, ~t_empty);
+                atomicAdd(&clock->drain_sum, t - t_empty);
+                atomicAdd(&clock->warps, 1u);
+                atomicAdd(&clock->drain_steps, (unsigned long long)d_steps);
+                atomicAdd(&clock->drain_lane_steps, (unsigned long long)d_lanes);
+                atomicAdd(&clock->drain_steals, (unsigned long long)d_steals);
             }
         }
     }

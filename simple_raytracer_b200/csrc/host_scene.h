@@ -49,6 +49,42 @@ struct DevBuf {
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
+constexpr int kMaxSubframes = 8;
+
+// Streams and events of the LBVH pipeline's launch chains (render.cu): sub-frame j runs
+// trace -> spawn on main[j] (main[0] is not used: chain 0 runs on the caller's stream) and
+// shadow -> colour on side[j].  Created on first use, travels with the Workspace.
+struct ChainStreams {
+    cudaStream_t main[kMaxSubframes] = { nullptr }, side[kMaxSubframes] = { nullptr };
+    cudaEvent_t fork[kMaxSubframes][kMaxLevels] = { { nullptr } };
+    cudaEvent_t side_done[kMaxSubframes] = { nullptr }, main_done[kMaxSubframes] = { nullptr }, begin = nullptr;
+    int chains = 0;      // chains whose streams / events exist
+    ChainStreams() = default;
+    ChainStreams(const ChainStreams&) = delete;
+    ChainStreams& operator=(const ChainStreams&) = delete;
+    ChainStreams(ChainStreams&& o) noexcept { steal(o); }
+    ChainStreams& operator=(ChainStreams&& o) noexcept
+    {
+        if (this != &o) { release(); steal(o); }
+        return *this;
+    }
+    ~ChainStreams() { release(); }
+    bool ensure(int n);  // render.cu
+    void sync() const;
+    void release();
+private:
+    void steal(ChainStreams& o)
+    {
+        for (int j = 0; j < kMaxSubframes; j++) {
+            main[j] = o.main[j]; side[j] = o.side[j]; side_done[j] = o.side_done[j]; main_done[j] = o.main_done[j];
+            o.main[j] = o.side[j] = nullptr; o.side_done[j] = o.main_done[j] = nullptr;
+            for (int l = 0; l < kMaxLevels; l++) { fork[j][l] = o.fork[j][l]; o.fork[j][l] = nullptr; }
+        }
+        begin = o.begin; o.begin = nullptr;
+        chains = o.chains; o.chains = 0;
+    }
+};
+
 // Wavefront work buffers: queues + node records per generation (scene_device.h).
 struct Workspace {
     DevBuf level_mem[kMaxLevels];
@@ -57,6 +93,7 @@ struct Workspace {
     DevBuf tiles;          // RGBA8 [local_tile][row][col]
     DevBuf primary_ids;
     DevBuf rgb24, flags8;  // scanline-order planes for rt_download_framebuffer
+    ChainStreams chains;
     int device = -1;
 };
 
@@ -79,19 +116,18 @@ struct SceneHost {
     Workspace ws;
 
     cudaStream_t stream = nullptr;      // owned
-    cudaStream_t stream2 = nullptr;     // owned: the shadow -> colour chain of the LBVH pipeline (render.cu)
-    cudaEvent_t ev_fork[kMaxLevels] = { nullptr }, ev_join = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t prof_ev[kMaxLevels + 2] = { nullptr };   // params.profile: boundaries of the generations
     cudaEvent_t prof_mid[kMaxLevels][2] = { { nullptr } };   // LBVH pipeline: after trace, after shadow
     bool prof_split = false;
     int prof_levels = 0;                                 // events recorded by the last frame (0 = none)
-    Counters* h_counters = nullptr;     // pinned
+    Counters* h_counters = nullptr;     // pinned, one per sub-frame
 
     // last frame
     bool rendered = false;
     RtRenderParams last{};
     int last_local_rows = 0, last_local_pixels = 0, last_accel = 0, last_launches = 0;
+    int last_subframes = 1;             // launch chains of the last frame (its queues were cut that many ways)
     bool have_primary_ids = false;
 };
 
@@ -112,6 +148,9 @@ struct TileLayout {
 TileLayout tile_layout(int height, int width, int world, int tile_rows);
 int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cudaStream_t stream, int* launches);
 int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* demand /* per level or null */);
+// Reads the counters of the last frame (stream must be idle): sums the sub-frames into `total`,
+// returns true when some queue overflowed and then fills `demand` with what to grow to.
+bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels]);
 void stash_workspace(Workspace&& ws);
 
 }  // namespace rt

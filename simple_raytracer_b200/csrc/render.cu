@@ -85,7 +85,63 @@ static size_t level_bytes(int level, size_t cap, bool bvh, int nl)
     // level 0 has no ray queue (primary rays are generated in place)
     size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16 + 8;
     if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 4;    // hp, hb, node_list, sh (wavefront_bvh.cuh)
-    return cap * per_slot + 256;
+    // slop: every sub-frame's slice starts on a 256-byte boundary
+    return cap * per_slot + 512 * (kMaxSubframes + 1);
+}
+
+// Launch chains of a frame.  Sub-frames only pay when the per-kernel tails are a large part
+// of the frame (few pixels per GPU); profiled / instrumented frames and the brute-force
+// path run as one serial chain.
+static int pick_subframes(const RtRenderParams& p, int accel, const TileLayout& tl)
+{
+    if (accel != RT_ACCEL_LBVH || p.profile || p.instrument) return 1;
+    static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
+    if (!overlap_knob) return 1;
+    static const int knob = tuning_int("RT_SUBFRAMES", 0, 0, kMaxSubframes);
+    int k = p.subframes ? p.subframes : knob;
+    if (k == 0) k = 1;      // measured (tools/subframe_sweep.sh): more chains never paid, see DESIGN.md 5.4
+    return std::max(1, std::min(k, tl.n_local_tiles));
+}
+
+bool ChainStreams::ensure(int n)
+{
+    if (!begin && !cuda_ok(cudaEventCreateWithFlags(&begin, cudaEventDisableTiming), "cudaEventCreate")) return false;
+    for (int j = chains; j < n; j++) {
+        if (j > 0 && !cuda_ok(cudaStreamCreateWithFlags(&main[j], cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        if (!cuda_ok(cudaStreamCreateWithFlags(&side[j], cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        for (int l = 0; l < kMaxLevels; l++)
+            if (!cuda_ok(cudaEventCreateWithFlags(&fork[j][l], cudaEventDisableTiming), "cudaEventCreate")) return false;
+        if (!cuda_ok(cudaEventCreateWithFlags(&side_done[j], cudaEventDisableTiming), "cudaEventCreate") ||
+            !cuda_ok(cudaEventCreateWithFlags(&main_done[j], cudaEventDisableTiming), "cudaEventCreate")) return false;
+        chains = j + 1;
+    }
+    return true;
+}
+
+void ChainStreams::sync() const
+{
+    for (int j = 0; j < chains; j++) {
+        if (main[j]) cudaStreamSynchronize(main[j]);
+        if (side[j]) cudaStreamSynchronize(side[j]);
+    }
+}
+
+void ChainStreams::release()
+{
+    for (int j = 0; j < kMaxSubframes; j++) {
+        if (main[j]) cudaStreamDestroy(main[j]);
+        if (side[j]) cudaStreamDestroy(side[j]);
+        if (side_done[j]) cudaEventDestroy(side_done[j]);
+        if (main_done[j]) cudaEventDestroy(main_done[j]);
+        main[j] = side[j] = nullptr; side_done[j] = main_done[j] = nullptr;
+        for (int l = 0; l < kMaxLevels; l++) {
+            if (fork[j][l]) cudaEventDestroy(fork[j][l]);
+            fork[j][l] = nullptr;
+        }
+    }
+    if (begin) cudaEventDestroy(begin);
+    begin = nullptr;
+    chains = 0;
 }
 
 static int pick_accel(const SceneHost* s, int requested)
@@ -111,11 +167,12 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
     const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
     const size_t npx = (size_t)tl.n_local_pixels;
     const bool bvh = pick_accel(s, p.accel) == RT_ACCEL_LBVH;
-    if (!ws.counters.reserve(sizeof(Counters)) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
+    if (!ws.counters.reserve(sizeof(Counters) * kMaxSubframes) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
     if (p.instrument && !ws.primary_ids.reserve(npx * sizeof(int))) return RT_E_NOMEM;
     for (int l = 0; l <= p.max_depth; l++) {
         size_t want;
-        if (l == 0) want = npx;
+        // level 0: one slot per pixel; the sub-frames' virtual layouts pad up to one tile each
+        if (l == 0) want = npx + (size_t)kMaxSubframes * p.tile_rows * s->width;
         else if (demand) want = std::max<size_t>((size_t)ws.capacity[l], (size_t)(demand[l] * 1.25) + 1024);
         else {
             // rays of generation l per pixel seen on the example scenes: <= ~1.2, 0.5, 0.25, ...
@@ -132,15 +189,22 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
     return RT_OK;
 }
 
-static void fill_levels(const SceneHost* s, int max_depth, bool bvh, FrameParams* P)
+// Capacity of one sub-frame's queue of generation l when the level memory is cut K ways.
+static size_t chain_capacity(const SceneHost* s, int l, int K, size_t chain_pixels)
+{
+    return l == 0 ? chain_pixels : (size_t)s->ws.capacity[l] / (size_t)K;
+}
+
+static void fill_levels(const SceneHost* s, int max_depth, bool bvh, int K, int j, size_t chain_pixels, FrameParams* P)
 {
     const Workspace& ws = s->ws;
     for (int l = 0; l < kMaxLevels; l++) {
         LevelBuffers& L = P->level[l];
         std::memset(&L, 0, sizeof L);
         if (l > max_depth) continue;
-        const size_t cap = (size_t)ws.capacity[l];
-        char* base = ws.level_mem[l].as<char>();
+        const size_t cap = chain_capacity(s, l, K, chain_pixels);
+        const size_t slice = (level_bytes(l, cap, bvh, s->nl) - 512 * kMaxSubframes + 255) / 256 * 256;
+        char* base = ws.level_mem[l].as<char>() + (size_t)j * slice;
         L.capacity = (int)cap;
         if (l > 0) {
             L.rq_o = (float4*)base; base += cap * 16;
@@ -170,7 +234,19 @@ static void launch_level(const FrameParams& P, int level, int grid, size_t smem,
     level_kernel<Factory><<<grid, kBlock, smem, st>>>(P, level);
 }
 
+static int persistent_grid(long long work, int sms, int mult)
+{
+    return (int)std::max<long long>(1, std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * mult));
+}
+
 // Enqueues one frame on `stream`.  The queues must already be sized (ensure_workspace).
+//
+// LBVH pipeline: the rank's tiles are dealt out to K sub-frames (tile t of the rank's buffer
+// -> sub-frame t % K), each a complete, independent chain of generation launches with its own
+// queues and counters: trace(g) -> spawn(g) -> trace(g+1) ... on one stream and
+// shadow(g) -> colour(g) on a second one.  A persistent walk kernel ends with a tail in which
+// a few long rays keep a few warps busy; with 2K streams the other chains' blocks fill the
+// SMs during that tail (the frame of a 1/8 shard is otherwise half tails).
 int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cudaStream_t stream, int* launches)
 {
     const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
@@ -179,25 +255,48 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         const int rc = build_bvh(s);
         if (rc != RT_OK) return rc;
     }
-    FrameParams P;
-    std::memset(&P, 0, sizeof P);
-    P.scene = scene_view(s);
-    P.cam = s->cam;
-    fill_levels(s, p.max_depth, accel == RT_ACCEL_LBVH, &P);
-    P.counters = s->ws.counters.as<Counters>();
-    P.tiles = tiles_out ? tiles_out : s->ws.tiles.as<uchar4>();
-    P.primary_ids = p.instrument ? s->ws.primary_ids.as<int>() : nullptr;
-    P.max_depth = p.max_depth; P.epsilon = p.epsilon;
-    P.rank = p.rank; P.world = p.world_size; P.tile_rows = p.tile_rows;
-    P.n_local_rows = tl.n_local_rows; P.n_local_pixels = tl.n_local_pixels;
+    const bool lbvh = accel == RT_ACCEL_LBVH;
+    const int K = pick_subframes(p, accel, tl);
+    static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
+    const bool overlap = lbvh && overlap_knob && !p.profile && !p.instrument;
+    // sub-frame j is virtual rank (rank + world*j) of (world*K): the same interleaved-tile arithmetic
+    const TileLayout vl = tile_layout(s->height, s->width, p.world_size * K, p.tile_rows);
+
     static const int refill = tuning_int("RT_REFILL_LANES", 6, 1, 32);
     static const int grid_mult = tuning_int("RT_GRID_MULT", 16, 1, 64);
-    P.refill_lanes = refill;
     static const int inner_min = tuning_int("RT_INNER_MIN_LANES", 4, 1, 32);
     static const int leaf_min = tuning_int("RT_LEAF_MIN_LANES", 1, 1, 32);
-    P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
+    static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
+    // Work sharing in the walk kernels' tails.  0: never, 1: always, 2: for launches of at most
+    // RT_STEAL_MAX_KRAYS thousand queue slots.  Measured on the 4K stress frame (tools/steal_sweep.sh):
+    // 1/8 shard 7.43 -> 7.00 ms, 1/4 shard 12.34 -> 12.22, whole frame 42.3 -> 44.5 (the sharing
+    // build's main loop carries more state), hence the size rule.
+    static const int steal_env = tuning_int("RT_STEAL", 2, 0, 2);
+    static const int steal_shadow_env = tuning_int("RT_STEAL_SHADOW", 2, 0, 2);
+    static const long long steal_max_work = 1000LL * tuning_int("RT_STEAL_MAX_KRAYS", 1500, 0, 2000000);
+    const int steal = p.work_sharing == 1 ? 1 : p.work_sharing == 2 ? 0 : steal_env;
+    const int steal_shadow = p.work_sharing == 1 ? 1 : p.work_sharing == 2 ? 0 : steal_shadow_env;
+    static const int shadow_mult = tuning_int("RT_SHADOW_GRID_MULT", 0, 0, 64);   // 0: same as RT_GRID_MULT
 
-    RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters), stream));
+    static thread_local FrameParams PS[kMaxSubframes];
+    for (int j = 0; j < K; j++) {
+        FrameParams& P = PS[j];
+        std::memset(&P, 0, sizeof P);
+        P.scene = scene_view(s);
+        P.cam = s->cam;
+        fill_levels(s, p.max_depth, lbvh, K, j, (size_t)vl.n_local_pixels, &P);
+        P.counters = s->ws.counters.as<Counters>() + j;
+        P.tiles = tiles_out ? tiles_out : s->ws.tiles.as<uchar4>();
+        P.primary_ids = p.instrument ? s->ws.primary_ids.as<int>() : nullptr;
+        P.max_depth = p.max_depth; P.epsilon = p.epsilon;
+        P.rank = p.rank + p.world_size * j; P.world = p.world_size * K; P.tile_rows = p.tile_rows;
+        P.n_local_rows = vl.n_local_rows; P.n_local_pixels = vl.n_local_pixels;
+        P.out_mul = K; P.out_add = j; P.out_tiles = tl.n_local_tiles;
+        P.refill_lanes = refill; P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
+        P.steal = 1;
+    }
+
+    RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
     const int sms = sm_count(s->device);
     const size_t smem = (size_t)(s->nf * kTriWords + s->ns * kSphWords) * sizeof(float4);
     const bool stage = accel == RT_ACCEL_BRUTE && smem <= 48 * 1024;
@@ -210,75 +309,87 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             for (int j = 0; j < 2; j++)
                 if (!s->prof_mid[k][j]) RT_CUDA(cudaEventCreate(&s->prof_mid[k][j]));
     }
-    s->prof_split = p.profile && accel == RT_ACCEL_LBVH;
-    static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
-    const bool overlap = accel == RT_ACCEL_LBVH && overlap_knob && !p.profile && !p.instrument;
-    if (overlap && !s->stream2) {
-        RT_CUDA(cudaStreamCreateWithFlags(&s->stream2, cudaStreamNonBlocking));
-        for (int k = 0; k < kMaxLevels; k++) RT_CUDA(cudaEventCreateWithFlags(&s->ev_fork[k], cudaEventDisableTiming));
-        RT_CUDA(cudaEventCreateWithFlags(&s->ev_join, cudaEventDisableTiming));
+    s->prof_split = p.profile && lbvh;
+    ChainStreams& cs = s->ws.chains;
+    if (overlap) {
+        if (!cs.ensure(K)) return RT_E_CUDA;
+        if (K > 1) {
+            RT_CUDA(cudaEventRecord(cs.begin, stream));    // the counters are cleared
+            for (int j = 1; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
+        }
     }
     for (int l = 0; l <= p.max_depth; l++) {
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
-        // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
-        const long long work = l == 0 ? tl.n_local_pixels : s->ws.capacity[l];
-        int grid = (int)std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * grid_mult);
-        if (grid < 1) grid = 1;
-        if (accel == RT_ACCEL_LBVH) {
+        for (int j = 0; j < K; j++) {
+            const FrameParams& P = PS[j];
+            // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
+            const long long work = P.level[l].capacity;
+            const int grid = persistent_grid(work, sms, grid_mult);
+            if (!lbvh) {
+                if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
+                else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
+                n++;
+                continue;
+            }
             // trace: one thread per ray; shadow: one chain per node; colour / spawn: one thread per node
-            const long long sh_work = work * std::max(1, s->nl);
-            const int sh_grid = (int)std::max<long long>(1, std::min<long long>((sh_work + kBlock - 1) / kBlock, (long long)sms * grid_mult));
-            static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
-            if (p.instrument) bvh_trace_kernel<true><<<grid, kBlock, 0, stream>>>(P, l);
-            else bvh_trace_kernel<false><<<grid, kBlock, 0, stream>>>(P, l);
+            cudaStream_t ms = (overlap && j > 0) ? cs.main[j] : stream;
+            const int sh_grid = persistent_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
+            const bool sharing = steal == 1 || (steal == 2 && work <= steal_max_work);
+            if (p.instrument) {
+                if (sharing) bvh_trace_kernel<true, true><<<grid, kBlock, 0, ms>>>(P, l);
+                else bvh_trace_kernel<true, false><<<grid, kBlock, 0, ms>>>(P, l);
+            } else {
+                if (sharing) bvh_trace_kernel<false, true><<<grid, kBlock, 0, ms>>>(P, l);
+                else bvh_trace_kernel<false, false><<<grid, kBlock, 0, ms>>>(P, l);
+            }
             n++;
             // shadow -> colour depends only on this generation's hits, spawn -> next trace too:
             // two chains on two streams (profiled / instrumented frames stay serial)
-            cudaStream_t side = stream;
+            cudaStream_t side = ms;
             if (overlap) {
-                RT_CUDA(cudaEventRecord(s->ev_fork[l], stream));
-                RT_CUDA(cudaStreamWaitEvent(s->stream2, s->ev_fork[l], 0));
-                side = s->stream2;
+                RT_CUDA(cudaEventRecord(cs.fork[j][l], ms));
+                RT_CUDA(cudaStreamWaitEvent(cs.side[j], cs.fork[j][l], 0));
+                side = cs.side[j];
                 // the critical chain first: spawn feeds the next generation's trace
-                if (l < p.max_depth) { bvh_shade_kernel<false, true><<<grid, kBlock, 0, stream>>>(P, l); n++; }
+                if (l < p.max_depth) { bvh_shade_kernel<false, true><<<grid, kBlock, 0, ms>>>(P, l); n++; }
             }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
             if (s->nl) {
-                if (p.instrument) bvh_shadow_kernel<true, false><<<sh_grid, kBlock, 0, side>>>(P, l);
-                else if (near_first) bvh_shadow_kernel<false, true><<<sh_grid, kBlock, 0, side>>>(P, l);
-                else bvh_shadow_kernel<false, false><<<sh_grid, kBlock, 0, side>>>(P, l);
+                const bool sh_sharing = steal_shadow == 1 || (steal_shadow == 2 && work <= steal_max_work);
+                if (p.instrument) {
+                    if (sh_sharing) bvh_shadow_kernel<true, false, true><<<sh_grid, kBlock, 0, side>>>(P, l);
+                    else bvh_shadow_kernel<true, false, false><<<sh_grid, kBlock, 0, side>>>(P, l);
+                } else if (near_first) bvh_shadow_kernel<false, true, false><<<sh_grid, kBlock, 0, side>>>(P, l);
+                else if (sh_sharing) bvh_shadow_kernel<false, false, true><<<sh_grid, kBlock, 0, side>>>(P, l);
+                else bvh_shadow_kernel<false, false, false><<<sh_grid, kBlock, 0, side>>>(P, l);
                 n++;
             }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
-            if (overlap) {
-                bvh_shade_kernel<true, false><<<grid, kBlock, 0, side>>>(P, l);
-                n++;
-            } else {
-                bvh_shade_kernel<true, true><<<grid, kBlock, 0, stream>>>(P, l);
-                n++;
-            }
-        } else {
-            if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
-            else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
+            if (overlap) bvh_shade_kernel<true, false><<<grid, kBlock, 0, side>>>(P, l);
+            else bvh_shade_kernel<true, true><<<grid, kBlock, 0, ms>>>(P, l);
             n++;
         }
     }
-    if (overlap) {
-        RT_CUDA(cudaEventRecord(s->ev_join, s->stream2));
-        RT_CUDA(cudaStreamWaitEvent(stream, s->ev_join, 0));
-    }
     if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 1], stream));
-    for (int l = p.max_depth - 1; l >= 0; l--) {
-        const long long work = l == 0 ? tl.n_local_pixels : s->ws.capacity[l];
-        int grid = (int)std::min<long long>((work + 255) / 256, (long long)sms * 8);
-        if (grid < 1) grid = 1;
-        combine_kernel<<<grid, 256, 0, stream>>>(P, l);
-        n++;
-    }
-    if (p.max_depth == 0) {   // no backward pass above: generation 0 still has to be quantised
-        int grid = (int)std::min<long long>((tl.n_local_pixels + 255) / 256, (long long)sms * 8);
-        combine_kernel<<<grid, 256, 0, stream>>>(P, 0);
-        n++;
+    // bottom-up combine per chain, on the chain's main stream once its colour kernels are done
+    for (int j = 0; j < K; j++) {
+        const FrameParams& P = PS[j];
+        cudaStream_t ms = (overlap && j > 0) ? cs.main[j] : stream;
+        if (overlap) {
+            RT_CUDA(cudaEventRecord(cs.side_done[j], cs.side[j]));
+            RT_CUDA(cudaStreamWaitEvent(ms, cs.side_done[j], 0));
+        }
+        for (int l = std::max(p.max_depth - 1, 0); l >= 0; l--) {
+            // (max_depth == 0: no backward pass, but generation 0 still has to be quantised)
+            const long long work = P.level[l].capacity;
+            const int grid = (int)std::max<long long>(1, std::min<long long>((work + 255) / 256, (long long)sms * 8));
+            combine_kernel<<<grid, 256, 0, ms>>>(P, l);
+            n++;
+        }
+        if (overlap && j > 0) {
+            RT_CUDA(cudaEventRecord(cs.main_done[j], ms));
+            RT_CUDA(cudaStreamWaitEvent(stream, cs.main_done[j], 0));
+        }
     }
     RT_CUDA(cudaGetLastError());
     if (p.profile) {
@@ -291,10 +402,49 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     s->rendered = true;
     s->last = p;
     s->last_local_rows = tl.n_local_rows; s->last_local_pixels = tl.n_local_pixels;
-    s->last_accel = accel; s->last_launches = n + 1;
+    s->last_accel = accel; s->last_launches = n + 1; s->last_subframes = K;
     s->have_primary_ids = p.instrument != 0;
     if (launches) *launches = n + 1;
     return RT_OK;
+}
+
+// Sums the sub-frames' counters of the last frame and checks every queue against the slice
+// it had.  demand: what the whole generation would have needed had every slice been as full
+// as the fullest one.
+bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels])
+{
+    const int K = s->last_subframes;
+    const RtRenderParams& p = s->last;
+    Counters t;
+    std::memset(&t, 0, sizeof t);
+    bool overflow = false;
+    double factor = 1.0;
+    unsigned fullest[kMaxLevels] = { 0 };
+    for (int j = 0; j < K; j++) {
+        const Counters& c = s->h_counters[j];
+        overflow = overflow || c.overflow != 0;
+        t.overflow |= c.overflow;
+        for (int l = 0; l < kMaxLevels; l++) {
+            t.rays[l] += c.rays[l]; t.nodes[l] += c.nodes[l]; t.rays_reflect[l] += c.rays_reflect[l];
+            fullest[l] = std::max(fullest[l], c.rays[l]);
+            if (l >= 1 && l <= p.max_depth) {
+                const unsigned cap = (unsigned)(s->ws.capacity[l] / K);
+                if (c.rays[l] > cap) {
+                    overflow = true;
+                    // a truncated generation under-reports what the deeper ones need: scale those up with it
+                    factor = std::max(factor, (double)c.rays[l] / (double)std::max(1u, cap));
+                }
+            }
+        }
+        t.bvh_nodes += c.bvh_nodes; t.prim_tests += c.prim_tests; t.texels += c.texels;
+        t.shadow_boxes += c.shadow_boxes; t.shadow_prims += c.shadow_prims; t.shadow_walks += c.shadow_walks;
+        if (j == 0) std::memcpy(t.clock, c.clock, sizeof t.clock);      // instrumented frames have one chain
+    }
+    if (total) *total = t;
+    if (demand)
+        for (int l = 0; l < kMaxLevels; l++)
+            demand[l] = (unsigned)std::min(2.0e9, (double)fullest[l] * K * factor + 64.0 * K);
+    return overflow;
 }
 
 int launch_split_planes(SceneHost* s, cudaStream_t st)

@@ -114,6 +114,14 @@ constexpr int kRayKindReflect = 1;   // bit0: 0 = transmission ray, 1 = reflecti
 constexpr int kRayStateExiting = 2;  // bit1: previous_ray_state == EXITING
 constexpr int kRayNStackShift = 2;   // bits 2..5: medium stack length
 
+// Instrumented walk kernels: %globaltimer stamps (ns).  first / empty hold ~t so that a zeroed
+// record means "unset" and atomicMax finds the minimum.
+struct WalkClock {
+    unsigned long long inv_first, inv_empty, last, drain_sum;
+    unsigned long long drain_steps, drain_lane_steps, drain_steals;   // inner-loop passes after the queue ran dry, lanes active in them
+    unsigned int warps, pad;
+};
+
 struct Counters {
     unsigned int rays[kMaxLevels];        // rays queued for level d (level 0: unused)
     unsigned int nodes[kMaxLevels];       // hits shaded at level d
@@ -125,6 +133,7 @@ struct Counters {
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
     unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
+    WalkClock clock[2][kMaxLevels];                     // instrumented LBVH frames: [0] trace, [1] shadow kernels
 };
 
 struct FrameParams {
@@ -139,9 +148,14 @@ struct FrameParams {
     int rank, world, tile_rows;
     int n_local_rows;     // rows of the tile buffer (padded to whole tiles)
     int n_local_pixels;   // n_local_rows * width
+    // Sub-frames (render.cu): a rank's tiles are dealt out to out_mul independent launch
+    // chains; for chain j, `rank`/`world` above are the VIRTUAL ones (rank + world*j, world*out_mul)
+    // and virtual local tile vt is tile vt*out_mul + out_add of the rank's tile buffer.
+    int out_mul, out_add, out_tiles;
     int refill_lanes;     // persistent kernels: fetch new rays when this many lanes of a warp are idle
     int inner_min_lanes;  // ... leave the inner-node loop when fewer lanes than this can still descend
     int leaf_min_lanes;   // ... leave the leaf loop when fewer lanes than this hold a leaf
+    int steal;            // ... idle lanes take subtrees from busy ones once the queue is dry (closest-hit walks)
 };
 
 }  // namespace rt

@@ -36,6 +36,17 @@ RT_DEV int global_row(const FrameParams& P, int local_row)
     return (tile * P.world + P.rank) * P.tile_rows + in_tile;
 }
 
+// Slot of the rank's tile buffer that pixel slot `slot` of this sub-frame lands in; -1 for
+// the virtual padding tiles past the end of the buffer.
+RT_DEV int out_slot(const FrameParams& P, unsigned slot)
+{
+    if (P.out_mul == 1) return (int)slot;
+    const unsigned per_tile = (unsigned)(P.tile_rows * P.cam.width);
+    const unsigned vt = slot / per_tile, rem = slot - vt * per_tile;
+    const unsigned t = vt * (unsigned)P.out_mul + (unsigned)P.out_add;
+    return t < (unsigned)P.out_tiles ? (int)(t * per_tile + rem) : -1;
+}
+
 // Shared-memory staging of the primitive tables for small scenes: every lane of a
 // warp walks the same primitive at the same time, so the reads are broadcasts.
 template <bool kStage>
@@ -222,7 +233,7 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
         const unsigned hm = __ballot_sync(0xffffffffu, hit);
         if ((threadIdx.x & 31) == 0 && hm) atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
     }
-    if (active && level == 0 && P.primary_ids) P.primary_ids[slot] = hit ? S.obj[h.obj].z : 0;
+    if (active && level == 0 && P.primary_ids) P.primary_ids[out_slot(P, slot)] = hit ? S.obj[h.obj].z : 0;
     if (P.primary_ids) {   // instrumented frame: one texel per shaded hit on a textured object
         const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[h.obj].y >= 0);
         if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
@@ -294,7 +305,8 @@ __global__ void __launch_bounds__(256) combine_kernel(const __grid_constant__ Fr
                 if (q == (int)0x80000000) { flags |= 1u << k; out[k] = 0; }
                 else out[k] = (unsigned char)min(max(q, 0), 255);
             }
-            P.tiles[slot] = make_uchar4(out[0], out[1], out[2], (unsigned char)flags);
+            const int dst = out_slot(P, slot);
+            if (dst >= 0) P.tiles[dst] = make_uchar4(out[0], out[1], out[2], (unsigned char)flags);
         }
     }
 }

@@ -41,9 +41,14 @@ RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool sha
 
 // One closest-hit job of the persistent trace kernel: plain closest hit (primary, reflection,
 // sphere-incidence transmission) or the face-incidence rule (main.cpp:992-1011).
-template <bool kCount>
+template <bool kCount, bool kStealing>
 struct TraceJob {
     static constexpr bool kOrdered = true;       // closest hit: near children first, the bound shrinks
+    // min over (t, order) / OR of `aborted` are folds in any visiting order, so the subtrees of
+    // one ray may be walked by several lanes.  Two builds of the kernel: the work-sharing one
+    // ends sooner (the stragglers of the last rays are split up) but its main loop carries
+    // more state; render.cu picks it for launches short enough for the tail to matter.
+    static constexpr bool kSteal = kStealing;
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
@@ -119,6 +124,47 @@ struct TraceJob {
 
     RT_DEV bool next(V3&, V3&, float&, float&) { return false; }
 
+    // work sharing at the end of a launch (persistent_walk): a helper lane walks a subtree
+    // for the ray of lane src with a copy of its state ...
+    RT_DEV void adopt(int src, bool take, V3& wo, V3& wray)
+    {
+        constexpr unsigned kFull = 0xffffffffu;
+        const float ox = __shfl_sync(kFull, o.x, src), oy = __shfl_sync(kFull, o.y, src), oz = __shfl_sync(kFull, o.z, src);
+        const float rx = __shfl_sync(kFull, ray.x, src), ry = __shfl_sync(kFull, ray.y, src), rz = __shfl_sync(kFull, ray.z, src);
+        const float bt = __shfl_sync(kFull, best.t, src), bb = __shfl_sync(kFull, best.b, src), bg = __shfl_sync(kFull, best.g, src);
+        const int bo = __shfl_sync(kFull, best.obj, src), bord = __shfl_sync(kFull, best_order, src);
+        const int bk = __shfl_sync(kFull, back, src);
+        const int fl = __shfl_sync(kFull, (skip_spheres ? 1 : 0) | (padding ? 2 : 0), src);
+        if (take) {
+            o = mk3(ox, oy, oz); ray = mk3(rx, ry, rz);
+            best.t = bt; best.b = bb; best.g = bg; best.obj = bo; best_order = bord;
+            back = bk; skip_spheres = (fl & 1) != 0; padding = (fl & 2) != 0; aborted = false;
+        }
+        wo = o; wray = ray;
+    }
+    // ... and its result is folded into the owner's with the very comparison visit() uses
+    RT_DEV void merge(int src, bool mine)
+    {
+        constexpr unsigned kFull = 0xffffffffu;
+        const float bt = __shfl_sync(kFull, best.t, src), bb = __shfl_sync(kFull, best.b, src), bg = __shfl_sync(kFull, best.g, src);
+        const int bo = __shfl_sync(kFull, best.obj, src), bord = __shfl_sync(kFull, best_order, src);
+        const int ab = __shfl_sync(kFull, aborted ? 1 : 0, src);
+        if (!mine) return;
+        if (back >= 0) { aborted = aborted || ab != 0; return; }
+        if (bo >= 0 && (bt < best.t || (bt == best.t && bord < best_order))) {
+            best.t = bt; best.b = bb; best.g = bg; best.obj = bo; best_order = bord;
+        }
+    }
+
+    // lanes walking subtrees of one ray: the nearest hit any of them has found bounds them all
+    // (positive floats order like their bit patterns; FLT_MAX = nothing yet); a face-rule walk
+    // has no bound, it ends when any lane has found the reason to abort
+    RT_DEV float share(unsigned group, float tmax)
+    {
+        if (__reduce_or_sync(group, aborted ? 1u : 0u)) { aborted = true; return -1.0f; }
+        return __uint_as_float(__reduce_min_sync(group, __float_as_uint(fmaxf(tmax, 0.0f))));
+    }
+
     RT_DEV void sphere_candidate(const float4& w0, int order, float tmin)
     {
         float tf, tn;
@@ -152,21 +198,22 @@ struct TraceJob {
             write_miss(P, level, slot, padding, aborted);
         }
         if (P.primary_ids) {   // instrumented frame
-            if (fin && !padding && level == 0) P.primary_ids[slot] = hit ? S.obj[best.obj].z : 0;
+            if (fin && !padding && level == 0) P.primary_ids[out_slot(P, slot)] = hit ? S.obj[best.obj].z : 0;
             const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[best.obj].y >= 0);
             if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
         }
     }
 };
 
-template <bool kCount>
-__global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
+template <bool kCount, bool kStealing>
+__global__ void __launch_bounds__(kBlock, kStealing ? 7 : 0) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
                                       : min(P.counters->rays[level], (unsigned)P.level[level].capacity);
-    TraceJob<kCount> job{ P, acc, level };
-    acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes);
+    TraceJob<kCount, kStealing> job{ P, acc, level };
+    acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
+                        kCount ? &P.counters->clock[0][level] : nullptr, P.steal != 0);
     flush_bvh_counters(acc, P.counters);
 }
 
@@ -176,8 +223,13 @@ __global__ void __launch_bounds__(kBlock) bvh_trace_kernel(const __grid_constant
 // is exactly 0 it stays 0 whatever the later lights meet: the chain stops there and the
 // remaining records are never read (RecordedShadow stops at the same point).  In a dense
 // scene that removes most shadow walks without changing a bit of the result.
-template <bool kCount, bool kNearFirst>
+template <bool kCount, bool kNearFirst, bool kStealing>
 struct ShadowJob {
+    // One light's walk is a fold in any order too: "an opaque occluder exists" is an OR and the
+    // partial factors are collected and sorted by iteration order before they are multiplied
+    // (shadow_end), so helpers only have to hand over their finds.  The chain over the lights
+    // stays with the owner lane.
+    static constexpr bool kSteal = kStealing;
     static constexpr bool kOrdered = kNearFirst; // any hit: order is only a heuristic (near boxes first finds occluders sooner?)
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
@@ -217,6 +269,49 @@ struct ShadowJob {
         return true;
     }
     RT_DEV float visit(const float4* w, float tmax) { return v(w, tmax); }
+
+    RT_DEV void adopt(int src, bool take, V3& wo, V3& wray)
+    {
+        constexpr unsigned kFull = 0xffffffffu;
+        const float ox = __shfl_sync(kFull, v.o.x, src), oy = __shfl_sync(kFull, v.o.y, src), oz = __shfl_sync(kFull, v.o.z, src);
+        const float rx = __shfl_sync(kFull, v.ray.x, src), ry = __shfl_sync(kFull, v.ray.y, src), rz = __shfl_sync(kFull, v.ray.z, src);
+        const float t0 = __shfl_sync(kFull, v.tmin, src), t1 = __shfl_sync(kFull, v.tmax_hit, src);
+        const int sf = __shfl_sync(kFull, v.self, src);
+        const int fl = __shfl_sync(kFull, (v.use_tmax ? 1 : 0) | (v.skip_spheres ? 2 : 0) | (v.count_all ? 4 : 0), src);
+        if (take) {
+            v.o = mk3(ox, oy, oz); v.ray = mk3(rx, ry, rz); v.tmin = t0; v.tmax_hit = t1; v.self = sf;
+            v.use_tmax = (fl & 1) != 0; v.skip_spheres = (fl & 2) != 0; v.count_all = (fl & 4) != 0;
+            v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false;
+        }
+        wo = v.o; wray = v.ray;
+    }
+    RT_DEV void merge(int src, bool mine)
+    {
+        constexpr unsigned kFull = 0xffffffffu;
+        const int op = __shfl_sync(kFull, v.opaque ? 1 : 0, src), h = __shfl_sync(kFull, v.hits, src);
+        const int np = __shfl_sync(kFull, v.n_partial, src);
+        const float ov = __shfl_sync(kFull, v.overflow_mask, src);
+        if (mine) {
+            v.hits += h;
+            v.opaque = v.opaque || op != 0;
+            if (ov != 1.0f) v.overflow_mask = clamp01(fmul(ov, v.overflow_mask));
+        }
+        for (int i = 0; i < np; i++) {
+            // (constant indices after unrolling: the lists stay in registers)
+            int po = 0; float pk = 0.0f;
+            #pragma unroll
+            for (int q = 0; q < BvhAccelT<kCount>::kMaxPartial; q++) if (q == i) { po = v.p_order[q]; pk = v.p_k[q]; }
+            po = __shfl_sync(kFull, po, src); pk = __shfl_sync(kFull, pk, src);
+            if (mine) { v.hits--; v.add(po, pk); }
+        }
+    }
+    // an opaque occluder found by any lane ends the walk of this light for all of them
+    RT_DEV float share(unsigned group, float tmax)
+    {
+        if (__reduce_or_sync(group, v.opaque ? 1u : 0u) && !v.count_all) return -1.0f;
+        return tmax;
+    }
+
     RT_DEV void retire(bool fin)
     {
         if (!fin) return;
@@ -241,13 +336,14 @@ struct ShadowJob {
     }
 };
 
-template <bool kCount, bool kNearFirst>
+template <bool kCount, bool kNearFirst, bool kStealing>
 __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned n_nodes = P.counters->nodes[level];
-    ShadowJob<kCount, kNearFirst> job{ P, acc, level, n_nodes };
-    acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes);
+    ShadowJob<kCount, kNearFirst, kStealing> job{ P, acc, level, n_nodes };
+    acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
+                        kCount ? &P.counters->clock[1][level] : nullptr, P.steal != 0);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
         unsigned long long w = job.walks;

@@ -21,9 +21,10 @@ def _ptr(a: Optional[np.ndarray]):
 
 
 def make_params(max_depth: int = 4, epsilon: float = 1.0e-3, accel: int = abi.RT_ACCEL_AUTO, rank: int = 0,
-                world_size: int = 1, tile_rows: int = 8, instrument: bool = False, profile: bool = False) -> abi.RtRenderParams:
+                world_size: int = 1, tile_rows: int = 8, instrument: bool = False, profile: bool = False,
+                subframes: int = 0, work_sharing: int = 0) -> abi.RtRenderParams:
     return abi.RtRenderParams(max_depth, epsilon, accel, rank, world_size, tile_rows, 1 if instrument else 0,
-                              1 if profile else 0)
+                              1 if profile else 0, subframes, work_sharing)
 
 
 class DeviceScene:
@@ -70,6 +71,15 @@ class DeviceScene:
         """Enqueue-only render into a caller-provided device tile buffer (rt_render_async)."""
         abi.check(self._lib.rt_render_async(self._h, C.byref(params), C.c_void_p(dev_tiles_ptr or None),
                                             C.c_void_p(stream_ptr or None)), "rt_render_async")
+
+    def async_frame_ok(self) -> bool:
+        """After the async frame's stream was synchronised: False = a queue overflowed (queues
+        have been grown, render the frame again) (rt_async_frame_status)."""
+        rc = self._lib.rt_async_frame_status(self._h)
+        if rc == abi.RT_E_NOMEM:
+            return False
+        abi.check(rc, "rt_async_frame_status")
+        return True
 
     def download(self, rgb: Optional[np.ndarray] = None, flags: Optional[np.ndarray] = None
                  ) -> Tuple[np.ndarray, np.ndarray]:

@@ -12,7 +12,7 @@ import numpy as np
 import pytest
 
 from simple_raytracer_b200 import abi, scenegen
-from simple_raytracer_b200.renderer import DeviceScene
+from simple_raytracer_b200.renderer import DeviceScene, make_params
 from tests import common
 from tests import oracle_lib as O
 
@@ -233,6 +233,73 @@ def test_row_tile_sharding_is_byte_identical():
                 ds.render(rank=rank, world_size=world, tile_rows=tile_rows)
                 ds.download(rgb, flags)
             assert np.array_equal(rgb, full_rgb) and np.array_equal(flags, full_flags), (world, tile_rows)
+
+
+@pytest.mark.parametrize("world,tile_rows", [(1, 8), (2, 5), (3, 7)])
+def test_subframe_chains_never_change_a_pixel(world, tile_rows):
+    """The LBVH pipeline deals a rank's tiles out to 1..8 independent launch chains (render.cu);
+    every split must give the bytes of the serial single-chain frame, with the same node
+    counts — also when the tile count is not a multiple of the chain count."""
+    scene = scenegen.coverage_scene(96, 101)
+    with DeviceScene(scene) as ds:
+        for rank in range(world):
+            kw = dict(rank=rank, world_size=world, tile_rows=tile_rows, accel=abi.RT_ACCEL_LBVH)
+            st1 = ds.render(subframes=1, **kw)
+            want = ds.download()
+            want = (want[0].copy(), want[1].copy())
+            for k in (2, 3, 4, 8):
+                st = ds.render(subframes=k, **kw)
+                got = ds.download()
+                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), (rank, k)
+                assert list(st.nodes_per_level) == list(st1.nodes_per_level), (rank, k)
+                assert st.rays_reflect == st1.rays_reflect and st.rays_transmit == st1.rays_transmit
+
+
+def test_work_sharing_in_the_walk_tails_never_changes_a_pixel():
+    """Idle lanes walking subtrees for the last rays of a launch (persistent_walk, Job::kSteal): the
+    frame must equal the one without it and the brute-force one — triangles, spheres, transparent
+    occluders (partial shadow factors are merged across lanes) and the face-incidence rule included."""
+    for scene in (scenegen.coverage_scene(128, 96), scenegen.stress_scene(8000, 100, 128, 96)):
+        with DeviceScene(scene) as ds:
+            ds.render(accel=abi.RT_ACCEL_BRUTE)
+            want = ds.download()
+            want = (want[0].copy(), want[1].copy())
+            stats = []
+            for mode in (2, 1):
+                stats.append(ds.render(accel=abi.RT_ACCEL_LBVH, work_sharing=mode))
+                got = ds.download()
+                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), mode
+            assert list(stats[0].nodes_per_level) == list(stats[1].nodes_per_level)
+            # the instrumented build shares work too and must still agree on every primary hit
+            ds.render(accel=abi.RT_ACCEL_LBVH, work_sharing=1, instrument=True)
+            ids_lbvh = ds.download_primary_ids().copy()
+            ds.render(accel=abi.RT_ACCEL_BRUTE, instrument=True)
+            assert np.array_equal(ids_lbvh, ds.download_primary_ids())
+
+
+def test_async_frame_status_reports_overflow_and_recovers():
+    """rt_render_async cannot redo a truncated frame: rt_async_frame_status must say so, grow the
+    queues, and the next async frame must then equal the synchronous one."""
+    import torch
+    scene = scenegen.stress_scene(20000, 50, 256, 200)
+    with DeviceScene(scene) as ds:
+        prm = make_params(accel=abi.RT_ACCEL_LBVH)
+        n = ds.tile_buffer_bytes(1, 8)
+        buf = torch.zeros(n, dtype=torch.uint8, device="cuda")
+        ok = False
+        for _ in range(8):          # first guesses may or may not be large enough: both paths end here
+            ds.render_async(prm, buf.data_ptr(), 0)
+            torch.cuda.synchronize()
+            if ds.async_frame_ok():
+                ok = True
+                break
+        assert ok
+        got = buf.cpu().numpy().reshape(-1, 4)
+        ds.render(prm)
+        rgb, flags = ds.download()
+        H, W = scene.height, scene.width
+        assert np.array_equal(got[: H * W, :3].reshape(H, W, 3), rgb)
+        assert np.array_equal(got[: H * W, 3].reshape(H, W), flags)
 
 
 def test_render_is_deterministic():

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--world", type=int, default=1)
     ap.add_argument("--rank", type=int, default=0)
     ap.add_argument("--tile-rows", type=int, default=10)
+    ap.add_argument("--subframes", type=int, default=0)
     a = ap.parse_args()
     sc = scenegen.stress_scene(a.tris, a.spheres, a.w, a.h)
     t0 = time.time()
@@ -32,17 +33,20 @@ def main():
         rays = st.rays_primary + st.rays_shadow + st.rays_transmit + st.rays_reflect
         best = None
         for _ in range(a.reps):
-            s = ds.render(profile=not a.nop, **kw)
+            s = ds.render(profile=not a.nop, subframes=a.subframes, **kw)
             if best is None or s.render_ms < best.render_ms:
                 best = s
         out = dict(upload_s=round(up, 3), first_render_s=round(first, 3), ms=round(best.render_ms, 3), rays=int(rays),
                    mrays_s=round(rays / best.render_ms / 1e3, 1), nodes=list(best.nodes_per_level)[:a.depth + 1],
                    level_ms=[round(x, 3) for x in list(best.level_ms)[:a.depth + 1]], combine_ms=round(best.combine_ms, 3), trace_ms=[round(x, 3) for x in list(best.trace_ms)[:a.depth + 1]], shadow_ms=[round(x, 3) for x in list(best.shadow_ms)[:a.depth + 1]], shade_ms=[round(x, 3) for x in list(best.shade_ms)[:a.depth + 1]],
-                   launches=best.kernel_launches)
+                   launches=best.kernel_launches, subframes=a.subframes)
         if not a.no_instrument:
             si = ds.render(instrument=True, **kw)
             out.update(boxes_per_ray=round(si.bvh_nodes_visited / rays, 1), prims_per_ray=round(si.prim_tests / rays, 2),
                        texels=int(si.texel_fetches), shadow_walked=int(si.shadow_rays_walked), shadow_ref=int(si.rays_shadow), instr_ms=round(si.render_ms, 2))
+            for name in ("trace_span_ms", "trace_drain_ms", "trace_warp_drain_ms", "shadow_span_ms", "shadow_drain_ms", "shadow_warp_drain_ms",
+                         "trace_drain_steps", "trace_drain_lanes", "trace_drain_steals", "shadow_drain_steps", "shadow_drain_lanes"):
+                out[name] = [round(x, 3) for x in list(getattr(si, name))[:a.depth + 1]]
         print(json.dumps(out), flush=True)
 
 if __name__ == "__main__":
