@@ -231,6 +231,13 @@ int rt_render_async(RtScene* scene, const RtRenderParams* params,
  * again.  A synchronous rt_render of the same view beforehand sizes the queues exactly. */
 int rt_async_frame_status(RtScene* scene);
 
+/* Device buffers of freed scenes (tables, LBVH build temporaries, wavefront queues) are
+ * kept in a process-wide cache and handed to the next rt_upload_scene / rt_render, so a
+ * load-render-free loop does not pay cudaMalloc / cudaFree (and cudaFree's device
+ * synchronisation) per scene.  This returns everything cached to the driver; the
+ * result is the number of bytes released. */
+size_t rt_release_cached_memory(void);
+
 /* After an allgather of every rank's tile buffer ([rank][local_tile][row][col]
  * RGBA8, device memory) puts the pixels in scanline order:
  * dev_rgba_out[height][width] RGBA8. Asynchronous on cuda_stream. */

@@ -130,8 +130,7 @@ int rt_upload_scene(const RtSceneDesc* desc, RtScene** out)
     int rc = RT_OK;
     if (!cuda_ok(cudaGetDevice(&s->device), "cudaGetDevice") ||
         !cuda_ok(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking), "cudaStreamCreate") ||
-        !cuda_ok(cudaEventCreate(&s->ev0), "cudaEventCreate") || !cuda_ok(cudaEventCreate(&s->ev1), "cudaEventCreate") ||
-        !cuda_ok(cudaMallocHost((void**)&s->h_counters, sizeof(Counters) * kMaxSubframes), "cudaMallocHost"))
+        !cuda_ok(cudaEventCreate(&s->ev0), "cudaEventCreate") || !cuda_ok(cudaEventCreate(&s->ev1), "cudaEventCreate"))
         rc = RT_E_CUDA;
     if (rc == RT_OK) rc = build_scene(desc, s);
     if (rc != RT_OK) { rt_free_scene(sc); return rc; }
@@ -154,7 +153,6 @@ void rt_free_scene(RtScene* scene)
     for (int k = 0; k < kMaxLevels; k++)
         for (int j = 0; j < 2; j++)
             if (s->prof_mid[k][j]) cudaEventDestroy(s->prof_mid[k][j]);
-    if (s->h_counters) cudaFreeHost(s->h_counters);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete scene;
 }
@@ -194,6 +192,15 @@ int rt_render_async(RtScene* scene, const RtRenderParams* params, void* dev_tile
     RT_CUDA(cudaSetDevice(s->device));
     if ((rc = ensure_workspace(s, p, nullptr)) != RT_OK) return rc;
     return enqueue_frame(s, p, (uchar4*)dev_tiles, cuda_stream ? (cudaStream_t)cuda_stream : s->stream, nullptr);
+}
+
+size_t rt_release_cached_memory(void)
+{
+    {
+        Workspace drop;
+        stash_workspace(std::move(drop));      // the retired workspace goes first
+    }
+    return dev_release_cached();
 }
 
 int rt_async_frame_status(RtScene* scene)

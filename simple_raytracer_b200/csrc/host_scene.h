@@ -18,7 +18,12 @@ bool cuda_ok(cudaError_t e, const char* what);   // false + rt_last_error on fai
         if (!::rt::cuda_ok((call), #call)) return RT_E_CUDA; \
     } while (0)
 
-// Device allocation that frees itself.
+// devmem.cu: device blocks come from / go back to a process-wide cache
+void* dev_alloc(size_t n, size_t* capacity);
+void dev_free(void* p, size_t capacity);
+size_t dev_release_cached();     // cudaFree of everything cached; returns the bytes released
+
+// Device allocation that frees itself (into the cache: only release a buffer whose work is done).
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
@@ -34,7 +39,7 @@ struct DevBuf {
     ~DevBuf() { release(); }
     void release()
     {
-        if (p) cudaFree(p);
+        if (p) dev_free(p, bytes);
         p = nullptr; bytes = 0;
     }
     // grows only; contents are NOT preserved
@@ -42,14 +47,43 @@ struct DevBuf {
     {
         if (n <= bytes) return true;
         release();
-        if (!cuda_ok(cudaMalloc(&p, n ? n : 16), "cudaMalloc")) { p = nullptr; return false; }
-        bytes = n;
+        p = dev_alloc(n, &bytes);     // bytes = the block's capacity (>= n)
+        if (!p) { bytes = 0; return false; }
         return true;
     }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
 constexpr int kMaxSubframes = 8;
+
+// Pinned host allocation that frees itself.
+struct PinnedBuf {
+    void* p = nullptr;
+    size_t bytes = 0;
+    PinnedBuf() = default;
+    PinnedBuf(const PinnedBuf&) = delete;
+    PinnedBuf& operator=(const PinnedBuf&) = delete;
+    PinnedBuf(PinnedBuf&& o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+    PinnedBuf& operator=(PinnedBuf&& o) noexcept
+    {
+        if (this != &o) { release(); p = o.p; bytes = o.bytes; o.p = nullptr; o.bytes = 0; }
+        return *this;
+    }
+    ~PinnedBuf() { release(); }
+    void release()
+    {
+        if (p) cudaFreeHost(p);
+        p = nullptr; bytes = 0;
+    }
+    bool reserve(size_t n)
+    {
+        if (n <= bytes) return true;
+        release();
+        if (!cuda_ok(cudaMallocHost(&p, n), "cudaMallocHost")) { p = nullptr; return false; }
+        bytes = n;
+        return true;
+    }
+};
 
 // Streams and events of the LBVH pipeline's launch chains (render.cu): sub-frame j runs
 // trace -> spawn on main[j] (main[0] is not used: chain 0 runs on the caller's stream) and
@@ -94,6 +128,7 @@ struct Workspace {
     DevBuf primary_ids;
     DevBuf rgb24, flags8;  // scanline-order planes for rt_download_framebuffer
     ChainStreams chains;
+    PinnedBuf h_counters;  // one Counters per sub-frame
     int device = -1;
 };
 
@@ -121,7 +156,7 @@ struct SceneHost {
     cudaEvent_t prof_mid[kMaxLevels][2] = { { nullptr } };   // LBVH pipeline: after trace, after shadow
     bool prof_split = false;
     int prof_levels = 0;                                 // events recorded by the last frame (0 = none)
-    Counters* h_counters = nullptr;     // pinned, one per sub-frame
+    Counters* h_counters = nullptr;     // = ws.h_counters (pinned, one per sub-frame), set by ensure_workspace
 
     // last frame
     bool rendered = false;

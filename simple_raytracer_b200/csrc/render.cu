@@ -167,6 +167,8 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
     const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
     const size_t npx = (size_t)tl.n_local_pixels;
     const bool bvh = pick_accel(s, p.accel) == RT_ACCEL_LBVH;
+    if (!ws.h_counters.reserve(sizeof(Counters) * kMaxSubframes)) return RT_E_NOMEM;
+    s->h_counters = static_cast<Counters*>(ws.h_counters.p);
     if (!ws.counters.reserve(sizeof(Counters) * kMaxSubframes) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
     if (p.instrument && !ws.primary_ids.reserve(npx * sizeof(int))) return RT_E_NOMEM;
     for (int l = 0; l <= p.max_depth; l++) {

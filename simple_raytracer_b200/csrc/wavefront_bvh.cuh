@@ -49,6 +49,7 @@ struct TraceJob {
     // ends sooner (the stragglers of the last rays are split up) but its main loop carries
     // more state; render.cu picks it for launches short enough for the tail to matter.
     static constexpr bool kSteal = kStealing;
+    static constexpr bool kWideLoads = false;
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
@@ -230,6 +231,7 @@ struct ShadowJob {
     // (shadow_end), so helpers only have to hand over their finds.  The chain over the lights
     // stays with the owner lane.
     static constexpr bool kSteal = kStealing;
+    static constexpr bool kWideLoads = true;     // 256-bit node loads (bvh.cuh: test_node)
     static constexpr bool kOrdered = kNearFirst; // any hit: order is only a heuristic (near boxes first finds occluders sooner?)
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;

@@ -277,6 +277,28 @@ def test_work_sharing_in_the_walk_tails_never_changes_a_pixel():
             assert np.array_equal(ids_lbvh, ds.download_primary_ids())
 
 
+def test_cached_device_memory_is_reused_and_can_be_released():
+    """Freed scenes leave their device blocks in a process-wide cache (devmem.cu): a second upload
+    of the same scene must give the same frame from recycled (dirty) blocks, and
+    rt_release_cached_memory must hand the bytes back."""
+    lib = abi.load_rt()
+    scene = scenegen.stress_scene(5000, 50, 96, 64)
+    frames = []
+    for _ in range(3):
+        with DeviceScene(scene) as ds:
+            ds.render(accel=abi.RT_ACCEL_LBVH)
+            rgb, flags = ds.download()
+            frames.append((rgb.copy(), flags.copy()))
+    for f in frames[1:]:
+        assert np.array_equal(f[0], frames[0][0]) and np.array_equal(f[1], frames[0][1])
+    assert lib.rt_release_cached_memory() > 0
+    assert lib.rt_release_cached_memory() == 0
+    with DeviceScene(scene) as ds:              # and everything still works from fresh blocks
+        ds.render(accel=abi.RT_ACCEL_LBVH)
+        rgb, flags = ds.download()
+    assert np.array_equal(rgb, frames[0][0]) and np.array_equal(flags, frames[0][1])
+
+
 def test_async_frame_status_reports_overflow_and_recovers():
     """rt_render_async cannot redo a truncated frame: rt_async_frame_status must say so, grow the
     queues, and the next async frame must then equal the synchronous one."""
