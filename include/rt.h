@@ -238,6 +238,17 @@ int rt_async_frame_status(RtScene* scene);
  * result is the number of bytes released. */
 size_t rt_release_cached_memory(void);
 
+/* The reference's output file, formatted on the device (replaces the writer loop
+ * main.cpp:628-641): "P3 \n" "W H \n" "255 \n" and one "r g b \n" line per
+ * pixel, NaN channels as 18446744071562067968 and primary-miss pixels as the un-clamped
+ * (int)(bkgcolor*255), byte for byte what rt_host_format_ppm produces from the downloaded
+ * frame.  dev_rgba: width*height RGBA8 in scanline order with the flags in A, in DEVICE
+ * memory (the output of rt_deinterleave_tiles), or NULL for the frame of this scene's last
+ * single-rank rt_render.  *text points at pinned host memory owned by the scene's
+ * workspace: valid until the next call on this scene or rt_free_scene; *len excludes the
+ * terminating NUL. */
+int rt_format_ppm_device(RtScene* scene, const void* dev_rgba, const char** text, size_t* len);
+
 /* After an allgather of every rank's tile buffer ([rank][local_tile][row][col]
  * RGBA8, device memory) puts the pixels in scanline order:
  * dev_rgba_out[height][width] RGBA8. Asynchronous on cuda_stream. */

@@ -97,7 +97,7 @@ class RtStats(C.Structure):
 # The exported symbols of each library — tests check that every one resolves.
 RT_SYMBOLS = [
     "rt_upload_scene", "rt_render", "rt_download_framebuffer", "rt_free_scene", "rt_last_error",
-    "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_async_frame_status", "rt_release_cached_memory", "rt_deinterleave_tiles", "rt_set_camera",
+    "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_async_frame_status", "rt_release_cached_memory", "rt_format_ppm_device", "rt_deinterleave_tiles", "rt_set_camera",
     "rt_trace_closest", "rt_trace_shadow", "rt_download_primary_ids", "rt_tile_layout",
 ]
 RT_HOST_SYMBOLS = [
@@ -143,6 +143,8 @@ def load_rt() -> C.CDLL:
     lib.rt_tile_layout.restype = C.c_int
     lib.rt_render_async.argtypes = [vp, _p(RtRenderParams), vp, vp]
     lib.rt_render_async.restype = C.c_int
+    lib.rt_format_ppm_device.argtypes = [vp, vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.rt_format_ppm_device.restype = C.c_int
     lib.rt_release_cached_memory.argtypes = []
     lib.rt_release_cached_memory.restype = C.c_size_t
     lib.rt_async_frame_status.argtypes = [vp]

@@ -330,6 +330,21 @@ int rt_download_framebuffer(RtScene* scene, uint8_t* rgb, uint8_t* flags)
     return RT_OK;
 }
 
+int rt_format_ppm_device(RtScene* scene, const void* dev_rgba, const char** text, size_t* len)
+{
+    if (!scene || !text || !len) { set_error("rt_format_ppm_device: null argument"); return RT_E_INVALID; }
+    SceneHost* s = &scene->h;
+    RT_CUDA(cudaSetDevice(s->device));
+    const uchar4* px = static_cast<const uchar4*>(dev_rgba);
+    if (!px) {
+        // the scene's own frame: tiles of a single-rank render ARE scanline order
+        if (!s->rendered) { set_error("rt_format_ppm_device before rt_render"); return RT_E_STATE; }
+        if (s->last.world_size != 1) { set_error("rt_format_ppm_device: the last frame is one rank's shard; pass the assembled frame"); return RT_E_STATE; }
+        px = s->ws.tiles.as<uchar4>();
+    }
+    return format_ppm_device(s, px, text, len, s->stream);
+}
+
 int rt_deinterleave_tiles(const RtScene* scene, const void* dev_gathered, void* dev_rgba_out, int32_t world_size,
                           int32_t tile_rows, void* cuda_stream)
 {

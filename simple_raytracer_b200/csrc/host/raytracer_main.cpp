@@ -64,22 +64,27 @@ int main(int argc, char* argv[])
     if (rc != RT_OK) { std::fprintf(stderr, "rt_render: %s\n", rt_last_error()); return 1; }
     double t3 = now_s();
 
-    const size_t npx = (size_t)desc->width * (size_t)desc->height;
-    std::vector<uint8_t> rgb(npx * 3), flags(npx);
-    rc = rt_download_framebuffer(scene, rgb.data(), flags.data());
-    if (rc != RT_OK) { std::fprintf(stderr, "rt_download_framebuffer: %s\n", rt_last_error()); return 1; }
+    // the P3 text is formatted on the device (rt_format_ppm_device); the host only writes it out
+    const char* text = nullptr; size_t text_len = 0;
+    rc = rt_format_ppm_device(scene, nullptr, &text, &text_len);
+    if (rc != RT_OK) { std::fprintf(stderr, "rt_format_ppm_device: %s\n", rt_last_error()); return 1; }
     double t4 = now_s();
 
     char out_path[4096];
     if (rt_host_output_path(scene_path, out_path, sizeof out_path) != RT_OK) return 1;
-    rc = rt_host_write_ppm(out_path, desc->width, desc->height, rgb.data(), flags.data(), desc->bkg);
-    if (rc != RT_OK) { std::printf("ERROR: failed to create ppm image\n"); return 0; }   // main.cpp:621
+    {
+        FILE* f = std::fopen(out_path, "wb");
+        if (!f) { std::printf("ERROR: failed to create ppm image\n"); return 0; }   // main.cpp:621
+        const size_t put = std::fwrite(text, 1, text_len, f);
+        std::fclose(f);
+        if (put != text_len) { std::fprintf(stderr, "short write to %s\n", out_path); return 1; }
+    }
     double t5 = now_s();
 
     if (verbose) {
         std::fprintf(stderr,
                      "parse %.3f ms | upload %.3f ms | render %.3f ms (device %.3f ms, %llu nodes, accel %s) | "
-                     "download %.3f ms | write %.3f ms\n",
+                     "format+download %.3f ms | write %.3f ms\n",
                      (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, stats.render_ms,
                      (unsigned long long)stats.nodes_total, stats.accel_used == RT_ACCEL_LBVH ? "lbvh" : "brute",
                      (t4 - t3) * 1e3, (t5 - t4) * 1e3);

@@ -8,11 +8,14 @@
 #include "host_common.h"
 
 #include <cerrno>
+#include <charconv>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <string_view>
 #include <unordered_map>
 
 namespace rthost {
@@ -62,36 +65,93 @@ struct ParseError { std::string msg; };
 
 [[noreturn]] void fail(const std::string& msg) { throw ParseError{ msg }; }
 
-float need_float(const std::vector<std::string>& a, size_t i, const char* what)
+// The reference keeps v / vn / vt in std::maps keyed by a running 1-based count; a
+// missing key reads as zeros (std::map::operator[], main.cpp:489-511).  The keys are
+// dense, so a vector with slot 0 unused is the same mapping.
+template <class T>
+T lookup(const std::vector<T>& m, unsigned key)
+{
+    return (key >= 1 && (size_t)key < m.size()) ? m[key] : T{};
+}
+
+using Tok = std::string_view;
+
+// The arguments of one command: a window into the line's token list.
+struct Args {
+    const Tok* p;
+    size_t n;
+    size_t size() const { return n; }
+    const Tok& operator[](size_t i) const { return p[i]; }
+};
+
+// std::stof on a token, fast: plain decimal tokens go through std::from_chars (correctly
+// rounded, like glibc's strtof); anything else — leading blanks or '+', hex floats, inf /
+// nan, trailing junk such as a '\r', results that strtof flags with ERANGE (overflow,
+// subnormals) — takes the strtof path so every corner keeps std::stof's behaviour.
+bool parse_float_tok(Tok t, float* out)
+{
+    // from_chars refuses what only strtof takes (leading blanks, '+', hex) and stops before
+    // trailing junk: all of that shows as "did not consume the whole token"
+    float v;
+    const char* const e = t.data() + t.size();
+    const auto r = std::from_chars(t.data(), e, v);
+    if (r.ec == std::errc() && r.ptr == e) {
+        if (std::isnormal(v)) { *out = v; return true; }
+        if (v == 0.0f) {
+            // exact zeros ("0", "-0.000") are fine; a non-zero decimal that ROUNDS to zero is
+            // ERANGE for strtof -> slow path decides
+            bool zero_digits = true;
+            for (char c : t) { if (c == 'e' || c == 'E') break; if (c >= '1' && c <= '9') { zero_digits = false; break; } }
+            if (zero_digits) { *out = v; return true; }
+        }
+    }
+    return parse_float(std::string(t), out);
+}
+
+float need_float(const Args& a, size_t i, const char* what)
 {
     float v;
-    if (i >= a.size() || !parse_float(a[i], &v)) fail(std::string("ERROR: Invalid args for ") + what + ". Please verify.");
+    if (i >= a.size() || !parse_float_tok(a[i], &v)) fail(std::string("ERROR: Invalid args for ") + what + ". Please verify.");
     return v;
 }
 
-int need_int(const std::vector<std::string>& a, size_t i, const char* what)
+int need_int(const Args& a, size_t i, const char* what)
 {
     int v;
-    if (i >= a.size() || !parse_int(a[i], &v)) fail(std::string("ERROR: Invalid ") + what + ". Please verify.");
+    if (i >= a.size() || !parse_int(std::string(a[i]), &v)) fail(std::string("ERROR: Invalid ") + what + ". Please verify.");
     return v;
 }
 
-// 1-based maps where a missing key reads as zeros (std::map::operator[],
-// main.cpp:489-511)
-template <class T>
-T lookup(const std::unordered_map<unsigned, T>& m, unsigned key)
+// sscanf("%d") on [p, e): optional sign + digits (tokens cannot start with a blank here).
+// false when there is no digit.  Values beyond int take the slow sscanf path (ok = false).
+bool scan_int(const char*& p, const char* e, int* out, bool* exotic)
 {
-    auto it = m.find(key);
-    return it == m.end() ? T{} : it->second;
+    const char* q = p;
+    bool neg = false;
+    if (q < e && (*q == '+' || *q == '-')) { neg = (*q == '-'); q++; }
+    if (q >= e || *q < '0' || *q > '9') return false;
+    long long v = 0;
+    while (q < e && *q >= '0' && *q <= '9') {
+        v = v * 10 + (*q - '0');
+        if (v > 0x7fffffffLL) { *exotic = true; return false; }
+        q++;
+    }
+    *out = (int)(neg ? -v : v);
+    p = q;
+    return true;
 }
 
 struct Parser {
     OwnedScene* out;
     std::string texture_dir;
 
-    std::unordered_map<unsigned, Vec3> vertices, normals;
-    std::unordered_map<unsigned, Vec2> texcoords;
-    unsigned obj_id = 0, n_v = 0, n_vn = 0, n_vt = 0;
+    std::vector<Vec3> vertices{ Vec3{} }, normals{ Vec3{} };     // slot 0 unused (keys are 1-based)
+    std::vector<Vec2> texcoords{ Vec2{} };
+    unsigned obj_id = 0;
+    // The reference reads the file again at every `texture` command (main.cpp:318); the same
+    // path gives the same texels, so later commands reuse the first copy.
+    std::unordered_map<std::string, int> texture_by_path;
+    std::unordered_map<std::string, int> material_by_value;
     int current_material = -1, current_texture = -1;
     bool use_texture = false, has_material = false;
     bool seen_imsize = false, seen_eye = false, seen_viewdir = false, seen_updir = false, seen_hfov = false,
@@ -110,7 +170,7 @@ struct Parser {
         *mat = current_material;
     }
 
-    void command(const std::string& cmd, const std::vector<std::string>& a)
+    void command(Tok cmd, const Args& a)
     {
         RtSceneDesc& d = out->desc;
         if (cmd == "eye") {                                   // main.cpp:143-162
@@ -150,20 +210,35 @@ struct Parser {
             } else {
                 m.opacity = 1.0f; m.eta = 1.0f;
             }
-            out->materials.push_back(m);
-            current_material = (int)out->materials.size() - 1;
+            // (a scene that restates the material before every object would otherwise carry one
+            // record per object: identical values share a record)
+            const std::string key(reinterpret_cast<const char*>(&m), sizeof m);
+            const auto known = material_by_value.find(key);
+            if (known != material_by_value.end()) {
+                current_material = known->second;
+            } else {
+                out->materials.push_back(m);
+                current_material = (int)out->materials.size() - 1;
+                material_by_value.emplace(key, current_material);
+            }
             has_material = true;
         } else if (cmd == "texture") {                        // 309-327
             use_texture = true;
-            std::string path = a[0];
+            std::string path(a[0]);
             if (!texture_dir.empty() && !path.empty() && path[0] != '/') path = texture_dir + "/" + path;
-            RtTexture t{};
-            std::vector<uint8_t> px;
-            if (read_texture_p3(path, &t.width, &t.height, &px) != RT_OK)
-                fail("ERROR: Issue reading 'texture' from ppm. Please verify. (" + g_error + ")");
-            out->textures.push_back(t);
-            out->texture_pixels.push_back(std::move(px));
-            current_texture = (int)out->textures.size() - 1;
+            const auto known = texture_by_path.find(path);
+            if (known != texture_by_path.end()) {
+                current_texture = known->second;
+            } else {
+                RtTexture t{};
+                std::vector<uint8_t> px;
+                if (read_texture_p3(path, &t.width, &t.height, &px) != RT_OK)
+                    fail("ERROR: Issue reading 'texture' from ppm. Please verify. (" + g_error + ")");
+                out->textures.push_back(t);
+                out->texture_pixels.push_back(std::move(px));
+                current_texture = (int)out->textures.size() - 1;
+                texture_by_path.emplace(path, current_texture);
+            }
         } else if (cmd == "sphere") {                         // 328-377
             obj_id++;
             RtSphere s{};
@@ -178,69 +253,110 @@ struct Parser {
             for (int k = 0; k < 3; k++) l.xyz[k] = need_float(a, k, "'light' command");
             for (int k = 0; k < 3; k++) l.rgb[k] = need_float(a, 4 + k, "'light' command");
             out->lights.push_back(l);
-        } else if (cmd == "v") {                              // 412-430
-            n_v++;
-            Vec3 p{ need_float(a, 0, "vertex"), need_float(a, 1, "vertex"), need_float(a, 2, "vertex") };
-            vertices[n_v] = p;
-        } else if (cmd == "vn") {                             // 431-449
-            n_vn++;
-            Vec3 p{ need_float(a, 0, "vertex normal"), need_float(a, 1, "vertex normal"), need_float(a, 2, "vertex normal") };
-            normals[n_vn] = p;
-        } else if (cmd == "vt") {                             // 450-469
-            Vec2 p{ need_float(a, 0, "texture coordinate"), need_float(a, 1, "texture coordinate") };
-            n_vt++;
-            texcoords[n_vt] = p;
-        } else if (cmd == "f") {                              // 470-552
-            obj_id++;
-            RtFace f{};                                       // new Face() value-initialises: zeros
-            f.id = (int32_t)obj_id;
-            if (a.size() < 3) fail("ERROR: Invalid args for 'f' (face) object. Please verify.");
-            for (int i = 0; i < 3; i++) {
-                unsigned t = 0, n = 0, v = 0;
-                const char* s = a[i].c_str();
-                Vec3 p{}, nn{}; Vec2 tc{};
-                bool set_n = false, set_t = false;
-                // per-vertex format sniffing, in the reference's order (487-517)
-                if (std::sscanf(s, "%d/%d/%d", (int*)&v, (int*)&t, (int*)&n) == 3) {
-                    f.smooth = 1; set_n = set_t = true;
-                } else if (std::sscanf(s, "%d//%d", (int*)&v, (int*)&n) == 2) {
-                    f.smooth = 1; set_n = true;
-                } else if (std::sscanf(s, "%d/%d", (int*)&v, (int*)&t) == 2) {
-                    f.smooth = 0; set_t = true;
-                } else if (std::sscanf(s, "%d", (int*)&v) == 1) {
-                    f.smooth = 0;
-                } else {
-                    fail("ERROR: Invalid args for 'f' object. Please verify.");
-                }
-                p = lookup(vertices, v);
-                f.v[i][0] = p.x; f.v[i][1] = p.y; f.v[i][2] = p.z;
-                if (set_n) { nn = lookup(normals, n); f.vn[i][0] = nn.x; f.vn[i][1] = nn.y; f.vn[i][2] = nn.z; }
-                if (set_t) { tc = lookup(texcoords, t); f.vt[i][0] = tc.x; f.vt[i][1] = tc.y; }
-            }
-            // has_texture is decided by the parser state, not by the face format (523-534)
-            material_and_texture(&f.material, &f.texture);
-            out->faces.push_back(f);
         }
+        // v / vn / vt / f never get here: geometry() takes them
     }
 
-    void run(std::istream& in)
+    // The four geometry commands (main.cpp:412-552), which are all but a few lines of a
+    // large scene file, on string views: no per-line allocations.
+    bool geometry(Tok cmd, const Args& a, Tok line)
     {
-        std::string line;
-        while (std::getline(in, line)) {                      // main.cpp:106
-            std::vector<std::string> args;
-            std::istringstream ss(line);
-            std::string tok;
-            while (std::getline(ss, tok, ' ')) {              // 112: split on ' ' only
+        if (cmd == "v") {                                     // 412-430
+            Vec3 p{ need_float(a, 0, "vertex"), need_float(a, 1, "vertex"), need_float(a, 2, "vertex") };
+            vertices.push_back(p);
+            return true;
+        }
+        if (cmd == "vn") {                                    // 431-449
+            Vec3 p{ need_float(a, 0, "vertex normal"), need_float(a, 1, "vertex normal"), need_float(a, 2, "vertex normal") };
+            normals.push_back(p);
+            return true;
+        }
+        if (cmd == "vt") {                                    // 450-469
+            Vec2 p{ need_float(a, 0, "texture coordinate"), need_float(a, 1, "texture coordinate") };
+            texcoords.push_back(p);
+            return true;
+        }
+        if (cmd != "f") return false;
+        (void)line;
+        obj_id++;                                             // 470-552
+        RtFace f{};                                           // new Face() value-initialises: zeros
+        f.id = (int32_t)obj_id;
+        if (a.size() < 3) fail("ERROR: Invalid args for 'f' (face) object. Please verify.");
+        for (int i = 0; i < 3; i++) {
+            int v = 0, t = 0, n = 0;
+            bool set_n = false, set_t = false;
+            // Per-vertex format sniffing in the reference's order (487-517): "%d/%d/%d" must
+            // convert 3, else "%d//%d" 2, else "%d/%d" 2, else "%d" 1.  Written out: a spec that
+            // breaks off midway degrades to the longest form that still converts.
+            const char* p = a[i].data();
+            const char* e = p + a[i].size();
+            bool exotic = false;
+            int form = -1;                                    // 0: v, 1: v/t, 2: v//n, 3: v/t/n
+            if (scan_int(p, e, &v, &exotic)) {
+                form = 0;
+                if (p < e && *p == '/') {
+                    const char* q = p + 1;
+                    if (q < e && *q == '/') {
+                        q++;
+                        if (scan_int(q, e, &n, &exotic)) form = 2;
+                    } else if (scan_int(q, e, &t, &exotic)) {
+                        form = 1;
+                        if (q < e && *q == '/') { q++; if (scan_int(q, e, &n, &exotic)) form = 3; }
+                    }
+                }
+            }
+            if (exotic || (form < 0 && !a[i].empty() && (a[i][0] == ' ' || a[i][0] == '\t' || a[i][0] == '\r' ||
+                                                         a[i][0] == '\v' || a[i][0] == '\f'))) {
+                // out-of-int indices or leading blanks (sscanf skips them): ask sscanf itself
+                const std::string z(a[i]);
+                const char* s = z.c_str();
+                v = t = n = 0;
+                if (std::sscanf(s, "%d/%d/%d", &v, &t, &n) == 3) form = 3;
+                else if (std::sscanf(s, "%d//%d", &v, &n) == 2) form = 2;
+                else if (std::sscanf(s, "%d/%d", &v, &t) == 2) form = 1;
+                else if (std::sscanf(s, "%d", &v) == 1) form = 0;
+                else form = -1;
+            }
+            if (form < 0) fail("ERROR: Invalid args for 'f' object. Please verify.");
+            f.smooth = (form >= 2) ? 1 : 0;
+            set_n = form >= 2; set_t = (form == 1 || form == 3);
+            const Vec3 pv = lookup(vertices, (unsigned)v);
+            f.v[i][0] = pv.x; f.v[i][1] = pv.y; f.v[i][2] = pv.z;
+            if (set_n) { const Vec3 nn = lookup(normals, (unsigned)n); f.vn[i][0] = nn.x; f.vn[i][1] = nn.y; f.vn[i][2] = nn.z; }
+            if (set_t) { const Vec2 tc = lookup(texcoords, (unsigned)t); f.vt[i][0] = tc.x; f.vt[i][1] = tc.y; }
+        }
+        // has_texture is decided by the parser state, not by the face format (523-534)
+        material_and_texture(&f.material, &f.texture);
+        out->faces.push_back(f);
+        return true;
+    }
+
+    void run(const char* data, size_t size)
+    {
+        std::vector<Tok> toks;
+        const char* p = data;
+        const char* const end = data + size;
+        while (p < end) {                                     // main.cpp:106: std::getline on '\n'
+            const char* nl = (const char*)std::memchr(p, '\n', (size_t)(end - p));
+            const char* le = nl ? nl : end;
+            const Tok line(p, (size_t)(le - p));
+            p = nl ? nl + 1 : end;
+            toks.clear();
+            const char* q = line.data();
+            while (q < le) {                                  // 112: split on ' ' only
+                const char* te = q;
+                while (te < le && *te != ' ') te++;
                 // 114: `!del.empty() || del.at(0) != '#'` -> an empty token throws
                 // std::out_of_range outside every try block: the reference aborts.
-                if (tok.empty())
-                    fail("basic_string::at: empty token (double or leading space) in line '" + line + "'");
-                args.push_back(tok);
+                if (te == q)
+                    fail("basic_string::at: empty token (double or leading space) in line '" + std::string(line) + "'");
+                toks.emplace_back(q, (size_t)(te - q));
+                q = te < le ? te + 1 : le;
             }
-            if (args.empty()) continue;                       // 119
-            std::string cmd = args[0];
-            args.erase(args.begin());
-            if (args.empty()) continue;                       // 136: no arguments -> ignored
+            if (toks.size() < 2) continue;                    // 119 / 136: no command or no arguments -> ignored
+            const Tok cmd = toks[0];
+            const Args args{ toks.data() + 1, toks.size() - 1 };
+            if (geometry(cmd, args, line)) continue;
             command(cmd, args);                               // unknown commands fall through silently
         }
         // required commands, in the reference's order (574-602)
@@ -262,10 +378,26 @@ extern "C" int rt_host_parse_scene_file(const char* path, const char* texture_di
 {
     if (!path || !out) { set_error("rt_host_parse_scene_file: null argument"); return RT_E_INVALID; }
     *out = nullptr;
-    std::ifstream in(path);
-    if (!in.is_open()) {                                      // main.cpp:567
-        set_error(std::string("ERROR: Issue reading input file '") + path + "'. Please verify path.");
-        return RT_E_IO;
+    std::vector<char> text;
+    {
+        FILE* fp = std::fopen(path, "rb");
+        if (!fp) {                                            // main.cpp:567
+            set_error(std::string("ERROR: Issue reading input file '") + path + "'. Please verify path.");
+            return RT_E_IO;
+        }
+        std::fseek(fp, 0, SEEK_END);
+        const long n = std::ftell(fp);
+        std::fseek(fp, 0, SEEK_SET);
+        bool ok = n >= 0;
+        if (ok) {
+            try { text.resize((size_t)n); } catch (const std::exception&) { ok = false; }
+        }
+        if (ok && n > 0) ok = std::fread(text.data(), 1, (size_t)n, fp) == (size_t)n;
+        std::fclose(fp);
+        if (!ok) {
+            set_error(std::string("ERROR: Issue reading input file '") + path + "'. Please verify path.");
+            return RT_E_IO;
+        }
     }
     OwnedScene* scene = new (std::nothrow) OwnedScene();
     if (!scene) { set_error("out of memory"); return RT_E_NOMEM; }
@@ -273,7 +405,7 @@ extern "C" int rt_host_parse_scene_file(const char* path, const char* texture_di
     p.out = scene;
     if (texture_dir) p.texture_dir = texture_dir;
     try {
-        p.run(in);
+        p.run(text.data(), text.size());
     } catch (const ParseError& e) {
         set_error(e.msg);
         delete scene;

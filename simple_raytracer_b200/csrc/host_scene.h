@@ -129,6 +129,9 @@ struct Workspace {
     DevBuf rgb24, flags8;  // scanline-order planes for rt_download_framebuffer
     ChainStreams chains;
     PinnedBuf h_counters;  // one Counters per sub-frame
+    // ppm_device.cu: per-block byte counts and offsets, the text on the device and in pinned host memory
+    DevBuf ppm_blocks, ppm_offsets, ppm_text;
+    PinnedBuf ppm_total_host, ppm_host;
     int device = -1;
 };
 
@@ -187,6 +190,9 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
 // returns true when some queue overflowed and then fills `demand` with what to grow to.
 bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels]);
 void stash_workspace(Workspace&& ws);
+
+// ppm_device.cu
+int format_ppm_device(SceneHost* s, const uchar4* px, const char** text, size_t* len, cudaStream_t st);
 
 }  // namespace rt
 

@@ -92,6 +92,13 @@ class DeviceScene:
         abi.check(self._lib.rt_download_framebuffer(self._h, _ptr(rgb), _ptr(flags)), "rt_download_framebuffer")
         return rgb, flags
 
+    def ppm_text(self, dev_rgba_ptr: int = 0) -> bytes:
+        """The P3 file of the frame, formatted on the device (rt_format_ppm_device)."""
+        text = C.c_void_p(); n = C.c_size_t()
+        abi.check(self._lib.rt_format_ppm_device(self._h, C.c_void_p(dev_rgba_ptr or None), C.byref(text), C.byref(n)),
+                  "rt_format_ppm_device")
+        return C.string_at(text, n.value)
+
     def download_primary_ids(self) -> np.ndarray:
         ids = np.zeros((self.scene.height, self.scene.width), dtype=np.int32)
         abi.check(self._lib.rt_download_primary_ids(self._h, _ptr(ids)), "rt_download_primary_ids")

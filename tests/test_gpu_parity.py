@@ -277,6 +277,27 @@ def test_work_sharing_in_the_walk_tails_never_changes_a_pixel():
             assert np.array_equal(ids_lbvh, ds.download_primary_ids())
 
 
+def test_device_formatted_ppm_equals_the_host_formatter():
+    """rt_format_ppm_device against rt_host_format_ppm on the downloaded frame: NaN
+    channels (Test1 has them), primary misses with an out-of-range bkgcolor, 1/2/3-digit values,
+    a pixel count that is not a multiple of the block size."""
+    from simple_raytracer_b200 import ppm
+    scene, _ = common.golden_frame("reflection_transparency_tests/Test1")
+    cases = [scene, scenegen.coverage_scene(131, 77).copy(bkg=(2.0, -0.5, 0.25)), scenegen.coverage_scene(16, 2)]
+    for sc in cases:
+        with DeviceScene(sc) as ds:
+            ds.render()
+            rgb, flags = ds.download()
+            want = ppm.format_ppm(rgb, flags, bkg=sc.bkg)
+            got = ds.ppm_text()
+            assert got == (want if isinstance(want, bytes) else want.encode()), (sc.width, sc.height)
+    assert (flags & 8).any()
+    with DeviceScene(scene) as ds:
+        ds.render()
+        _, fl = ds.download()
+        assert (fl & 7).any()           # the NaN token really was exercised
+
+
 def test_cached_device_memory_is_reused_and_can_be_released():
     """Freed scenes leave their device blocks in a process-wide cache (devmem.cu): a second upload
     of the same scene must give the same frame from recycled (dirty) blocks, and
