@@ -17,7 +17,7 @@ ARCH      := -gencode arch=compute_100a,code=sm_100a
 # conservative culling arithmetic may fuse.  No -use_fast_math.
 NVCCFLAGS := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC,-ffp-contract=off -Iinclude -I$(CSRC) \
              --expt-relaxed-constexpr -cudart static
-HOSTFLAGS := -std=c++17 -O2 -ffp-contract=off -fPIC -Wall -Wextra -Iinclude -I$(CSRC)/host
+HOSTFLAGS := -std=c++17 -O2 -ffp-contract=off -fPIC -pthread -Wall -Wextra -Iinclude -I$(CSRC)/host
 
 CU_SRCS   := $(wildcard $(CSRC)/*.cu)
 CU_HDRS   := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.h) include/rt.h

@@ -106,6 +106,106 @@ def test_parser_errors(tmp_path, text, needle):
     assert e.value.code == abi.RT_E_PARSE and needle in e.value.message
 
 
+def _parse_with(path, threads, chunk_bytes):
+    """-> ('ok', every array of the scene as bytes) or ('err', code, message)"""
+    old = {k: os.environ.get(k) for k in ("RT_HOST_THREADS", "RT_HOST_CHUNK_BYTES")}
+    os.environ["RT_HOST_THREADS"] = str(threads)
+    os.environ["RT_HOST_CHUNK_BYTES"] = str(chunk_bytes)
+    try:
+        s = Scene.from_file(path)
+        cam = np.array([s.width, s.height, *s.eye, *s.viewdir, *s.updir, s.hfov_deg, *s.bkg, s.bkg_eta], dtype=np.float64)
+        return ("ok", cam.tobytes(), s.materials.tobytes(), s.spheres.tobytes(), s.faces.tobytes(), s.lights.tobytes(),
+                tuple(t.tobytes() for t in s.textures))
+    except abi.RtError as e:
+        return ("err", e.code, e.message)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def test_chunked_parallel_parse_equals_the_sequential_one(tmp_path):
+    """The parser cuts the file into chunks parsed by several threads and links them afterwards
+    (scene_parser.cpp): whatever the cut points, the scene — object ids, the material / texture an
+    object captured, forward and missing vertex references, vertex counts — and the FIRST error
+    must be those of the one-chunk (= line by line) parse."""
+    rng = np.random.default_rng(5)
+    tex = tmp_path / "t.ppm"
+    tex.write_text(scenegen.p3_text(scenegen.make_texture("checker", 4, 4, 1)))
+    texts = []
+    # generated scenes: state restated per object (to_text) and a soup with shared state
+    sc = scenegen.coverage_scene(16, 12)
+    paths = []
+    for i, t in enumerate(sc.textures):
+        q = tmp_path / f"c{i}.ppm"
+        q.write_text(scenegen.p3_text(t))
+        paths.append(str(q))
+    texts.append(sc.to_text(paths))
+    soup = scenegen.random_soup(300, 20, 9)
+    spaths = []
+    for i, t in enumerate(soup.textures):
+        q = tmp_path / f"s{i}.ppm"
+        q.write_text(scenegen.p3_text(t))
+        spaths.append(str(q))
+    texts.append(soup.to_text(spaths))
+    # hand-made: state carried across many lines, forward / missing / negative references, every face form
+    lines = [BASE.strip(), "light 0 -1 0 0 1 1 1", "bkgcolor 0.3 0.2 0.1 1.5", "bkgcolor 0.5 0.5 0.5"]
+    nv = nvn = nvt = 0
+    for k in range(400):
+        r = rng.integers(0, 10)
+        if r == 0:
+            lines.append("mtlcolor " + " ".join(f"{x:.3f}" for x in rng.uniform(0, 1, 10)) + (" 0.5 1.3" if k % 3 else ""))
+        elif r == 1:
+            lines.append(f"texture {tex}")
+        elif r == 2 and k > 20:
+            lines.append("sphere " + " ".join(f"{x:.2f}" for x in rng.uniform(-3, 3, 4)))
+        elif r in (3, 4):
+            lines.append("v " + " ".join(f"{x:.4f}" for x in rng.uniform(-3, 3, 3))); nv += 1
+        elif r == 5:
+            lines.append("vn " + " ".join(f"{x:.4f}" for x in rng.uniform(-1, 1, 3))); nvn += 1
+        elif r == 6:
+            lines.append("vt " + " ".join(f"{x:.4f}" for x in rng.uniform(0, 1, 2))); nvt += 1
+        elif k > 20:
+            def ref(n):
+                return int(rng.integers(-1, n + 4))          # includes 0, -1 and not-yet-defined keys
+            form = rng.integers(0, 4)
+            spec = []
+            for _ in range(3):
+                a, b, c = ref(nv), ref(nvt), ref(nvn)
+                spec.append([f"{a}", f"{a}/{b}", f"{a}//{c}", f"{a}/{b}/{c}"][(form + rng.integers(0, 2)) % 4])
+            lines.append("f " + " ".join(spec))
+    good = "\n".join(lines[:6] + ["mtlcolor 1 1 1 1 1 1 0 1 0 1"] + lines[6:]) + "\n"
+    texts.append(good)
+    texts.append(good.rstrip("\n"))                                  # no newline at the end
+    texts.append(good.replace("\n", "\r\n"))                         # CRLF: the \r stays in the last token
+    # failing files: the first error in file order wins, wherever the cuts fall
+    texts.append("\n".join(lines) + "\n")                             # objects before any mtlcolor (maybe)
+    bad = good.split("\n")
+    for at, what in ((50, "v 1 2"), (120, "f 1 2"), (200, "sphere 1 2 x 4"), (260, "light  0 0 0 1 1 1 1"),
+                     (300, "texture missing.ppm"), (10, "imsize 1 1")):
+        b2 = list(bad)
+        b2.insert(at, what)
+        b2.insert(at + 40, "mtlcolor 1 1")                           # a later error must not win
+        texts.append("\n".join(b2))
+    # state errors: an object before any mtlcolor; `texture` before any mtlcolor
+    b2 = list(lines); b2.insert(6, "sphere 0 0 0 1"); texts.append("\n".join(b2) + "\n")
+    b2 = list(lines); b2.insert(6, f"texture {tex}"); b2.insert(9, "sphere 0 0 0 1"); texts.append("\n".join(b2) + "\n")
+    outcomes = []
+    for i, text in enumerate(texts):
+        path = _write(tmp_path, text, f"d{i}.txt")
+        want = _parse_with(path, 1, 1 << 30)
+        outcomes.append(want[2] if want[0] == "err" else "ok")
+        for threads, chunk in ((4, 64), (3, 257), (8, 4096)):
+            got = _parse_with(path, threads, chunk)
+            assert got == want, (i, threads, chunk, got[:3] if got[0] == "err" else "scene differs", want[:3] if want[0] == "err" else "")
+    assert outcomes.count("ok") >= 4
+    for needle in ("Invalid args for vertex", "'f' (face) object", "'sphere' object", "empty token", "Issue reading 'texture'",
+                   "Invalid image dimensions", "Must define a 'mtlcolor'.", "Must define a 'mtlcolor' and 'texture'"):
+        assert any(needle in o for o in outcomes), needle
+
+
 def test_parser_missing_file(tmp_path):
     with pytest.raises(abi.RtError) as e:
         Scene.from_file(str(tmp_path / "absent.txt"))
