@@ -10,7 +10,11 @@
 // pixel).
 #include "host_common.h"
 
+#include <algorithm>
+#include <atomic>
 #include <cctype>
+#include <chrono>
+#include <thread>
 #include <cerrno>
 #include <cstdio>
 #include <cstdlib>
@@ -54,8 +58,84 @@ bool stoi_token(const char* b, const char* e, long* out)
 
 }  // namespace
 
+namespace {
+
+// One chunk of the pixel part of a P3 file (utility.h:70-112): lines starting with '#' are
+// skipped, an empty line aborts (line.at(0) throws), tokens are split on ' ' only, empty
+// tokens are dropped, every other token goes through std::stoi.  Values are appended to
+// `out` up to the first token that does not convert, whose index and message are kept — the
+// caller decides whether that token is ever reached (the reference splits the WHOLE file into
+// tokens first, where an empty line is fatal wherever it is, and then converts only the first
+// width*height*3 of them).
+struct BodyChunk {
+    const char* begin = nullptr;
+    const char* end = nullptr;
+    bool at_line_start = true;
+    std::vector<uint8_t> out;
+    const char* err_at = nullptr;      // a token that does not convert / is out of range
+    size_t err_token = 0;              // ... and its index among this chunk's value tokens
+    const char* err_msg = nullptr;
+    const char* empty_line_at = nullptr;
+};
+
+void parse_body_chunk(BodyChunk& c)
+{
+    const char* p = c.begin;
+    const char* const end = c.end;
+    bool line_start = c.at_line_start;
+    c.out.reserve((size_t)(end - p) / 3);
+    while (p < end) {
+        if (line_start) {
+            if (*p == '\n') { c.empty_line_at = p; return; }                          // utility.h:77 on ""
+            if (*p == '#') {                                                        // comment line
+                const char* nl = (const char*)std::memchr(p, '\n', (size_t)(end - p));
+                p = nl ? nl + 1 : end;
+                continue;
+            }
+            line_start = false;
+        }
+        const char ch = *p;
+        if (ch == ' ') { p++; continue; }                                           // utility.h:85: empty tokens dropped
+        if (ch == '\n') { p++; line_start = true; continue; }
+        if (c.err_at) {                                                             // only empty lines matter from here on
+            const char* nl = (const char*)std::memchr(p, '\n', (size_t)(end - p));
+            p = nl ? nl : end;
+            continue;
+        }
+        // a token: the common case is 1-3 digits
+        const char* t = p;
+        unsigned v = 0;
+        while (p < end && (unsigned)(*p - '0') <= 9u && p - t < 4) { v = v * 10u + (unsigned)(*p - '0'); p++; }
+        if (p > t && (p == end || *p == ' ' || *p == '\n') ) {
+            if (v > 255u) { c.err_at = t; c.err_token = c.out.size(); c.err_msg = "value outside 0..255"; continue; }
+            c.out.push_back((uint8_t)v);
+            continue;
+        }
+        // anything else: std::stoi's rules (leading blanks such as '\r' or '\t', sign, trailing junk)
+        const char* te = t;
+        while (te < end && *te != ' ' && *te != '\n') te++;
+        long lv;
+        p = te;
+        if (!stoi_token(t, te, &lv)) { c.err_at = t; c.err_token = c.out.size(); c.err_msg = "stoi"; continue; }
+        if (lv < 0 || lv > 255) { c.err_at = t; c.err_token = c.out.size(); c.err_msg = "value outside 0..255"; continue; }
+        c.out.push_back((uint8_t)lv);
+    }
+}
+
+unsigned host_threads()
+{
+    unsigned n = std::max(1u, std::thread::hardware_concurrency());
+    if (const char* e = std::getenv("RT_HOST_THREADS")) { const long v = std::strtol(e, nullptr, 10); if (v > 0) n = (unsigned)v; }
+    return std::min(n, 64u);
+}
+
+}  // namespace
+
 int read_texture_p3(const std::string& path, int32_t* width, int32_t* height, std::vector<uint8_t>* rgb)
 {
+    const bool verbose = std::getenv("RT_HOST_VERBOSE") != nullptr;
+    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_begin = now();
     std::vector<char> data;
     if (!read_file(path, &data)) {
         // the reference does not notice (width/height stay uninitialised, utility.h:62-67,115)
@@ -65,8 +145,11 @@ int read_texture_p3(const std::string& path, int32_t* width, int32_t* height, st
     const char* p = data.data();
     const char* end = p + data.size();
     long w = -1, h = -1;
-    size_t token_no = 0, need = 0, have = 0;
-    while (p < end) {
+    size_t token_no = 0, need = 0;
+    const char* body = nullptr;        // first byte after the "255" token
+    bool body_at_line_start = false;
+    // header: "P3", width, height, "255" — the first four non-empty tokens outside comment lines
+    while (p < end && !body) {
         const char* eol = (const char*)std::memchr(p, '\n', (size_t)(end - p));
         const char* line_end = eol ? eol : end;
         if (line_end == p) {                                  // utility.h:77 line.at(0) on "" throws
@@ -75,7 +158,7 @@ int read_texture_p3(const std::string& path, int32_t* width, int32_t* height, st
         }
         if (*p != '#') {                                      // utility.h:77 comment lines
             const char* t = p;
-            while (t < line_end) {
+            while (t < line_end && !body) {
                 const char* te = (const char*)std::memchr(t, ' ', (size_t)(line_end - t));
                 if (!te) te = line_end;
                 if (te > t) {                                 // utility.h:85 non-empty tokens only
@@ -94,32 +177,84 @@ int read_texture_p3(const std::string& path, int32_t* width, int32_t* height, st
                             return RT_E_PARSE;
                         }
                         need = (size_t)w * (size_t)h * 3;
-                        rgb->assign(need, 0);
-                    } else if (token_no == 4) {
+                    } else {
                         if (!(te - t == 3 && t[0] == '2' && t[1] == '5' && t[2] == '5')) {
                             set_error("PPM pixel value must be between 0 - 255 .");
                             return RT_E_PARSE;
                         }
-                    } else if (have < need) {                 // surplus tokens are ignored like in the reference
-                        long v;
-                        if (!stoi_token(t, te, &v)) { set_error("texture '" + path + "': stoi"); return RT_E_PARSE; }
-                        if (v < 0 || v > 255) {
-                            set_error("texture '" + path + "': value outside 0..255");
-                            return RT_E_PARSE;
-                        }
-                        (*rgb)[have++] = (uint8_t)v;          // row-major, x fastest (utility.h:123-130)
+                        body = te;
                     }
                 }
                 t = te < line_end ? te + 1 : line_end;
             }
         }
-        p = eol ? eol + 1 : end;
+        if (!body) p = eol ? eol + 1 : end;
     }
-    if (token_no < 4 || have < need) {
+    if (!body) { set_error("texture '" + path + "': too few tokens"); return RT_E_PARSE; }
+
+    // pixel values: chunks cut after line ends, one thread each
+    const double t_read = now();
+    const unsigned threads = host_threads();
+    const size_t body_bytes = (size_t)(end - body);
+    size_t n_chunks = std::max<size_t>(1, std::min<size_t>(body_bytes / (256u << 10), (size_t)threads * 4));
+    if (const char* e = std::getenv("RT_HOST_CHUNK_BYTES")) {
+        const long cb = std::strtol(e, nullptr, 10);
+        if (cb > 0) n_chunks = std::max<size_t>(1, std::min<size_t>(body_bytes / (size_t)cb + 1, 4096));
+    }
+    if (threads == 1) n_chunks = 1;
+    std::vector<BodyChunk> chunks;
+    {
+        const char* q = body;
+        for (size_t k = 0; k < n_chunks && q < end; k++) {
+            const char* r = (k + 1 == n_chunks) ? end : std::min(end, body + (body_bytes / n_chunks) * (k + 1));
+            if (r < q) r = q;
+            if (r < end) {
+                const char* nl = (const char*)std::memchr(r, '\n', (size_t)(end - r));
+                r = nl ? nl + 1 : end;
+            }
+            BodyChunk c;
+            c.begin = q; c.end = r; c.at_line_start = (k > 0) || body_at_line_start;
+            chunks.push_back(std::move(c));
+            q = r;
+        }
+    }
+    {
+        std::atomic<size_t> next{ 0 };
+        auto work = [&]() { for (size_t k; (k = next.fetch_add(1)) < chunks.size();) parse_body_chunk(chunks[k]); };
+        std::vector<std::thread> pool;
+        const unsigned extra = chunks.size() > 1 ? (unsigned)std::min<size_t>(threads, chunks.size()) - 1 : 0;
+        for (unsigned t = 0; t < extra; t++) pool.emplace_back(work);
+        work();
+        for (std::thread& t : pool) t.join();
+    }
+    const double t_parsed = now();
+    for (const BodyChunk& c : chunks)
+        if (c.empty_line_at) {
+            set_error("texture '" + path + "': empty line (basic_string::at)");
+            return RT_E_PARSE;
+        }
+    // in file order: a token that does not convert matters only among the first `need`
+    rgb->assign(need, 0);
+    size_t have = 0;
+    for (const BodyChunk& c : chunks) {
+        if (have >= need) break;
+        if (c.err_at && have + c.err_token < need) {
+            set_error("texture '" + path + "': " + c.err_msg);
+            return RT_E_PARSE;
+        }
+        const size_t take = std::min(c.out.size(), need - have);
+        if (take) std::memcpy(rgb->data() + have, c.out.data(), take);
+        have += take;
+        if (c.err_at) break;           // values after the bad token of this chunk were not collected
+    }
+    if (have < need) {
         set_error("texture '" + path + "': too few tokens");
         return RT_E_PARSE;
     }
     *width = (int32_t)w; *height = (int32_t)h;
+    if (verbose)
+        std::fprintf(stderr, "read_texture_p3: %zu chunks, %u threads: read %.1f ms, parse %.1f ms, gather %.1f ms\n",
+                     chunks.size(), threads, t_read - t_begin, t_parsed - t_read, now() - t_parsed);
     return RT_OK;
 }
 

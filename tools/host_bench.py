@@ -35,15 +35,21 @@ with tempfile.TemporaryDirectory() as td:
     open(p, "w").write(scenegen.p3_text(tex))
     sz = os.path.getsize(p)
     w_ = C.c_int32(); h_ = C.c_int32(); buf = C.POINTER(C.c_uint8)()
-    best = 1e9
-    for _ in range(3):
-        t0 = time.perf_counter()
-        rc = host.rt_host_read_texture_p3(os.fsencode(p), C.byref(w_), C.byref(h_), C.byref(buf))
-        best = min(best, time.perf_counter() - t0)
-        assert rc == 0
-        host.rt_host_free(buf)
-    out["read_p3_2048x1024_ms"] = round(best * 1e3, 1)
-    out["read_p3_MBps"] = round(sz / best / 1e6, 1)
+    for thr in ("1", ""):
+        if thr:
+            os.environ["RT_HOST_THREADS"] = thr
+        else:
+            os.environ.pop("RT_HOST_THREADS", None)
+        best = 1e9
+        for _ in range(4):
+            t0 = time.perf_counter()
+            rc = host.rt_host_read_texture_p3(os.fsencode(p), C.byref(w_), C.byref(h_), C.byref(buf))
+            best = min(best, time.perf_counter() - t0)
+            assert rc == 0
+            host.rt_host_free(buf)
+        tag = "1thread" if thr else "allthreads"
+        out[f"read_p3_2048x1024_ms_{tag}"] = round(best * 1e3, 1)
+        out[f"read_p3_MBps_{tag}"] = round(sz / best / 1e6, 1)
     # f-3: scene text of a triangle soup
     ntri = int(os.environ.get("HOST_BENCH_TRIS", "200000"))
     sc = scenegen.stress_scene(ntri, 1000, 64, 64, tex_size=16)
@@ -53,12 +59,23 @@ with tempfile.TemporaryDirectory() as td:
     sp = os.path.join(td, "scene.txt")
     t0 = time.perf_counter(); open(sp, "w").write(sc.to_text(paths)); gen = time.perf_counter() - t0
     sz = os.path.getsize(sp)
-    t0 = time.perf_counter()
-    sc2 = Scene.from_file(sp)
-    dt = time.perf_counter() - t0
-    assert len(sc2.faces) == ntri
     out["parse_scene_tris"] = ntri
-    out["parse_scene_ms"] = round(dt * 1e3, 1)
-    out["parse_scene_MBps"] = round(sz / dt / 1e6, 1)
+    desc = C.POINTER(abi.RtSceneDesc)()
+    for thr in ("1", ""):
+        if thr:
+            os.environ["RT_HOST_THREADS"] = thr
+        else:
+            os.environ.pop("RT_HOST_THREADS", None)
+        best = 1e9
+        for _ in range(3):
+            t0 = time.perf_counter()
+            rc = host.rt_host_parse_scene_file(os.fsencode(sp), None, C.byref(desc))
+            best = min(best, time.perf_counter() - t0)
+            assert rc == 0 and desc.contents.n_faces == ntri
+            host.rt_host_free_scene_desc(desc)
+        tag = "1thread" if thr else "allthreads"
+        out[f"parse_scene_ms_{tag}"] = round(best * 1e3, 1)
+        out[f"parse_scene_MBps_{tag}"] = round(sz / best / 1e6, 1)
+    out["host_cpus"] = os.cpu_count()
     out["scene_file_MB"] = round(sz / 1e6, 1)
 print(json.dumps(out))
