@@ -229,6 +229,55 @@ def test_texture_loader(tmp_path):
         assert needle in e.value.message
 
 
+def test_texture_loader_chunks_agree_with_one_pass(tmp_path):
+    """The pixel part of a P3 file is parsed in parallel chunks (ppm_io.cpp): same pixels and same
+    verdict as the single chunk, incl. the reference's order of failures — an empty line anywhere is
+    fatal (it tokenises the whole file first), a bad token only among the first w*h*3."""
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 256, (23, 17, 3), dtype=np.uint8)
+    rows = [" ".join(map(str, r.reshape(-1))) for r in img]
+    body = "\n".join(rows) + "\n"
+    files = {
+        "plain": "P3\n17 23\n255\n" + body,
+        "comments": "P3\n17 23\n255\n" + "\n".join(r + ("\n# note" if i % 5 == 0 else "") for i, r in enumerate(rows)) + "\n",
+        "one_line_header": "P3 17 23 255 " + body,
+        "crlf_values": "P3\n17 23\n255\n" + body.replace("\n", "\r\n"),
+        "surplus_junk": "P3\n17 23\n255\n" + body + "these tokens are never converted 999 -1\n",
+        "surplus_then_empty_line": "P3\n17 23\n255\n" + body + "1 2 3\n\n4 5 6\n",
+        "bad_token_early": "P3\n17 23\n255\n" + body.replace(rows[3], rows[3].replace(" ", " x ", 1), 1),
+        "bad_and_empty": "P3\n17 23\n255\n" + body.replace(rows[3], "300 1 2", 1) + "\n\n",
+        "too_few": "P3\n17 23\n255\n" + "\n".join(rows[:20]) + "\n",
+        "no_final_newline": "P3\n17 23\n255\n" + body.rstrip("\n"),
+    }
+
+    def load(path, threads, chunk):
+        old = {k: os.environ.get(k) for k in ("RT_HOST_THREADS", "RT_HOST_CHUNK_BYTES")}
+        os.environ["RT_HOST_THREADS"] = str(threads)
+        os.environ["RT_HOST_CHUNK_BYTES"] = str(chunk)
+        try:
+            return ("ok", ppm.read_texture_p3(path).tobytes())
+        except abi.RtError as e:
+            return ("err", e.message)
+        finally:
+            for k, v in old.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+
+    verdicts = {}
+    for name, text in files.items():
+        path = _write(tmp_path, text, name + ".ppm")
+        want = load(path, 1, 1 << 30)
+        verdicts[name] = want
+        for threads, chunk in ((4, 50), (3, 333), (8, 4096)):
+            assert load(path, threads, chunk) == want, (name, threads, chunk)
+    for name in ("plain", "comments", "one_line_header", "crlf_values", "surplus_junk", "no_final_newline"):
+        assert verdicts[name] == ("ok", img.tobytes()), name
+    assert "empty line" in verdicts["surplus_then_empty_line"][1] and "empty line" in verdicts["bad_and_empty"][1]
+    assert "stoi" in verdicts["bad_token_early"][1] and "too few" in verdicts["too_few"][1]
+
+
 def test_ppm_writer_text_is_the_reference_dialect():
     rgb = np.array([[[0, 7, 255], [12, 100, 99]], [[1, 2, 3], [0, 0, 0]]], dtype=np.uint8)
     flags = np.array([[0, 0], [7, 8]], dtype=np.uint8)
