@@ -239,7 +239,7 @@ struct BvhAccelT {
 
     template <class Job>
     RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes, int inner_min = 1, int leaf_min = 1,
-                                WalkClock* clock = nullptr, bool steal = true) const
+                                WalkClock* clock = nullptr, bool steal = true, unsigned job_budget = 0xffffffffu) const
     {
         constexpr int kDone = kWalkDone;
         constexpr unsigned kFull = 0xffffffffu;
@@ -264,6 +264,7 @@ struct BvhAccelT {
         RayQ rq = make_rayq(mk3(0.f, 0.f, 0.f), mk3(1.f, 1.f, 1.f));
         float tmin = 0.f, tmax = 0.f;
         unsigned long long t_empty = 0;
+        unsigned fetched = 0;
         bool worked = false;
         unsigned d_steps = 0, d_lanes = 0, d_steals = 0;
         if (kCount && clock && lane == 0) atomicMax(&clock->inv_first, ~globaltimer());
@@ -289,7 +290,10 @@ struct BvhAccelT {
                 unsigned base = 0;
                 if (lane == 0) base = atomicAdd(counter, (unsigned)__popc(dead));
                 base = __shfl_sync(kFull, base, 0);
-                if (base + (unsigned)__popc(dead) >= total) {
+                // (job_budget: a warp stops fetching after that many jobs, so that its block ends and
+                // the slot can go to a kernel of higher priority — render.cu)
+                fetched += (unsigned)__popc(dead);
+                if (base + (unsigned)__popc(dead) >= total || fetched >= job_budget) {
                     pool_empty = true;
                     if (kCount && clock) t_empty = globaltimer();
                 }

@@ -86,8 +86,9 @@ struct PinnedBuf {
 };
 
 // Streams and events of the LBVH pipeline's launch chains (render.cu): sub-frame j runs
-// trace -> spawn on main[j] (main[0] is not used: chain 0 runs on the caller's stream) and
-// shadow -> colour on side[j].  Created on first use, travels with the Workspace.
+// trace -> spawn on main[j] (highest stream priority: the critical path) and shadow -> colour
+// on side[j] (lowest); both fork from and join the caller's stream.  Created on first use,
+// travels with the Workspace.
 struct ChainStreams {
     cudaStream_t main[kMaxSubframes] = { nullptr }, side[kMaxSubframes] = { nullptr };
     cudaEvent_t fork[kMaxSubframes][kMaxLevels] = { { nullptr } };

@@ -107,8 +107,11 @@ bool ChainStreams::ensure(int n)
 {
     if (!begin && !cuda_ok(cudaEventCreateWithFlags(&begin, cudaEventDisableTiming), "cudaEventCreate")) return false;
     for (int j = chains; j < n; j++) {
-        if (j > 0 && !cuda_ok(cudaStreamCreateWithFlags(&main[j], cudaStreamNonBlocking), "cudaStreamCreate")) return false;
-        if (!cuda_ok(cudaStreamCreateWithFlags(&side[j], cudaStreamNonBlocking), "cudaStreamCreate")) return false;
+        // the trace -> spawn chain is the critical path: highest priority; shadow -> colour lowest
+        int lo = 0, hi = 0;
+        if (!cuda_ok(cudaDeviceGetStreamPriorityRange(&lo, &hi), "cudaDeviceGetStreamPriorityRange")) return false;
+        if (!cuda_ok(cudaStreamCreateWithPriority(&main[j], cudaStreamNonBlocking, hi), "cudaStreamCreate")) return false;
+        if (!cuda_ok(cudaStreamCreateWithPriority(&side[j], cudaStreamNonBlocking, lo), "cudaStreamCreate")) return false;
         for (int l = 0; l < kMaxLevels; l++)
             if (!cuda_ok(cudaEventCreateWithFlags(&fork[j][l], cudaEventDisableTiming), "cudaEventCreate")) return false;
         if (!cuda_ok(cudaEventCreateWithFlags(&side_done[j], cudaEventDisableTiming), "cudaEventCreate") ||
@@ -278,6 +281,9 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     static const long long steal_max_work = 1000LL * tuning_int("RT_STEAL_MAX_KRAYS", 1500, 0, 2000000);
     const int steal = p.work_sharing == 1 ? 1 : p.work_sharing == 2 ? 0 : steal_env;
     const int steal_shadow = p.work_sharing == 1 ? 1 : p.work_sharing == 2 ? 0 : steal_shadow_env;
+    // Any-hit blocks that end after a bounded number of jobs + a high-priority trace chain: a trace
+    // launch that becomes ready gets SM slots at once instead of waiting behind persistent shadow blocks
+    static const int shadow_budget = tuning_int("RT_SHADOW_JOB_BUDGET", 0, 0, 1 << 20);
     static const int shadow_mult = tuning_int("RT_SHADOW_GRID_MULT", 0, 0, 64);   // 0: same as RT_GRID_MULT
 
     static thread_local FrameParams PS[kMaxSubframes];
@@ -296,6 +302,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         P.out_mul = K; P.out_add = j; P.out_tiles = tl.n_local_tiles;
         P.refill_lanes = refill; P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
         P.steal = 1;
+        P.shadow_job_budget = overlap ? shadow_budget : 0;
     }
 
     RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
@@ -315,10 +322,8 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     ChainStreams& cs = s->ws.chains;
     if (overlap) {
         if (!cs.ensure(K)) return RT_E_CUDA;
-        if (K > 1) {
-            RT_CUDA(cudaEventRecord(cs.begin, stream));    // the counters are cleared
-            for (int j = 1; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
-        }
+        RT_CUDA(cudaEventRecord(cs.begin, stream));        // the counters are cleared
+        for (int j = 0; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
     }
     for (int l = 0; l <= p.max_depth; l++) {
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
@@ -334,8 +339,10 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 continue;
             }
             // trace: one thread per ray; shadow: one chain per node; colour / spawn: one thread per node
-            cudaStream_t ms = (overlap && j > 0) ? cs.main[j] : stream;
-            const int sh_grid = persistent_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
+            cudaStream_t ms = overlap ? cs.main[j] : stream;
+            int sh_grid = persistent_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
+            if (overlap && shadow_budget > 0)   // bounded blocks: as many as the queue may need (surplus blocks end at once)
+                sh_grid = (int)std::max<long long>(sh_grid, std::min<long long>((work + 4LL * shadow_budget - 1) / (4LL * shadow_budget) + 1, 1 << 20));
             const bool sharing = steal == 1 || (steal == 2 && work <= steal_max_work);
             if (p.instrument) {
                 if (sharing) bvh_trace_kernel<true, true><<<grid, kBlock, 0, ms>>>(P, l);
@@ -376,7 +383,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     // bottom-up combine per chain, on the chain's main stream once its colour kernels are done
     for (int j = 0; j < K; j++) {
         const FrameParams& P = PS[j];
-        cudaStream_t ms = (overlap && j > 0) ? cs.main[j] : stream;
+        cudaStream_t ms = overlap ? cs.main[j] : stream;
         if (overlap) {
             RT_CUDA(cudaEventRecord(cs.side_done[j], cs.side[j]));
             RT_CUDA(cudaStreamWaitEvent(ms, cs.side_done[j], 0));
@@ -388,7 +395,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             combine_kernel<<<grid, 256, 0, ms>>>(P, l);
             n++;
         }
-        if (overlap && j > 0) {
+        if (overlap) {
             RT_CUDA(cudaEventRecord(cs.main_done[j], ms));
             RT_CUDA(cudaStreamWaitEvent(stream, cs.main_done[j], 0));
         }

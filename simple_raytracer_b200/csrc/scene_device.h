@@ -155,6 +155,7 @@ struct FrameParams {
     int refill_lanes;     // persistent kernels: fetch new rays when this many lanes of a warp are idle
     int inner_min_lanes;  // ... leave the inner-node loop when fewer lanes than this can still descend
     int leaf_min_lanes;   // ... leave the leaf loop when fewer lanes than this hold a leaf
+    int shadow_job_budget; // ... any-hit kernel: jobs a warp takes before it stops fetching (0 = no limit)
     int steal;            // ... idle lanes take subtrees from busy ones once the queue is dry (closest-hit walks)
 };
 

@@ -345,7 +345,8 @@ __global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constan
     const unsigned n_nodes = P.counters->nodes[level];
     ShadowJob<kCount, kNearFirst, kStealing> job{ P, acc, level, n_nodes };
     acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
-                        kCount ? &P.counters->clock[1][level] : nullptr, P.steal != 0);
+                        kCount ? &P.counters->clock[1][level] : nullptr, P.steal != 0,
+                        P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
         unsigned long long w = job.walks;
