@@ -329,6 +329,7 @@ struct BvhAccelT {
                         job.adopt(src, take, o, ray);
                         if (give) bot += n_give;
                         if (kCount) d_steals += (unsigned)pairs;
+                        __syncwarp();      // the donors' earlier stack writes are visible to the takers
                         if (take) {
                             alive = true; owner = owner_s;
                             tmin = tmin_s; tmax = tmax_s;
