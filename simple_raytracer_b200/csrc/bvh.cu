@@ -414,6 +414,125 @@ __global__ void emit_prims_kernel(int n, int nf, const unsigned* __restrict__ so
     }
 }
 
+
+// ---- 8-wide compressed nodes for the any-hit walk (layout: bvh.cuh, Node8) ------------------
+// Breadth-first collapse of the binary tree, one launch per level: a thread takes one binary
+// node of the current level's queue, opens its children greedily by surface area until it
+// holds 8 entries (or only primitives), reserves CONSECUTIVE slots for its inner entries in
+// the next level's queue and for its primitives in the node-ordered primitive table (one
+// atomicAdd each), so that a child is found by base + rank and no per-child index is stored.
+struct Collapse8Counters { unsigned next_count, prim_count; };
+
+__device__ float box_area(float4 lo, float4 hi)
+{
+    const float dx = fmaxf(hi.x - lo.x, 0.0f), dy = fmaxf(hi.y - lo.y, 0.0f), dz = fmaxf(hi.z - lo.z, 0.0f);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void collapse8_kernel(int n_prims, int nf, unsigned cur_count, unsigned cur_offset, unsigned next_offset,
+                                 const int* __restrict__ queue_cur, int* __restrict__ queue_next,
+                                 Collapse8Counters* __restrict__ counters, const unsigned* __restrict__ sorted_vals,
+                                 const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
+                                 const int2* __restrict__ children, const float4* __restrict__ node_lo,
+                                 const float4* __restrict__ node_hi, const float4* __restrict__ tri,
+                                 const float4* __restrict__ sph, uint4* __restrict__ nodes8, float4* __restrict__ prims8)
+{
+    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= cur_count) return;
+    const int root = queue_cur[t];
+    int ent[8];
+    int n_e = 2;
+    { const int2 ch = children[root]; ent[0] = ch.x; ent[1] = ch.y; }
+    while (n_e < 8) {
+        int best = -1; float best_area = -1.0f;
+        for (int k = 0; k < n_e; k++) {
+            if (ent[k] < 0) continue;
+            const float a = box_area(node_lo[ent[k]], node_hi[ent[k]]);
+            if (a > best_area || best < 0) { best_area = a; best = k; }
+        }
+        if (best < 0) break;
+        const int2 ch = children[ent[best]];
+        ent[best] = ch.x; ent[n_e++] = ch.y;
+    }
+    // slots: inner entries first, then the primitives (bvh.cuh: a child is base + slot, a primitive
+    // prim_base + slot - n_inner)
+    {
+        int tmp[8], m = 0;
+        for (int k = 0; k < n_e; k++) if (ent[k] >= 0) tmp[m++] = ent[k];
+        for (int k = 0; k < n_e; k++) if (ent[k] < 0) tmp[m++] = ent[k];
+        for (int k = 0; k < n_e; k++) ent[k] = tmp[k];
+    }
+    float4 lo[8], hi[8];
+    float nlo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, nhi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    unsigned imask = 0, lmask = 0;
+    for (int k = 0; k < n_e; k++) {
+        if (ent[k] < 0) { const unsigned p = sorted_vals[~ent[k]]; lo[k] = prim_lo[p]; hi[k] = prim_hi[p]; lmask |= 1u << k; }
+        else { lo[k] = node_lo[ent[k]]; hi[k] = node_hi[ent[k]]; imask |= 1u << k; }
+        const float l[3] = { lo[k].x, lo[k].y, lo[k].z }, h[3] = { hi[k].x, hi[k].y, hi[k].z };
+        for (int c = 0; c < 3; c++) { nlo[c] = fminf(nlo[c], l[c]); nhi[c] = fmaxf(nhi[c], h[c]); }
+    }
+    const unsigned n_in = (unsigned)__popc(imask), n_leaf = (unsigned)__popc(lmask);
+    const unsigned child_base = next_offset + (n_in ? atomicAdd(&counters->next_count, n_in) : 0u);
+    const unsigned prim_base = n_leaf ? atomicAdd(&counters->prim_count, n_leaf) : 0u;
+    // the frame: as write_node4
+    float origin[3], q[3];
+    unsigned eb[3];
+    for (int c = 0; c < 3; c++) {
+        float ext = nhi[c] - nlo[c];
+        if (!(ext >= 0.0f) || !isfinite(ext)) ext = 0.0f;
+        int e = -120;
+        if (ext > 0.0f) { int k; frexpf(ext / 250.0f, &k); e = k; }
+        const float maxabs = fmaxf(fabsf(nlo[c]), fabsf(nhi[c]));
+        if (maxabs > 0.0f && isfinite(maxabs)) e = max(e, ilogbf(maxabs) - 17);
+        e = min(max(e, -120), 120);
+        q[c] = ldexpf(1.0f, e);
+        eb[c] = (unsigned)(e + 127);
+        origin[c] = nlo[c] - 2.0f * q[c];
+    }
+    unsigned planes[3][4] = { { 0, 0, 0, 0 }, { 0, 0, 0, 0 }, { 0, 0, 0, 0 } };   // [axis][child pair]
+    unsigned rank_in = 0, rank_leaf = 0;
+    for (int k = 0; k < 8; k++) {
+        unsigned ql[3] = { 255u, 255u, 255u }, qh[3] = { 0u, 0u, 0u };            // empty slot: never hit
+        if (k < n_e) {
+            const float l[3] = { lo[k].x, lo[k].y, lo[k].z }, h[3] = { hi[k].x, hi[k].y, hi[k].z };
+            for (int c = 0; c < 3; c++) {
+                const float fl = floorf((l[c] - origin[c]) / q[c]) - 1.0f;
+                const float fh = ceilf((h[c] - origin[c]) / q[c]) + 1.0f;
+                ql[c] = (unsigned)fminf(fmaxf(fl, 0.0f), 255.0f);
+                qh[c] = (unsigned)fminf(fmaxf(fh, 0.0f), 255.0f);
+            }
+            if (ent[k] >= 0) {
+                queue_next[child_base - next_offset + rank_in] = ent[k];
+                rank_in++;
+            } else {
+                // the primitive's record, node-ordered (spheres widened to the triangle record size)
+                const int p = (int)sorted_vals[~ent[k]];
+                float4* o = prims8 + (size_t)(prim_base + rank_leaf) * kTriWords;
+                if (p < nf) {
+                    const float4* w = tri + (size_t)p * kTriWords;
+                    for (int qd = 0; qd < kTriWords; qd++) o[qd] = w[qd];
+                } else {
+                    const float4* w = sph + (size_t)(p - nf) * kSphWords;
+                    o[0] = w[0];
+                    o[1] = o[2] = o[3] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    o[4] = make_float4(0.0f, w[1].x, w[1].y, __int_as_float(1));
+                }
+                rank_leaf++;
+            }
+        }
+        for (int c = 0; c < 3; c++) planes[c][k >> 1] |= (ql[c] | (qh[c] << 8)) << ((k & 1) * 16);
+    }
+    uint4* w = nodes8 + (size_t)(cur_offset + t) * 6;
+    w[0] = make_uint4(__float_as_uint(origin[0]), __float_as_uint(origin[1]), __float_as_uint(origin[2]),
+                      eb[0] | (eb[1] << 8) | (eb[2] << 16) | (n_in << 24));
+    w[1] = make_uint4(child_base, prim_base, lmask, imask);
+    w[2] = make_uint4(planes[0][0], planes[0][1], planes[0][2], planes[0][3]);
+    w[3] = make_uint4(planes[1][0], planes[1][1], planes[1][2], planes[1][3]);
+    w[4] = make_uint4(planes[2][0], planes[2][1], planes[2][2], planes[2][3]);
+    w[5] = make_uint4(0u, 0u, 0u, 0u);
+    (void)n_prims;
+}
+
 }  // namespace
 
 int build_bvh(SceneHost* s)
@@ -467,6 +586,41 @@ int build_bvh(SceneHost* s)
     }
     emit_prims_kernel<<<(n + 1 + B - 1) / B, B, 0, st>>>(n, s->nf, vin, s->tri.as<float4>(), s->sph.as<float4>(), s->bvh_tri.as<float4>());
     RT_CUDA(cudaGetLastError());
+    // the 8-wide tree of the any-hit walk (scenes with a binary tree worth collapsing)
+    s->bvh8_n_nodes = 0;
+    static const int use8 = tuning_int("RT_BVH8", 1, 0, 1);
+    if (use8 && n > 8) {
+        DevBuf queue_a, queue_b, counters;
+        PinnedBuf h_count;
+        if (!queue_a.reserve(N * 4) || !queue_b.reserve(N * 4) || !counters.reserve(sizeof(Collapse8Counters)) ||
+            !h_count.reserve(sizeof(Collapse8Counters)) ||
+            !s->bvh8_nodes.reserve((size_t)n_internal * 96) || !s->bvh8_prims.reserve((N + 1) * kTriWords * 16))
+            return RT_E_NOMEM;
+        RT_CUDA(cudaMemsetAsync(counters.p, 0, sizeof(Collapse8Counters), st));
+        RT_CUDA(cudaMemsetAsync(queue_a.p, 0, 4, st));                    // level 0: the binary root (node 0)
+        int* qc = queue_a.as<int>(); int* qn = queue_b.as<int>();
+        unsigned cur_count = 1, cur_offset = 0;
+        Collapse8Counters* hc = static_cast<Collapse8Counters*>(h_count.p);
+        for (int level = 0; cur_count > 0; level++) {
+            if (level > 64) { set_error("collapse8: tree deeper than 64 levels"); return RT_E_CUDA; }
+            const unsigned next_offset = cur_offset + cur_count;
+            collapse8_kernel<<<(cur_count + B - 1) / B, B, 0, st>>>(n, s->nf, cur_count, cur_offset, next_offset, qc, qn,
+                                                                  counters.as<Collapse8Counters>(), vin, box_lo.as<float4>(),
+                                                                  box_hi.as<float4>(), children.as<int2>(), node_lo.as<float4>(),
+                                                                  node_hi.as<float4>(), s->tri.as<float4>(), s->sph.as<float4>(),
+                                                                  s->bvh8_nodes.as<uint4>(), s->bvh8_prims.as<float4>());
+            RT_CUDA(cudaGetLastError());
+            RT_CUDA(cudaMemcpyAsync(hc, counters.p, sizeof(Collapse8Counters), cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaStreamSynchronize(st));
+            const unsigned next_count = hc->next_count;
+            // next level: its queue counter starts at zero again (the primitive counter runs on)
+            RT_CUDA(cudaMemsetAsync(counters.p, 0, sizeof(unsigned), st));
+            std::swap(qc, qn);
+            cur_offset = next_offset; cur_count = next_count;
+        }
+        if (hc->prim_count != (unsigned)n) { set_error("collapse8: primitive count mismatch"); return RT_E_CUDA; }
+        s->bvh8_n_nodes = (int)cur_offset;
+    }
     RT_CUDA(cudaStreamSynchronize(st));
     s->bvh_n_nodes = n_internal; s->bvh_root = 0; s->bvh_built = true;
     return RT_OK;

@@ -53,6 +53,8 @@ struct BvhAccelT {
     const float4* prims;   // Morton order, kTriWords words per slot
     const float4* tri;     // file order (direct tests of one known object)
     const float4* sph;
+    const uint4* nodes8;   // 8-wide tree of the any-hit walk (Node8 below), null when not built
+    const float4* prims8;  // ... and its node-ordered primitive records
     int nf, ns;
     int root;              // node index; n_nodes == 0 means empty scene
     int n_nodes;
@@ -167,6 +169,70 @@ struct BvhAccelT {
         return next;
     }
 
+
+    // ---- the 8-wide tree (any-hit walks) ------------------------------------------------------
+    // Node8, 96 bytes (bvh.cu: collapse8_kernel):
+    //   w0: frame origin x, y, z | ex, ey, ez, n_inner (bits 24..27)
+    //   w1: child_base, prim_base, -, -
+    //   w2 / w3 / w4: x / y / z planes, word j = lo, hi of slot 2j | lo, hi of slot 2j+1
+    // Slots 0 .. n_inner-1 are inner nodes (node index child_base + slot), the next slots are
+    // primitives (record prim_base + slot - n_inner), the rest are empty (lo = 255 > hi = 0).
+    // Children are found by base + rank, so a stack entry can stand for ALL pending inner
+    // children of a node: (child_base << 8) | mask of slots still to visit ("group"); >= 0.
+    // Primitives travel as the usual leaf codes (< 0).
+    template <class Push, class Pop>
+    RT_DEV int step8(const uint4* __restrict__ nd8, int group, const RayQ& r, float tmin, float tmax, Push& push, Pop& pop) const
+    {
+        // next child of the group; what is left of the group goes back on the stack (caller)
+        const unsigned mask = (unsigned)group & 0xffu;
+        const unsigned slot = (unsigned)__ffs((int)mask) - 1u;
+        const unsigned node = ((unsigned)group >> 8) + slot;
+        const unsigned rest = mask & (mask - 1u);
+        if (rest) push((int)(((unsigned)group & ~0xffu) | rest));
+        const uint4* w = nd8 + (size_t)node * 6;
+        uint4 h, c, px, py, pz;
+        asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+            : "=r"(h.x), "=r"(h.y), "=r"(h.z), "=r"(h.w), "=r"(c.x), "=r"(c.y), "=r"(c.z), "=r"(c.w) : "l"(w));
+        asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+            : "=r"(px.x), "=r"(px.y), "=r"(px.z), "=r"(px.w), "=r"(py.x), "=r"(py.y), "=r"(py.z), "=r"(py.w) : "l"(w + 2));
+        pz = __ldg(w + 4);
+        if (kCount) cnt_boxes += 1;
+        const float sx = __uint_as_float((h.w & 0xffu) << 23) * r.inv.x;
+        const float sy = __uint_as_float(((h.w >> 8) & 0xffu) << 23) * r.inv.y;
+        const float sz = __uint_as_float(((h.w >> 16) & 0xffu) << 23) * r.inv.z;
+        const float cx = fmaf(-8388608.0f, sx, (__uint_as_float(h.x) - r.o.x) * r.inv.x);
+        const float cy = fmaf(-8388608.0f, sy, (__uint_as_float(h.y) - r.o.y) * r.inv.y);
+        const float cz = fmaf(-8388608.0f, sz, (__uint_as_float(h.z) - r.o.z) * r.inv.z);
+        const unsigned wx[4] = { px.x, px.y, px.z, px.w }, wy[4] = { py.x, py.y, py.z, py.w }, wz[4] = { pz.x, pz.y, pz.z, pz.w };
+        // (lo, hi) of an even slot sit in bytes 0, 1 of its word, of an odd slot two further up
+        const unsigned yn = r.sn[1] - 2u, yf = r.sf[1] - 2u;
+        unsigned hit = 0;
+        #pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const unsigned up = (k & 1) ? 2u : 0u;
+            const float nx = fmaf(__uint_as_float(__byte_perm(wx[k >> 1], 0x4B000000u, r.sn[0] + up)), sx, cx);
+            const float ny = fmaf(__uint_as_float(__byte_perm(wy[k >> 1], 0x4B000000u, yn + up)), sy, cy);
+            const float nz = fmaf(__uint_as_float(__byte_perm(wz[k >> 1], 0x4B000000u, r.sn[2] + up)), sz, cz);
+            const float fx = fmaf(__uint_as_float(__byte_perm(wx[k >> 1], 0x4B000000u, r.sf[0] + up)), sx, cx);
+            const float fy = fmaf(__uint_as_float(__byte_perm(wy[k >> 1], 0x4B000000u, yf + up)), sy, cy);
+            const float fz = fmaf(__uint_as_float(__byte_perm(wz[k >> 1], 0x4B000000u, r.sf[2] + up)), sz, cz);
+            const float tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, tmin));
+            const float tf = fminf(fminf(fx, fy), fminf(fz, tmax));
+            if (tn <= tf) hit |= 1u << k;
+        }
+        const unsigned n_inner = (h.w >> 24) & 15u;
+        const unsigned inner = hit & ((1u << n_inner) - 1u);
+        unsigned leaves = hit >> n_inner;
+        if (inner) push((int)((c.x << 8) | inner));
+        // primitives last = on top of the stack: an any-hit walk wants them first
+        while (leaves) {
+            const unsigned k = (unsigned)__ffs((int)leaves) - 1u;
+            leaves &= leaves - 1u;
+            push(~(int)((c.y + k) << 3));
+        }
+        return pop();
+    }
+
     // Generic traversal, "while-while" with one postponed leaf per lane (Aila & Laine 2009):
     // lanes keep descending inner nodes until every lane of the warp holds a leaf, then all
     // test primitives together; that keeps box tests and primitive tests in separate,
@@ -245,8 +311,10 @@ struct BvhAccelT {
         constexpr unsigned kFull = 0xffffffffu;
         // loop invariants in registers (the accelerator object itself may sit in local memory)
         const float4* __restrict__ const nd = nodes;
-        const float4* __restrict__ const pr = prims;
-        const int root_ = root;
+        const uint4* __restrict__ const nd8 = nodes8;
+        const bool wide8 = Job::kWide8 && nodes8 != nullptr;
+        const float4* __restrict__ const pr = wide8 ? prims8 : prims;
+        const int root_ = wide8 ? 1 : root;      // 8-wide: the group "slot 0 of base 0" = node 0
         const bool have_tree = n_nodes != 0;
         const unsigned lane = threadIdx.x & 31u;
         const unsigned lt = (1u << lane) - 1u;
@@ -359,7 +427,8 @@ struct BvhAccelT {
                     d_lanes += (unsigned)__popc(__ballot_sync(kFull, alive && (unsigned)node < (unsigned)kDone));
                 }
                 if (alive && (unsigned)node < (unsigned)kDone) {
-                    node = step<Job::kOrdered, Job::kWideLoads>(nd, node, rq, tmin, tmax, push, pop);
+                    if (Job::kWide8 && wide8) node = step8(nd8, node, rq, tmin, tmax, push, pop);
+                    else node = step<Job::kOrdered, Job::kWideLoads>(nd, node, rq, tmin, tmax, push, pop);
                     if (node < 0 && leaf == 0) {
                         leaf = node;
                         node = pop();
@@ -625,6 +694,7 @@ RT_DEV BvhAccelT<kCount> make_bvh_accel(const SceneView& S)
 {
     BvhAccelT<kCount> a;
     a.nodes = S.bvh.nodes; a.prims = S.bvh_tri; a.tri = S.tri; a.sph = S.sph;
+    a.nodes8 = S.bvh.n_nodes8 > 0 ? S.bvh.nodes8 : nullptr; a.prims8 = S.bvh.prims8;
     a.nf = S.nf; a.ns = S.ns; a.root = S.bvh.root; a.n_nodes = S.bvh.n_nodes; a.count_all = false;
     return a;
 }

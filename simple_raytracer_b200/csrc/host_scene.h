@@ -148,7 +148,8 @@ struct SceneHost {
 
     DevBuf tri, sph, face_attr, obj, mat, light, tex_desc, texels;
     DevBuf bvh_nodes, bvh_tri, bvh_sph;
-    int bvh_n_nodes = 0, bvh_root = 0;
+    DevBuf bvh8_nodes, bvh8_prims;      // the 8-wide tree of the any-hit walk (bvh.cu: collapse8_kernel)
+    int bvh_n_nodes = 0, bvh_root = 0, bvh8_n_nodes = 0;
     bool bvh_built = false;
 
     CameraView cam{};

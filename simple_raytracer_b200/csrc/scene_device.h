@@ -50,6 +50,9 @@ struct BvhView {
     const float4* nodes;     // 4 words per node, see bvh.cuh
     int n_nodes;
     int root;
+    const uint4* nodes8;     // 6 words per node (Node8, bvh.cuh); n_nodes8 == 0: not built
+    const float4* prims8;    // primitive records in the order the 8-wide nodes reference them
+    int n_nodes8;
 };
 
 struct SceneView {

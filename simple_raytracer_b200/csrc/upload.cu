@@ -336,6 +336,7 @@ SceneView scene_view(const SceneHost* s)
     v.tex_desc = s->tex_desc.as<int4>(); v.texels = s->texels.as<uchar4>();
     v.bvh.nodes = s->bvh_nodes.as<float4>(); v.bvh.n_nodes = s->bvh_n_nodes; v.bvh.root = s->bvh_root;
     v.bvh_tri = s->bvh_tri.as<float4>(); v.bvh_sph = s->bvh_sph.as<float4>();
+    v.bvh.nodes8 = s->bvh8_nodes.as<uint4>(); v.bvh.prims8 = s->bvh8_prims.as<float4>(); v.bvh.n_nodes8 = s->bvh8_n_nodes;
     for (int k = 0; k < 3; k++) v.bkg[k] = s->bkg[k];
     v.bkg_eta = s->bkg_eta;
     v.zero_mask_exit = s->zero_mask_exit ? 1 : 0;

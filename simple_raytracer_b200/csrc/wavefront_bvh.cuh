@@ -50,6 +50,7 @@ struct TraceJob {
     // more state; render.cu picks it for launches short enough for the tail to matter.
     static constexpr bool kSteal = kStealing;
     static constexpr bool kWideLoads = false;
+    static constexpr bool kWide8 = false;
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
     int level;
@@ -232,6 +233,7 @@ struct ShadowJob {
     // stays with the owner lane.
     static constexpr bool kSteal = kStealing;
     static constexpr bool kWideLoads = true;     // 256-bit node loads (bvh.cuh: test_node)
+    static constexpr bool kWide8 = true;         // walks the 8-wide tree when the scene has one (bvh.cuh: step8)
     static constexpr bool kOrdered = kNearFirst; // any hit: order is only a heuristic (near boxes first finds occluders sooner?)
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
