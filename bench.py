@@ -232,7 +232,8 @@ def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
         per_kernel = {
             # 64 B per 4-wide node visited + 80 B per primitive record tested + the ray read and the hit written
             "bvh_trace_kernel": 64 * tb + 80 * tp + 64 * closest_rays,
-            "bvh_shadow_kernel": 64 * sb + 80 * sp + 20 * walked,
+            # (the any-hit walk uses the 8-wide tree: 80 B loaded per node visited)
+            "bvh_shadow_kernel": 80 * sb + 80 * sp + 20 * walked,
             # 64 B per shaded hit + 4 B per texel
             "bvh_shade_kernel": 64 * nodes + 4 * int(st.texel_fetches),
         }
@@ -385,7 +386,7 @@ def run_ours(args) -> dict:
                                 "algorithmic_bytes_per_frame": work["per_kernel"][k],
                                 "achieved_gbs": work["per_kernel"][k] / (sum(v) * 1e-3) / 1e9 if sum(v) else None}
                             for k, v in kernel_ms.items()},
-                "note": "algorithmic bytes = 64 B per node visit + 80 B per primitive test; they are mostly served by "
+                "note": "algorithmic bytes = 64 B per 4-wide node visit (closest hit) / 80 B per 8-wide node visit (any hit) + 80 B per primitive test; they are mostly served by "
                         "L1/L2 (the tree is shared by all rays): the walk is bound by the L1/TEX gather pipe and SIMT "
                         "divergence, not by HBM - see DESIGN.md 6 and profiles/"}
     else:
