@@ -20,6 +20,11 @@
 #include "bvh.cuh"
 #include "wavefront.cuh"
 
+// colour / spawn kernels: 6 blocks per SM (<= 80 registers) instead of the 5 the compiler picks
+// on its own (96): they are latency-bound gathers, the extra warps pay for the two spills
+#ifndef RT_SHADE_MIN_BLOCKS
+#define RT_SHADE_MIN_BLOCKS 6
+#endif
 namespace rt {
 
 static_assert(kWalkBlock == kBlock, "the shared-memory stack is laid out for kBlock threads");
@@ -380,7 +385,7 @@ struct NoShadow {
 // scheduler (render.cu) runs trace -> spawn -> trace -> ... on one stream and shadow -> colour
 // on a second one, which fills the tail of every persistent launch with the other chain's work.
 template <bool kColour, bool kSpawn>
-__global__ void __launch_bounds__(kBlock) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const LevelBuffers& LB = P.level[level];
     const unsigned n_nodes = P.counters->nodes[level];
