@@ -298,6 +298,37 @@ def test_device_formatted_ppm_equals_the_host_formatter():
         assert (fl & 7).any()           # the NaN token really was exercised
 
 
+@pytest.mark.parametrize("name", ["reflection_transparency_tests/Test1", "basic_geometry_tests/purple_pyramid"])
+def test_cli_writes_the_file_the_reference_program_writes(tmp_path, name):
+    """`bin/raytracer scene.txt` (parser -> rt_upload_scene -> rt_render -> rt_format_ppm_device -> file)
+    next to the reference program on the same scene file: same header, same line structure, the
+    same NaN tokens in the same places, every channel within 1 LSB on >= 99.9 % of the pixels."""
+    import os, subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cli, ref = os.path.join(root, "bin", "raytracer"), os.path.join(root, "oracle", "_ref", "raytracer_ref")
+    if not (os.path.exists(cli) and os.path.exists(ref)):
+        pytest.skip("bin/raytracer or oracle/_ref/raytracer_ref not built")
+    scene, _ = common.golden_frame(name)
+    text = common.scene_text(name)
+    text = "\n".join(f"imsize {scene.width} {scene.height}" if l.startswith("imsize ") else l for l in text.split("\n"))
+    for d in ("ours", "theirs"):
+        (tmp_path / d).mkdir()
+        (tmp_path / d / "scene.txt").write_text(text)
+    subprocess.run([ref, "scene.txt"], cwd=str(tmp_path / "theirs"), check=True, capture_output=True)
+    subprocess.run([cli, "scene.txt"], cwd=str(tmp_path / "ours"), check=True, capture_output=True)
+    a = (tmp_path / "ours" / "scene.ppm").read_bytes().split(b"\n")
+    b = (tmp_path / "theirs" / "scene.ppm").read_bytes().split(b"\n")
+    assert a[:3] == b[:3] and len(a) == len(b) and a[-1] == b[-1] == b""
+    nan = b"18446744071562067968"
+    va = np.array([[-1 if t == nan else int(t) for t in l.split()] for l in a[3:-1]], dtype=np.int64)
+    vb = np.array([[-1 if t == nan else int(t) for t in l.split()] for l in b[3:-1]], dtype=np.int64)
+    assert va.shape == vb.shape == (scene.width * scene.height, 3)
+    assert np.array_equal(va == -1, vb == -1)
+    ok = (np.abs(va - vb) <= 1).all(axis=1)
+    assert ok.mean() >= PIXEL_BAR, float(ok.mean())
+    assert all(l.endswith(b" ") for l in a[:-1])                 # the dialect: a blank before every line end
+
+
 def test_cached_device_memory_is_reused_and_can_be_released():
     """Freed scenes leave their device blocks in a process-wide cache (devmem.cu): a second upload
     of the same scene must give the same frame from recycled (dirty) blocks, and
