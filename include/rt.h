@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 2
+#define RT_ABI_VERSION 3
 
 /* ---- status codes ------------------------------------------------------ */
 #define RT_OK            0
@@ -133,6 +133,12 @@ typedef struct RtRenderParams {
                               idle lanes take subtrees off the stacks of the lanes
                               still walking.  0 = for short launches (default),
                               1 = always, 2 = never.  Never changes a pixel.   */
+    int32_t occluder_hints;/* LBVH any-hit kernel: a shadow walk that ends at an opaque
+                              occluder leaves that primitive as a hint for later shadow
+                              rays from the same surface primitive to the same light,
+                              which test it first (exactly) and skip the walk when it
+                              blocks them too.  0 = on (default), 1 = on, 2 = off.
+                              Never changes a pixel.                             */
 } RtRenderParams;
 
 /* Filled by rt_render when a non-NULL pointer is passed.  The ray counts
@@ -172,6 +178,8 @@ typedef struct RtStats {
        dry, the lanes active in such a pass, and the subtrees handed to idle lanes. */
     double   trace_drain_steps[8], trace_drain_lanes[8], trace_drain_steals[8];
     double   shadow_drain_steps[8], shadow_drain_lanes[8];
+    uint64_t shadow_hint_hits;   /* instrument, LBVH: shadow rays settled by an occluder hint (not walked,
+                                    not counted in shadow_rays_walked) */
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

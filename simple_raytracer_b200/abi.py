@@ -67,7 +67,7 @@ class RtRenderParams(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("epsilon", C.c_float), ("accel", C.c_int32),
                 ("rank", C.c_int32), ("world_size", C.c_int32), ("tile_rows", C.c_int32),
                 ("instrument", C.c_int32), ("profile", C.c_int32), ("subframes", C.c_int32),
-                ("work_sharing", C.c_int32)]
+                ("work_sharing", C.c_int32), ("occluder_hints", C.c_int32)]
 
 
 class RtStats(C.Structure):
@@ -84,7 +84,7 @@ class RtStats(C.Structure):
                 ("shadow_warp_drain_ms", C.c_double * 8),
                 ("trace_drain_steps", C.c_double * 8), ("trace_drain_lanes", C.c_double * 8),
                 ("trace_drain_steals", C.c_double * 8), ("shadow_drain_steps", C.c_double * 8),
-                ("shadow_drain_lanes", C.c_double * 8)]
+                ("shadow_drain_lanes", C.c_double * 8), ("shadow_hint_hits", C.c_uint64)]
 
     def as_dict(self) -> dict:
         d = {}
@@ -118,7 +118,8 @@ def load_rt() -> C.CDLL:
     global _rt
     if _rt is not None:
         return _rt
-    path = os.path.join(LIB_DIR, "librt_b200.so")
+    # RT_B200_LIB: another in-tree build of the same library (tools/: compile-time variants for sweeps)
+    path = os.environ.get("RT_B200_LIB") or os.path.join(LIB_DIR, "librt_b200.so")
     if not os.path.exists(path):
         raise ImportError(
             f"{path} is missing: build it with `make` (nvcc, sm_100a). "

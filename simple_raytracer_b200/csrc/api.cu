@@ -42,6 +42,7 @@ int check_params(const RtRenderParams* in, RtRenderParams* out)
     if (out->tile_rows < 1) { set_error("tile_rows must be >= 1"); return RT_E_INVALID; }
     if (out->subframes < 0 || out->subframes > kMaxSubframes) { set_error("subframes must be in 0..8"); return RT_E_INVALID; }
     if (out->work_sharing < 0 || out->work_sharing > 2) { set_error("work_sharing must be 0, 1 or 2"); return RT_E_INVALID; }
+    if (out->occluder_hints < 0 || out->occluder_hints > 2) { set_error("occluder_hints must be 0, 1 or 2"); return RT_E_INVALID; }
     if (out->accel < RT_ACCEL_AUTO || out->accel > RT_ACCEL_LBVH) { set_error("bad accel"); return RT_E_INVALID; }
     return RT_OK;
 }
@@ -264,6 +265,7 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->bvh_nodes_visited = c.bvh_nodes; stats->prim_tests = c.prim_tests; stats->texel_fetches = c.texels;
         stats->shadow_boxes_tested = c.shadow_boxes; stats->shadow_prim_tests = c.shadow_prims;
         stats->shadow_rays_walked = (s->last_accel == RT_ACCEL_LBVH && p.instrument) ? c.shadow_walks : stats->rays_shadow;
+        stats->shadow_hint_hits = c.shadow_hint_hits;
         stats->accel_used = s->last_accel; stats->kernel_launches = launches; stats->queue_regrows = regrows;
         if (p.instrument && s->last_accel == RT_ACCEL_LBVH) {
             for (int l = 0; l <= p.max_depth; l++)

@@ -286,6 +286,7 @@ struct BvhAccelT {
     //   job.retire(bool finishing)       -> called by ALL lanes whenever some lane finishes
     //                                       (warp collectives allowed inside)
     //   job.next(o, ray, tmin, tmax)     -> true when the finished lane's job has another ray
+    //   job.first_leaf()                 -> a leaf code (< 0) to test before the tree walk of the ray just set up, 0 = none
     //   Job::kOrdered                    -> visit near children first (closest hit) or not (any hit)
     //   Job::kSteal                      -> once the job queue is dry, lanes whose ray has finished take
     //                                       subtrees off the stacks of the lanes still walking (a kernel
@@ -351,6 +352,12 @@ struct BvhAccelT {
             sp = 0; bot = 0; leaf = 0; owner = lane;
             node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
             rq = make_rayq(o, ray);
+            if (node != kDone) {
+                // a primitive the job wants tested before the tree is opened (an occluder hint): it
+                // travels as the postponed leaf, the root waits on the stack
+                const int fl = job.first_leaf();
+                if (fl < 0) { push(node); node = kDone; leaf = fl; }
+            }
         };
         for (;;) {
             const unsigned dead = __ballot_sync(kFull, !alive);
@@ -454,6 +461,8 @@ struct BvhAccelT {
                     if (node < 0) {
                         leaf = node;
                         node = pop();
+                    } else if (node == kDone) {
+                        node = pop();      // (only start()'s first leaf leaves entries under a finished node)
                     }
                 }
             }

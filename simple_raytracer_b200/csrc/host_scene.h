@@ -127,6 +127,7 @@ struct Workspace {
     DevBuf counters;
     DevBuf tiles;          // RGBA8 [local_tile][row][col]
     DevBuf primary_ids;
+    DevBuf hints;          // occluder hints of the any-hit kernel: (nf + ns) * nl ints
     DevBuf rgb24, flags8;  // scanline-order planes for rt_download_framebuffer
     ChainStreams chains;
     PinnedBuf h_counters;  // one Counters per sub-frame

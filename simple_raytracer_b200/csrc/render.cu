@@ -174,6 +174,7 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
     s->h_counters = static_cast<Counters*>(ws.h_counters.p);
     if (!ws.counters.reserve(sizeof(Counters) * kMaxSubframes) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
     if (p.instrument && !ws.primary_ids.reserve(npx * sizeof(int))) return RT_E_NOMEM;
+    if (bvh && s->nl > 0 && !ws.hints.reserve((size_t)(s->nf + s->ns) * s->nl * sizeof(int))) return RT_E_NOMEM;
     for (int l = 0; l <= p.max_depth; l++) {
         size_t want;
         // level 0: one slot per pixel; the sub-frames' virtual layouts pad up to one tile each
@@ -285,6 +286,15 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     // launch that becomes ready gets SM slots at once instead of waiting behind persistent shadow blocks
     static const int shadow_budget = tuning_int("RT_SHADOW_JOB_BUDGET", 0, 0, 1 << 20);
     static const int shadow_mult = tuning_int("RT_SHADOW_GRID_MULT", 0, 0, 64);   // 0: same as RT_GRID_MULT
+    // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob) and the interleaved passes
+    // that make them available in time
+    static const int hint_env = tuning_int("RT_HINT", 1, 0, 1);
+    static const int hint_passes = tuning_int("RT_HINT_PASSES", 16, 1, 256);
+    static const int hint_group = tuning_int("RT_HINT_GROUP", 1, 1, 4096);
+    static const int hint_min_chunk = 1024 * tuning_int("RT_HINT_MIN_CHUNK_K", 256, 1, 1 << 20);
+    static const int hint_mode = tuning_int("RT_HINT_MODE", 3, 0, 3);
+    static const int hint_keep = tuning_int("RT_HINT_KEEP", 0, 0, 1);      // experiments only: hints survive the frame
+    const bool hints = lbvh && s->nl > 0 && (p.occluder_hints == 1 || (p.occluder_hints == 0 && hint_env));
 
     static thread_local FrameParams PS[kMaxSubframes];
     for (int j = 0; j < K; j++) {
@@ -303,9 +313,15 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         P.refill_lanes = refill; P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
         P.steal = 1;
         P.shadow_job_budget = overlap ? shadow_budget : 0;
+        P.occluder_hint = hints ? s->ws.hints.as<int>() : nullptr;
+        P.hint_prims = s->nf + s->ns;
+        P.hint_passes = hint_passes; P.hint_group = hint_group; P.hint_min_chunk = hint_min_chunk;
+        P.hint_mode = hint_mode;
     }
 
     RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
+    // every frame starts without hints: a frame never depends on an earlier one
+    if (hints && !(hint_keep && s->rendered)) RT_CUDA(cudaMemsetAsync(s->ws.hints.p, 0xff, (size_t)(s->nf + s->ns) * s->nl * sizeof(int), stream));
     const int sms = sm_count(s->device);
     const size_t smem = (size_t)(s->nf * kTriWords + s->ns * kSphWords) * sizeof(float4);
     const bool stage = accel == RT_ACCEL_BRUTE && smem <= 48 * 1024;
@@ -447,6 +463,7 @@ bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxL
         }
         t.bvh_nodes += c.bvh_nodes; t.prim_tests += c.prim_tests; t.texels += c.texels;
         t.shadow_boxes += c.shadow_boxes; t.shadow_prims += c.shadow_prims; t.shadow_walks += c.shadow_walks;
+        t.shadow_hint_hits += c.shadow_hint_hits;
         if (j == 0) std::memcpy(t.clock, c.clock, sizeof t.clock);      // instrumented frames have one chain
     }
     if (total) *total = t;

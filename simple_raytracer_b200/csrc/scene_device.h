@@ -136,6 +136,7 @@ struct Counters {
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
     unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
+    unsigned long long shadow_hint_hits;                // ... of the elided ones: settled by the hinted occluder, no tree walk
     WalkClock clock[2][kMaxLevels];                     // instrumented LBVH frames: [0] trace, [1] shadow kernels
 };
 
@@ -160,6 +161,15 @@ struct FrameParams {
     int leaf_min_lanes;   // ... leave the leaf loop when fewer lanes than this hold a leaf
     int shadow_job_budget; // ... any-hit kernel: jobs a warp takes before it stops fetching (0 = no limit)
     int steal;            // ... idle lanes take subtrees from busy ones once the queue is dry (closest-hit walks)
+    // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob): hint[li * n_prims + order of the
+    // surface's primitive] = record index (any-hit primitive table) of the opaque occluder that last ended
+    // a shadow walk from that primitive towards light li, -1 = none yet.  Cleared at every frame start.
+    int* occluder_hint;   // null: off
+    int hint_prims;       // nf + ns
+    int hint_passes;      // the node list is taken in up to this many interleaved passes (>= 1)
+    int hint_group;       // ... of groups of this many consecutive nodes
+    int hint_min_chunk;   // ... but no pass shorter than this many nodes
+    int hint_mode;        // experiments: bit 0 = test hints, bit 1 = record them (3 = normal)
 };
 
 }  // namespace rt

@@ -25,6 +25,10 @@
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 6
 #endif
+// any-hit kernel: 8 blocks per SM (64 registers)
+#ifndef RT_SHADOW_MIN_BLOCKS
+#define RT_SHADOW_MIN_BLOCKS 8
+#endif
 namespace rt {
 
 static_assert(kWalkBlock == kBlock, "the shared-memory stack is laid out for kBlock threads");
@@ -130,6 +134,7 @@ struct TraceJob {
     }
 
     RT_DEV bool next(V3&, V3&, float&, float&) { return false; }
+    RT_DEV int first_leaf() { return 0; }
 
     // work sharing at the end of a launch (persistent_walk): a helper lane walks a subtree
     // for the ray of lane src with a copy of its state ...
@@ -244,13 +249,48 @@ struct ShadowJob {
     const BvhAccelT<kCount>& acc;
     int level;
     unsigned n_nodes;
+    // Occluder hints.  "Some opaque primitive blocks this shadow ray" is all the reference's product
+    // needs to become exactly 0 (every factor is in [0,1]; main.cpp:909 / 946), and WHICH primitive
+    // proves it does not matter.  Neighbouring surface points of one primitive are mostly blocked by
+    // the same occluder, so the walk that finds one leaves its record index in
+    // hint[light][surface primitive] and later jobs from that primitive test that record first
+    // (one 80-byte exact test instead of a tree walk).  A stale or missing hint only costs the
+    // test: the result never depends on it.  For hints to be THERE in time the node list is taken
+    // in interleaved passes (perm): pass p handles the groups g with g % passes == p, so the
+    // neighbours of a node were finished a whole pass earlier, not in the same warp.
+    const float4* pr;            // the any-hit walk's primitive table (what persistent_walk visits)
+    int* hint;                   // null: off
+    unsigned pass_jobs, passes, group;
     // per node
     unsigned k;
     int li;
     V3 p; int self;
     float mask;
+    int found;                   // record index of the opaque occluder this walk ended at, -1
+    int hinted;                  // record index first_leaf() handed to the walk, -1
     unsigned long long walks = 0;      // instrumented variant: shadow rays actually walked by this thread
+    unsigned long long hint_hits = 0;  // ... and settled by a hint
     typename BvhAccelT<kCount>::ShadowVisit v;
+
+    // jobs of the launch and the job -> node permutation described above
+    RT_DEV unsigned plan()
+    {
+        passes = 1; group = 1; pass_jobs = n_nodes;
+        if (hint && P.hint_passes > 1) {
+            group = (unsigned)max(P.hint_group, 1);
+            const unsigned groups = (n_nodes + group - 1) / group;
+            passes = min((unsigned)P.hint_passes, max(n_nodes / (unsigned)max(P.hint_min_chunk, 1), 1u));
+            pass_jobs = (groups + passes - 1) / passes * group;
+        }
+        return pass_jobs * passes;
+    }
+    RT_DEV unsigned perm(unsigned j) const
+    {
+        if (passes == 1) return j;
+        const unsigned ps = j / pass_jobs, r = j - ps * pass_jobs;
+        const unsigned g = r / group, w = r - g * group;
+        return (g * passes + ps) * group + w;
+    }
 
     RT_DEV void setup(V3& wo, V3& wray, float& tmin, float& tmax)
     {
@@ -267,17 +307,34 @@ struct ShadowJob {
             acc.shadow_begin(p, wray, self, tmin, tmax, true, v);
         }
         wo = p;
+        found = -1;
+    }
+    // The hinted record as a leaf code: persistent_walk tests it (through visit(), like any leaf)
+    // before it opens the root.
+    RT_DEV int first_leaf()
+    {
+        hinted = -1;
+        if (!hint || v.count_all || !(P.hint_mode & 1)) return 0;
+        hinted = __ldcg(hint + (size_t)li * P.hint_prims + self);
+        return hinted >= 0 ? ~(hinted << 3) : 0;
     }
     RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        k = j; li = 0; mask = 1.0f;                                              // 788
+        k = perm(j); li = 0; mask = 1.0f;                                        // 788
+        if (k >= n_nodes) { k = 0xffffffffu; return false; }                     // padding of the last groups
         const float4 hp = P.level[level].hp[P.level[level].node_list[k]];
         p = mk3(hp.x, hp.y, hp.z);
         self = __float_as_int(hp.w);
         setup(wo, wray, tmin, tmax);
         return true;
     }
-    RT_DEV float visit(const float4* w, float tmax) { return v(w, tmax); }
+    RT_DEV float visit(const float4* w, float tmax)
+    {
+        const bool before = v.opaque;
+        const float r = v(w, tmax);
+        if (v.opaque && !before) found = (int)((w - pr) / kTriWords);
+        return r;
+    }
 
     RT_DEV void adopt(int src, bool take, V3& wo, V3& wray)
     {
@@ -291,6 +348,7 @@ struct ShadowJob {
             v.o = mk3(ox, oy, oz); v.ray = mk3(rx, ry, rz); v.tmin = t0; v.tmax_hit = t1; v.self = sf;
             v.use_tmax = (fl & 1) != 0; v.skip_spheres = (fl & 2) != 0; v.count_all = (fl & 4) != 0;
             v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false;
+            found = -1;
         }
         wo = v.o; wray = v.ray;
     }
@@ -300,9 +358,11 @@ struct ShadowJob {
         const int op = __shfl_sync(kFull, v.opaque ? 1 : 0, src), h = __shfl_sync(kFull, v.hits, src);
         const int np = __shfl_sync(kFull, v.n_partial, src);
         const float ov = __shfl_sync(kFull, v.overflow_mask, src);
+        const int fd = __shfl_sync(kFull, found, src);
         if (mine) {
             v.hits += h;
             v.opaque = v.opaque || op != 0;
+            if (fd >= 0) found = fd;
             if (ov != 1.0f) v.overflow_mask = clamp01(fmul(ov, v.overflow_mask));
         }
         for (int i = 0; i < np; i++) {
@@ -323,13 +383,15 @@ struct ShadowJob {
 
     RT_DEV void retire(bool fin)
     {
-        if (!fin) return;
-        if (kCount) walks++;
+        if (!fin || k == 0xffffffffu) return;
         acc.shadow_end(v);
+        const bool by_hint = v.opaque && found >= 0 && found == hinted;
+        if (kCount) { if (by_hint) hint_hits++; else walks++; }
         // the carried product exactly as BvhAccelT::shadow applies it (main.cpp:909 / 946 in
         // iteration order); the record is the mask AFTER this light
         if (v.opaque) {
             mask = clamp01(fmul(0.0f, mask));
+            if (hint && found >= 0 && !by_hint && (P.hint_mode & 2)) __stcg(hint + (size_t)li * P.hint_prims + self, found);
         } else {
             for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
             if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
@@ -338,7 +400,7 @@ struct ShadowJob {
     }
     RT_DEV bool next(V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        if (mask == 0.0f || li + 1 >= P.scene.nl) return false;
+        if (k == 0xffffffffu || mask == 0.0f || li + 1 >= P.scene.nl) return false;
         li++;
         setup(wo, wray, tmin, tmax);
         return true;
@@ -346,19 +408,22 @@ struct ShadowJob {
 };
 
 template <bool kCount, bool kNearFirst, bool kStealing>
-__global__ void __launch_bounds__(kBlock) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kBlock, kCount ? 0 : RT_SHADOW_MIN_BLOCKS) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned n_nodes = P.counters->nodes[level];
     ShadowJob<kCount, kNearFirst, kStealing> job{ P, acc, level, n_nodes };
-    acc.persistent_walk(n_nodes, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
+    job.pr = acc.nodes8 ? acc.prims8 : acc.prims;
+    job.hint = P.occluder_hint;
+    const unsigned n_jobs = job.plan();
+    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
                         kCount ? &P.counters->clock[1][level] : nullptr, P.steal != 0,
                         P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
-        unsigned long long w = job.walks;
-        for (int o = 16; o > 0; o >>= 1) w += __shfl_down_sync(0xffffffffu, w, o);
-        if ((threadIdx.x & 31) == 0) atomicAdd(&P.counters->shadow_walks, w);
+        unsigned long long w = job.walks, hh = job.hint_hits;
+        for (int o = 16; o > 0; o >>= 1) { w += __shfl_down_sync(0xffffffffu, w, o); hh += __shfl_down_sync(0xffffffffu, hh, o); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&P.counters->shadow_walks, w); atomicAdd(&P.counters->shadow_hint_hits, hh); }
     }
 }
 

@@ -8,6 +8,8 @@ Bars (BASELINE.json north_star):
 Integer / index work (hit ids, t bit patterns, node counts, hit counts) is held to
 bit-exactness.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -275,6 +277,66 @@ def test_work_sharing_in_the_walk_tails_never_changes_a_pixel():
             ids_lbvh = ds.download_primary_ids().copy()
             ds.render(accel=abi.RT_ACCEL_BRUTE, instrument=True)
             assert np.array_equal(ids_lbvh, ds.download_primary_ids())
+
+
+def test_occluder_hints_never_change_a_pixel():
+    """Shadow rays that test a hinted occluder before (instead of) walking the tree (ShadowJob::
+    first_leaf): frames with hints on / off equal the brute-force frame; the instrumented frame
+    reports hint hits, and walked + hinted shadow rays never exceed the reference's count."""
+    for scene in (scenegen.coverage_scene(128, 96), scenegen.stress_scene(8000, 100, 160, 120)):
+        with DeviceScene(scene) as ds:
+            ds.render(accel=abi.RT_ACCEL_BRUTE)
+            want = ds.download()
+            want = (want[0].copy(), want[1].copy())
+            stats = []
+            for mode in (2, 1, 0):
+                stats.append(ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=mode))
+                got = ds.download()
+                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), mode
+            assert list(stats[0].nodes_per_level) == list(stats[1].nodes_per_level) == list(stats[2].nodes_per_level)
+            off = ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=2, instrument=True)
+            on = ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=1, instrument=True)
+            got = ds.download()
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+            assert off.shadow_hint_hits == 0
+            assert on.shadow_rays_walked + on.shadow_hint_hits <= on.rays_shadow
+            # a hint replaces a walk one for one: the chains stop at the same light either way
+            assert on.shadow_rays_walked + on.shadow_hint_hits == off.shadow_rays_walked
+    assert on.shadow_hint_hits > 0          # the dense stress scene does produce hits
+
+
+def test_interleaved_shadow_passes_never_change_a_pixel():
+    """The any-hit kernel takes the node list in interleaved passes so that hints are there in time
+    (ShadowJob::perm).  The knobs are process-wide, so a child process renders with 1024-node
+    passes and ragged groups; its frames must equal this process's brute-force frames."""
+    import subprocess, sys, tempfile
+    code = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "from simple_raytracer_b200 import abi, scenegen\n"
+        "from simple_raytracer_b200.renderer import DeviceScene\n"
+        "out = {}\n"
+        "for name, sc in (('cov', scenegen.coverage_scene(128, 96)), ('stress', scenegen.stress_scene(8000, 100, 160, 120))):\n"
+        "    with DeviceScene(sc) as ds:\n"
+        "        ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=1)\n"
+        "        rgb, fl = ds.download()\n"
+        "        out[name + '_rgb'] = rgb.copy(); out[name + '_fl'] = fl.copy()\n"
+        "np.savez(sys.argv[1], **out)\n" % os.path.dirname(common.HERE))
+    want = {}
+    for name, sc in (("cov", scenegen.coverage_scene(128, 96)), ("stress", scenegen.stress_scene(8000, 100, 160, 120))):
+        with DeviceScene(sc) as ds:
+            ds.render(accel=abi.RT_ACCEL_BRUTE)
+            rgb, fl = ds.download()
+            want[name] = (rgb.copy(), fl.copy())
+    for group in ("1", "3", "32"):
+        with tempfile.TemporaryDirectory() as td:
+            path = os.path.join(td, "frames.npz")
+            env = dict(os.environ, RT_HINT_MIN_CHUNK_K="1", RT_HINT_PASSES="7", RT_HINT_GROUP=group)
+            subprocess.run([sys.executable, "-c", code, path], check=True, env=env, timeout=600)
+            got = np.load(path)
+            for name in want:
+                assert np.array_equal(got[name + "_rgb"], want[name][0]), (group, name)
+                assert np.array_equal(got[name + "_fl"], want[name][1]), (group, name)
 
 
 def test_device_formatted_ppm_equals_the_host_formatter():

@@ -32,7 +32,7 @@ def test_every_declared_symbol_is_exported():
         assert getattr(rt, n) is not None
     for n in names_host:
         assert getattr(host, n) is not None
-    assert rt.rt_abi_version() == 2
+    assert rt.rt_abi_version() == 3
 
 
 def test_struct_layouts_match_the_header():
