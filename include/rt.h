@@ -139,6 +139,13 @@ typedef struct RtRenderParams {
                               which test it first (exactly) and skip the walk when it
                               blocks them too.  0 = on (default), 1 = on, 2 = off.
                               Never changes a pixel.                             */
+    int32_t fused_trace;   /* LBVH pipeline: the closest-hit rays of ALL generations in one
+                              persistent launch that spawns the next generation's rays as
+                              it goes (one kernel tail per frame instead of one per
+                              generation), then all shadow chains in one launch.
+                              0 = off (default: one launch chain per generation; measured
+                              faster on B200), 1 = on, 2 = off.  Never
+                              changes a pixel.                                   */
 } RtRenderParams;
 
 /* Filled by rt_render when a non-NULL pointer is passed.  The ray counts

@@ -67,7 +67,8 @@ class RtRenderParams(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("epsilon", C.c_float), ("accel", C.c_int32),
                 ("rank", C.c_int32), ("world_size", C.c_int32), ("tile_rows", C.c_int32),
                 ("instrument", C.c_int32), ("profile", C.c_int32), ("subframes", C.c_int32),
-                ("work_sharing", C.c_int32), ("occluder_hints", C.c_int32)]
+                ("work_sharing", C.c_int32), ("occluder_hints", C.c_int32),
+                ("fused_trace", C.c_int32)]
 
 
 class RtStats(C.Structure):

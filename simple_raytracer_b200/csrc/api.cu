@@ -42,6 +42,7 @@ int check_params(const RtRenderParams* in, RtRenderParams* out)
     if (out->tile_rows < 1) { set_error("tile_rows must be >= 1"); return RT_E_INVALID; }
     if (out->subframes < 0 || out->subframes > kMaxSubframes) { set_error("subframes must be in 0..8"); return RT_E_INVALID; }
     if (out->work_sharing < 0 || out->work_sharing > 2) { set_error("work_sharing must be 0, 1 or 2"); return RT_E_INVALID; }
+    if (out->fused_trace < 0 || out->fused_trace > 2) { set_error("fused_trace must be 0, 1 or 2"); return RT_E_INVALID; }
     if (out->occluder_hints < 0 || out->occluder_hints > 2) { set_error("occluder_hints must be 0, 1 or 2"); return RT_E_INVALID; }
     if (out->accel < RT_ACCEL_AUTO || out->accel > RT_ACCEL_LBVH) { set_error("bad accel"); return RT_E_INVALID; }
     return RT_OK;
@@ -240,7 +241,9 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         RT_CUDA(cudaStreamSynchronize(s->stream));
         RT_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         unsigned demand[kMaxLevels];
-        if (!frame_overflowed(s, &total, demand)) break;
+        const bool again = frame_overflowed(s, &total, demand);
+        if (total.work.stalled) { set_error("fused trace kernel: a warp waited 2 s for work that never came (frame invalid)"); return RT_E_CUDA; }
+        if (!again) break;
         if (++regrows > 16) { set_error("wavefront queues still overflow after 16 regrows"); return RT_E_NOMEM; }
         if ((rc = ensure_workspace(s, p, demand)) != RT_OK) return rc;
     }

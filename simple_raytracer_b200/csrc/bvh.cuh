@@ -35,7 +35,14 @@ namespace rt {
 
 constexpr int kBvhStack = 96;     // local-memory part of the traversal stack (entries)
 constexpr int kSmemStack = 24;    // shared-memory part of the persistent walk's stack (entries per thread)
-constexpr int kWalkBlock = 128;   // block size of the persistent walk kernels (= kBlock)
+// Block size of the persistent walk kernels.  A block's registers stay taken until its LAST warp
+// has finished, so in a launch's tail smaller blocks hand their SM share to the other launch
+// chain's blocks sooner.
+#ifndef RT_WALK_BLOCK
+#define RT_WALK_BLOCK 128
+#endif
+constexpr int kWalkBlock = RT_WALK_BLOCK;
+constexpr int kWalkScale = 128 / kWalkBlock;   // blocks per SM are quoted for 128-thread blocks
 constexpr int kLeafMax = 4;       // scenes of <= kLeafMax primitives are a single node
 constexpr int kLeafDefault = 1;   // primitives per leaf otherwise: with one triangle per leaf the parent's box test
                                   // rejects most of the 80-byte exact tests (measured: 32 -> 6.4 tests per ray)
@@ -503,6 +510,143 @@ struct BvhAccelT {
                 atomicAdd(&clock->drain_steps, (unsigned long long)d_steps);
                 atomicAdd(&clock->drain_lane_steps, (unsigned long long)d_lanes);
                 atomicAdd(&clock->drain_steals, (unsigned long long)d_steals);
+            }
+        }
+    }
+
+    // ---- all generations in one launch -----------------------------------------------------------
+    // persistent_walk() over ONE work list that the kernel itself extends: a ray that has found
+    // its hit spawns its children at once (job.retire) and appends them to the list, so the
+    // generations of a frame overlap and the launch has a single tail instead of one per
+    // generation.  Tickets are handed out in order with one atomicAdd per warp; ticket t < n0 is
+    // primary ray t, ticket n0 + e is entry e of `order` = (generation << 28) | queue slot,
+    // 0xffffffff while not yet written.  A lane may hold a ticket for an entry that does not exist
+    // yet: it polls it once per pass of its warp.  The frame is traced when every published ray
+    // has retired (retired == n0 + tail, checked by whoever retires): tickets still waiting are
+    // void then.  Nothing blocks: waiting lanes never keep the walking lanes of their warp from
+    // walking, and any published entry is, or will be, held by exactly one lane.
+    //   job.begin(generation, slot, o, ray, tmin, tmax) -> false when the ray needs no tree walk
+    //   job.visit(words, tcur)
+    //   job.retire(fin)        ALL lanes; appends the hit, spawns and publishes the children,
+    //                          counts the retired rays and raises q->done
+    RT_DEV static unsigned ld_volatile(const unsigned* p)
+    {
+        unsigned v;
+        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+        return v;
+    }
+
+    template <class Job>
+    RT_DEV void persistent_walk_all(unsigned n0, WorkQueue* q, const unsigned* order, unsigned order_cap, Job& job,
+                                    int refill_lanes, int inner_min = 1, int leaf_min = 1) const
+    {
+        constexpr int kDone = kWalkDone;
+        constexpr unsigned kFull = 0xffffffffu;
+        const float4* __restrict__ const nd = nodes;
+        const float4* __restrict__ const pr = prims;
+        const int root_ = root;
+        const bool have_tree = n_nodes != 0;
+        const unsigned lane = threadIdx.x & 31u;
+        const unsigned lt = (1u << lane) - 1u;
+        __shared__ int s_stack[kSmemStack][kWalkBlock];
+        int stack[kBvhStack];
+        const int tid = threadIdx.x;
+        int sp = 0, node = kDone, leaf = 0;
+        bool alive = false, waiting = false, finished = false;
+        unsigned ticket = 0, spins = 0;
+        RayQ rq = make_rayq(mk3(0.f, 0.f, 0.f), mk3(1.f, 1.f, 1.f));
+        float tmin = 0.f, tmax = 0.f;
+        auto pop = [&]() {
+            if (sp == 0) return kDone;
+            --sp;
+            return sp < kSmemStack ? s_stack[sp][tid] : stack[sp - kSmemStack];
+        };
+        auto push = [&](int v) {
+            if (sp < kSmemStack) s_stack[sp][tid] = v;
+            else if (sp < kSmemStack + kBvhStack) stack[sp - kSmemStack] = v;
+            else return;
+            sp++;
+        };
+        for (;;) {
+            if (!finished) {
+                const unsigned idle = __ballot_sync(kFull, !alive && !waiting);
+                const unsigned busy = __ballot_sync(kFull, alive);
+                if (__popc(idle) >= refill_lanes || (idle != 0u && busy == 0u)) {
+                    unsigned base = 0;
+                    if (lane == 0) base = atomicAdd(&q->head, (unsigned)__popc(idle));
+                    base = __shfl_sync(kFull, base, 0);
+                    if (!alive && !waiting) { ticket = base + (unsigned)__popc(idle & lt); waiting = true; }
+                }
+                if (waiting) {
+                    unsigned gen = 0, slot = ticket;
+                    bool ok = ticket < n0;
+                    if (!ok) {
+                        const unsigned e = ticket - n0;
+                        const unsigned v = e < order_cap ? ld_volatile(order + e) : 0xffffffffu;
+                        if (v != 0xffffffffu) { ok = true; gen = v >> 28; slot = v & 0x0fffffffu; }
+                    }
+                    if (ok) {
+                        V3 o, ray;
+                        const bool need_walk = job.begin((int)gen, slot, o, ray, tmin, tmax);
+                        alive = true; waiting = false;
+                        sp = 0; leaf = 0;
+                        node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
+                        rq = make_rayq(o, ray);
+                    }
+                }
+                if (!__any_sync(kFull, alive)) {
+                    // nobody in this warp has a ray: either the frame is traced, or the entries of
+                    // our tickets are still to come
+                    unsigned d = 0;
+                    if (lane == 0) d = ld_volatile(&q->done);
+                    d = __shfl_sync(kFull, d, 0);
+                    if (d) { finished = true; waiting = false; }
+                    else {
+                        __nanosleep(400);
+                        if (++spins > (1u << 22)) {          // ~2 s without a ray: give up loudly
+                            if (lane == 0) atomicExch(&q->stalled, 1u);
+                            finished = true; waiting = false;
+                        }
+                        continue;
+                    }
+                }
+            }
+            if (!__any_sync(kFull, alive)) break;
+            spins = 0;
+            // inner nodes, until every live lane holds a leaf (or has nothing left)
+            for (;;) {
+                if (alive && (unsigned)node < (unsigned)kDone) {
+                    node = step<true, false>(nd, node, rq, tmin, tmax, push, pop);
+                    if (node < 0 && leaf == 0) {
+                        leaf = node;
+                        node = pop();
+                    }
+                }
+                if (__popc(__ballot_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) < inner_min) break;
+            }
+            // pending leaves
+            for (bool first = true;; first = false) {
+                const int holders = __popc(__ballot_sync(kFull, alive && leaf < 0));
+                if (holders == 0 || (!first && holders < leaf_min)) break;
+                if (alive && leaf < 0) {
+                    const int code = ~leaf;
+                    const int first_slot = code >> 3, count = (code & 7) + 1;
+                    leaf = 0;
+                    for (int k = 0; k < count; k++) {
+                        if (kCount) cnt_prims++;
+                        tmax = job.visit(pr + (size_t)(first_slot + k) * kTriWords, tmax);
+                        if (tmax < 0.0f) { node = kDone; sp = 0; break; }
+                    }
+                    if (node < 0) {
+                        leaf = node;
+                        node = pop();
+                    }
+                }
+            }
+            const bool fin = alive && node == kDone && leaf == 0;
+            if (__any_sync(kFull, fin)) {
+                job.retire(fin);
+                if (fin) alive = false;
             }
         }
     }

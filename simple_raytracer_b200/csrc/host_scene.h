@@ -127,6 +127,8 @@ struct Workspace {
     DevBuf counters;
     DevBuf tiles;          // RGBA8 [local_tile][row][col]
     DevBuf primary_ids;
+    DevBuf hit_order;      // ... and its hit list (hits waiting for the spawn half of ShadeRay)
+    DevBuf work_order;     // fused trace kernel: the work list (one entry per spawned ray)
     DevBuf hints;          // occluder hints of the any-hit kernel: (nf + ns) * nl ints
     DevBuf rgb24, flags8;  // scanline-order planes for rt_download_framebuffer
     ChainStreams chains;

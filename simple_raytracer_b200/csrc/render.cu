@@ -192,6 +192,14 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
             ws.capacity[l] = (int)want;
         }
     }
+    if (bvh) {
+        size_t entries = 0;
+        for (int l = 1; l <= p.max_depth; l++) entries += (size_t)ws.capacity[l];
+        if (!ws.work_order.reserve(std::max<size_t>(entries, 1) * sizeof(unsigned))) return RT_E_NOMEM;
+        size_t hits = 0;
+        for (int l = 0; l < p.max_depth; l++) hits += l == 0 ? npx + (size_t)kMaxSubframes * p.tile_rows * s->width : (size_t)ws.capacity[l];
+        if (!ws.hit_order.reserve(std::max<size_t>(hits, 1) * sizeof(unsigned))) return RT_E_NOMEM;
+    }
     return RT_OK;
 }
 
@@ -240,6 +248,12 @@ static void launch_level(const FrameParams& P, int level, int grid, size_t smem,
     level_kernel<Factory><<<grid, kBlock, smem, st>>>(P, level);
 }
 
+// ... of a walk kernel (blocks of kWalkBlock threads; mult counts 128-thread blocks per SM)
+static int walk_grid(long long work, int sms, int mult)
+{
+    return (int)std::max<long long>(1, std::min<long long>((work + kWalkBlock - 1) / kWalkBlock, (long long)sms * mult * kWalkScale));
+}
+
 static int persistent_grid(long long work, int sms, int mult)
 {
     return (int)std::max<long long>(1, std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * mult));
@@ -262,9 +276,14 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         if (rc != RT_OK) return rc;
     }
     const bool lbvh = accel == RT_ACCEL_LBVH;
-    const int K = pick_subframes(p, accel, tl);
+    // Fused trace: every generation's closest-hit rays in ONE persistent launch that spawns as it goes
+    // (wavefront_bvh.cuh: bvh_trace_all_kernel), then every generation's shadow chains in one launch
+    static const int fused_env = tuning_int("RT_FUSED", 0, 0, 1);
+    static const int spawn_every = tuning_int("RT_SPAWN_EVERY", 8, 2, 64);
+    const bool fused = lbvh && (p.fused_trace == 1 || (p.fused_trace == 0 && fused_env)) && p.subframes <= 1;
+    const int K = fused ? 1 : pick_subframes(p, accel, tl);
     static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
-    const bool overlap = lbvh && overlap_knob && !p.profile && !p.instrument;
+    const bool overlap = lbvh && overlap_knob && !p.profile && !p.instrument && !fused;
     // sub-frame j is virtual rank (rank + world*j) of (world*K): the same interleaved-tile arithmetic
     const TileLayout vl = tile_layout(s->height, s->width, p.world_size * K, p.tile_rows);
 
@@ -290,9 +309,9 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     // that make them available in time
     static const int hint_env = tuning_int("RT_HINT", 1, 0, 1);
     static const int hint_passes = tuning_int("RT_HINT_PASSES", 16, 1, 256);
-    static const int hint_group = tuning_int("RT_HINT_GROUP", 1, 1, 4096);
+    static const int hint_group = tuning_int("RT_HINT_GROUP", 32, 1, 4096);
     static const int hint_min_chunk = 1024 * tuning_int("RT_HINT_MIN_CHUNK_K", 256, 1, 1 << 20);
-    static const int hint_mode = tuning_int("RT_HINT_MODE", 3, 0, 3);
+    static const int hint_mode = tuning_int("RT_HINT_MODE", 7, 0, 7);
     static const int hint_keep = tuning_int("RT_HINT_KEEP", 0, 0, 1);      // experiments only: hints survive the frame
     const bool hints = lbvh && s->nl > 0 && (p.occluder_hints == 1 || (p.occluder_hints == 0 && hint_env));
 
@@ -317,6 +336,17 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         P.hint_prims = s->nf + s->ns;
         P.hint_passes = hint_passes; P.hint_group = hint_group; P.hint_min_chunk = hint_min_chunk;
         P.hint_mode = hint_mode;
+        if (fused) {
+            size_t entries = 0;
+            for (int l = 1; l <= p.max_depth; l++) entries += (size_t)s->ws.capacity[l];
+            P.work_order = s->ws.work_order.as<unsigned>();
+            P.work_capacity = (unsigned)std::min<size_t>(entries, 0xffffffffu);
+            size_t hits = 0;
+            for (int l = 0; l < p.max_depth; l++) hits += (size_t)P.level[l].capacity;
+            P.hit_order = s->ws.hit_order.as<unsigned>();
+            P.hit_capacity = (unsigned)std::min<size_t>(hits, 0xffffffffu);
+            P.spawn_every = spawn_every;
+        }
     }
 
     RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
@@ -341,13 +371,49 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         RT_CUDA(cudaEventRecord(cs.begin, stream));        // the counters are cleared
         for (int j = 0; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
     }
-    for (int l = 0; l <= p.max_depth; l++) {
+    if (fused) {
+        const FrameParams& P = PS[0];
+        if (P.work_capacity) RT_CUDA(cudaMemsetAsync(P.work_order, 0xff, (size_t)P.work_capacity * sizeof(unsigned), stream));
+        if (P.hit_capacity) RT_CUDA(cudaMemsetAsync(P.hit_order, 0xff, (size_t)P.hit_capacity * sizeof(unsigned), stream));
+        // exactly the blocks that are resident at once: a block only ends when the frame is traced
+        static int resident[2] = { 0, 0 };
+        const int ri = p.instrument ? 1 : 0;
+        if (!resident[ri]) {
+            int nb = 0;
+            if (p.instrument) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, bvh_trace_all_kernel<true>, kWalkBlock, 0));
+            else RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, bvh_trace_all_kernel<false>, kWalkBlock, 0));
+            resident[ri] = std::max(nb, 1);
+        }
+        // (at least one spawner warp: warp w spawns when w % spawn_every == spawn_every - 1)
+        const int grid = std::max((int)std::min<long long>(((long long)P.n_local_pixels + kWalkBlock - 1) / kWalkBlock, (long long)sms * resident[ri]), (spawn_every * 32 + kWalkBlock - 1) / kWalkBlock);
+        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[0], stream));
+        if (p.instrument) bvh_trace_all_kernel<true><<<grid, kWalkBlock, 0, stream>>>(P);
+        else bvh_trace_all_kernel<false><<<grid, kWalkBlock, 0, stream>>>(P);
+        n++;
+        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[0][0], stream));
+        if (s->nl) {
+            long long work = 0;
+            for (int l = 0; l <= p.max_depth; l++) work += P.level[l].capacity;
+            const int sh_grid = walk_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
+            if (p.instrument) bvh_shadow_kernel<true, false, false><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1);
+            else bvh_shadow_kernel<false, false, false><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1);
+            n++;
+        }
+        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[0][1], stream));
+        for (int l = 0; l <= p.max_depth; l++) {
+            const int cgrid = persistent_grid(P.level[l].capacity, sms, grid_mult);
+            bvh_shade_kernel<true, false><<<cgrid, kBlock, 0, stream>>>(P, l);
+            n++;
+        }
+    }
+    for (int l = 0; l <= p.max_depth && !fused; l++) {
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
         for (int j = 0; j < K; j++) {
             const FrameParams& P = PS[j];
             // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
             const long long work = P.level[l].capacity;
             const int grid = persistent_grid(work, sms, grid_mult);
+            const int wgrid = walk_grid(work, sms, grid_mult);
             if (!lbvh) {
                 if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
                 else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
@@ -356,16 +422,16 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             }
             // trace: one thread per ray; shadow: one chain per node; colour / spawn: one thread per node
             cudaStream_t ms = overlap ? cs.main[j] : stream;
-            int sh_grid = persistent_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
+            int sh_grid = walk_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
             if (overlap && shadow_budget > 0)   // bounded blocks: as many as the queue may need (surplus blocks end at once)
                 sh_grid = (int)std::max<long long>(sh_grid, std::min<long long>((work + 4LL * shadow_budget - 1) / (4LL * shadow_budget) + 1, 1 << 20));
             const bool sharing = steal == 1 || (steal == 2 && work <= steal_max_work);
             if (p.instrument) {
-                if (sharing) bvh_trace_kernel<true, true><<<grid, kBlock, 0, ms>>>(P, l);
-                else bvh_trace_kernel<true, false><<<grid, kBlock, 0, ms>>>(P, l);
+                if (sharing) bvh_trace_kernel<true, true><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
+                else bvh_trace_kernel<true, false><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
             } else {
-                if (sharing) bvh_trace_kernel<false, true><<<grid, kBlock, 0, ms>>>(P, l);
-                else bvh_trace_kernel<false, false><<<grid, kBlock, 0, ms>>>(P, l);
+                if (sharing) bvh_trace_kernel<false, true><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
+                else bvh_trace_kernel<false, false><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
             }
             n++;
             // shadow -> colour depends only on this generation's hits, spawn -> next trace too:
@@ -382,11 +448,11 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             if (s->nl) {
                 const bool sh_sharing = steal_shadow == 1 || (steal_shadow == 2 && work <= steal_max_work);
                 if (p.instrument) {
-                    if (sh_sharing) bvh_shadow_kernel<true, false, true><<<sh_grid, kBlock, 0, side>>>(P, l);
-                    else bvh_shadow_kernel<true, false, false><<<sh_grid, kBlock, 0, side>>>(P, l);
-                } else if (near_first) bvh_shadow_kernel<false, true, false><<<sh_grid, kBlock, 0, side>>>(P, l);
-                else if (sh_sharing) bvh_shadow_kernel<false, false, true><<<sh_grid, kBlock, 0, side>>>(P, l);
-                else bvh_shadow_kernel<false, false, false><<<sh_grid, kBlock, 0, side>>>(P, l);
+                    if (sh_sharing) bvh_shadow_kernel<true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
+                    else bvh_shadow_kernel<true, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
+                } else if (near_first) bvh_shadow_kernel<false, true, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
+                else if (sh_sharing) bvh_shadow_kernel<false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
+                else bvh_shadow_kernel<false, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
                 n++;
             }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
@@ -395,7 +461,8 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             n++;
         }
     }
-    if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 1], stream));
+    const int prof_n = fused ? 1 : p.max_depth + 1;      // a fused frame is profiled as one "generation"
+    if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[prof_n], stream));
     // bottom-up combine per chain, on the chain's main stream once its colour kernels are done
     for (int j = 0; j < K; j++) {
         const FrameParams& P = PS[j];
@@ -418,8 +485,8 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     }
     RT_CUDA(cudaGetLastError());
     if (p.profile) {
-        RT_CUDA(cudaEventRecord(s->prof_ev[p.max_depth + 2], stream));
-        s->prof_levels = p.max_depth + 1;
+        RT_CUDA(cudaEventRecord(s->prof_ev[prof_n + 1], stream));
+        s->prof_levels = prof_n;
     }
     if (tiles_out && tiles_out != s->ws.tiles.as<uchar4>())
         RT_CUDA(cudaMemcpyAsync(s->ws.tiles.p, tiles_out, (size_t)tl.n_local_pixels * sizeof(uchar4),
@@ -464,6 +531,7 @@ bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxL
         t.bvh_nodes += c.bvh_nodes; t.prim_tests += c.prim_tests; t.texels += c.texels;
         t.shadow_boxes += c.shadow_boxes; t.shadow_prims += c.shadow_prims; t.shadow_walks += c.shadow_walks;
         t.shadow_hint_hits += c.shadow_hint_hits;
+        t.work.stalled |= c.work.stalled;
         if (j == 0) std::memcpy(t.clock, c.clock, sizeof t.clock);      // instrumented frames have one chain
     }
     if (total) *total = t;

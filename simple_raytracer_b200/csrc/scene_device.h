@@ -125,6 +125,20 @@ struct WalkClock {
     unsigned int warps, pad;
 };
 
+// Work list of the fused trace kernel (bvh.cuh: persistent_walk_all).  Tickets below the number of
+// primary rays are pixels; ticket n0 + e is entry e of FrameParams::work_order.
+struct WorkQueue {
+    unsigned int head;      // tickets handed out
+    unsigned int tail;      // entries allocated (each is written right after)
+    unsigned int retired;   // rays finished, children published: the frame is traced when == n0 + tail
+    unsigned int done;
+    unsigned int stalled;   // watchdog: a warp gave up waiting (never expected; the frame is invalid)
+    // hits waiting for the spawn half of ShadeRay (FrameParams::hit_order), taken 32 at a time by the
+    // kernel's spawner warps
+    unsigned int hit_head, hit_tail;
+    unsigned int pad;
+};
+
 struct Counters {
     unsigned int rays[kMaxLevels];        // rays queued for level d (level 0: unused)
     unsigned int nodes[kMaxLevels];       // hits shaded at level d
@@ -138,6 +152,7 @@ struct Counters {
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
     unsigned long long shadow_hint_hits;                // ... of the elided ones: settled by the hinted occluder, no tree walk
     WalkClock clock[2][kMaxLevels];                     // instrumented LBVH frames: [0] trace, [1] shadow kernels
+    WorkQueue work;                                     // fused trace kernel
 };
 
 struct FrameParams {
@@ -169,6 +184,13 @@ struct FrameParams {
     int hint_passes;      // the node list is taken in up to this many interleaved passes (>= 1)
     int hint_group;       // ... of groups of this many consecutive nodes
     int hint_min_chunk;   // ... but no pass shorter than this many nodes
+    // Fused trace kernel: one entry per spawned ray, (generation << 28) | queue slot, 0xffffffff = not
+    // written yet (cleared at every frame start); work_capacity = the generations' capacities summed
+    unsigned int* work_order;
+    unsigned int work_capacity;
+    unsigned int* hit_order;      // same encoding: the hits of generations < max_depth, in arrival order
+    unsigned int hit_capacity;
+    int spawn_every;              // every spawn_every-th warp of the fused kernel spawns instead of walking
     int hint_mode;        // experiments: bit 0 = test hints, bit 1 = record them (3 = normal)
 };
 

@@ -94,9 +94,11 @@ RT_DEV bool load_ray(const FrameParams& P, int level, unsigned slot, RayIn& r)
         r.ray = vnorm(vsub(p, r.o));                                                // 728
         return true;
     }
+    // (ld.global.cg: in the fused trace kernel the entry was written by another SM during this very
+    // launch, and a neighbouring entry may have pulled a stale copy of its line into this SM's L1)
     const LevelBuffers& LB = P.level[level];
-    const float4 qo = LB.rq_o[slot], qd = LB.rq_d[slot];
-    const int4 qm = LB.rq_m[slot], qs = LB.rq_s[slot];
+    const float4 qo = __ldcg(LB.rq_o + slot), qd = __ldcg(LB.rq_d + slot);
+    const int4 qm = __ldcg(LB.rq_m + slot), qs = __ldcg(LB.rq_s + slot);
     r.o = mk3(qo.x, qo.y, qo.z); r.n_i = qo.w;
     r.ray = mk3(qd.x, qd.y, qd.z); r.n_t = qd.w;
     r.inc = qm.y;
@@ -137,10 +139,12 @@ RT_DEV void write_miss(const FrameParams& P, int level, unsigned slot, bool padd
 //            to the queue of generation level+1 -> nr_b, nr_c.
 // The fused brute-force kernel does both in one call, the LBVH pipeline in two kernels.
 // Must be called by all 32 lanes of a warp (`hit` false for idle lanes): queue slots are
-// handed out with one atomicAdd per warp.
-template <bool kColour, bool kSpawn, class ShadowSrc>
+// handed out with one atomicAdd per warp.  kMixed: the lanes' `level`s may differ (the fused
+// trace kernel): one atomicAdd per warp and generation present.  children: the queue slots of
+// the transmission / reflection ray in generation level + 1 (-1 = none), when asked for.
+template <bool kColour, bool kSpawn, class ShadowSrc, bool kMixed = false>
 RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int level, unsigned slot, RayIn& r,
-                            const Hit& h, bool hit)
+                            const Hit& h, bool hit, int* children = nullptr)
 {
     const SceneView& S = P.scene;
     const LevelBuffers& LB = P.level[level];
@@ -168,18 +172,20 @@ RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int l
     }
 
     // ---- spawn: warp-aggregated slot allocation in the next generation's queue -----
-    const unsigned mt = __ballot_sync(0xffffffffu, sp.want_t);
-    const unsigned mr = __ballot_sync(0xffffffffu, sp.want_r);
     int child_t = -1, child_r = -1;
-    if (mt | mr) {                                   // warp-uniform
-        const LevelBuffers& NB = P.level[level + 1];
+    for (int L = kMixed ? 0 : level; L <= (kMixed ? P.max_depth - 1 : level); L++) {
+        const unsigned mt = __ballot_sync(0xffffffffu, sp.want_t && level == L);
+        const unsigned mr = __ballot_sync(0xffffffffu, sp.want_r && level == L);
+        if (!(mt | mr)) continue;                    // warp-uniform
+        const LevelBuffers& NB = P.level[L + 1];
         const int nt = __popc(mt), nr = __popc(mr);
         unsigned basei = 0;
         if ((threadIdx.x & 31) == 0) {
-            basei = atomicAdd(&P.counters->rays[level + 1], (unsigned)(nt + nr));
-            if (nr) atomicAdd(&P.counters->rays_reflect[level + 1], (unsigned)nr);
+            basei = atomicAdd(&P.counters->rays[L + 1], (unsigned)(nt + nr));
+            if (nr) atomicAdd(&P.counters->rays_reflect[L + 1], (unsigned)nr);
         }
         basei = __shfl_sync(0xffffffffu, basei, 0);
+        if (level != L) continue;
         const unsigned lt = lanemask_lt();
         const int flags_common = (c_exiting ? kRayStateExiting : 0) | (r.ns << kRayNStackShift);
         if (sp.want_t) {
@@ -207,6 +213,7 @@ RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int l
             }
         }
     }
+    if (children) { children[0] = child_t; children[1] = child_r; }
 
     if (!hit || level == P.max_depth) return;
     // a node without children is finished by the combine pass like any other: x + 0 leaves a

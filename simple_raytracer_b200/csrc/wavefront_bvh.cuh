@@ -25,13 +25,17 @@
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 6
 #endif
+// fused trace kernel: blocks per SM it is compiled for (0 = the compiler's choice)
+#ifndef RT_TRACE_ALL_MIN_BLOCKS
+#define RT_TRACE_ALL_MIN_BLOCKS 7
+#endif
 // any-hit kernel: 8 blocks per SM (64 registers)
 #ifndef RT_SHADOW_MIN_BLOCKS
 #define RT_SHADOW_MIN_BLOCKS 8
 #endif
 namespace rt {
 
-static_assert(kWalkBlock == kBlock, "the shared-memory stack is laid out for kBlock threads");
+static_assert(kWalkBlock == 32 || kWalkBlock == 64 || kWalkBlock == 128, "walk kernels: 1, 2 or 4 warps per block");
 
 template <bool kCount>
 RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool shadow = false)
@@ -218,7 +222,7 @@ struct TraceJob {
 };
 
 template <bool kCount, bool kStealing>
-__global__ void __launch_bounds__(kBlock, kStealing ? 7 : 0) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kWalkBlock, (kStealing || kWalkScale > 1 ? 7 : 0) * kWalkScale) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
@@ -226,6 +230,176 @@ __global__ void __launch_bounds__(kBlock, kStealing ? 7 : 0) bvh_trace_kernel(co
     TraceJob<kCount, kStealing> job{ P, acc, level };
     acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
                         kCount ? &P.counters->clock[0][level] : nullptr, P.steal != 0);
+    flush_bvh_counters(acc, P.counters);
+}
+
+// A dummy shadow source for the spawn half (it never asks).
+struct NoShadow {
+    RT_DEV void operator()(int, V3, V3, int, float, float, bool, float&) const {}
+};
+
+// ---- the FUSED trace kernel -------------------------------------------------------------------
+// Every generation's closest-hit rays in one persistent launch (BvhAccelT::persistent_walk_all).
+// Walker warps walk rays of any generation; a ray that hits something below the last generation
+// is appended to the hit list, where the kernel's SPAWNER warps (every spawn_every-th) take hits
+// 32 at a time, run the spawn half of ShadeRay at full warp width and publish the children to
+// the work list the walkers draw from.  (Spawning inside the walkers' retire step runs the
+// double-precision Fresnel code with one or two lanes active: measured 38.6 ms against 21 + 2.2.)
+RT_DEV void st_volatile(unsigned* p, unsigned v)
+{
+    asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+RT_DEV unsigned ld_volatile_u32(const unsigned* p)
+{
+    unsigned v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// `n` rays of this warp are through (children, if any, already published): the frame is traced
+// when every published ray has retired.  Lane 0 only.
+RT_DEV void count_retired(WorkQueue* q, unsigned n0, unsigned n)
+{
+    const unsigned r = atomicAdd(&q->retired, n) + n;
+    if (r == n0 + ld_volatile_u32(&q->tail)) atomicExch(&q->done, 1u);
+}
+
+template <bool kCount>
+struct TraceAllJob : TraceJob<kCount, false> {
+    using Base = TraceJob<kCount, false>;
+    WorkQueue* q;
+    unsigned n0;
+
+    RT_DEV bool begin(int gen, unsigned slot_, V3& wo, V3& wray, float& tmin, float& tmax)
+    {
+        this->level = gen;
+        return Base::begin(slot_, wo, wray, tmin, tmax);
+    }
+
+    RT_DEV void retire(bool fin)
+    {
+        constexpr unsigned kFull = 0xffffffffu;
+        const FrameParams& P = this->P;
+        const SceneView& S = P.scene;
+        const int level = this->level;
+        const unsigned slot = this->slot;
+        const unsigned lt = lanemask_lt();
+        const bool lane0 = (threadIdx.x & 31) == 0;
+        if (fin && !this->padding && this->back < 0 && this->skip_spheres) {
+            const float tmin = level == 0 ? 0.0f : P.epsilon;
+            for (int i = 0; i < this->acc.ns; i++) this->sphere_candidate(this->acc.sph[(size_t)i * kSphWords], this->acc.nf + i, tmin);
+        }
+        const bool hit = fin && !this->padding && !this->aborted && this->best.obj >= 0;
+        // the node lists: one atomic per warp and generation present
+        for (int L = 0; L <= P.max_depth; L++) {
+            const unsigned hm = __ballot_sync(kFull, hit && level == L);
+            if (!hm) continue;
+            unsigned base = 0;
+            if (lane0) base = atomicAdd(&P.counters->nodes[L], (unsigned)__popc(hm));
+            base = __shfl_sync(kFull, base, 0);
+            if (hit && level == L) {
+                const LevelBuffers& LB = P.level[L];
+                const V3 p = vadd(this->o, vmulf(this->ray, this->best.t));      // 1245 / 1303, same as finish_hit
+                LB.hp[slot] = make_float4(p.x, p.y, p.z, __int_as_float(this->best.obj));
+                LB.hb[slot] = make_float4(this->best.b, this->best.g, this->best.t, 0.0f);
+                LB.node_list[base + __popc(hm & lt)] = (int)slot;
+                if (L < P.max_depth) LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
+            }
+        }
+        if (fin && !hit) write_miss(P, level, slot, this->padding, this->aborted);
+        if (P.primary_ids) {   // instrumented frame
+            if (fin && !this->padding && level == 0) P.primary_ids[out_slot(P, slot)] = hit ? S.obj[this->best.obj].z : 0;
+            const unsigned tm = __ballot_sync(kFull, hit && S.obj[this->best.obj].y >= 0);
+            if (lane0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
+        }
+        // hits that may have children go to the spawners; everything else is through
+        const bool parent = hit && level < P.max_depth;
+        const unsigned pm = __ballot_sync(kFull, parent);
+        if (pm) {
+            unsigned base = 0;
+            if (lane0) base = atomicAdd(&q->hit_tail, (unsigned)__popc(pm));
+            base = __shfl_sync(kFull, base, 0);
+            if (P.hint_mode & 4) __threadfence();                   // the hit records before the entries that announce them
+            if (parent) st_volatile(P.hit_order + base + __popc(pm & lt), ((unsigned)level << 28) | slot);
+        }
+        const unsigned fm = __ballot_sync(kFull, fin && !parent);
+        if (lane0 && fm) count_retired(q, n0, (unsigned)__popc(fm));
+    }
+};
+
+// A spawner warp of the fused kernel.
+RT_DEV void spawner_loop(const FrameParams& P, WorkQueue* q, unsigned n0)
+{
+    constexpr unsigned kFull = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned base = 0, pending = 0, polls = 0, spins = 0;
+    for (;;) {
+        if (!pending) {
+            if (lane == 0) base = atomicAdd(&q->hit_head, 32u);
+            base = __shfl_sync(kFull, base, 0);
+            pending = kFull; polls = 0;
+        }
+        const unsigned e = base + lane;
+        unsigned v = 0xffffffffu;
+        if (((pending >> lane) & 1u) && e < P.hit_capacity) v = ld_volatile_u32(P.hit_order + e);
+        const unsigned present = __ballot_sync(kFull, v != 0xffffffffu);
+        if (present != 0u && (present == pending || ++polls > 4u)) {
+            // the spawn half of ShadeRay for the hits that have arrived, then the children's entries
+            const bool mine = ((present >> lane) & 1u) != 0u;
+            const int level = mine ? (int)(v >> 28) : 0;
+            const unsigned slot = v & 0x0fffffffu;
+            RayIn r; r.ns = 0;
+            Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
+            if (mine) {
+                load_ray(P, level, slot, r);
+                const float4 hp = __ldcg(P.level[level].hp + slot), hb = __ldcg(P.level[level].hb + slot);
+                h.obj = __float_as_int(hp.w); h.b = hb.x; h.g = hb.y; h.t = hb.z;
+            }
+            int children[2] = { -1, -1 };
+            const NoShadow none;
+            shade_and_spawn<false, true, NoShadow, true>(P, none, level, slot, r, h, mine, children);
+            const unsigned mt = __ballot_sync(kFull, children[0] >= 0), mr = __ballot_sync(kFull, children[1] >= 0);
+            if (mt | mr) {
+                unsigned wb = 0;
+                if (lane == 0) wb = atomicAdd(&q->tail, (unsigned)(__popc(mt) + __popc(mr)));
+                wb = __shfl_sync(kFull, wb, 0);
+                __threadfence();               // the rays' records before the entries that announce them
+                const unsigned tag = (unsigned)(level + 1) << 28;
+                if (children[0] >= 0) st_volatile(P.work_order + wb + __popc(mt & lt), tag | (unsigned)children[0]);
+                if (children[1] >= 0) st_volatile(P.work_order + wb + __popc(mt) + __popc(mr & lt), tag | (unsigned)children[1]);
+            }
+            __threadfence();                   // tail before retired
+            __syncwarp();
+            if (lane == 0) count_retired(q, n0, (unsigned)__popc(present));
+            pending &= ~present;
+            polls = 0; spins = 0;
+            continue;
+        }
+        unsigned d = 0;
+        if (lane == 0) d = ld_volatile_u32(&q->done);
+        if (__shfl_sync(kFull, d, 0)) break;
+        __nanosleep(300);
+        if (++spins > (1u << 22)) {              // ~2 s without a hit: give up loudly
+            if (lane == 0) atomicExch(&q->stalled, 1u);
+            break;
+        }
+    }
+}
+
+template <bool kCount>
+__global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_TRACE_ALL_MIN_BLOCKS) * kWalkScale) bvh_trace_all_kernel(const __grid_constant__ FrameParams P)
+{
+    const unsigned n0 = (unsigned)P.n_local_pixels;
+    const unsigned warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const auto acc = make_bvh_accel<kCount>(P.scene);
+    if (warp % (unsigned)P.spawn_every == (unsigned)P.spawn_every - 1u) {
+        spawner_loop(P, &P.counters->work, n0);
+    } else {
+        TraceAllJob<kCount> job{ { P, acc, 0 }, &P.counters->work, n0 };
+        acc.persistent_walk_all(n0, &P.counters->work, P.work_order, P.work_capacity, job,
+                                P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes);
+    }
     flush_bvh_counters(acc, P.counters);
 }
 
@@ -260,6 +434,11 @@ struct ShadowJob {
     // neighbours of a node were finished a whole pass earlier, not in the same warp.
     const float4* pr;            // the any-hit walk's primitive table (what persistent_walk visits)
     int* hint;                   // null: off
+    // all_levels: ONE launch walks the nodes of every generation (after the fused trace kernel): job
+    // j counts through generation 0's node list, then generation 1's, ...; `level` and `n_nodes`
+    // are then per lane
+    bool all_levels;
+    unsigned total;              // jobs before padding: n_nodes, or all generations' nodes
     unsigned pass_jobs, passes, group;
     // per node
     unsigned k;
@@ -275,11 +454,16 @@ struct ShadowJob {
     // jobs of the launch and the job -> node permutation described above
     RT_DEV unsigned plan()
     {
-        passes = 1; group = 1; pass_jobs = n_nodes;
+        total = n_nodes;
+        if (all_levels) {
+            total = 0;
+            for (int l = 0; l <= P.max_depth; l++) total += P.counters->nodes[l];
+        }
+        passes = 1; group = 1; pass_jobs = total;
         if (hint && P.hint_passes > 1) {
             group = (unsigned)max(P.hint_group, 1);
-            const unsigned groups = (n_nodes + group - 1) / group;
-            passes = min((unsigned)P.hint_passes, max(n_nodes / (unsigned)max(P.hint_min_chunk, 1), 1u));
+            const unsigned groups = (total + group - 1) / group;
+            passes = min((unsigned)P.hint_passes, max(total / (unsigned)max(P.hint_min_chunk, 1), 1u));
             pass_jobs = (groups + passes - 1) / passes * group;
         }
         return pass_jobs * passes;
@@ -321,7 +505,12 @@ struct ShadowJob {
     RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
     {
         k = perm(j); li = 0; mask = 1.0f;                                        // 788
-        if (k >= n_nodes) { k = 0xffffffffu; return false; }                     // padding of the last groups
+        if (k >= total) { k = 0xffffffffu; return false; }                       // padding of the last groups
+        if (all_levels) {
+            level = 0;
+            n_nodes = P.counters->nodes[0];
+            while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
+        }
         const float4 hp = P.level[level].hp[P.level[level].node_list[k]];
         p = mk3(hp.x, hp.y, hp.z);
         self = __float_as_int(hp.w);
@@ -408,16 +597,18 @@ struct ShadowJob {
 };
 
 template <bool kCount, bool kNearFirst, bool kStealing>
-__global__ void __launch_bounds__(kBlock, kCount ? 0 : RT_SHADOW_MIN_BLOCKS) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_SHADOW_MIN_BLOCKS) * kWalkScale) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
-    const unsigned n_nodes = P.counters->nodes[level];
+    const unsigned n_nodes = level < 0 ? 0u : P.counters->nodes[level];      // level < 0: every generation's nodes
     ShadowJob<kCount, kNearFirst, kStealing> job{ P, acc, level, n_nodes };
     job.pr = acc.nodes8 ? acc.prims8 : acc.prims;
     job.hint = P.occluder_hint;
+    job.all_levels = level < 0;
     const unsigned n_jobs = job.plan();
-    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
-                        kCount ? &P.counters->clock[1][level] : nullptr, P.steal != 0,
+    const int cl = level < 0 ? 0 : level;
+    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[cl], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
+                        kCount ? &P.counters->clock[1][cl] : nullptr, P.steal != 0,
                         P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
@@ -437,11 +628,6 @@ struct RecordedShadow {
         if (mask == 0.0f) return;     // the chain stopped here: later records were never written (and 0 stays 0)
         mask = rec[(size_t)li * n_nodes];
     }
-};
-
-// A dummy shadow source for the spawn half (it never asks).
-struct NoShadow {
-    RT_DEV void operator()(int, V3, V3, int, float, float, bool, float&) const {}
 };
 
 // kColour / kSpawn select the half of ShadeRay this launch does (wavefront.cuh:

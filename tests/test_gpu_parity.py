@@ -339,6 +339,32 @@ def test_interleaved_shadow_passes_never_change_a_pixel():
                 assert np.array_equal(got[name + "_fl"], want[name][1]), (group, name)
 
 
+@pytest.mark.parametrize("depth", [0, 1, 4])
+def test_fused_trace_kernel_never_changes_a_pixel(depth):
+    """All generations' closest-hit rays in one persistent launch whose spawner warps feed its own
+    work list (bvh_trace_all_kernel), then all shadow chains in one launch: frames, node and ray
+    counts and primary hit ids equal those of the per-generation launch chains and of brute force —
+    also for frames of a few pixels (fewer rays than lanes) and at depth 0 (nothing to spawn)."""
+    scenes = (scenegen.coverage_scene(128, 96), scenegen.stress_scene(8000, 100, 160, 120), scenegen.coverage_scene(16, 2))
+    for scene in scenes:
+        with DeviceScene(scene) as ds:
+            ds.render(accel=abi.RT_ACCEL_BRUTE, max_depth=depth)
+            want = ds.download()
+            want = (want[0].copy(), want[1].copy())
+            stats = {}
+            for mode in (2, 1):
+                stats[mode] = ds.render(accel=abi.RT_ACCEL_LBVH, fused_trace=mode, max_depth=depth)
+                got = ds.download()
+                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), (mode, scene.width)
+            assert list(stats[1].nodes_per_level) == list(stats[2].nodes_per_level)
+            assert stats[1].rays_reflect == stats[2].rays_reflect and stats[1].rays_transmit == stats[2].rays_transmit
+            assert stats[1].kernel_launches < stats[2].kernel_launches or depth == 0
+            ds.render(accel=abi.RT_ACCEL_LBVH, fused_trace=1, instrument=True, max_depth=depth)
+            ids_fused = ds.download_primary_ids().copy()
+            ds.render(accel=abi.RT_ACCEL_BRUTE, instrument=True, max_depth=depth)
+            assert np.array_equal(ids_fused, ds.download_primary_ids())
+
+
 def test_device_formatted_ppm_equals_the_host_formatter():
     """rt_format_ppm_device against rt_host_format_ppm on the downloaded frame: NaN
     channels (Test1 has them), primary misses with an out-of-range bkgcolor, 1/2/3-digit values,

@@ -39,7 +39,7 @@ def test_struct_layouts_match_the_header():
     # sizes implied by include/rt.h on LP64
     assert C.sizeof(abi.RtMaterial) == 48 and C.sizeof(abi.RtSphere) == 28
     assert C.sizeof(abi.RtFace) == 112 and C.sizeof(abi.RtLight) == 28 and C.sizeof(abi.RtTexture) == 16
-    assert C.sizeof(abi.RtRenderParams) == 40
+    assert C.sizeof(abi.RtRenderParams) == 48
     assert C.sizeof(abi.RtSceneDesc) == 8 + 12 * 3 + 4 + 12 + 4 + 5 * 16
 
 
