@@ -137,8 +137,9 @@ typedef struct RtRenderParams {
                               occluder leaves that primitive as a hint for later shadow
                               rays from the same surface primitive to the same light,
                               which test it first (exactly) and skip the walk when it
-                              blocks them too.  0 = on (default), 1 = on, 2 = off.
-                              Never changes a pixel.                             */
+                              blocks them too.  0 = off (default: the extra state costs
+                              the kernel more than the skipped walks save on B200,
+                              DESIGN.md 5.5), 1 = on, 2 = off.  Never changes a pixel. */
     int32_t fused_trace;   /* LBVH pipeline: the closest-hit rays of ALL generations in one
                               persistent launch that spawns the next generation's rays as
                               it goes (one kernel tail per frame instead of one per

@@ -33,8 +33,33 @@
 
 namespace rt {
 
+// How the walks read primitive records (80 B, random, little reuse): 0 = like everything else,
+// 1 = ld.global.nc.L1::no_allocate, 2 = ld.global.nc.L1::evict_first, so that they do not push
+// the upper tree out of L1.
+#ifndef RT_PRIM_LOAD
+#define RT_PRIM_LOAD 0
+#endif
+RT_DEV float4 ldp(const float4* p)
+{
+#if RT_PRIM_LOAD == 1
+    float4 v;
+    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#elif RT_PRIM_LOAD == 2
+    float4 v;
+    asm("ld.global.nc.L1::evict_first.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#else
+    return *p;
+#endif
+}
+
+// shared-memory part of the persistent walk's stack (entries per thread)
+#ifndef RT_SMEM_STACK
+#define RT_SMEM_STACK 24
+#endif
 constexpr int kBvhStack = 96;     // local-memory part of the traversal stack (entries)
-constexpr int kSmemStack = 24;    // shared-memory part of the persistent walk's stack (entries per thread)
+constexpr int kSmemStack = RT_SMEM_STACK;
 // Block size of the persistent walk kernels.  A block's registers stay taken until its LAST warp
 // has finished, so in a launch's tail smaller blocks hand their SM share to the other launch
 // chain's blocks sooner.
@@ -317,6 +342,7 @@ struct BvhAccelT {
     {
         constexpr int kDone = kWalkDone;
         constexpr unsigned kFull = 0xffffffffu;
+        constexpr bool kJobBudget = false;     // bounded any-hit blocks (RT_SHADOW_JOB_BUDGET): measured, never paid; compiled out
         // loop invariants in registers (the accelerator object itself may sit in local memory)
         const float4* __restrict__ const nd = nodes;
         const uint4* __restrict__ const nd8 = nodes8;
@@ -359,11 +385,13 @@ struct BvhAccelT {
             sp = 0; bot = 0; leaf = 0; owner = lane;
             node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
             rq = make_rayq(o, ray);
-            if (node != kDone) {
-                // a primitive the job wants tested before the tree is opened (an occluder hint): it
-                // travels as the postponed leaf, the root waits on the stack
-                const int fl = job.first_leaf();
-                if (fl < 0) { push(node); node = kDone; leaf = fl; }
+            if constexpr (Job::kFirstLeaf) {
+                if (node != kDone) {
+                    // a primitive the job wants tested before the tree is opened (an occluder hint): it
+                    // travels as the postponed leaf, the root waits on the stack
+                    const int fl = job.first_leaf();
+                    if (fl < 0) { push(node); node = kDone; leaf = fl; }
+                }
             }
         };
         for (;;) {
@@ -374,8 +402,8 @@ struct BvhAccelT {
                 base = __shfl_sync(kFull, base, 0);
                 // (job_budget: a warp stops fetching after that many jobs, so that its block ends and
                 // the slot can go to a kernel of higher priority — render.cu)
-                fetched += (unsigned)__popc(dead);
-                if (base + (unsigned)__popc(dead) >= total || fetched >= job_budget) {
+                if (kJobBudget) fetched += (unsigned)__popc(dead);
+                if (base + (unsigned)__popc(dead) >= total || (kJobBudget && fetched >= job_budget)) {
                     pool_empty = true;
                     if (kCount && clock) t_empty = globaltimer();
                 }
@@ -468,7 +496,7 @@ struct BvhAccelT {
                     if (node < 0) {
                         leaf = node;
                         node = pop();
-                    } else if (node == kDone) {
+                    } else if (Job::kFirstLeaf && node == kDone) {
                         node = pop();      // (only start()'s first leaf leaves entries under a finished node)
                     }
                 }
@@ -763,17 +791,17 @@ struct BvhAccelT {
         }
         RT_DEV float operator()(const float4* w, float tmax)
         {
-            const float4 w4 = w[4];
+            const float4 w4 = ldp(w + 4);
             const int order = __float_as_int(w4.z);
             if (order == self) return tmax;
             if (__float_as_int(w4.w) == 0) {
                 float t, b, g;
-                if (tri_distance(w[0], o, ray, t) && t > tmin && (!use_tmax || t < tmax_hit) &&
-                    tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g))
+                if (tri_distance(ldp(w), o, ray, t) && t > tmin && (!use_tmax || t < tmax_hit) &&
+                    tri_inside(ldp(w + 1), ldp(w + 2), ldp(w + 3), w4, o, ray, t, b, g))
                     add(order, w4.y);
             } else if (!skip_spheres) {
                 float tf, tn;
-                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                const int n = sphere_roots(ldp(w), o, ray, tf, tn);
                 if (n >= 1 && tf > tmin && (!use_tmax || tf < tmax_hit)) add(order, w4.y);
                 if (n == 2 && tn > tmin && (!use_tmax || tn < tmax_hit)) add(order, w4.y);
             }

@@ -307,7 +307,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     static const int shadow_mult = tuning_int("RT_SHADOW_GRID_MULT", 0, 0, 64);   // 0: same as RT_GRID_MULT
     // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob) and the interleaved passes
     // that make them available in time
-    static const int hint_env = tuning_int("RT_HINT", 1, 0, 1);
+    static const int hint_env = tuning_int("RT_HINT", 0, 0, 1);
     static const int hint_passes = tuning_int("RT_HINT_PASSES", 16, 1, 256);
     static const int hint_group = tuning_int("RT_HINT_GROUP", 32, 1, 4096);
     static const int hint_min_chunk = 1024 * tuning_int("RT_HINT_MIN_CHUNK_K", 256, 1, 1 << 20);
@@ -315,6 +315,16 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     static const int hint_keep = tuning_int("RT_HINT_KEEP", 0, 0, 1);      // experiments only: hints survive the frame
     const bool hints = lbvh && s->nl > 0 && (p.occluder_hints == 1 || (p.occluder_hints == 0 && hint_env));
 
+    // L1 / shared-memory split of the walk kernels (percent of the maximum shared memory; -1 = the driver's choice)
+    static const int carveout = tuning_int("RT_CARVEOUT", -1, -1, 100);
+    static bool carveout_set = false;
+    if (carveout >= 0 && !carveout_set) {
+        carveout_set = true;
+        cudaFuncSetAttribute(bvh_trace_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        cudaFuncSetAttribute(bvh_trace_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        cudaFuncSetAttribute(bvh_shadow_kernel<false, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+        cudaFuncSetAttribute(bvh_shadow_kernel<false, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
+    }
     static thread_local FrameParams PS[kMaxSubframes];
     for (int j = 0; j < K; j++) {
         FrameParams& P = PS[j];
@@ -395,8 +405,8 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             long long work = 0;
             for (int l = 0; l <= p.max_depth; l++) work += P.level[l].capacity;
             const int sh_grid = walk_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
-            if (p.instrument) bvh_shadow_kernel<true, false, false><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1);
-            else bvh_shadow_kernel<false, false, false><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1);
+            if (p.instrument) { if (hints) bvh_shadow_kernel<true, false, false, true, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); else bvh_shadow_kernel<true, false, false, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); }
+            else { if (hints) bvh_shadow_kernel<false, false, false, true, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); else bvh_shadow_kernel<false, false, false, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); }
             n++;
         }
         if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[0][1], stream));
@@ -448,11 +458,11 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             if (s->nl) {
                 const bool sh_sharing = steal_shadow == 1 || (steal_shadow == 2 && work <= steal_max_work);
                 if (p.instrument) {
-                    if (sh_sharing) bvh_shadow_kernel<true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
-                    else bvh_shadow_kernel<true, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
+                    if (sh_sharing) { if (hints) bvh_shadow_kernel<true, false, true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
+                    else { if (hints) bvh_shadow_kernel<true, false, false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<true, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
                 } else if (near_first) bvh_shadow_kernel<false, true, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
-                else if (sh_sharing) bvh_shadow_kernel<false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
-                else bvh_shadow_kernel<false, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
+                else if (sh_sharing) { if (hints) bvh_shadow_kernel<false, false, true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
+                else { if (hints) bvh_shadow_kernel<false, false, false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<false, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
                 n++;
             }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));

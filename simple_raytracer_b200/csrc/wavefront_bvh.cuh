@@ -106,7 +106,7 @@ struct TraceJob {
     RT_DEV float visit(const float4* w, float tmax)
     {
         const float tmin = level == 0 ? 0.0f : P.epsilon;
-        const float4 w4 = w[4];
+        const float4 w4 = ldp(w + 4);
         const int order = __float_as_int(w4.z);
         const bool is_tri = __float_as_int(w4.w) == 0;
         if (back >= 0) {
@@ -116,10 +116,10 @@ struct TraceJob {
             bool bad = false;
             if (is_tri) {
                 float t, b, g;
-                if (tri_distance(w[0], o, ray, t) && t > tmin && t < limit) bad = tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g);
+                if (tri_distance(ldp(w), o, ray, t) && t > tmin && t < limit) bad = tri_inside(ldp(w + 1), ldp(w + 2), ldp(w + 3), w4, o, ray, t, b, g);
             } else {
                 float tf, tn;
-                const int n = sphere_roots(w[0], o, ray, tf, tn);
+                const int n = sphere_roots(ldp(w), o, ray, tf, tn);
                 bad = (n >= 1 && tf > tmin && tf < limit) || (n == 2 && tn > tmin && tn < limit);
             }
             if (bad) { aborted = true; return -1.0f; }
@@ -127,17 +127,18 @@ struct TraceJob {
         }
         if (is_tri) {
             float t;
-            if (tri_distance(w[0], o, ray, t) && t > tmin && (t < best.t || (t == best.t && order < best_order))) {
+            if (tri_distance(ldp(w), o, ray, t) && t > tmin && (t < best.t || (t == best.t && order < best_order))) {
                 float b, g;
-                if (tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g)) { best.t = t; best.obj = order; best.b = b; best.g = g; best_order = order; }
+                if (tri_inside(ldp(w + 1), ldp(w + 2), ldp(w + 3), w4, o, ray, t, b, g)) { best.t = t; best.obj = order; best.b = b; best.g = g; best_order = order; }
             }
         } else if (!skip_spheres) {
-            sphere_candidate(w[0], order, tmin);
+            sphere_candidate(ldp(w), order, tmin);
         }
         return fminf(tmax, best.t);
     }
 
     RT_DEV bool next(V3&, V3&, float&, float&) { return false; }
+    static constexpr bool kFirstLeaf = false;
     RT_DEV int first_leaf() { return 0; }
 
     // work sharing at the end of a launch (persistent_walk): a helper lane walks a subtree
@@ -409,7 +410,22 @@ __global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_TRACE_ALL_MIN_BLO
 // is exactly 0 it stays 0 whatever the later lights meet: the chain stops there and the
 // remaining records are never read (RecordedShadow stops at the same point).  In a dense
 // scene that removes most shadow walks without changing a bit of the result.
-template <bool kCount, bool kNearFirst, bool kStealing>
+// The launch plan of the any-hit kernel, the same for every thread: kept in shared memory so that
+// it costs the walk loop no registers (the kernel sits at its 64-register limit).
+struct ShadowPlan {
+    unsigned total;              // jobs before padding: this generation's nodes, or all generations'
+    unsigned pass_jobs, passes, group;
+};
+RT_DEV ShadowPlan& shadow_plan()
+{
+    __shared__ ShadowPlan plan;
+    return plan;
+}
+
+constexpr int kFoundNone = -1;
+constexpr int kFoundByHint = 0x7fffffff;
+
+template <bool kCount, bool kNearFirst, bool kStealing, bool kAllLevels, bool kHints>
 struct ShadowJob {
     // One light's walk is a fold in any order too: "an opaque occluder exists" is an OR and the
     // partial factors are collected and sorted by iteration order before they are multiplied
@@ -419,8 +435,12 @@ struct ShadowJob {
     static constexpr bool kWideLoads = true;     // 256-bit node loads (bvh.cuh: test_node)
     static constexpr bool kWide8 = true;         // walks the 8-wide tree when the scene has one (bvh.cuh: step8)
     static constexpr bool kOrdered = kNearFirst; // any hit: order is only a heuristic (near boxes first finds occluders sooner?)
+    static constexpr bool kFirstLeaf = kHints;   // first_leaf() may hand out a record to test before the walk
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
+    // kAllLevels: ONE launch walks the nodes of every generation (after the fused trace kernel): job
+    // j counts through generation 0's node list, then generation 1's, ...; `level` and `n_nodes`
+    // are then per lane
     int level;
     unsigned n_nodes;
     // Occluder hints.  "Some opaque primitive blocks this shadow ray" is all the reference's product
@@ -432,48 +452,45 @@ struct ShadowJob {
     // test: the result never depends on it.  For hints to be THERE in time the node list is taken
     // in interleaved passes (perm): pass p handles the groups g with g % passes == p, so the
     // neighbours of a node were finished a whole pass earlier, not in the same warp.
-    const float4* pr;            // the any-hit walk's primitive table (what persistent_walk visits)
-    int* hint;                   // null: off
-    // all_levels: ONE launch walks the nodes of every generation (after the fused trace kernel): job
-    // j counts through generation 0's node list, then generation 1's, ...; `level` and `n_nodes`
-    // are then per lane
-    bool all_levels;
-    unsigned total;              // jobs before padding: n_nodes, or all generations' nodes
-    unsigned pass_jobs, passes, group;
     // per node
     unsigned k;
     int li;
     V3 p; int self;
     float mask;
-    int found;                   // record index of the opaque occluder this walk ended at, -1
-    int hinted;                  // record index first_leaf() handed to the walk, -1
+    // >= 0 and < kFoundByHint: record index of the opaque occluder this walk ended at; kFoundByHint:
+    // that was the hinted record; <= -2: -2 - (record index first_leaf() handed out), nothing found yet
+    int found;
     unsigned long long walks = 0;      // instrumented variant: shadow rays actually walked by this thread
     unsigned long long hint_hits = 0;  // ... and settled by a hint
     typename BvhAccelT<kCount>::ShadowVisit v;
 
-    // jobs of the launch and the job -> node permutation described above
-    RT_DEV unsigned plan()
+    // the table persistent_walk visits (read where needed: no register across the walk)
+    RT_DEV const float4* records() const { return P.scene.bvh.n_nodes8 > 0 ? P.scene.bvh.prims8 : P.scene.bvh_tri; }
+
+    // jobs of the launch and the job -> node permutation described above (one thread per block,
+    // before the walk; the caller synchronises)
+    RT_DEV static void make_plan(const FrameParams& P, int level)
     {
-        total = n_nodes;
-        if (all_levels) {
-            total = 0;
-            for (int l = 0; l <= P.max_depth; l++) total += P.counters->nodes[l];
+        ShadowPlan& pl = shadow_plan();
+        unsigned total = 0;
+        if (kAllLevels) { for (int l = 0; l <= P.max_depth; l++) total += P.counters->nodes[l]; }
+        else total = P.counters->nodes[level];
+        pl.total = total; pl.passes = 1; pl.group = 1; pl.pass_jobs = total;
+        if (kHints && P.hint_passes > 1) {
+            pl.group = (unsigned)max(P.hint_group, 1);
+            const unsigned groups = (total + pl.group - 1) / pl.group;
+            pl.passes = min((unsigned)P.hint_passes, max(total / (unsigned)max(P.hint_min_chunk, 1), 1u));
+            pl.pass_jobs = (groups + pl.passes - 1) / pl.passes * pl.group;
         }
-        passes = 1; group = 1; pass_jobs = total;
-        if (hint && P.hint_passes > 1) {
-            group = (unsigned)max(P.hint_group, 1);
-            const unsigned groups = (total + group - 1) / group;
-            passes = min((unsigned)P.hint_passes, max(total / (unsigned)max(P.hint_min_chunk, 1), 1u));
-            pass_jobs = (groups + passes - 1) / passes * group;
-        }
-        return pass_jobs * passes;
     }
-    RT_DEV unsigned perm(unsigned j) const
+    RT_DEV static unsigned perm(unsigned j)
     {
-        if (passes == 1) return j;
-        const unsigned ps = j / pass_jobs, r = j - ps * pass_jobs;
-        const unsigned g = r / group, w = r - g * group;
-        return (g * passes + ps) * group + w;
+        if (!kHints) return j;
+        const ShadowPlan& pl = shadow_plan();
+        if (pl.passes == 1) return j;
+        const unsigned ps = j / pl.pass_jobs, r = j - ps * pl.pass_jobs;
+        const unsigned g = r / pl.group, w = r - g * pl.group;
+        return (g * pl.passes + ps) * pl.group + w;
     }
 
     RT_DEV void setup(V3& wo, V3& wray, float& tmin, float& tmax)
@@ -491,22 +508,23 @@ struct ShadowJob {
             acc.shadow_begin(p, wray, self, tmin, tmax, true, v);
         }
         wo = p;
-        found = -1;
+        found = kFoundNone;
     }
     // The hinted record as a leaf code: persistent_walk tests it (through visit(), like any leaf)
     // before it opens the root.
     RT_DEV int first_leaf()
     {
-        hinted = -1;
-        if (!hint || v.count_all || !(P.hint_mode & 1)) return 0;
-        hinted = __ldcg(hint + (size_t)li * P.hint_prims + self);
-        return hinted >= 0 ? ~(hinted << 3) : 0;
+        if (!kHints || v.count_all || !(P.hint_mode & 1)) return 0;
+        const int h = __ldcg(P.occluder_hint + (size_t)li * P.hint_prims + self);
+        if (h < 0) return 0;
+        found = -2 - h;
+        return ~(h << 3);
     }
     RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
     {
         k = perm(j); li = 0; mask = 1.0f;                                        // 788
-        if (k >= total) { k = 0xffffffffu; return false; }                       // padding of the last groups
-        if (all_levels) {
+        if (kHints && k >= shadow_plan().total) { k = 0xffffffffu; return false; }   // padding of the last groups
+        if (kAllLevels) {
             level = 0;
             n_nodes = P.counters->nodes[0];
             while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
@@ -519,9 +537,11 @@ struct ShadowJob {
     }
     RT_DEV float visit(const float4* w, float tmax)
     {
-        const bool before = v.opaque;
         const float r = v(w, tmax);
-        if (v.opaque && !before) found = (int)((w - pr) / kTriWords);
+        if (kHints && r < 0.0f) {          // (count_all walks never stop; found stays unused there)
+            const int idx = (int)((w - records()) / kTriWords);
+            found = (found == -2 - idx) ? kFoundByHint : idx;
+        }
         return r;
     }
 
@@ -537,7 +557,7 @@ struct ShadowJob {
             v.o = mk3(ox, oy, oz); v.ray = mk3(rx, ry, rz); v.tmin = t0; v.tmax_hit = t1; v.self = sf;
             v.use_tmax = (fl & 1) != 0; v.skip_spheres = (fl & 2) != 0; v.count_all = (fl & 4) != 0;
             v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false;
-            found = -1;
+            found = kFoundNone;
         }
         wo = v.o; wray = v.ray;
     }
@@ -551,7 +571,7 @@ struct ShadowJob {
         if (mine) {
             v.hits += h;
             v.opaque = v.opaque || op != 0;
-            if (fd >= 0) found = fd;
+            if (kHints && fd >= 0 && fd != kFoundByHint && found < 0) found = fd;
             if (ov != 1.0f) v.overflow_mask = clamp01(fmul(ov, v.overflow_mask));
         }
         for (int i = 0; i < np; i++) {
@@ -572,15 +592,16 @@ struct ShadowJob {
 
     RT_DEV void retire(bool fin)
     {
-        if (!fin || k == 0xffffffffu) return;
+        if (!fin || (kHints && k == 0xffffffffu)) return;
         acc.shadow_end(v);
-        const bool by_hint = v.opaque && found >= 0 && found == hinted;
+        const bool by_hint = kHints && v.opaque && found == kFoundByHint;
         if (kCount) { if (by_hint) hint_hits++; else walks++; }
         // the carried product exactly as BvhAccelT::shadow applies it (main.cpp:909 / 946 in
         // iteration order); the record is the mask AFTER this light
         if (v.opaque) {
             mask = clamp01(fmul(0.0f, mask));
-            if (hint && found >= 0 && !by_hint && (P.hint_mode & 2)) __stcg(hint + (size_t)li * P.hint_prims + self, found);
+            if (kHints && found >= 0 && !by_hint && (P.hint_mode & 2))
+                __stcg(P.occluder_hint + (size_t)li * P.hint_prims + self, found);
         } else {
             for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
             if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
@@ -589,24 +610,24 @@ struct ShadowJob {
     }
     RT_DEV bool next(V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        if (k == 0xffffffffu || mask == 0.0f || li + 1 >= P.scene.nl) return false;
+        if ((kHints && k == 0xffffffffu) || mask == 0.0f || li + 1 >= P.scene.nl) return false;
         li++;
         setup(wo, wray, tmin, tmax);
         return true;
     }
 };
 
-template <bool kCount, bool kNearFirst, bool kStealing>
-__global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_SHADOW_MIN_BLOCKS) * kWalkScale) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
+// level < 0 (kAllLevels): every generation's nodes
+template <bool kCount, bool kNearFirst, bool kStealing, bool kAllLevels = false, bool kHints = false>
+__global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : kHints ? RT_SHADOW_MIN_BLOCKS : 0) * kWalkScale) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
 {
+    using Job = ShadowJob<kCount, kNearFirst, kStealing, kAllLevels, kHints>;
     const auto acc = make_bvh_accel<kCount>(P.scene);
-    const unsigned n_nodes = level < 0 ? 0u : P.counters->nodes[level];      // level < 0: every generation's nodes
-    ShadowJob<kCount, kNearFirst, kStealing> job{ P, acc, level, n_nodes };
-    job.pr = acc.nodes8 ? acc.prims8 : acc.prims;
-    job.hint = P.occluder_hint;
-    job.all_levels = level < 0;
-    const unsigned n_jobs = job.plan();
-    const int cl = level < 0 ? 0 : level;
+    if (threadIdx.x == 0) Job::make_plan(P, level);
+    __syncthreads();
+    const unsigned n_jobs = shadow_plan().pass_jobs * shadow_plan().passes;
+    Job job{ P, acc, kAllLevels ? 0 : level, kAllLevels ? 0u : shadow_plan().total };
+    const int cl = kAllLevels ? 0 : level;
     acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[cl], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
                         kCount ? &P.counters->clock[1][cl] : nullptr, P.steal != 0,
                         P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
