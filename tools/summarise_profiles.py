@@ -62,9 +62,10 @@ if __name__ == '__main__':
     launches('gpurun_out/r1_bench_launches.csv', f'profiles/{tag}_bench_launches.txt',
              "# ncu --metrics gpu__time_duration.sum --clock-control none -c 400 python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu\n"
              "# (stress_1M_4k on one B200; per-launch times under ncu are serialised and cold: read the SHARES)\n")
-    full('gpurun_out/r1_bvh_full_c.ncu-rep', f'profiles/{tag}_bvh_kernels_ncu_full_c.txt',
+    full('gpurun_out/r1_bvh_full_d.ncu-rep', f'profiles/{tag}_bvh_kernels_ncu_full_d.txt',
          "# ncu --set full --clock-control none --import-source on -k regex:bvh_(trace|shadow|shade)_kernel -s 40 -c 8\n"
          "#   python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu      (stress_1M_4k, one B200)\n"
-         "# State: 4-wide quantised LBVH, persistent while-while walk, shared-memory stack, shadow chains, two streams,\n"
-         "#        256-bit node loads in the any-hit kernel (full-frame launches: the builds without work sharing).\n",
+         "# State: closest hit on the 4-wide quantised LBVH, any hit on the 8-wide one (256-bit node loads), persistent\n"
+         "#        while-while walks, shared-memory stack, shadow chains, two streams; occluder hints and the fused trace\n"
+         "#        kernel off (DESIGN.md 5.5).  Full-frame launches: the builds without work sharing.\n",
          f'profiles/{tag}_traffic.json')
