@@ -99,7 +99,9 @@ static int pick_subframes(const RtRenderParams& p, int accel, const TileLayout& 
     if (!overlap_knob) return 1;
     static const int knob = tuning_int("RT_SUBFRAMES", 0, 0, kMaxSubframes);
     int k = p.subframes ? p.subframes : knob;
-    if (k == 0) k = 1;      // measured (tools/subframe_sweep.sh): more chains never paid, see DESIGN.md 5.4
+    // measured (tools/merge_sweep2.sh, two-phase frame): two interleaved chains pay from about 3 M pixels
+    // per rank on (4K: 40.1 -> 39.3 ms whole, 21.2 -> 20.5 ms half), one chain below; see DESIGN.md 5.4
+    if (k == 0) k = tl.n_local_pixels >= 3000000 ? 2 : 1;
     return std::max(1, std::min(k, tl.n_local_tiles));
 }
 
@@ -307,6 +309,10 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     static const int shadow_mult = tuning_int("RT_SHADOW_GRID_MULT", 0, 0, 64);   // 0: same as RT_GRID_MULT
     // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob) and the interleaved passes
     // that make them available in time
+    // Generations from this one on share ONE any-hit launch after the last trace (fewer kernel tails,
+    // less overlap with the trace chain); 99 = every generation has its own
+    static const int merge_env = tuning_int("RT_SHADOW_MERGE_FROM", 0, 0, 99);
+    static const long long merge_max_work = 1000LL * tuning_int("RT_SHADOW_MERGE_MAX_KRAYS", 2000000, 0, 2000000);
     static const int hint_env = tuning_int("RT_HINT", 0, 0, 1);
     static const int hint_passes = tuning_int("RT_HINT_PASSES", 16, 1, 256);
     static const int hint_group = tuning_int("RT_HINT_GROUP", 32, 1, 4096);
@@ -455,6 +461,24 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 if (l < p.max_depth) { bvh_shade_kernel<false, true><<<grid, kBlock, 0, ms>>>(P, l); n++; }
             }
             if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
+            const bool merged = overlap && s->nl && l >= merge_env && (long long)P.level[0].capacity <= merge_max_work;
+            if (merged) {
+                // this generation's shadow chains wait for the merged launch after the last trace
+                if (l == p.max_depth) {
+                    long long mwork = 0;
+                    for (int m = merge_env; m <= p.max_depth; m++) mwork += P.level[m].capacity;
+                    const int mgrid = walk_grid(mwork * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
+                    const bool msharing = steal_shadow == 1 || (steal_shadow == 2 && mwork <= steal_max_work);
+                    if (msharing) bvh_shadow_kernel<false, false, true, true, false><<<mgrid, kWalkBlock, 0, side>>>(P, -merge_env - 1);
+                    else bvh_shadow_kernel<false, false, false, true, false><<<mgrid, kWalkBlock, 0, side>>>(P, -merge_env - 1);
+                    n++;
+                    for (int m = merge_env; m <= p.max_depth; m++) {
+                        bvh_shade_kernel<true, false><<<persistent_grid(P.level[m].capacity, sms, grid_mult), kBlock, 0, side>>>(P, m);
+                        n++;
+                    }
+                }
+                continue;
+            }
             if (s->nl) {
                 const bool sh_sharing = steal_shadow == 1 || (steal_shadow == 2 && work <= steal_max_work);
                 if (p.instrument) {

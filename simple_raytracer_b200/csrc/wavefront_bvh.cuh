@@ -413,7 +413,8 @@ __global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_TRACE_ALL_MIN_BLO
 // The launch plan of the any-hit kernel, the same for every thread: kept in shared memory so that
 // it costs the walk loop no registers (the kernel sits at its 64-register limit).
 struct ShadowPlan {
-    unsigned total;              // jobs before padding: this generation's nodes, or all generations'
+    int first_level;             // kAllLevels: the launch covers generations first_level .. max_depth
+    unsigned total;              // jobs before padding: this generation's nodes, or those generations'
     unsigned pass_jobs, passes, group;
 };
 RT_DEV ShadowPlan& shadow_plan()
@@ -473,7 +474,8 @@ struct ShadowJob {
     {
         ShadowPlan& pl = shadow_plan();
         unsigned total = 0;
-        if (kAllLevels) { for (int l = 0; l <= P.max_depth; l++) total += P.counters->nodes[l]; }
+        pl.first_level = kAllLevels ? -level - 1 : level;      // level = -(first generation) - 1
+        if (kAllLevels) { for (int l = pl.first_level; l <= P.max_depth; l++) total += P.counters->nodes[l]; }
         else total = P.counters->nodes[level];
         pl.total = total; pl.passes = 1; pl.group = 1; pl.pass_jobs = total;
         if (kHints && P.hint_passes > 1) {
@@ -525,8 +527,8 @@ struct ShadowJob {
         k = perm(j); li = 0; mask = 1.0f;                                        // 788
         if (kHints && k >= shadow_plan().total) { k = 0xffffffffu; return false; }   // padding of the last groups
         if (kAllLevels) {
-            level = 0;
-            n_nodes = P.counters->nodes[0];
+            level = shadow_plan().first_level;
+            n_nodes = P.counters->nodes[level];
             while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
         }
         const float4 hp = P.level[level].hp[P.level[level].node_list[k]];
@@ -617,7 +619,7 @@ struct ShadowJob {
     }
 };
 
-// level < 0 (kAllLevels): every generation's nodes
+// level < 0 (kAllLevels): the nodes of generations -level - 1 .. max_depth in one launch
 template <bool kCount, bool kNearFirst, bool kStealing, bool kAllLevels = false, bool kHints = false>
 __global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : kHints ? RT_SHADOW_MIN_BLOCKS : 0) * kWalkScale) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
 {
@@ -627,7 +629,7 @@ __global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : kHints ? RT_SHADOW_M
     __syncthreads();
     const unsigned n_jobs = shadow_plan().pass_jobs * shadow_plan().passes;
     Job job{ P, acc, kAllLevels ? 0 : level, kAllLevels ? 0u : shadow_plan().total };
-    const int cl = kAllLevels ? 0 : level;
+    const int cl = kAllLevels ? -level - 1 : level;
     acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[cl], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
                         kCount ? &P.counters->clock[1][cl] : nullptr, P.steal != 0,
                         P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
