@@ -25,6 +25,10 @@
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 6
 #endif
+// closest-hit kernel: blocks per SM it is compiled for (0 = as it comes: 72 registers, 7 blocks)
+#ifndef RT_TRACE_MIN_BLOCKS
+#define RT_TRACE_MIN_BLOCKS 0
+#endif
 // fused trace kernel: blocks per SM it is compiled for (0 = the compiler's choice)
 #ifndef RT_TRACE_ALL_MIN_BLOCKS
 #define RT_TRACE_ALL_MIN_BLOCKS 7
@@ -223,7 +227,7 @@ struct TraceJob {
 };
 
 template <bool kCount, bool kStealing>
-__global__ void __launch_bounds__(kWalkBlock, (kStealing || kWalkScale > 1 ? 7 : 0) * kWalkScale) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kWalkBlock, (RT_TRACE_MIN_BLOCKS && !kCount ? RT_TRACE_MIN_BLOCKS : (kStealing || kWalkScale > 1 ? 7 : 0)) * kWalkScale) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
 {
     const auto acc = make_bvh_accel<kCount>(P.scene);
     const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
