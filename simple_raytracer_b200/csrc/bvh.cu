@@ -429,6 +429,54 @@ __device__ float box_area(float4 lo, float4 hi)
     return dx * dy + dy * dz + dz * dx;
 }
 
+// The 4-wide tree by greedy collapse (instead of "every other level", emit_nodes4_kernel): one
+// thread per 4-wide node of the current level takes its binary node, opens the entry with the
+// largest surface area until it holds four, writes the node at the binary node's own index and
+// queues its inner entries for the next level.  Fuller nodes and fewer levels than the fixed
+// two-level collapse; same node format, so the walk does not change.
+__global__ void collapse4_kernel(int n, unsigned cur_count, const int* __restrict__ queue_cur, int* __restrict__ queue_next,
+                                 unsigned* __restrict__ next_count, const unsigned* __restrict__ sorted_vals,
+                                 const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
+                                 const int2* __restrict__ children, const float4* __restrict__ node_lo,
+                                 const float4* __restrict__ node_hi, float4* __restrict__ nodes)
+{
+    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= cur_count) return;
+    const int root = queue_cur[t];
+    int ent[4];
+    int n_e = 2;
+    { const int2 ch = children[root]; ent[0] = ch.x; ent[1] = ch.y; }
+    while (n_e < 4) {
+        int best = -1; float best_area = -1.0f;
+        for (int k = 0; k < n_e; k++) {
+            if (ent[k] < 0) continue;
+            const float a = box_area(node_lo[ent[k]], node_hi[ent[k]]);
+            if (a > best_area || best < 0) { best_area = a; best = k; }
+        }
+        if (best < 0) break;
+        const int2 ch = children[ent[best]];
+        ent[best] = ch.x; ent[n_e++] = ch.y;
+    }
+    float4 lo[4], hi[4];
+    int code[4];
+    unsigned n_in = 0;
+    for (int k = 0; k < n_e; k++) {
+        if (ent[k] < 0) {
+            const int slot = ~ent[k];
+            const unsigned p = sorted_vals[slot];
+            lo[k] = prim_lo[p]; hi[k] = prim_hi[p]; code[k] = ~(slot << 3);
+        } else {
+            lo[k] = node_lo[ent[k]]; hi[k] = node_hi[ent[k]]; code[k] = ent[k];
+            n_in++;
+        }
+    }
+    if (n_in) {
+        unsigned at = atomicAdd(next_count, n_in);
+        for (int k = 0; k < n_e; k++) if (ent[k] >= 0) queue_next[at++] = ent[k];
+    }
+    write_node4(nodes + (size_t)root * 4, n_e, lo, hi, code, ~(n << 3));
+}
+
 __global__ void collapse8_kernel(int n_prims, int nf, unsigned cur_count, unsigned cur_offset, unsigned next_offset,
                                  const int* __restrict__ queue_cur, int* __restrict__ queue_next,
                                  Collapse8Counters* __restrict__ counters, const unsigned* __restrict__ sorted_vals,
@@ -577,10 +625,32 @@ int build_bvh(SceneHost* s)
         hierarchy_kernel<<<G, B, 0, st>>>(kin, n, children.as<int2>(), range.as<int2>(), par_i.as<int>(), par_l.as<int>());
         refit_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(), par_i.as<int>(),
                                       par_l.as<int>(), node_lo.as<float4>(), node_hi.as<float4>(), arrivals.as<unsigned>());
-        depth_kernel<<<G, B, 0, st>>>(n, par_i.as<int>(), odd.as<unsigned char>());
-        emit_nodes4_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
-                                            range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(),
-                                            odd.as<unsigned char>(), s->bvh_nodes.as<float4>(), leaf_max);
+        static const int greedy4 = tuning_int("RT_BVH4_GREEDY", 1, 0, 1);
+        if (greedy4 && leaf_max == 1) {
+            DevBuf queue_a, queue_b, count;
+            PinnedBuf h_count;
+            if (!queue_a.reserve(N * 4) || !queue_b.reserve(N * 4) || !count.reserve(4) || !h_count.reserve(4)) return RT_E_NOMEM;
+            RT_CUDA(cudaMemsetAsync(queue_a.p, 0, 4, st));                    // level 0: the binary root (node 0)
+            int* qc = queue_a.as<int>(); int* qn = queue_b.as<int>();
+            unsigned cur_count = 1;
+            for (int level = 0; cur_count > 0; level++) {
+                if (level > 96) { set_error("collapse4: tree deeper than 96 levels"); return RT_E_CUDA; }
+                RT_CUDA(cudaMemsetAsync(count.p, 0, 4, st));
+                collapse4_kernel<<<(cur_count + B - 1) / B, B, 0, st>>>(n, cur_count, qc, qn, count.as<unsigned>(), vin,
+                                                                      box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
+                                                                      node_lo.as<float4>(), node_hi.as<float4>(), s->bvh_nodes.as<float4>());
+                RT_CUDA(cudaGetLastError());
+                RT_CUDA(cudaMemcpyAsync(h_count.p, count.p, 4, cudaMemcpyDeviceToHost, st));
+                RT_CUDA(cudaStreamSynchronize(st));
+                cur_count = *static_cast<unsigned*>(h_count.p);
+                std::swap(qc, qn);
+            }
+        } else {
+            depth_kernel<<<G, B, 0, st>>>(n, par_i.as<int>(), odd.as<unsigned char>());
+            emit_nodes4_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
+                                                range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(),
+                                                odd.as<unsigned char>(), s->bvh_nodes.as<float4>(), leaf_max);
+        }
     } else {
         emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), vin, s->bvh_nodes.as<float4>());
     }
