@@ -120,16 +120,20 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(const unsigned
     hist[threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];   // digit-major: a scan gives global offsets
 }
 
-// exclusive scan of `count` values by one block
-__global__ void __launch_bounds__(1024) scan_kernel(unsigned* __restrict__ data, int count)
+// Exclusive scan of the digit-major histogram in two small steps (a single block over all
+// 256 * nblocks counters took 0.12 ms per pass for 1 M keys): one block per digit scans its row
+// of per-block counts in place and leaves the row total; one block then scans the 256 totals.
+// The scatter kernel adds the two.
+__global__ void __launch_bounds__(256) scan_rows_kernel(unsigned* __restrict__ hist, int nblocks, unsigned* __restrict__ totals)
 {
-    __shared__ unsigned warp_sums[32];
+    __shared__ unsigned warp_sums[8];
     __shared__ unsigned carry;
+    unsigned* row = hist + (size_t)blockIdx.x * nblocks;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    for (int base = 0; base < count; base += 1024) {
+    for (int base = 0; base < nblocks; base += 256) {
         const int i = base + threadIdx.x;
-        const unsigned v = i < count ? data[i] : 0u;
+        const unsigned v = i < nblocks ? row[i] : 0u;
         unsigned x = v;
         for (int o = 1; o < 32; o <<= 1) {
             const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
@@ -137,35 +141,45 @@ __global__ void __launch_bounds__(1024) scan_kernel(unsigned* __restrict__ data,
         }
         if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = x;
         __syncthreads();
-        if (threadIdx.x < 32) {
-            unsigned s = warp_sums[threadIdx.x];
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned y = __shfl_up_sync(0xffffffffu, s, o);
-                if (threadIdx.x >= o) s += y;
-            }
-            warp_sums[threadIdx.x] = s;
-        }
-        __syncthreads();
-        const unsigned before = (threadIdx.x >> 5) ? warp_sums[(threadIdx.x >> 5) - 1] : 0u;
+        unsigned before = 0;
+        for (int w = 0; w < (int)(threadIdx.x >> 5); w++) before += warp_sums[w];
         const unsigned c = carry;
-        if (i < count) data[i] = c + before + x - v;
+        if (i < nblocks) row[i] = c + before + x - v;
         __syncthreads();
-        if (threadIdx.x == 1023) carry = c + before + x;
+        if (threadIdx.x == 255) carry = c + before + x;
         __syncthreads();
     }
+    if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+}
+
+__global__ void __launch_bounds__(256) scan_totals_kernel(unsigned* __restrict__ totals)
+{
+    __shared__ unsigned warp_sums[8];
+    const unsigned v = totals[threadIdx.x];
+    unsigned x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned y = __shfl_up_sync(0xffffffffu, x, o);
+        if ((threadIdx.x & 31) >= o) x += y;
+    }
+    if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = x;
+    __syncthreads();
+    unsigned before = 0;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) before += warp_sums[w];
+    totals[threadIdx.x] = before + x - v;
 }
 
 // stable scatter: ranks inside a block come from warp match + per-warp digit counts
 __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(const unsigned* __restrict__ keys_in,
                                                                      const unsigned* __restrict__ vals_in, int n, int shift,
-                                                                     const unsigned* __restrict__ offsets, int nblocks,
+                                                                     const unsigned* __restrict__ offsets,
+                                                                     const unsigned* __restrict__ digit_offsets, int nblocks,
                                                                      unsigned* __restrict__ keys_out, unsigned* __restrict__ vals_out)
 {
     constexpr int kWarps = kSortThreads / 32;
     __shared__ unsigned digit_base[256];
     __shared__ unsigned warp_cnt[kWarps][256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    digit_base[threadIdx.x] = offsets[threadIdx.x * nblocks + blockIdx.x];
+    digit_base[threadIdx.x] = offsets[threadIdx.x * nblocks + blockIdx.x] + digit_offsets[threadIdx.x];
     for (int w = 0; w < kWarps; w++) warp_cnt[w][threadIdx.x] = 0;
     __syncthreads();
     const int base = blockIdx.x * kSortTile;
@@ -421,7 +435,6 @@ __global__ void emit_prims_kernel(int n, int nf, const unsigned* __restrict__ so
 // holds 8 entries (or only primitives), reserves CONSECUTIVE slots for its inner entries in
 // the next level's queue and for its primitives in the node-ordered primitive table (one
 // atomicAdd each), so that a child is found by base + rank and no per-child index is stored.
-struct Collapse8Counters { unsigned next_count, prim_count; };
 
 __device__ float box_area(float4 lo, float4 hi)
 {
@@ -434,15 +447,19 @@ __device__ float box_area(float4 lo, float4 hi)
 // largest surface area until it holds four, writes the node at the binary node's own index and
 // queues its inner entries for the next level.  Fuller nodes and fewer levels than the fixed
 // two-level collapse; same node format, so the walk does not change.
-__global__ void collapse4_kernel(int n, unsigned cur_count, const int* __restrict__ queue_cur, int* __restrict__ queue_next,
-                                 unsigned* __restrict__ next_count, const unsigned* __restrict__ sorted_vals,
+// counts[l] = nodes of level l (level 0: the binary root, not stored): the host launches a fixed
+// number of levels back to back without reading anything back.
+constexpr int kCollapseLevels = 128;     // entries of the level-count arrays
+__global__ void collapse4_kernel(int n, int level, unsigned* __restrict__ counts, const int* __restrict__ queue_cur,
+                                 int* __restrict__ queue_next, const unsigned* __restrict__ sorted_vals,
                                  const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
                                  const int2* __restrict__ children, const float4* __restrict__ node_lo,
                                  const float4* __restrict__ node_hi, float4* __restrict__ nodes)
 {
-    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= cur_count) return;
-    const int root = queue_cur[t];
+    const unsigned cur_count = level == 0 ? 1u : counts[level];
+    unsigned* const next_count = counts + level + 1;
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < cur_count; t += gridDim.x * blockDim.x) {
+    const int root = level == 0 ? 0 : queue_cur[t];
     int ent[4];
     int n_e = 2;
     { const int2 ch = children[root]; ent[0] = ch.x; ent[1] = ch.y; }
@@ -475,19 +492,24 @@ __global__ void collapse4_kernel(int n, unsigned cur_count, const int* __restric
         for (int k = 0; k < n_e; k++) if (ent[k] >= 0) queue_next[at++] = ent[k];
     }
     write_node4(nodes + (size_t)root * 4, n_e, lo, hi, code, ~(n << 3));
+    }
 }
 
-__global__ void collapse8_kernel(int n_prims, int nf, unsigned cur_count, unsigned cur_offset, unsigned next_offset,
+// (level counts on the device as in collapse4_kernel; level l's nodes start at the sum of the earlier counts)
+__global__ void collapse8_kernel(int n_prims, int nf, int level, unsigned* __restrict__ counts, unsigned* __restrict__ prim_count,
                                  const int* __restrict__ queue_cur, int* __restrict__ queue_next,
-                                 Collapse8Counters* __restrict__ counters, const unsigned* __restrict__ sorted_vals,
+                                 const unsigned* __restrict__ sorted_vals,
                                  const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
                                  const int2* __restrict__ children, const float4* __restrict__ node_lo,
                                  const float4* __restrict__ node_hi, const float4* __restrict__ tri,
                                  const float4* __restrict__ sph, uint4* __restrict__ nodes8, float4* __restrict__ prims8)
 {
-    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= cur_count) return;
-    const int root = queue_cur[t];
+    const unsigned cur_count = level == 0 ? 1u : counts[level];
+    unsigned cur_offset = 0;
+    for (int l = 0; l < level; l++) cur_offset += l == 0 ? 1u : counts[l];
+    const unsigned next_offset = cur_offset + cur_count;
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < cur_count; t += gridDim.x * blockDim.x) {
+    const int root = level == 0 ? 0 : queue_cur[t];
     int ent[8];
     int n_e = 2;
     { const int2 ch = children[root]; ent[0] = ch.x; ent[1] = ch.y; }
@@ -520,8 +542,8 @@ __global__ void collapse8_kernel(int n_prims, int nf, unsigned cur_count, unsign
         for (int c = 0; c < 3; c++) { nlo[c] = fminf(nlo[c], l[c]); nhi[c] = fmaxf(nhi[c], h[c]); }
     }
     const unsigned n_in = (unsigned)__popc(imask), n_leaf = (unsigned)__popc(lmask);
-    const unsigned child_base = next_offset + (n_in ? atomicAdd(&counters->next_count, n_in) : 0u);
-    const unsigned prim_base = n_leaf ? atomicAdd(&counters->prim_count, n_leaf) : 0u;
+    const unsigned child_base = next_offset + (n_in ? atomicAdd(counts + level + 1, n_in) : 0u);
+    const unsigned prim_base = n_leaf ? atomicAdd(prim_count, n_leaf) : 0u;
     // the frame: as write_node4
     float origin[3], q[3];
     unsigned eb[3];
@@ -578,6 +600,7 @@ __global__ void collapse8_kernel(int n_prims, int nf, unsigned cur_count, unsign
     w[3] = make_uint4(planes[1][0], planes[1][1], planes[1][2], planes[1][3]);
     w[4] = make_uint4(planes[2][0], planes[2][1], planes[2][2], planes[2][3]);
     w[5] = make_uint4(0u, 0u, 0u, 0u);
+    }
     (void)n_prims;
 }
 
@@ -603,7 +626,7 @@ int build_bvh(SceneHost* s)
     DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals, odd;
     const size_t N = (size_t)n;
     if (!box_lo.reserve(N * 16) || !box_hi.reserve(N * 16) || !keys_a.reserve(N * 4) || !keys_b.reserve(N * 4) ||
-        !vals_a.reserve(N * 4) || !vals_b.reserve(N * 4) || !hist.reserve((size_t)256 * nblocks * 4) ||
+        !vals_a.reserve(N * 4) || !vals_b.reserve(N * 4) || !hist.reserve((size_t)256 * (nblocks + 1) * 4) ||
         !children.reserve(N * 8) || !range.reserve(N * 8) || !par_i.reserve(N * 4) || !par_l.reserve(N * 4) ||
         !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4) || !odd.reserve(N))
         return RT_E_NOMEM;
@@ -615,8 +638,10 @@ int build_bvh(SceneHost* s)
     unsigned *kin = keys_a.as<unsigned>(), *kout = keys_b.as<unsigned>(), *vin = vals_a.as<unsigned>(), *vout = vals_b.as<unsigned>();
     for (int shift = 0; shift < 32; shift += 8) {
         radix_hist_kernel<<<nblocks, kSortThreads, 0, st>>>(kin, n, shift, hist.as<unsigned>(), nblocks);
-        scan_kernel<<<1, 1024, 0, st>>>(hist.as<unsigned>(), 256 * nblocks);
-        radix_scatter_kernel<<<nblocks, kSortThreads, 0, st>>>(kin, vin, n, shift, hist.as<unsigned>(), nblocks, kout, vout);
+        scan_rows_kernel<<<256, 256, 0, st>>>(hist.as<unsigned>(), nblocks, hist.as<unsigned>() + (size_t)256 * nblocks);
+        scan_totals_kernel<<<1, 256, 0, st>>>(hist.as<unsigned>() + (size_t)256 * nblocks);
+        radix_scatter_kernel<<<nblocks, kSortThreads, 0, st>>>(kin, vin, n, shift, hist.as<unsigned>(),
+                                                               hist.as<unsigned>() + (size_t)256 * nblocks, nblocks, kout, vout);
         std::swap(kin, kout); std::swap(vin, vout);
     }
     // 4 passes: the sorted data is back in keys_a / vals_a
@@ -627,23 +652,27 @@ int build_bvh(SceneHost* s)
                                       par_l.as<int>(), node_lo.as<float4>(), node_hi.as<float4>(), arrivals.as<unsigned>());
         static const int greedy4 = tuning_int("RT_BVH4_GREEDY", 1, 0, 1);
         if (greedy4 && leaf_max == 1) {
-            DevBuf queue_a, queue_b, count;
-            PinnedBuf h_count;
-            if (!queue_a.reserve(N * 4) || !queue_b.reserve(N * 4) || !count.reserve(4) || !h_count.reserve(4)) return RT_E_NOMEM;
-            RT_CUDA(cudaMemsetAsync(queue_a.p, 0, 4, st));                    // level 0: the binary root (node 0)
+            DevBuf queue_a, queue_b, counts;
+            PinnedBuf h_counts;
+            const size_t cbytes = (size_t)kCollapseLevels * sizeof(unsigned);
+            if (!queue_a.reserve(N * 4) || !queue_b.reserve(N * 4) || !counts.reserve(cbytes) || !h_counts.reserve(cbytes)) return RT_E_NOMEM;
+            RT_CUDA(cudaMemsetAsync(counts.p, 0, cbytes, st));
             int* qc = queue_a.as<int>(); int* qn = queue_b.as<int>();
-            unsigned cur_count = 1;
-            for (int level = 0; cur_count > 0; level++) {
-                if (level > 96) { set_error("collapse4: tree deeper than 96 levels"); return RT_E_CUDA; }
-                RT_CUDA(cudaMemsetAsync(count.p, 0, 4, st));
-                collapse4_kernel<<<(cur_count + B - 1) / B, B, 0, st>>>(n, cur_count, qc, qn, count.as<unsigned>(), vin,
-                                                                      box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
-                                                                      node_lo.as<float4>(), node_hi.as<float4>(), s->bvh_nodes.as<float4>());
+            const int cgrid = std::min((n + B - 1) / B, 148 * 8);
+            const unsigned* hc = static_cast<const unsigned*>(h_counts.p);
+            // a batch of levels without a word from the device, then a look at where it stands
+            for (int level = 0, batch = 24;; batch = 8) {
+                for (int k = 0; k < batch && level < kCollapseLevels - 1; k++, level++) {
+                    collapse4_kernel<<<cgrid, B, 0, st>>>(n, level, counts.as<unsigned>(), qc, qn, vin, box_lo.as<float4>(),
+                                                         box_hi.as<float4>(), children.as<int2>(), node_lo.as<float4>(),
+                                                         node_hi.as<float4>(), s->bvh_nodes.as<float4>());
+                    std::swap(qc, qn);
+                }
                 RT_CUDA(cudaGetLastError());
-                RT_CUDA(cudaMemcpyAsync(h_count.p, count.p, 4, cudaMemcpyDeviceToHost, st));
+                RT_CUDA(cudaMemcpyAsync(h_counts.p, counts.p, cbytes, cudaMemcpyDeviceToHost, st));
                 RT_CUDA(cudaStreamSynchronize(st));
-                cur_count = *static_cast<unsigned*>(h_count.p);
-                std::swap(qc, qn);
+                if (hc[level] == 0) break;
+                if (level >= kCollapseLevels - 1) { set_error("collapse4: tree deeper than 127 levels"); return RT_E_CUDA; }
             }
         } else {
             depth_kernel<<<G, B, 0, st>>>(n, par_i.as<int>(), odd.as<unsigned char>());
@@ -660,36 +689,35 @@ int build_bvh(SceneHost* s)
     s->bvh8_n_nodes = 0;
     static const int use8 = tuning_int("RT_BVH8", 1, 0, 1);
     if (use8 && n > 8) {
-        DevBuf queue_a, queue_b, counters;
-        PinnedBuf h_count;
-        if (!queue_a.reserve(N * 4) || !queue_b.reserve(N * 4) || !counters.reserve(sizeof(Collapse8Counters)) ||
-            !h_count.reserve(sizeof(Collapse8Counters)) ||
+        DevBuf queue_a, queue_b, counts;
+        PinnedBuf h_counts;
+        const size_t cbytes = (size_t)(kCollapseLevels + 1) * sizeof(unsigned);      // [kCollapseLevels] = primitives placed
+        if (!queue_a.reserve(N * 4) || !queue_b.reserve(N * 4) || !counts.reserve(cbytes) || !h_counts.reserve(cbytes) ||
             !s->bvh8_nodes.reserve((size_t)n_internal * 96) || !s->bvh8_prims.reserve((N + 1) * kTriWords * 16))
             return RT_E_NOMEM;
-        RT_CUDA(cudaMemsetAsync(counters.p, 0, sizeof(Collapse8Counters), st));
-        RT_CUDA(cudaMemsetAsync(queue_a.p, 0, 4, st));                    // level 0: the binary root (node 0)
+        RT_CUDA(cudaMemsetAsync(counts.p, 0, cbytes, st));
         int* qc = queue_a.as<int>(); int* qn = queue_b.as<int>();
-        unsigned cur_count = 1, cur_offset = 0;
-        Collapse8Counters* hc = static_cast<Collapse8Counters*>(h_count.p);
-        for (int level = 0; cur_count > 0; level++) {
-            if (level > 64) { set_error("collapse8: tree deeper than 64 levels"); return RT_E_CUDA; }
-            const unsigned next_offset = cur_offset + cur_count;
-            collapse8_kernel<<<(cur_count + B - 1) / B, B, 0, st>>>(n, s->nf, cur_count, cur_offset, next_offset, qc, qn,
-                                                                  counters.as<Collapse8Counters>(), vin, box_lo.as<float4>(),
-                                                                  box_hi.as<float4>(), children.as<int2>(), node_lo.as<float4>(),
-                                                                  node_hi.as<float4>(), s->tri.as<float4>(), s->sph.as<float4>(),
-                                                                  s->bvh8_nodes.as<uint4>(), s->bvh8_prims.as<float4>());
+        const int cgrid = std::min((n + B - 1) / B, 148 * 8);
+        const unsigned* hc = static_cast<const unsigned*>(h_counts.p);
+        int level = 0;
+        for (int batch = 16;; batch = 8) {
+            for (int k = 0; k < batch && level < kCollapseLevels - 1; k++, level++) {
+                collapse8_kernel<<<cgrid, B, 0, st>>>(n, s->nf, level, counts.as<unsigned>(), counts.as<unsigned>() + kCollapseLevels,
+                                                     qc, qn, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
+                                                     node_lo.as<float4>(), node_hi.as<float4>(), s->tri.as<float4>(),
+                                                     s->sph.as<float4>(), s->bvh8_nodes.as<uint4>(), s->bvh8_prims.as<float4>());
+                std::swap(qc, qn);
+            }
             RT_CUDA(cudaGetLastError());
-            RT_CUDA(cudaMemcpyAsync(hc, counters.p, sizeof(Collapse8Counters), cudaMemcpyDeviceToHost, st));
+            RT_CUDA(cudaMemcpyAsync(h_counts.p, counts.p, cbytes, cudaMemcpyDeviceToHost, st));
             RT_CUDA(cudaStreamSynchronize(st));
-            const unsigned next_count = hc->next_count;
-            // next level: its queue counter starts at zero again (the primitive counter runs on)
-            RT_CUDA(cudaMemsetAsync(counters.p, 0, sizeof(unsigned), st));
-            std::swap(qc, qn);
-            cur_offset = next_offset; cur_count = next_count;
+            if (hc[level] == 0) break;
+            if (level >= kCollapseLevels - 1) { set_error("collapse8: tree deeper than 127 levels"); return RT_E_CUDA; }
         }
-        if (hc->prim_count != (unsigned)n) { set_error("collapse8: primitive count mismatch"); return RT_E_CUDA; }
-        s->bvh8_n_nodes = (int)cur_offset;
+        if (hc[kCollapseLevels] != (unsigned)n) { set_error("collapse8: primitive count mismatch"); return RT_E_CUDA; }
+        unsigned total = 1;
+        for (int l = 1; l < level; l++) total += hc[l];
+        s->bvh8_n_nodes = (int)total;
     }
     RT_CUDA(cudaStreamSynchronize(st));
     s->bvh_n_nodes = n_internal; s->bvh_root = 0; s->bvh_built = true;
