@@ -291,8 +291,12 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
 
     static const int refill = tuning_int("RT_REFILL_LANES", 6, 1, 32);
     static const int grid_mult = tuning_int("RT_GRID_MULT", 16, 1, 64);
-    static const int inner_min = tuning_int("RT_INNER_MIN_LANES", 4, 1, 32);
-    static const int leaf_min = tuning_int("RT_LEAF_MIN_LANES", 1, 1, 32);
+    static const int inner_min = tuning_int("RT_INNER_MIN_LANES", 8, 1, 32);
+    static const int leaf_min = tuning_int("RT_LEAF_MIN_LANES", 8, 1, 32);
+    // ... of the any-hit kernel (0 = as the closest-hit kernel)
+    static const int sh_refill = tuning_int("RT_SHADOW_REFILL_LANES", 0, 0, 32);
+    static const int sh_inner_min = tuning_int("RT_SHADOW_INNER_MIN_LANES", 6, 0, 32);
+    static const int sh_leaf_min = tuning_int("RT_SHADOW_LEAF_MIN_LANES", 6, 0, 32);
     static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
     // Work sharing in the walk kernels' tails.  0: never, 1: always, 2: for launches of at most
     // RT_STEAL_MAX_KRAYS thousand queue slots.  Measured on the 4K stress frame (tools/steal_sweep.sh):
@@ -346,6 +350,9 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         P.n_local_rows = vl.n_local_rows; P.n_local_pixels = vl.n_local_pixels;
         P.out_mul = K; P.out_add = j; P.out_tiles = tl.n_local_tiles;
         P.refill_lanes = refill; P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
+        P.sh_refill_lanes = sh_refill ? sh_refill : refill;
+        P.sh_inner_min_lanes = sh_inner_min ? sh_inner_min : inner_min;
+        P.sh_leaf_min_lanes = sh_leaf_min ? sh_leaf_min : leaf_min;
         P.steal = 1;
         P.shadow_job_budget = overlap ? shadow_budget : 0;
         P.occluder_hint = hints ? s->ws.hints.as<int>() : nullptr;

@@ -174,6 +174,7 @@ struct FrameParams {
     int refill_lanes;     // persistent kernels: fetch new rays when this many lanes of a warp are idle
     int inner_min_lanes;  // ... leave the inner-node loop when fewer lanes than this can still descend
     int leaf_min_lanes;   // ... leave the leaf loop when fewer lanes than this hold a leaf
+    int sh_refill_lanes, sh_inner_min_lanes, sh_leaf_min_lanes;   // the same three for the any-hit kernel
     int shadow_job_budget; // ... any-hit kernel: jobs a warp takes before it stops fetching (0 = no limit)
     int steal;            // ... idle lanes take subtrees from busy ones once the queue is dry (closest-hit walks)
     // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob): hint[li * n_prims + order of the

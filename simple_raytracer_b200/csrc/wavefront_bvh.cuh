@@ -634,7 +634,7 @@ __global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : kHints ? RT_SHADOW_M
     const unsigned n_jobs = shadow_plan().pass_jobs * shadow_plan().passes;
     Job job{ P, acc, kAllLevels ? 0 : level, kAllLevels ? 0u : shadow_plan().total };
     const int cl = kAllLevels ? -level - 1 : level;
-    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[cl], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
+    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[cl], job, P.sh_refill_lanes, P.sh_inner_min_lanes, P.sh_leaf_min_lanes,
                         kCount ? &P.counters->clock[1][cl] : nullptr, P.steal != 0,
                         P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
     flush_bvh_counters(acc, P.counters, true);
