@@ -322,7 +322,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     static const int hint_passes = tuning_int("RT_HINT_PASSES", 16, 1, 256);
     static const int hint_group = tuning_int("RT_HINT_GROUP", 32, 1, 4096);
     static const int hint_min_chunk = 1024 * tuning_int("RT_HINT_MIN_CHUNK_K", 256, 1, 1 << 20);
-    static const int hint_mode = tuning_int("RT_HINT_MODE", 7, 0, 7);
+    static const int hint_mode = tuning_int("RT_HINT_MODE", 3, 0, 3);
     static const int hint_keep = tuning_int("RT_HINT_KEEP", 0, 0, 1);      // experiments only: hints survive the frame
     const bool hints = lbvh && s->nl > 0 && (p.occluder_hints == 1 || (p.occluder_hints == 0 && hint_env));
 

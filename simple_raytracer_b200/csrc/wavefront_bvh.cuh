@@ -324,7 +324,7 @@ struct TraceAllJob : TraceJob<kCount, false> {
             unsigned base = 0;
             if (lane0) base = atomicAdd(&q->hit_tail, (unsigned)__popc(pm));
             base = __shfl_sync(kFull, base, 0);
-            if (P.hint_mode & 4) __threadfence();                   // the hit records before the entries that announce them
+            __threadfence();                   // the hit records before the entries that announce them
             if (parent) st_volatile(P.hit_order + base + __popc(pm & lt), ((unsigned)level << 28) | slot);
         }
         const unsigned fm = __ballot_sync(kFull, fin && !parent);
