@@ -20,10 +20,11 @@
 #include "bvh.cuh"
 #include "wavefront.cuh"
 
-// colour / spawn kernels: 6 blocks per SM (<= 80 registers) instead of the 5 the compiler picks
-// on its own (96): they are latency-bound gathers, the extra warps pay for the two spills
+// colour / spawn kernels: 8 blocks per SM (64 registers, a few spills) instead of the 5 the compiler
+// picks on its own (96): they are latency-bound gathers and the extra warps pay for the spills
+// (measured A/B, 15 frames each, twice: 4K frame 37.81 -> 37.44 ms; 6 blocks: 37.8)
 #ifndef RT_SHADE_MIN_BLOCKS
-#define RT_SHADE_MIN_BLOCKS 6
+#define RT_SHADE_MIN_BLOCKS 8
 #endif
 // closest-hit kernel: blocks per SM it is compiled for (0 = as it comes: 72 registers, 7 blocks)
 #ifndef RT_TRACE_MIN_BLOCKS
