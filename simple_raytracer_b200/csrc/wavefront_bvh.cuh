@@ -660,9 +660,9 @@ struct RecordedShadow {
 
 // kColour / kSpawn select the half of ShadeRay this launch does (wavefront.cuh:
 // shade_and_spawn).  The spawn half depends only on the hits, so the next generation's trace
-// kernel can start while this generation's shadow rays are still being walked: the frame
-// scheduler (render.cu) runs trace -> spawn -> trace -> ... on one stream and shadow -> colour
-// on a second one, which fills the tail of every persistent launch with the other chain's work.
+// kernel can start before this generation's shadow rays have been walked: the frame scheduler
+// (render.cu) runs the chain trace -> spawn -> trace -> ... first and all generations' shadow
+// chains in one any-hit launch after it, then the colour halves.
 template <bool kColour, bool kSpawn>
 __global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
 {
