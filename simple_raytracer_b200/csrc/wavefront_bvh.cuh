@@ -664,7 +664,7 @@ struct RecordedShadow {
 // (render.cu) runs the chain trace -> spawn -> trace -> ... first and all generations' shadow
 // chains in one any-hit launch after it, then the colour halves.
 template <bool kColour, bool kSpawn>
-__global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
+RT_DEV void shade_level(const FrameParams& P, int level)
 {
     const LevelBuffers& LB = P.level[level];
     const unsigned n_nodes = P.counters->nodes[level];
@@ -688,6 +688,18 @@ __global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_shade_kernel(
             const NoShadow none;
             shade_and_spawn<kColour, kSpawn>(P, none, level, slot, r, h, hit);
         }
+    }
+}
+
+// kRange: generations -level - 1 .. max_depth one after the other in this launch (the colour halves
+// after the merged any-hit launch: nothing orders them among themselves)
+template <bool kColour, bool kSpawn, bool kRange = false>
+__global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
+{
+    if constexpr (kRange) {
+        for (int l = -level - 1; l <= P.max_depth; l++) shade_level<kColour, kSpawn>(P, l);
+    } else {
+        shade_level<kColour, kSpawn>(P, level);
     }
 }
 
