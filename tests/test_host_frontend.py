@@ -327,3 +327,29 @@ def test_render_without_gpu_fails_loudly():
     with pytest.raises(abi.RtError) as e:
         DeviceScene(scenegen.coverage_scene(16, 12))
     assert e.value.code == abi.RT_E_CUDA and "no CPU fallback" in e.value.message
+
+
+def test_ctypes_mirror_has_the_sizes_the_c_compiler_sees(tmp_path):
+    """sizeof / offsetof of the ABI structs as gcc lays them out from include/rt.h against the
+    ctypes mirror (a mismatch in RtStats would let rt_render write past the Python object)."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    root = os.path.dirname(common.HERE)
+    src = tmp_path / "sizes.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "rt.h"\n'
+        "int main(void) {\n"
+        '  printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(RtRenderParams), sizeof(RtStats), sizeof(RtSceneDesc),\n'
+        "         sizeof(RtMaterial), sizeof(RtFace), offsetof(RtStats, shadow_hint_hits), offsetof(RtRenderParams, fused_trace),\n"
+        "         offsetof(RtStats, shadow_rays_walked));\n"
+        "  return 0; }\n")
+    exe = tmp_path / "sizes"
+    subprocess.run([cc, "-std=c11", "-I", os.path.join(root, "include"), "-o", str(exe), str(src)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    want = [C.sizeof(abi.RtRenderParams), C.sizeof(abi.RtStats), C.sizeof(abi.RtSceneDesc), C.sizeof(abi.RtMaterial),
+            C.sizeof(abi.RtFace), abi.RtStats.shadow_hint_hits.offset, abi.RtRenderParams.fused_trace.offset,
+            abi.RtStats.shadow_rays_walked.offset]
+    assert got == want
