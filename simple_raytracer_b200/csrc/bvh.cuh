@@ -33,41 +33,19 @@
 
 namespace rt {
 
-// How the walks read primitive records (80 B, random, little reuse): 0 = like everything else,
-// 1 = ld.global.nc.L1::no_allocate, 2 = ld.global.nc.L1::evict_first, so that they do not push
-// the upper tree out of L1.
-#ifndef RT_PRIM_LOAD
-#define RT_PRIM_LOAD 0
-#endif
-RT_DEV float4 ldp(const float4* p)
-{
-#if RT_PRIM_LOAD == 1
-    float4 v;
-    asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-#elif RT_PRIM_LOAD == 2
-    float4 v;
-    asm("ld.global.nc.L1::evict_first.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-#else
-    return *p;
-#endif
-}
+RT_DEV float4 ldp(const float4* p) { return *p; }
 
 // shared-memory part of the persistent walk's stack (entries per thread)
-#ifndef RT_SMEM_STACK
-#define RT_SMEM_STACK 24
-#endif
 constexpr int kBvhStack = 96;     // local-memory part of the traversal stack (entries)
-constexpr int kSmemStack = RT_SMEM_STACK;
-// Block size of the persistent walk kernels.  A block's registers stay taken until its LAST warp
-// has finished, so in a launch's tail smaller blocks hand their SM share to the other launch
-// chain's blocks sooner.
-#ifndef RT_WALK_BLOCK
-#define RT_WALK_BLOCK 128
-#endif
-constexpr int kWalkBlock = RT_WALK_BLOCK;
-constexpr int kWalkScale = 128 / kWalkBlock;   // blocks per SM are quoted for 128-thread blocks
+constexpr int kSmemStack = 24;    // shared-memory part (16 / 32 measured the same or slower)
+// A walk never needs more than kStackNeed4(levels) / kStackNeed8(levels) entries on a tree of that many
+// levels (an ordered 4-wide step leaves at most 3 entries behind per level; an 8-wide step the rest of
+// the group it came from and the group of its inner children, plus at most 8 primitives on top):
+// build_bvh refuses trees that could overflow the stacks, the walks raise kOverflowStack should it
+// happen all the same.
+constexpr int kStackNeed4(int levels) { return 3 * levels + 2; }
+constexpr int kStackNeed8(int levels) { return 2 * levels + 10; }
+constexpr int kWalkBlock = 128;   // block size of the persistent walk kernels (64 / 32 measured slower)
 constexpr int kLeafMax = 4;       // scenes of <= kLeafMax primitives are a single node
 constexpr int kLeafDefault = 1;   // primitives per leaf otherwise: with one triangle per leaf the parent's box test
                                   // rejects most of the 80-byte exact tests (measured: 32 -> 6.4 tests per ray)
@@ -91,6 +69,7 @@ struct BvhAccelT {
     int root;              // node index; n_nodes == 0 means empty scene
     int n_nodes;
     bool count_all = false;   // shadow(): keep counting hits after an opaque occluder (parity probes)
+    unsigned* overflow_flag = nullptr;   // Counters::overflow of the frame (null: probes), see kOverflow*
     // instrumented variant only (kCount): nodes visited / primitives tested by this thread
     mutable unsigned long long cnt_boxes = 0, cnt_prims = 0;
 
@@ -119,24 +98,13 @@ struct BvhAccelT {
     }
 
     // Box test of the four children of one node.  t[k] = entry distance, mask bit k = hit.
-    template <bool kWide = false>
     RT_DEV void test_node(const float4* __restrict__ nd, int node, const RayQ& r, float tmin, float tmax,
                           float t[4], int code[4], unsigned& mask) const
     {
-        // kWide: the 64-byte node as two 256-bit loads (sm_100: LDG.E.256), half the L1 requests
-        // of four 128-bit ones — L1 request throughput is what bounds the walk.  The 8-register
-        // alignment they need costs the closest-hit kernel more than they save (it sits at its
-        // register limit), the any-hit kernel gains 5 %.
+        // (as two 256-bit loads the node costs half the L1 requests, but the 8-register alignment costs
+        // this kernel, which sits at its register limit, more than that saves: measured)
         const uint4* w = reinterpret_cast<const uint4*>(nd) + (size_t)node * 4;
-        uint4 h, c, b01, b23;
-        if (kWide) {
-            asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                : "=r"(h.x), "=r"(h.y), "=r"(h.z), "=r"(h.w), "=r"(c.x), "=r"(c.y), "=r"(c.z), "=r"(c.w) : "l"(w));
-            asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                : "=r"(b01.x), "=r"(b01.y), "=r"(b01.z), "=r"(b01.w), "=r"(b23.x), "=r"(b23.y), "=r"(b23.z), "=r"(b23.w) : "l"(w + 2));
-        } else {
-            h = __ldg(w); c = __ldg(w + 1); b01 = __ldg(w + 2); b23 = __ldg(w + 3);
-        }
+        const uint4 h = __ldg(w), c = __ldg(w + 1), b01 = __ldg(w + 2), b23 = __ldg(w + 3);
         if (kCount) cnt_boxes += 1;
         // plane distance = (origin + q * 2^e - o) * inv = (2^23 + q) * s + c,
         //   s = 2^e * inv,  c = (origin - o) * inv - 2^23 * s
@@ -165,42 +133,101 @@ struct BvhAccelT {
         }
     }
 
-    // One traversal step at inner node `node`: tests its children, pushes all hit children but
-    // the one to visit next and returns that one (a node index, a leaf code, or pop()'s result
-    // when nothing was hit).  kOrdered: nearest child next, the others pushed far-to-near.
-    template <bool kOrdered, bool kWide = false, class Push, class Pop>
-    RT_DEV int step(const float4* __restrict__ nd, int node, const RayQ& r, float tmin, float tmax, Push& push, Pop& pop) const
-    {
-        float t[4]; int code[4]; unsigned mask;
-        test_node<kWide>(nd, node, r, tmin, tmax, t, code, mask);
-        if (mask == 0) return pop();
-        if (kOrdered) {
-            #pragma unroll
-            for (int k = 0; k < 4; k++) if (!((mask >> k) & 1u)) t[k] = 3.402823466e+38f;
-            // sorting network on 4 (t, code) pairs, ascending
-            auto cswap = [&](int i, int j) {
-                const bool sw = t[j] < t[i];
-                const float ti = sw ? t[j] : t[i], tj = sw ? t[i] : t[j];
-                const int ci = sw ? code[j] : code[i], cj = sw ? code[i] : code[j];
-                t[i] = ti; t[j] = tj; code[i] = ci; code[j] = cj;
-            };
-            cswap(0, 1); cswap(2, 3); cswap(0, 2); cswap(1, 3); cswap(1, 2);
-            const int n = __popc(mask);
-            if (n > 3) push(code[3]);
-            if (n > 2) push(code[2]);
-            if (n > 1) push(code[1]);
-            return code[0];
+    // ---- traversal stacks ---------------------------------------------------------------------
+    // pop() -> kWalkDone when empty; push(v); push_sorted(n, c1, c2, c3): the 2nd .. 4th nearest of
+    // n hit children, farthest first, so that c1 ends on top.  An entry that does not fit raises
+    // kOverflowStack (the frame is then reported as failed, never silently wrong).
+    struct LocalStack {
+        int e[kBvhStack];
+        int sp = 0;
+        unsigned* flag;
+        RT_DEV int pop() { return sp ? e[--sp] : kWalkDone; }
+        RT_DEV void push(int v)
+        {
+            if (sp < kBvhStack) e[sp++] = v;
+            else if (flag) atomicOr(flag, kOverflowStack);
         }
-        int next = kWalkDone;
-        #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            if ((mask >> k) & 1u) {
-                if (next == kWalkDone) next = code[k]; else push(code[k]);
+        RT_DEV void push_sorted(int n, int c1, int c2, int c3)
+        {
+            if (n > 3) push(c3);
+            if (n > 2) push(c2);
+            if (n > 1) push(c1);
+        }
+    };
+
+    // The persistent walk's stack: the first kSmemStack entries live in shared memory, laid out
+    // [entry][thread] so that a warp's pushes and pops never conflict whatever the lanes' depths are
+    // (a local-memory stack costs one L1 wavefront per distinct depth, and L1 is what binds the
+    // loop); deeper entries overflow into local memory.  bot: entries below it were given to
+    // helper lanes (work sharing).
+    struct SharedStack {
+        int* col;                // &s_stack[0][threadIdx.x]
+        int* deep;               // local-memory part
+        int sp, bot;
+        unsigned* flag;
+        RT_DEV int pop()
+        {
+            if (sp == bot) return kWalkDone;
+            --sp;
+            return sp < kSmemStack ? col[sp * kWalkBlock] : deep[sp - kSmemStack];
+        }
+        RT_DEV void push(int v)
+        {
+            if (sp < kSmemStack) col[sp * kWalkBlock] = v;
+            else if (sp < kSmemStack + kBvhStack) deep[sp - kSmemStack] = v;
+            else { if (flag) atomicOr(flag, kOverflowStack); return; }
+            sp++;
+        }
+        RT_DEV void push_sorted(int n, int c1, int c2, int c3)
+        {
+            if (sp + 3 <= kSmemStack) {
+                // the common case without a branch per entry: predicated stores at fixed offsets
+                // below the new top
+                int* top = col + (sp + n - 1) * kWalkBlock;
+                if (n > 1) top[-1 * kWalkBlock] = c1;
+                if (n > 2) top[-2 * kWalkBlock] = c2;
+                if (n > 3) top[-3 * kWalkBlock] = c3;
+                sp += max(n, 1) - 1;
+            } else {
+                if (n > 3) push(c3);
+                if (n > 2) push(c2);
+                if (n > 1) push(c1);
             }
         }
-        return next;
+    };
+
+    RT_DEV static int select4(int c0, int c1, int c2, int c3, unsigned idx)
+    {
+        const int lo = (idx & 1u) ? c1 : c0, hi = (idx & 1u) ? c3 : c2;
+        return (idx & 2u) ? hi : lo;
     }
 
+    // One traversal step at inner node `node`: tests its four children, leaves all hit children
+    // but the nearest on the stack (far to near) and returns the nearest (a node index, a leaf
+    // code, or pop()'s result when nothing was hit).  Entry distances are >= tmin >= 0, so their
+    // bit patterns order like unsigned integers: the child index rides in the two lowest
+    // mantissa bits and the four keys go through a five-comparator network of integer min / max
+    // (order is only a heuristic here: every accepted hit comes from the exact primitive test).
+    // No branch depends on how many children were hit, so the lanes of a warp stay together.
+    template <class Stack>
+    RT_DEV int step(const float4* __restrict__ nd, int node, const RayQ& r, float tmin, float tmax, Stack& st) const
+    {
+        float t[4]; int code[4]; unsigned mask;
+        test_node(nd, node, r, tmin, tmax, t, code, mask);
+        unsigned k[4];
+        #pragma unroll
+        for (int i = 0; i < 4; i++)
+            k[i] = ((mask >> i) & 1u) ? ((__float_as_uint(t[i]) & ~3u) | (unsigned)i) : 0xffffffffu;
+        auto cswap = [&](int i, int j) { const unsigned lo = min(k[i], k[j]), hi = max(k[i], k[j]); k[i] = lo; k[j] = hi; };
+        cswap(0, 1); cswap(2, 3); cswap(0, 2); cswap(1, 3); cswap(1, 2);
+        const int n = __popc(mask);
+        const int c0 = select4(code[0], code[1], code[2], code[3], k[0]);
+        const int c1 = select4(code[0], code[1], code[2], code[3], k[1]);
+        const int c2 = select4(code[0], code[1], code[2], code[3], k[2]);
+        const int c3 = select4(code[0], code[1], code[2], code[3], k[3]);
+        st.push_sorted(n, c1, c2, c3);
+        return n ? c0 : st.pop();
+    }
 
     // ---- the 8-wide tree (any-hit walks) ------------------------------------------------------
     // Node8, 96 bytes (bvh.cu: collapse8_kernel):
@@ -212,15 +239,15 @@ struct BvhAccelT {
     // Children are found by base + rank, so a stack entry can stand for ALL pending inner
     // children of a node: (child_base << 8) | mask of slots still to visit ("group"); >= 0.
     // Primitives travel as the usual leaf codes (< 0).
-    template <class Push, class Pop>
-    RT_DEV int step8(const uint4* __restrict__ nd8, int group, const RayQ& r, float tmin, float tmax, Push& push, Pop& pop) const
+    template <class Stack>
+    RT_DEV int step8(const uint4* __restrict__ nd8, int group, const RayQ& r, float tmin, float tmax, Stack& st) const
     {
         // next child of the group; what is left of the group goes back on the stack (caller)
         const unsigned mask = (unsigned)group & 0xffu;
         const unsigned slot = (unsigned)__ffs((int)mask) - 1u;
         const unsigned node = ((unsigned)group >> 8) + slot;
         const unsigned rest = mask & (mask - 1u);
-        if (rest) push((int)(((unsigned)group & ~0xffu) | rest));
+        if (rest) st.push((int)(((unsigned)group & ~0xffu) | rest));
         const uint4* w = nd8 + (size_t)node * 6;
         uint4 h, c, px, py, pz;
         asm("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -255,14 +282,17 @@ struct BvhAccelT {
         const unsigned n_inner = (h.w >> 24) & 15u;
         const unsigned inner = hit & ((1u << n_inner) - 1u);
         unsigned leaves = hit >> n_inner;
-        if (inner) push((int)((c.x << 8) | inner));
-        // primitives last = on top of the stack: an any-hit walk wants them first
-        while (leaves) {
+        if (inner) st.push((int)((c.x << 8) | inner));
+        if (!leaves) return st.pop();
+        // primitives on top of the stack (an any-hit walk wants them first); the last one does not
+        // make the round trip through the stack
+        for (;;) {
             const unsigned k = (unsigned)__ffs((int)leaves) - 1u;
             leaves &= leaves - 1u;
-            push(~(int)((c.y + k) << 3));
+            const int leaf = ~(int)((c.y + k) << 3);
+            if (!leaves) return leaf;
+            st.push(leaf);
         }
-        return pop();
     }
 
     // Generic traversal, "while-while" with one postponed leaf per lane (Aila & Laine 2009):
@@ -278,18 +308,16 @@ struct BvhAccelT {
         if (n_nodes == 0 || !finite3(ray) || !finite3(o)) return;   // NaN/inf rays hit nothing in the reference either
         const RayQ rq = make_rayq(o, ray);
         constexpr int kDone = kWalkDone;
-        int stack[kBvhStack];
-        int sp = 0;
-        auto pop = [&]() { return sp ? stack[--sp] : kDone; };
-        auto push = [&](int v) { if (sp < kBvhStack) stack[sp++] = v; };
+        LocalStack st;
+        st.flag = overflow_flag;
         int node = root;      // >= 0: inner node index, < 0: leaf code, kDone: nothing left
         int leaf = 0;         // postponed leaf code (< 0), 0 = none
         while (node != kDone) {
             while ((unsigned)node < (unsigned)kDone) {
-                node = step<true>(nodes, node, rq, tmin, tmax, push, pop);
+                node = step(nodes, node, rq, tmin, tmax, st);
                 if (node < 0 && leaf == 0) {                       // postpone the first leaf, keep descending
                     leaf = node;
-                    node = pop();
+                    node = st.pop();
                 }
                 if (!__any_sync(__activemask(), leaf == 0)) break; // every lane has a leaf to test
             }
@@ -304,9 +332,27 @@ struct BvhAccelT {
                 leaf = 0;
                 if (node < 0) {                                    // the next node is a leaf too: take it now
                     leaf = node;
-                    node = pop();
+                    node = st.pop();
                 }
             }
+        }
+    }
+
+    // The same on the 8-wide tree (no ordering: any-hit walks and the parity probes of that tree).
+    template <class Visit>
+    RT_DEV void walk8(V3 o, V3 ray, float tmin, float tmax, Visit& visit) const
+    {
+        if (n_nodes == 0 || nodes8 == nullptr || !finite3(ray) || !finite3(o)) return;
+        const RayQ rq = make_rayq(o, ray);
+        LocalStack st;
+        st.flag = overflow_flag;
+        int node = 1;         // the group "slot 0 of base 0" = node 0
+        while (node != kWalkDone) {
+            if (node >= 0) { node = step8(nodes8, node, rq, tmin, tmax, st); continue; }
+            if (kCount) cnt_prims++;
+            tmax = visit(prims8 + (size_t)((~node) >> 3) * kTriWords, tmax);
+            if (tmax < 0.0f) return;
+            node = st.pop();
         }
     }
 
@@ -318,8 +364,7 @@ struct BvhAccelT {
     //   job.retire(bool finishing)       -> called by ALL lanes whenever some lane finishes
     //                                       (warp collectives allowed inside)
     //   job.next(o, ray, tmin, tmax)     -> true when the finished lane's job has another ray
-    //   job.first_leaf()                 -> a leaf code (< 0) to test before the tree walk of the ray just set up, 0 = none
-    //   Job::kOrdered                    -> visit near children first (closest hit) or not (any hit)
+    //   Job::kWide8                      -> walk the 8-wide tree (any hit, no ordering) when there is one
     //   Job::kSteal                      -> once the job queue is dry, lanes whose ray has finished take
     //                                       subtrees off the stacks of the lanes still walking (a kernel
     //                                       otherwise ends with ~0.3 ms in which a few long rays keep a few
@@ -338,11 +383,10 @@ struct BvhAccelT {
 
     template <class Job>
     RT_DEV void persistent_walk(unsigned total, unsigned* counter, Job& job, int refill_lanes, int inner_min = 1, int leaf_min = 1,
-                                WalkClock* clock = nullptr, bool steal = true, unsigned job_budget = 0xffffffffu) const
+                                WalkClock* clock = nullptr) const
     {
         constexpr int kDone = kWalkDone;
         constexpr unsigned kFull = 0xffffffffu;
-        constexpr bool kJobBudget = false;     // bounded any-hit blocks (RT_SHADOW_JOB_BUDGET): measured, never paid; compiled out
         // loop invariants in registers (the accelerator object itself may sit in local memory)
         const float4* __restrict__ const nd = nodes;
         const uint4* __restrict__ const nd8 = nodes8;
@@ -352,47 +396,24 @@ struct BvhAccelT {
         const bool have_tree = n_nodes != 0;
         const unsigned lane = threadIdx.x & 31u;
         const unsigned lt = (1u << lane) - 1u;
-        // Traversal stack: the first kSmemStack entries live in shared memory, laid out
-        // [entry][thread] so that a warp's pushes and pops never conflict whatever the lanes'
-        // depths are (a local-memory stack costs one L1 wavefront per distinct depth, and L1 is
-        // what binds this loop); deeper entries overflow into local memory.
         __shared__ int s_stack[kSmemStack][kWalkBlock];
-        int stack[kBvhStack];
+        int deep[kBvhStack];
         const int tid = threadIdx.x;
-        int sp = 0, node = kDone, leaf = 0;
-        int bot = 0;                 // stack bottom: entries below it were given to helper lanes
+        SharedStack st;
+        st.col = &s_stack[0][tid]; st.deep = deep; st.sp = 0; st.bot = 0; st.flag = overflow_flag;
+        int node = kDone, leaf = 0;
         unsigned owner = lane;       // != lane: this lane walks a subtree for lane `owner`
         bool alive = false, pool_empty = false;
         RayQ rq = make_rayq(mk3(0.f, 0.f, 0.f), mk3(1.f, 1.f, 1.f));
         float tmin = 0.f, tmax = 0.f;
         unsigned long long t_empty = 0;
-        unsigned fetched = 0;
         bool worked = false;
         unsigned d_steps = 0, d_lanes = 0, d_steals = 0;
         if (kCount && clock && lane == 0) atomicMax(&clock->inv_first, ~globaltimer());
-        auto pop = [&]() {
-            if (sp == bot) return kDone;
-            --sp;
-            return sp < kSmemStack ? s_stack[sp][tid] : stack[sp - kSmemStack];
-        };
-        auto push = [&](int v) {
-            if (sp < kSmemStack) s_stack[sp][tid] = v;
-            else if (sp < kSmemStack + kBvhStack) stack[sp - kSmemStack] = v;
-            else return;
-            sp++;
-        };
         auto start = [&](bool need_walk, V3 o, V3 ray) {
-            sp = 0; bot = 0; leaf = 0; owner = lane;
+            st.sp = 0; st.bot = 0; leaf = 0; owner = lane;
             node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
             rq = make_rayq(o, ray);
-            if constexpr (Job::kFirstLeaf) {
-                if (node != kDone) {
-                    // a primitive the job wants tested before the tree is opened (an occluder hint): it
-                    // travels as the postponed leaf, the root waits on the stack
-                    const int fl = job.first_leaf();
-                    if (fl < 0) { push(node); node = kDone; leaf = fl; }
-                }
-            }
         };
         for (;;) {
             const unsigned dead = __ballot_sync(kFull, !alive);
@@ -400,10 +421,7 @@ struct BvhAccelT {
                 unsigned base = 0;
                 if (lane == 0) base = atomicAdd(counter, (unsigned)__popc(dead));
                 base = __shfl_sync(kFull, base, 0);
-                // (job_budget: a warp stops fetching after that many jobs, so that its block ends and
-                // the slot can go to a kernel of higher priority — render.cu)
-                if (kJobBudget) fetched += (unsigned)__popc(dead);
-                if (base + (unsigned)__popc(dead) >= total || (kJobBudget && fetched >= job_budget)) {
+                if (base + (unsigned)__popc(dead) >= total) {
                     pool_empty = true;
                     if (kCount && clock) t_empty = globaltimer();
                 }
@@ -418,10 +436,10 @@ struct BvhAccelT {
                 }
             }
             if constexpr (Job::kSteal) {
-                if (pool_empty && steal) {
+                if (pool_empty) {
                     const unsigned idle = __ballot_sync(kFull, !alive);
                     // (only the shared-memory part of a stack can be read by another lane)
-                    const int avail = alive ? min(sp, kSmemStack) - bot : 0;
+                    const int avail = alive ? min(st.sp, kSmemStack) - st.bot : 0;
                     const unsigned donors = __ballot_sync(kFull, avail > 0);
                     if (idle != 0u && donors != 0u) {
                         // the r-th idle lane takes the lower half (the older entries: the farther,
@@ -432,12 +450,12 @@ struct BvhAccelT {
                         const bool take = !alive && rank < pairs;
                         const int n_give = give ? (avail + 1) / 2 : 0;
                         const int src = take ? (int)__fns(donors, 0, rank + 1) : (int)lane;
-                        const int from = __shfl_sync(kFull, bot, src), n_take = __shfl_sync(kFull, n_give, src);
+                        const int from = __shfl_sync(kFull, st.bot, src), n_take = __shfl_sync(kFull, n_give, src);
                         const float tmin_s = __shfl_sync(kFull, tmin, src), tmax_s = __shfl_sync(kFull, tmax, src);
                         const unsigned owner_s = __shfl_sync(kFull, owner, src);
                         V3 o, ray;
                         job.adopt(src, take, o, ray);
-                        if (give) bot += n_give;
+                        if (give) st.bot += n_give;
                         if (kCount) d_steals += (unsigned)pairs;
                         __syncwarp();      // the donors' earlier stack writes are visible to the takers
                         if (take) {
@@ -446,9 +464,9 @@ struct BvhAccelT {
                             rq = make_rayq(o, ray);
                             const int col = tid - (int)lane + src;
                             for (int i = 0; i < n_take; i++) s_stack[i][tid] = s_stack[from + i][col];
-                            sp = n_take; bot = 0; leaf = 0;
-                            node = pop();
-                            if (node < 0) { leaf = node; node = pop(); }
+                            st.sp = n_take; st.bot = 0; leaf = 0;
+                            node = st.pop();
+                            if (node < 0) { leaf = node; node = st.pop(); }
                         }
                         __syncwarp();
                     }
@@ -456,7 +474,7 @@ struct BvhAccelT {
                     const unsigned group = __match_any_sync(kFull, alive ? owner : 32u + lane);
                     if (group & (group - 1u)) {
                         tmax = job.share(group, tmax);
-                        if (tmax < 0.0f) { node = kDone; leaf = 0; sp = bot; }
+                        if (tmax < 0.0f) { node = kDone; leaf = 0; st.sp = st.bot; }
                     }
                 }
             }
@@ -469,11 +487,11 @@ struct BvhAccelT {
                     d_lanes += (unsigned)__popc(__ballot_sync(kFull, alive && (unsigned)node < (unsigned)kDone));
                 }
                 if (alive && (unsigned)node < (unsigned)kDone) {
-                    if (Job::kWide8 && wide8) node = step8(nd8, node, rq, tmin, tmax, push, pop);
-                    else node = step<Job::kOrdered, Job::kWideLoads>(nd, node, rq, tmin, tmax, push, pop);
+                    if (Job::kWide8 && wide8) node = step8(nd8, node, rq, tmin, tmax, st);
+                    else node = step(nd, node, rq, tmin, tmax, st);
                     if (node < 0 && leaf == 0) {
                         leaf = node;
-                        node = pop();
+                        node = st.pop();
                     }
                 }
                 if (__popc(__ballot_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) < inner_min) break;
@@ -486,18 +504,16 @@ struct BvhAccelT {
                 if (holders == 0 || (!first && holders < leaf_min)) break;
                 if (alive && leaf < 0) {
                     const int code = ~leaf;
-                    const int first = code >> 3, count = (code & 7) + 1;
+                    const int first_slot = code >> 3, count = (code & 7) + 1;
                     leaf = 0;
                     for (int k = 0; k < count; k++) {
                         if (kCount) cnt_prims++;
-                        tmax = job.visit(pr + (size_t)(first + k) * kTriWords, tmax);
-                        if (tmax < 0.0f) { node = kDone; sp = bot; break; }
+                        tmax = job.visit(pr + (size_t)(first_slot + k) * kTriWords, tmax);
+                        if (tmax < 0.0f) { node = kDone; st.sp = st.bot; break; }
                     }
                     if (node < 0) {
                         leaf = node;
-                        node = pop();
-                    } else if (Job::kFirstLeaf && node == kDone) {
-                        node = pop();      // (only start()'s first leaf leaves entries under a finished node)
+                        node = st.pop();
                     }
                 }
             }
@@ -538,143 +554,6 @@ struct BvhAccelT {
                 atomicAdd(&clock->drain_steps, (unsigned long long)d_steps);
                 atomicAdd(&clock->drain_lane_steps, (unsigned long long)d_lanes);
                 atomicAdd(&clock->drain_steals, (unsigned long long)d_steals);
-            }
-        }
-    }
-
-    // ---- all generations in one launch -----------------------------------------------------------
-    // persistent_walk() over ONE work list that the kernel itself extends: a ray that has found
-    // its hit spawns its children at once (job.retire) and appends them to the list, so the
-    // generations of a frame overlap and the launch has a single tail instead of one per
-    // generation.  Tickets are handed out in order with one atomicAdd per warp; ticket t < n0 is
-    // primary ray t, ticket n0 + e is entry e of `order` = (generation << 28) | queue slot,
-    // 0xffffffff while not yet written.  A lane may hold a ticket for an entry that does not exist
-    // yet: it polls it once per pass of its warp.  The frame is traced when every published ray
-    // has retired (retired == n0 + tail, checked by whoever retires): tickets still waiting are
-    // void then.  Nothing blocks: waiting lanes never keep the walking lanes of their warp from
-    // walking, and any published entry is, or will be, held by exactly one lane.
-    //   job.begin(generation, slot, o, ray, tmin, tmax) -> false when the ray needs no tree walk
-    //   job.visit(words, tcur)
-    //   job.retire(fin)        ALL lanes; appends the hit, spawns and publishes the children,
-    //                          counts the retired rays and raises q->done
-    RT_DEV static unsigned ld_volatile(const unsigned* p)
-    {
-        unsigned v;
-        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-        return v;
-    }
-
-    template <class Job>
-    RT_DEV void persistent_walk_all(unsigned n0, WorkQueue* q, const unsigned* order, unsigned order_cap, Job& job,
-                                    int refill_lanes, int inner_min = 1, int leaf_min = 1) const
-    {
-        constexpr int kDone = kWalkDone;
-        constexpr unsigned kFull = 0xffffffffu;
-        const float4* __restrict__ const nd = nodes;
-        const float4* __restrict__ const pr = prims;
-        const int root_ = root;
-        const bool have_tree = n_nodes != 0;
-        const unsigned lane = threadIdx.x & 31u;
-        const unsigned lt = (1u << lane) - 1u;
-        __shared__ int s_stack[kSmemStack][kWalkBlock];
-        int stack[kBvhStack];
-        const int tid = threadIdx.x;
-        int sp = 0, node = kDone, leaf = 0;
-        bool alive = false, waiting = false, finished = false;
-        unsigned ticket = 0, spins = 0;
-        RayQ rq = make_rayq(mk3(0.f, 0.f, 0.f), mk3(1.f, 1.f, 1.f));
-        float tmin = 0.f, tmax = 0.f;
-        auto pop = [&]() {
-            if (sp == 0) return kDone;
-            --sp;
-            return sp < kSmemStack ? s_stack[sp][tid] : stack[sp - kSmemStack];
-        };
-        auto push = [&](int v) {
-            if (sp < kSmemStack) s_stack[sp][tid] = v;
-            else if (sp < kSmemStack + kBvhStack) stack[sp - kSmemStack] = v;
-            else return;
-            sp++;
-        };
-        for (;;) {
-            if (!finished) {
-                const unsigned idle = __ballot_sync(kFull, !alive && !waiting);
-                const unsigned busy = __ballot_sync(kFull, alive);
-                if (__popc(idle) >= refill_lanes || (idle != 0u && busy == 0u)) {
-                    unsigned base = 0;
-                    if (lane == 0) base = atomicAdd(&q->head, (unsigned)__popc(idle));
-                    base = __shfl_sync(kFull, base, 0);
-                    if (!alive && !waiting) { ticket = base + (unsigned)__popc(idle & lt); waiting = true; }
-                }
-                if (waiting) {
-                    unsigned gen = 0, slot = ticket;
-                    bool ok = ticket < n0;
-                    if (!ok) {
-                        const unsigned e = ticket - n0;
-                        const unsigned v = e < order_cap ? ld_volatile(order + e) : 0xffffffffu;
-                        if (v != 0xffffffffu) { ok = true; gen = v >> 28; slot = v & 0x0fffffffu; }
-                    }
-                    if (ok) {
-                        V3 o, ray;
-                        const bool need_walk = job.begin((int)gen, slot, o, ray, tmin, tmax);
-                        alive = true; waiting = false;
-                        sp = 0; leaf = 0;
-                        node = (need_walk && have_tree && finite3(ray) && finite3(o)) ? root_ : kDone;
-                        rq = make_rayq(o, ray);
-                    }
-                }
-                if (!__any_sync(kFull, alive)) {
-                    // nobody in this warp has a ray: either the frame is traced, or the entries of
-                    // our tickets are still to come
-                    unsigned d = 0;
-                    if (lane == 0) d = ld_volatile(&q->done);
-                    d = __shfl_sync(kFull, d, 0);
-                    if (d) { finished = true; waiting = false; }
-                    else {
-                        __nanosleep(400);
-                        if (++spins > (1u << 22)) {          // ~2 s without a ray: give up loudly
-                            if (lane == 0) atomicExch(&q->stalled, 1u);
-                            finished = true; waiting = false;
-                        }
-                        continue;
-                    }
-                }
-            }
-            if (!__any_sync(kFull, alive)) break;
-            spins = 0;
-            // inner nodes, until every live lane holds a leaf (or has nothing left)
-            for (;;) {
-                if (alive && (unsigned)node < (unsigned)kDone) {
-                    node = step<true, false>(nd, node, rq, tmin, tmax, push, pop);
-                    if (node < 0 && leaf == 0) {
-                        leaf = node;
-                        node = pop();
-                    }
-                }
-                if (__popc(__ballot_sync(kFull, alive && leaf == 0 && (unsigned)node < (unsigned)kDone)) < inner_min) break;
-            }
-            // pending leaves
-            for (bool first = true;; first = false) {
-                const int holders = __popc(__ballot_sync(kFull, alive && leaf < 0));
-                if (holders == 0 || (!first && holders < leaf_min)) break;
-                if (alive && leaf < 0) {
-                    const int code = ~leaf;
-                    const int first_slot = code >> 3, count = (code & 7) + 1;
-                    leaf = 0;
-                    for (int k = 0; k < count; k++) {
-                        if (kCount) cnt_prims++;
-                        tmax = job.visit(pr + (size_t)(first_slot + k) * kTriWords, tmax);
-                        if (tmax < 0.0f) { node = kDone; sp = 0; break; }
-                    }
-                    if (node < 0) {
-                        leaf = node;
-                        node = pop();
-                    }
-                }
-            }
-            const bool fin = alive && node == kDone && leaf == 0;
-            if (__any_sync(kFull, fin)) {
-                job.retire(fin);
-                if (fin) alive = false;
             }
         }
     }
@@ -776,18 +655,21 @@ struct BvhAccelT {
     // Shadow product.  An opaque occluder (k == 0) makes the product exactly 0 whatever
     // the order, so the walk stops there.  Partial factors are multiplied in the
     // reference's iteration order (float products are not associative): they are
-    // collected, sorted by order, then applied.
+    // collected, sorted by order, then applied.  The any-hit kernel's visitor holds kMaxPartial
+    // of them in registers; a ray with more transparent occluders than that sets `overflowed`
+    // and its node is redone by bvh_shadow_redo_kernel through shadow() below, which has no
+    // limit — never a product in the wrong order.
     static constexpr int kMaxPartial = 12;
     struct ShadowVisit {
         V3 o, ray; float tmin, tmax_hit; bool use_tmax, skip_spheres, count_all; int self; int hits;
         int n_partial; int p_order[kMaxPartial]; float p_k[kMaxPartial];
-        float overflow_mask; bool opaque;
+        bool overflowed, opaque;
         RT_DEV void add(int order, float k)
         {
             hits++;
             if (k == 0.0f) { opaque = true; return; }
             if (n_partial < kMaxPartial) { p_order[n_partial] = order; p_k[n_partial] = k; n_partial++; }
-            else overflow_mask = clamp01(fmul(k, overflow_mask));
+            else overflowed = true;
         }
         RT_DEV float operator()(const float4* w, float tmax)
         {
@@ -805,16 +687,14 @@ struct BvhAccelT {
                 if (n >= 1 && tf > tmin && (!use_tmax || tf < tmax_hit)) add(order, w4.y);
                 if (n == 2 && tn > tmin && (!use_tmax || tn < tmax_hit)) add(order, w4.y);
             }
-            return (opaque && !count_all) ? -1.0f : tmax;
+            return ((opaque || overflowed) && !count_all) ? -1.0f : tmax;
         }
     };
 
-    // Walks the tree (and, for rays no box bounds, the sphere list) and leaves the partial
-    // factors sorted by iteration order in v.
     RT_DEV void shadow_begin(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, ShadowVisit& v) const
     {
         v.o = o; v.ray = ray; v.tmin = tmin; v.tmax_hit = tmax; v.use_tmax = use_tmax; v.self = self;
-        v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false; v.count_all = count_all;
+        v.hits = 0; v.n_partial = 0; v.overflowed = false; v.opaque = false; v.count_all = count_all;
         // The sphere quadratic assumes a unit ray (A == 1, main.cpp:1232).  For a ray of
         // length s != 1 (un-normalised directional lights, main.cpp:895) the accepted set is
         // rho^2 <= r^2 + (s^2 - 1) p^2 — unbounded for s > 1, so no box bounds it:
@@ -829,7 +709,7 @@ struct BvhAccelT {
         const float tmin = v.tmin, tmax = v.tmax_hit;
         const bool use_tmax = v.use_tmax;
         const int self = v.self;
-        if (v.skip_spheres && !(v.opaque && !count_all)) {
+        if (v.skip_spheres && !((v.opaque || v.overflowed) && !count_all)) {
             for (int i = 0; i < ns; i++) {
                 if (nf + i == self) continue;
                 const float4* w = sph + (size_t)i * kSphWords;
@@ -837,7 +717,7 @@ struct BvhAccelT {
                 const int n = sphere_roots(w[0], o, ray, tf, tn);
                 if (n >= 1 && tf > tmin && (!use_tmax || tf < tmax)) v.add(nf + i, w[1].x);
                 if (n == 2 && tn > tmin && (!use_tmax || tn < tmax)) v.add(nf + i, w[1].x);
-                if (v.opaque && !count_all) break;
+                if ((v.opaque || v.overflowed) && !count_all) break;
             }
         }
         if (v.opaque) return;
@@ -850,33 +730,92 @@ struct BvhAccelT {
         }
     }
 
-    RT_DEV void shadow_collect(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, ShadowVisit& v) const
-    {
-        shadow_begin(o, ray, self, tmin, tmax, use_tmax, v);
-        walk(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
-        shadow_end(v);
-    }
+    // The same product for ANY number of partial occluders, by one thread on its own (parity
+    // probes, bvh_shadow_redo_kernel): the walk is repeated, and each pass keeps the kWindow
+    // factors with the smallest iteration keys above the last one applied (key = 2 * order +
+    // {0: triangle / far root, 1: near root}: unique per hit, and the two roots of a sphere
+    // carry the same factor).  One pass for up to kWindow factors, ceil(n / kWindow) otherwise.
+    static constexpr int kWindow = 12;
+    struct ShadowWindow {
+        V3 o, ray; float tmin, tmax_hit; bool use_tmax, skip_spheres, count_all, counting; int self; int hits;
+        int last_key, n; int key[kWindow]; float kf[kWindow];
+        bool more, opaque;
+        RT_DEV void add(int order, int sub, float k)
+        {
+            if (counting) hits++;
+            if (k == 0.0f) { opaque = true; return; }
+            const int ky = 2 * order + sub;
+            if (ky <= last_key) return;
+            if (n == kWindow) {
+                more = true;
+                if (ky > key[kWindow - 1]) return;
+                n--;                                   // the largest key leaves the window
+            }
+            int i = n;
+            while (i > 0 && key[i - 1] > ky) { key[i] = key[i - 1]; kf[i] = kf[i - 1]; i--; }
+            key[i] = ky; kf[i] = k; n++;
+        }
+        RT_DEV void sphere(const float4& w0, int order, float k)
+        {
+            float tf, tn;
+            const int r = sphere_roots(w0, o, ray, tf, tn);
+            if (r >= 1 && tf > tmin && (!use_tmax || tf < tmax_hit)) add(order, 0, k);
+            if (r == 2 && tn > tmin && (!use_tmax || tn < tmax_hit)) add(order, 1, k);
+        }
+        RT_DEV float operator()(const float4* w, float tmax)
+        {
+            const float4 w4 = w[4];
+            const int order = __float_as_int(w4.z);
+            if (order == self) return tmax;
+            if (__float_as_int(w4.w) == 0) {
+                float t, b, g;
+                if (tri_distance(w[0], o, ray, t) && t > tmin && (!use_tmax || t < tmax_hit) &&
+                    tri_inside(w[1], w[2], w[3], w4, o, ray, t, b, g))
+                    add(order, 0, w4.y);
+            } else if (!skip_spheres) {
+                sphere(w[0], order, w4.y);
+            }
+            return (opaque && !count_all) ? -1.0f : tmax;
+        }
+    };
 
-    RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask) const
+    // wide8: walk the 8-wide tree (what the any-hit kernel walks) instead of the 4-wide one
+    RT_DEV int shadow(V3 o, V3 ray, int self, float tmin, float tmax, bool use_tmax, float& mask, bool wide8 = false) const
     {
-        ShadowVisit v;
-        shadow_collect(o, ray, self, tmin, tmax, use_tmax, v);
-        if (v.opaque) { mask = clamp01(fmul(0.0f, mask)); return v.hits; }
-        for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
-        if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
-        return v.hits;
+        ShadowWindow v;
+        v.o = o; v.ray = ray; v.tmin = tmin; v.tmax_hit = tmax; v.use_tmax = use_tmax; v.self = self;
+        v.count_all = count_all; v.skip_spheres = spheres_unbounded(ray);
+        v.hits = 0; v.last_key = -1; v.counting = true;
+        for (;;) {
+            v.n = 0; v.more = false; v.opaque = false;
+            if (wide8 && nodes8 != nullptr) walk8(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
+            else walk(o, ray, tmin, use_tmax ? tmax : 3.402823466e+38f, v);
+            if (v.skip_spheres && !(v.opaque && !count_all))
+                for (int i = 0; i < ns; i++) {
+                    if (nf + i == self) continue;
+                    const float4* w = sph + (size_t)i * kSphWords;
+                    v.sphere(w[0], nf + i, w[1].x);
+                    if (v.opaque && !count_all) break;
+                }
+            if (v.opaque) { mask = clamp01(fmul(0.0f, mask)); return v.hits; }
+            for (int i = 0; i < v.n; i++) mask = clamp01(fmul(v.kf[i], mask));
+            if (!v.more) return v.hits;
+            v.last_key = v.key[v.n - 1];
+            v.counting = false;
+        }
     }
 };
 
 using BvhAccel = BvhAccelT<false>;
 
 template <bool kCount>
-RT_DEV BvhAccelT<kCount> make_bvh_accel(const SceneView& S)
+__host__ __device__ __forceinline__ BvhAccelT<kCount> make_bvh_accel(const SceneView& S)
 {
     BvhAccelT<kCount> a;
     a.nodes = S.bvh.nodes; a.prims = S.bvh_tri; a.tri = S.tri; a.sph = S.sph;
     a.nodes8 = S.bvh.n_nodes8 > 0 ? S.bvh.nodes8 : nullptr; a.prims8 = S.bvh.prims8;
     a.nf = S.nf; a.ns = S.ns; a.root = S.bvh.root; a.n_nodes = S.bvh.n_nodes; a.count_all = false;
+    a.overflow_flag = nullptr;
     return a;
 }
 
