@@ -102,10 +102,10 @@ struct LevelBuffers {
     int2*   nr_c;   // slots of the transmission / reflection child in generation d+1 (-1 = none)
     float4* res;    // rgb, status
     // LBVH pipeline only (wavefront_bvh.cuh): the hit of slot i, the list of slots that hit
-    // something (= the ShadeRay nodes of this generation, in arrival order), and one shadow
-    // record per (node, light), light-major: sh[li * n_nodes + k] for node_list[k] = the carried
-    // shadow_mask after light li
-    float4* hp;     // hit point.xyz, as_float(object order)
+    // something (= the ShadeRay nodes of this generation, in slot order up to the order in which
+    // warps of the spawn kernel claim their 32 slots), and one shadow record per (node, light),
+    // light-major: sh[li * n_nodes + k] for node_list[k] = the carried shadow_mask after light li
+    float4* hp;     // hit point.xyz, as_float(object order); w = as_float(-1) for a slot without a hit
     float4* hb;     // b, g, t, 0
     int*    node_list;
     float*  sh;
@@ -125,34 +125,25 @@ struct WalkClock {
     unsigned int warps, pad;
 };
 
-// Work list of the fused trace kernel (bvh.cuh: persistent_walk_all).  Tickets below the number of
-// primary rays are pixels; ticket n0 + e is entry e of FrameParams::work_order.
-struct WorkQueue {
-    unsigned int head;      // tickets handed out
-    unsigned int tail;      // entries allocated (each is written right after)
-    unsigned int retired;   // rays finished, children published: the frame is traced when == n0 + tail
-    unsigned int done;
-    unsigned int stalled;   // watchdog: a warp gave up waiting (never expected; the frame is invalid)
-    // hits waiting for the spawn half of ShadeRay (FrameParams::hit_order), taken 32 at a time by the
-    // kernel's spawner warps
-    unsigned int hit_head, hit_tail;
-    unsigned int pad;
-};
+// Bits of Counters::overflow: the frame is incomplete and rt_render must not hand it out.
+constexpr unsigned kOverflowQueue = 1u;    // a wavefront queue was too small: queues are grown, the frame redone
+constexpr unsigned kOverflowStack = 2u;    // a traversal stack overflowed (build_bvh checks the depth: never expected)
+constexpr unsigned kOverflowRedo = 4u;     // more shadow chains to redo than the redo list holds
+
+constexpr int kRedoCapacity = 1 << 16;     // nodes per launch chain whose shadow chain may go through the slow exact path
 
 struct Counters {
     unsigned int rays[kMaxLevels];        // rays queued for level d (level 0: unused)
     unsigned int nodes[kMaxLevels];       // hits shaded at level d
     unsigned int rays_reflect[kMaxLevels];
-    unsigned int overflow;                // some queue was too small: frame must be redone
-    unsigned int pad;
+    unsigned int overflow;                // kOverflow* bits
+    unsigned int redo_count;              // entries of FrameParams::redo_list ((generation << 28) | node index)
     unsigned int fetch_trace[kMaxLevels];   // LBVH pipeline: next job of the persistent trace / shadow kernels
     unsigned int fetch_shadow[kMaxLevels];
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
     unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
-    unsigned long long shadow_hint_hits;                // ... of the elided ones: settled by the hinted occluder, no tree walk
     WalkClock clock[2][kMaxLevels];                     // instrumented LBVH frames: [0] trace, [1] shadow kernels
-    WorkQueue work;                                     // fused trace kernel
 };
 
 struct FrameParams {
@@ -175,24 +166,9 @@ struct FrameParams {
     int inner_min_lanes;  // ... leave the inner-node loop when fewer lanes than this can still descend
     int leaf_min_lanes;   // ... leave the leaf loop when fewer lanes than this hold a leaf
     int sh_refill_lanes, sh_inner_min_lanes, sh_leaf_min_lanes;   // the same three for the any-hit kernel
-    int shadow_job_budget; // ... any-hit kernel: jobs a warp takes before it stops fetching (0 = no limit)
-    int steal;            // ... idle lanes take subtrees from busy ones once the queue is dry (closest-hit walks)
-    // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob): hint[li * n_prims + order of the
-    // surface's primitive] = record index (any-hit primitive table) of the opaque occluder that last ended
-    // a shadow walk from that primitive towards light li, -1 = none yet.  Cleared at every frame start.
-    int* occluder_hint;   // null: off
-    int hint_prims;       // nf + ns
-    int hint_passes;      // the node list is taken in up to this many interleaved passes (>= 1)
-    int hint_group;       // ... of groups of this many consecutive nodes
-    int hint_min_chunk;   // ... but no pass shorter than this many nodes
-    // Fused trace kernel: one entry per spawned ray, (generation << 28) | queue slot, 0xffffffff = not
-    // written yet (cleared at every frame start); work_capacity = the generations' capacities summed
-    unsigned int* work_order;
-    unsigned int work_capacity;
-    unsigned int* hit_order;      // same encoding: the hits of generations < max_depth, in arrival order
-    unsigned int hit_capacity;
-    int spawn_every;              // every spawn_every-th warp of the fused kernel spawns instead of walking
-    int hint_mode;        // experiments: bit 0 = test hints, bit 1 = record them (3 = normal)
+    // Shadow chains the any-hit kernel could not finish exactly (more than BvhAccelT::kMaxPartial
+    // transparent occluders on one ray): redone by bvh_shadow_redo_kernel.  kRedoCapacity entries.
+    unsigned int* redo_list;
 };
 
 }  // namespace rt

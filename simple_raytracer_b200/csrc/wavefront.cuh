@@ -36,15 +36,26 @@ RT_DEV int global_row(const FrameParams& P, int local_row)
     return (tile * P.world + P.rank) * P.tile_rows + in_tile;
 }
 
-// Slot of the rank's tile buffer that pixel slot `slot` of this sub-frame lands in; -1 for
-// the virtual padding tiles past the end of the buffer.
-RT_DEV int out_slot(const FrameParams& P, unsigned slot)
+// Pixel of level-0 slot `slot`.  Slots run tile by tile; inside a tile (tile_rows rows of the
+// image) they run through blocks of 8 columns, row by row inside a block, so the 32 consecutive
+// slots a warp takes are an 8 x 4 patch of pixels rather than a 32 x 1 strip: primary rays of a
+// warp stay closer together in the tree, and so do the generations spawned from them (queues keep
+// slot order).  The last block of a row is narrower when the width is not a multiple of 8.
+//   lrow, col : row of this sub-frame's tile buffer / image column
+//   returns the index in the RANK's tile buffer [local_tile][row][col], -1 for the virtual
+//   padding tiles of a sub-frame past the end of the buffer.
+RT_DEV int pixel_of_slot(const FrameParams& P, unsigned slot, int& lrow, int& col)
 {
-    if (P.out_mul == 1) return (int)slot;
-    const unsigned per_tile = (unsigned)(P.tile_rows * P.cam.width);
+    const unsigned W = (unsigned)P.cam.width, tr = (unsigned)P.tile_rows;
+    const unsigned per_tile = tr * W, blk = 8u * tr;
     const unsigned vt = slot / per_tile, rem = slot - vt * per_tile;
+    const unsigned cb = rem / blk, r2 = rem - cb * blk;
+    unsigned rr, c;
+    if (cb * 8u + 8u <= W) { rr = r2 >> 3; c = cb * 8u + (r2 & 7u); }
+    else { const unsigned wl = W - cb * 8u; rr = r2 / wl; c = cb * 8u + (r2 - rr * wl); }
+    lrow = (int)(vt * tr + rr); col = (int)c;
     const unsigned t = vt * (unsigned)P.out_mul + (unsigned)P.out_add;
-    return t < (unsigned)P.out_tiles ? (int)(t * per_tile + rem) : -1;
+    return t < (unsigned)P.out_tiles ? (int)(t * per_tile + rr * W + c) : -1;
 }
 
 // Shared-memory staging of the primitive tables for small scenes: every lane of a
@@ -83,7 +94,8 @@ RT_DEV bool load_ray(const FrameParams& P, int level, unsigned slot, RayIn& r)
     r.o = mk3(0.f, 0.f, 0.f); r.ray = mk3(0.f, 0.f, 0.f);
     r.n_i = r.n_t = 0.f; r.inc = -1; r.ns = 0; r.reflect = r.exiting = false;
     if (level == 0) {
-        const int lrow = slot / P.cam.width, col = slot - lrow * P.cam.width;
+        int lrow, col;
+        pixel_of_slot(P, slot, lrow, col);
         const int row = global_row(P, lrow);
         if (row >= P.cam.height) return false;
         const V3 ul = mk3(P.cam.ul[0], P.cam.ul[1], P.cam.ul[2]);
@@ -94,8 +106,7 @@ RT_DEV bool load_ray(const FrameParams& P, int level, unsigned slot, RayIn& r)
         r.ray = vnorm(vsub(p, r.o));                                                // 728
         return true;
     }
-    // (ld.global.cg: in the fused trace kernel the entry was written by another SM during this very
-    // launch, and a neighbouring entry may have pulled a stale copy of its line into this SM's L1)
+    // (queue entries are read once or twice per frame: ld.global.cg keeps them out of L1, which the tree needs)
     const LevelBuffers& LB = P.level[level];
     const float4 qo = __ldcg(LB.rq_o + slot), qd = __ldcg(LB.rq_d + slot);
     const int4 qm = __ldcg(LB.rq_m + slot), qs = __ldcg(LB.rq_s + slot);
@@ -139,12 +150,11 @@ RT_DEV void write_miss(const FrameParams& P, int level, unsigned slot, bool padd
 //            to the queue of generation level+1 -> nr_b, nr_c.
 // The fused brute-force kernel does both in one call, the LBVH pipeline in two kernels.
 // Must be called by all 32 lanes of a warp (`hit` false for idle lanes): queue slots are
-// handed out with one atomicAdd per warp.  kMixed: the lanes' `level`s may differ (the fused
-// trace kernel): one atomicAdd per warp and generation present.  children: the queue slots of
-// the transmission / reflection ray in generation level + 1 (-1 = none), when asked for.
-template <bool kColour, bool kSpawn, class ShadowSrc, bool kMixed = false>
+// handed out with one atomicAdd per warp, transmission rays first, then reflection rays, so
+// the children of 32 consecutive slots are consecutive in the next generation's queue.
+template <bool kColour, bool kSpawn, class ShadowSrc>
 RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int level, unsigned slot, RayIn& r,
-                            const Hit& h, bool hit, int* children = nullptr)
+                            const Hit& h, bool hit)
 {
     const SceneView& S = P.scene;
     const LevelBuffers& LB = P.level[level];
@@ -173,19 +183,17 @@ RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int l
 
     // ---- spawn: warp-aggregated slot allocation in the next generation's queue -----
     int child_t = -1, child_r = -1;
-    for (int L = kMixed ? 0 : level; L <= (kMixed ? P.max_depth - 1 : level); L++) {
-        const unsigned mt = __ballot_sync(0xffffffffu, sp.want_t && level == L);
-        const unsigned mr = __ballot_sync(0xffffffffu, sp.want_r && level == L);
-        if (!(mt | mr)) continue;                    // warp-uniform
-        const LevelBuffers& NB = P.level[L + 1];
+    const unsigned mt = __ballot_sync(0xffffffffu, sp.want_t);
+    const unsigned mr = __ballot_sync(0xffffffffu, sp.want_r);
+    if (mt | mr) {                                   // warp-uniform
+        const LevelBuffers& NB = P.level[level + 1];
         const int nt = __popc(mt), nr = __popc(mr);
         unsigned basei = 0;
         if ((threadIdx.x & 31) == 0) {
-            basei = atomicAdd(&P.counters->rays[L + 1], (unsigned)(nt + nr));
-            if (nr) atomicAdd(&P.counters->rays_reflect[L + 1], (unsigned)nr);
+            basei = atomicAdd(&P.counters->rays[level + 1], (unsigned)(nt + nr));
+            if (nr) atomicAdd(&P.counters->rays_reflect[level + 1], (unsigned)nr);
         }
         basei = __shfl_sync(0xffffffffu, basei, 0);
-        if (level != L) continue;
         const unsigned lt = lanemask_lt();
         const int flags_common = (c_exiting ? kRayStateExiting : 0) | (r.ns << kRayNStackShift);
         if (sp.want_t) {
@@ -197,7 +205,7 @@ RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int l
                 NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common, r.stack[0]);
                 NB.rq_s[s] = make_int4(r.stack[1], r.stack[2], r.stack[3], r.stack[4]);
             } else {
-                P.counters->overflow = 1;
+                atomicOr(&P.counters->overflow, kOverflowQueue);
             }
         }
         if (sp.want_r) {
@@ -209,11 +217,10 @@ RT_DEV void shade_and_spawn(const FrameParams& P, const ShadowSrc& shadow, int l
                 NB.rq_m[s] = make_int4((int)slot, h.obj, flags_common | kRayKindReflect, r.stack[0]);
                 NB.rq_s[s] = make_int4(r.stack[1], r.stack[2], r.stack[3], r.stack[4]);
             } else {
-                P.counters->overflow = 1;
+                atomicOr(&P.counters->overflow, kOverflowQueue);
             }
         }
     }
-    if (children) { children[0] = child_t; children[1] = child_r; }
 
     if (!hit || level == P.max_depth) return;
     // a node without children is finished by the combine pass like any other: x + 0 leaves a
@@ -240,7 +247,10 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
         const unsigned hm = __ballot_sync(0xffffffffu, hit);
         if ((threadIdx.x & 31) == 0 && hm) atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
     }
-    if (active && level == 0 && P.primary_ids) P.primary_ids[out_slot(P, slot)] = hit ? S.obj[h.obj].z : 0;
+    if (active && level == 0 && P.primary_ids) {
+        int lrow, col;
+        P.primary_ids[pixel_of_slot(P, slot, lrow, col)] = hit ? S.obj[h.obj].z : 0;
+    }
     if (P.primary_ids) {   // instrumented frame: one texel per shaded hit on a textured object
         const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[h.obj].y >= 0);
         if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
@@ -312,7 +322,8 @@ __global__ void __launch_bounds__(256) combine_kernel(const __grid_constant__ Fr
                 if (q == (int)0x80000000) { flags |= 1u << k; out[k] = 0; }
                 else out[k] = (unsigned char)min(max(q, 0), 255);
             }
-            const int dst = out_slot(P, slot);
+            int lrow, col;
+            const int dst = pixel_of_slot(P, slot, lrow, col);
             if (dst >= 0) P.tiles[dst] = make_uchar4(out[0], out[1], out[2], (unsigned char)flags);
         }
     }
