@@ -1,20 +1,29 @@
-// wavefront_bvh.cuh — the LBVH pipeline: one generation = three kernels, each with ONE
-// kind of work per thread, so that the lanes of a warp stay in the same loop:
+// wavefront_bvh.cuh — the LBVH pipeline: every kernel has ONE kind of work per thread, so that
+// the lanes of a warp stay in the same loop:
 //
-//   bvh_trace_kernel   one thread per queued ray: closest hit (tree walk).  Hits are
-//                      appended to the generation's node list (one atomicAdd per warp),
-//                      misses get their final record at once.
-//   bvh_shadow_kernel  one thread per (node, light): the shadow ray of main.cpp:896 / 928
-//                      as an any-hit walk that stops at the first opaque occluder.  Threads
-//                      are light-major, so a warp holds neighbouring surface points and the
-//                      SAME light: directional lights give 32 parallel rays.
-//   bvh_shade_kernel   one thread per node: ShadeRay's arithmetic with the shadow products
-//                      read from the records, spawn of the two child rays.
+//   bvh_trace_kernel   one thread per queued ray: closest hit (persistent tree walk); the hit
+//                      (or "none") is left in the slot's record.
+//   bvh_spawn_kernel   one thread per slot, in slot order: lists the slots that hit something
+//                      (the ShadeRay nodes of the generation) and runs the half of ShadeRay that
+//                      depends only on the hit — medium state machine, Fresnel weights, the two
+//                      child rays appended to the next generation's queue.
+//   bvh_shadow_kernel  one job per node: the shadow rays (main.cpp:896 / 928) to light 0, 1, ...
+//                      as a chain of any-hit walks that stops as soon as the carried product is 0.
+//   bvh_shadow_redo_kernel  the few chains the any-hit kernel had to give up (more partial
+//                      occluders on one ray than its registers hold), by the exact slow path.
+//   bvh_colour_kernel  one thread per node: texture, Blinn-Phong sum over the lights with the
+//                      recorded shadow products.
 //
-// The fused level_kernel (wavefront.cuh) does all three in one thread, which is right for
+// The fused level_kernel (wavefront.cuh) does all of this in one thread, which is right for
 // the brute-force path (every lane walks the same primitive list in lock step) and wrong
 // here: with nine independent tree walks per thread a warp ran 3.8 of 32 lanes on average
 // (ncu, profiles/r1_level_fused_ncu.txt).
+//
+// Order.  Queues and node lists keep SLOT order (up to the order in which warps claim their 32
+// slots): generation 0's slots are 8 x 4 pixel patches (pixel_of_slot), and the children of 32
+// consecutive slots are consecutive in the next queue, so the 32 rays a warp of the walk kernels
+// fetches together started close together — in every generation.  (Round 1 appended hits in the
+// order the walks happened to finish: 18.7 of 32 lanes per instruction.)
 #pragma once
 
 #include "bvh.cuh"
@@ -26,21 +35,15 @@
 #ifndef RT_SHADE_MIN_BLOCKS
 #define RT_SHADE_MIN_BLOCKS 8
 #endif
-// closest-hit kernel: blocks per SM it is compiled for (0 = as it comes: 72 registers, 7 blocks)
+// closest-hit kernel: blocks per SM it is compiled for (0 = the compiler's choice)
 #ifndef RT_TRACE_MIN_BLOCKS
-#define RT_TRACE_MIN_BLOCKS 0
+#define RT_TRACE_MIN_BLOCKS 7
 #endif
-// fused trace kernel: blocks per SM it is compiled for (0 = the compiler's choice)
-#ifndef RT_TRACE_ALL_MIN_BLOCKS
-#define RT_TRACE_ALL_MIN_BLOCKS 7
-#endif
-// any-hit kernel: 8 blocks per SM (64 registers)
+// any-hit kernel: blocks per SM (0 = the compiler's choice; it lands on 64 registers = 8 blocks)
 #ifndef RT_SHADOW_MIN_BLOCKS
-#define RT_SHADOW_MIN_BLOCKS 8
+#define RT_SHADOW_MIN_BLOCKS 0
 #endif
 namespace rt {
-
-static_assert(kWalkBlock == 32 || kWalkBlock == 64 || kWalkBlock == 128, "walk kernels: 1, 2 or 4 warps per block");
 
 template <bool kCount>
 RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool shadow = false)
@@ -61,13 +64,11 @@ RT_DEV void flush_bvh_counters(const BvhAccelT<kCount>& a, Counters* c, bool sha
 // sphere-incidence transmission) or the face-incidence rule (main.cpp:992-1011).
 template <bool kCount, bool kStealing>
 struct TraceJob {
-    static constexpr bool kOrdered = true;       // closest hit: near children first, the bound shrinks
     // min over (t, order) / OR of `aborted` are folds in any visiting order, so the subtrees of
     // one ray may be walked by several lanes.  Two builds of the kernel: the work-sharing one
     // ends sooner (the stragglers of the last rays are split up) but its main loop carries
     // more state; render.cu picks it for launches short enough for the tail to matter.
     static constexpr bool kSteal = kStealing;
-    static constexpr bool kWideLoads = false;
     static constexpr bool kWide8 = false;
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
@@ -143,8 +144,6 @@ struct TraceJob {
     }
 
     RT_DEV bool next(V3&, V3&, float&, float&) { return false; }
-    static constexpr bool kFirstLeaf = false;
-    RT_DEV int first_leaf() { return 0; }
 
     // work sharing at the end of a launch (persistent_walk): a helper lane walks a subtree
     // for the ray of lane src with a copy of its state ...
@@ -204,38 +203,38 @@ struct TraceJob {
             for (int i = 0; i < acc.ns; i++) sphere_candidate(acc.sph[(size_t)i * kSphWords], acc.nf + i, tmin);
         }
         const bool hit = fin && !padding && !aborted && best.obj >= 0;
-        // append to the node list: one atomic per warp
-        const unsigned hm = __ballot_sync(0xffffffffu, hit);
-        unsigned base = 0;
-        if ((threadIdx.x & 31) == 0 && hm) base = atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
-        base = __shfl_sync(0xffffffffu, base, 0);
         if (hit) {
             const V3 p = vadd(o, vmulf(ray, best.t));                            // 1245 / 1303, same as finish_hit
             LB.hp[slot] = make_float4(p.x, p.y, p.z, __int_as_float(best.obj));
             LB.hb[slot] = make_float4(best.b, best.g, best.t, 0.0f);
-            LB.node_list[base + __popc(hm & lanemask_lt())] = (int)slot;
             // nodes of the last generation are finished by the colour kernel itself
             if (level < P.max_depth) LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
         } else if (fin) {
+            LB.hp[slot] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));        // bvh_spawn_kernel lists the hits
             write_miss(P, level, slot, padding, aborted);
         }
-        if (P.primary_ids) {   // instrumented frame
-            if (fin && !padding && level == 0) P.primary_ids[out_slot(P, slot)] = hit ? S.obj[best.obj].z : 0;
+        if (kCount && P.primary_ids) {   // instrumented frame
+            if (fin && !padding && level == 0) {
+                int lrow, col;
+                P.primary_ids[pixel_of_slot(P, slot, lrow, col)] = hit ? S.obj[best.obj].z : 0;
+            }
             const unsigned tm = __ballot_sync(0xffffffffu, hit && S.obj[best.obj].y >= 0);
             if ((threadIdx.x & 31) == 0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
         }
     }
 };
 
+
 template <bool kCount, bool kStealing>
-__global__ void __launch_bounds__(kWalkBlock, (RT_TRACE_MIN_BLOCKS && !kCount ? RT_TRACE_MIN_BLOCKS : (kStealing || kWalkScale > 1 ? 7 : 0)) * kWalkScale) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kWalkBlock, kCount ? 0 : RT_TRACE_MIN_BLOCKS) bvh_trace_kernel(const __grid_constant__ FrameParams P, int level)
 {
-    const auto acc = make_bvh_accel<kCount>(P.scene);
+    auto acc = make_bvh_accel<kCount>(P.scene);
+    acc.overflow_flag = &P.counters->overflow;
     const unsigned count = level == 0 ? (unsigned)P.n_local_pixels
                                       : min(P.counters->rays[level], (unsigned)P.level[level].capacity);
     TraceJob<kCount, kStealing> job{ P, acc, level };
     acc.persistent_walk(count, &P.counters->fetch_trace[level], job, P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes,
-                        kCount ? &P.counters->clock[0][level] : nullptr, P.steal != 0);
+                        kCount ? &P.counters->clock[0][level] : nullptr);
     flush_bvh_counters(acc, P.counters);
 }
 
@@ -244,169 +243,36 @@ struct NoShadow {
     RT_DEV void operator()(int, V3, V3, int, float, float, bool, float&) const {}
 };
 
-// ---- the FUSED trace kernel -------------------------------------------------------------------
-// Every generation's closest-hit rays in one persistent launch (BvhAccelT::persistent_walk_all).
-// Walker warps walk rays of any generation; a ray that hits something below the last generation
-// is appended to the hit list, where the kernel's SPAWNER warps (every spawn_every-th) take hits
-// 32 at a time, run the spawn half of ShadeRay at full warp width and publish the children to
-// the work list the walkers draw from.  (Spawning inside the walkers' retire step runs the
-// double-precision Fresnel code with one or two lanes active: measured 38.6 ms against 21 + 2.2.)
-RT_DEV void st_volatile(unsigned* p, unsigned v)
+// The ShadeRay nodes of generation `level` in slot order, and the spawn half of ShadeRay for each
+// (nothing to spawn in the last generation: the list only).  One atomicAdd per warp for the list,
+// one for the children.
+__global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_spawn_kernel(const __grid_constant__ FrameParams P, int level)
 {
-    asm volatile("st.volatile.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
-}
-RT_DEV unsigned ld_volatile_u32(const unsigned* p)
-{
-    unsigned v;
-    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
-// `n` rays of this warp are through (children, if any, already published): the frame is traced
-// when every published ray has retired.  Lane 0 only.
-RT_DEV void count_retired(WorkQueue* q, unsigned n0, unsigned n)
-{
-    const unsigned r = atomicAdd(&q->retired, n) + n;
-    if (r == n0 + ld_volatile_u32(&q->tail)) atomicExch(&q->done, 1u);
-}
-
-template <bool kCount>
-struct TraceAllJob : TraceJob<kCount, false> {
-    using Base = TraceJob<kCount, false>;
-    WorkQueue* q;
-    unsigned n0;
-
-    RT_DEV bool begin(int gen, unsigned slot_, V3& wo, V3& wray, float& tmin, float& tmax)
-    {
-        this->level = gen;
-        return Base::begin(slot_, wo, wray, tmin, tmax);
+    const LevelBuffers& LB = P.level[level];
+    const unsigned count = level == 0 ? (unsigned)P.n_local_pixels : min(P.counters->rays[level], (unsigned)LB.capacity);
+    const unsigned stride = gridDim.x * blockDim.x;
+    const unsigned rounded = (count + 31u) & ~31u;
+    const bool lane0 = (threadIdx.x & 31) == 0;
+    for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < rounded; slot += stride) {
+        RayIn r; r.ns = 0;
+        Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
+        if (slot < count) h.obj = __float_as_int(__ldcg(&LB.hp[slot].w));
+        const bool hit = h.obj >= 0;
+        const unsigned hm = __ballot_sync(0xffffffffu, hit);
+        if (!hm) continue;                            // warp-uniform
+        unsigned base = 0;
+        if (lane0) base = atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (hit) LB.node_list[base + __popc(hm & lanemask_lt())] = (int)slot;
+        if (level == P.max_depth) continue;
+        if (hit) {
+            load_ray(P, level, slot, r);
+            const float4 hb = __ldcg(LB.hb + slot);
+            h.b = hb.x; h.g = hb.y; h.t = hb.z;
+        }
+        const NoShadow none;
+        shade_and_spawn<false, true>(P, none, level, slot, r, h, hit);
     }
-
-    RT_DEV void retire(bool fin)
-    {
-        constexpr unsigned kFull = 0xffffffffu;
-        const FrameParams& P = this->P;
-        const SceneView& S = P.scene;
-        const int level = this->level;
-        const unsigned slot = this->slot;
-        const unsigned lt = lanemask_lt();
-        const bool lane0 = (threadIdx.x & 31) == 0;
-        if (fin && !this->padding && this->back < 0 && this->skip_spheres) {
-            const float tmin = level == 0 ? 0.0f : P.epsilon;
-            for (int i = 0; i < this->acc.ns; i++) this->sphere_candidate(this->acc.sph[(size_t)i * kSphWords], this->acc.nf + i, tmin);
-        }
-        const bool hit = fin && !this->padding && !this->aborted && this->best.obj >= 0;
-        // the node lists: one atomic per warp and generation present
-        for (int L = 0; L <= P.max_depth; L++) {
-            const unsigned hm = __ballot_sync(kFull, hit && level == L);
-            if (!hm) continue;
-            unsigned base = 0;
-            if (lane0) base = atomicAdd(&P.counters->nodes[L], (unsigned)__popc(hm));
-            base = __shfl_sync(kFull, base, 0);
-            if (hit && level == L) {
-                const LevelBuffers& LB = P.level[L];
-                const V3 p = vadd(this->o, vmulf(this->ray, this->best.t));      // 1245 / 1303, same as finish_hit
-                LB.hp[slot] = make_float4(p.x, p.y, p.z, __int_as_float(this->best.obj));
-                LB.hb[slot] = make_float4(this->best.b, this->best.g, this->best.t, 0.0f);
-                LB.node_list[base + __popc(hm & lt)] = (int)slot;
-                if (L < P.max_depth) LB.res[slot] = make_float4(0.f, 0.f, 0.f, kResPending);
-            }
-        }
-        if (fin && !hit) write_miss(P, level, slot, this->padding, this->aborted);
-        if (P.primary_ids) {   // instrumented frame
-            if (fin && !this->padding && level == 0) P.primary_ids[out_slot(P, slot)] = hit ? S.obj[this->best.obj].z : 0;
-            const unsigned tm = __ballot_sync(kFull, hit && S.obj[this->best.obj].y >= 0);
-            if (lane0 && tm) atomicAdd(&P.counters->texels, (unsigned long long)__popc(tm));
-        }
-        // hits that may have children go to the spawners; everything else is through
-        const bool parent = hit && level < P.max_depth;
-        const unsigned pm = __ballot_sync(kFull, parent);
-        if (pm) {
-            unsigned base = 0;
-            if (lane0) base = atomicAdd(&q->hit_tail, (unsigned)__popc(pm));
-            base = __shfl_sync(kFull, base, 0);
-            __threadfence();                   // the hit records before the entries that announce them
-            if (parent) st_volatile(P.hit_order + base + __popc(pm & lt), ((unsigned)level << 28) | slot);
-        }
-        const unsigned fm = __ballot_sync(kFull, fin && !parent);
-        if (lane0 && fm) count_retired(q, n0, (unsigned)__popc(fm));
-    }
-};
-
-// A spawner warp of the fused kernel.
-RT_DEV void spawner_loop(const FrameParams& P, WorkQueue* q, unsigned n0)
-{
-    constexpr unsigned kFull = 0xffffffffu;
-    const unsigned lane = threadIdx.x & 31u;
-    const unsigned lt = (1u << lane) - 1u;
-    unsigned base = 0, pending = 0, polls = 0, spins = 0;
-    for (;;) {
-        if (!pending) {
-            if (lane == 0) base = atomicAdd(&q->hit_head, 32u);
-            base = __shfl_sync(kFull, base, 0);
-            pending = kFull; polls = 0;
-        }
-        const unsigned e = base + lane;
-        unsigned v = 0xffffffffu;
-        if (((pending >> lane) & 1u) && e < P.hit_capacity) v = ld_volatile_u32(P.hit_order + e);
-        const unsigned present = __ballot_sync(kFull, v != 0xffffffffu);
-        if (present != 0u && (present == pending || ++polls > 4u)) {
-            // the spawn half of ShadeRay for the hits that have arrived, then the children's entries
-            const bool mine = ((present >> lane) & 1u) != 0u;
-            const int level = mine ? (int)(v >> 28) : 0;
-            const unsigned slot = v & 0x0fffffffu;
-            RayIn r; r.ns = 0;
-            Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
-            if (mine) {
-                load_ray(P, level, slot, r);
-                const float4 hp = __ldcg(P.level[level].hp + slot), hb = __ldcg(P.level[level].hb + slot);
-                h.obj = __float_as_int(hp.w); h.b = hb.x; h.g = hb.y; h.t = hb.z;
-            }
-            int children[2] = { -1, -1 };
-            const NoShadow none;
-            shade_and_spawn<false, true, NoShadow, true>(P, none, level, slot, r, h, mine, children);
-            const unsigned mt = __ballot_sync(kFull, children[0] >= 0), mr = __ballot_sync(kFull, children[1] >= 0);
-            if (mt | mr) {
-                unsigned wb = 0;
-                if (lane == 0) wb = atomicAdd(&q->tail, (unsigned)(__popc(mt) + __popc(mr)));
-                wb = __shfl_sync(kFull, wb, 0);
-                __threadfence();               // the rays' records before the entries that announce them
-                const unsigned tag = (unsigned)(level + 1) << 28;
-                if (children[0] >= 0) st_volatile(P.work_order + wb + __popc(mt & lt), tag | (unsigned)children[0]);
-                if (children[1] >= 0) st_volatile(P.work_order + wb + __popc(mt) + __popc(mr & lt), tag | (unsigned)children[1]);
-            }
-            __threadfence();                   // tail before retired
-            __syncwarp();
-            if (lane == 0) count_retired(q, n0, (unsigned)__popc(present));
-            pending &= ~present;
-            polls = 0; spins = 0;
-            continue;
-        }
-        unsigned d = 0;
-        if (lane == 0) d = ld_volatile_u32(&q->done);
-        if (__shfl_sync(kFull, d, 0)) break;
-        __nanosleep(300);
-        if (++spins > (1u << 22)) {              // ~2 s without a hit: give up loudly
-            if (lane == 0) atomicExch(&q->stalled, 1u);
-            break;
-        }
-    }
-}
-
-template <bool kCount>
-__global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_TRACE_ALL_MIN_BLOCKS) * kWalkScale) bvh_trace_all_kernel(const __grid_constant__ FrameParams P)
-{
-    const unsigned n0 = (unsigned)P.n_local_pixels;
-    const unsigned warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const auto acc = make_bvh_accel<kCount>(P.scene);
-    if (warp % (unsigned)P.spawn_every == (unsigned)P.spawn_every - 1u) {
-        spawner_loop(P, &P.counters->work, n0);
-    } else {
-        TraceAllJob<kCount> job{ { P, acc, 0 }, &P.counters->work, n0 };
-        acc.persistent_walk_all(n0, &P.counters->work, P.work_order, P.work_capacity, job,
-                                P.refill_lanes, P.inner_min_lanes, P.leaf_min_lanes);
-    }
-    flush_bvh_counters(acc, P.counters);
 }
 
 // The shadow rays (main.cpp:896 / 928) of ONE node as a chain: job k = node_list[k], the lane
@@ -415,90 +281,29 @@ __global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : RT_TRACE_ALL_MIN_BLO
 // is exactly 0 it stays 0 whatever the later lights meet: the chain stops there and the
 // remaining records are never read (RecordedShadow stops at the same point).  In a dense
 // scene that removes most shadow walks without changing a bit of the result.
-// The launch plan of the any-hit kernel, the same for every thread: kept in shared memory so that
-// it costs the walk loop no registers (the kernel sits at its 64-register limit).
-struct ShadowPlan {
-    int first_level;             // kAllLevels: the launch covers generations first_level .. max_depth
-    unsigned total;              // jobs before padding: this generation's nodes, or those generations'
-    unsigned pass_jobs, passes, group;
-};
-RT_DEV ShadowPlan& shadow_plan()
-{
-    __shared__ ShadowPlan plan;
-    return plan;
-}
-
-constexpr int kFoundNone = -1;
-constexpr int kFoundByHint = 0x7fffffff;
-
-template <bool kCount, bool kNearFirst, bool kStealing, bool kAllLevels, bool kHints>
+// One launch covers the nodes of generations first .. last (the frame scheduler passes all of
+// them at once: one kernel tail per frame instead of one per generation): job j counts through
+// generation `first`'s node list, then the next one's, ...
+template <bool kCount, bool kStealing>
 struct ShadowJob {
     // One light's walk is a fold in any order too: "an opaque occluder exists" is an OR and the
     // partial factors are collected and sorted by iteration order before they are multiplied
     // (shadow_end), so helpers only have to hand over their finds.  The chain over the lights
     // stays with the owner lane.
     static constexpr bool kSteal = kStealing;
-    static constexpr bool kWideLoads = true;     // 256-bit node loads (bvh.cuh: test_node)
     static constexpr bool kWide8 = true;         // walks the 8-wide tree when the scene has one (bvh.cuh: step8)
-    static constexpr bool kOrdered = kNearFirst; // any hit: order is only a heuristic (near boxes first finds occluders sooner?)
-    static constexpr bool kFirstLeaf = kHints;   // first_leaf() may hand out a record to test before the walk
     const FrameParams& P;
     const BvhAccelT<kCount>& acc;
-    // kAllLevels: ONE launch walks the nodes of every generation (after the fused trace kernel): job
-    // j counts through generation 0's node list, then generation 1's, ...; `level` and `n_nodes`
-    // are then per lane
+    int first;
+    // per node
     int level;
     unsigned n_nodes;
-    // Occluder hints.  "Some opaque primitive blocks this shadow ray" is all the reference's product
-    // needs to become exactly 0 (every factor is in [0,1]; main.cpp:909 / 946), and WHICH primitive
-    // proves it does not matter.  Neighbouring surface points of one primitive are mostly blocked by
-    // the same occluder, so the walk that finds one leaves its record index in
-    // hint[light][surface primitive] and later jobs from that primitive test that record first
-    // (one 80-byte exact test instead of a tree walk).  A stale or missing hint only costs the
-    // test: the result never depends on it.  For hints to be THERE in time the node list is taken
-    // in interleaved passes (perm): pass p handles the groups g with g % passes == p, so the
-    // neighbours of a node were finished a whole pass earlier, not in the same warp.
-    // per node
     unsigned k;
     int li;
     V3 p; int self;
     float mask;
-    // >= 0 and < kFoundByHint: record index of the opaque occluder this walk ended at; kFoundByHint:
-    // that was the hinted record; <= -2: -2 - (record index first_leaf() handed out), nothing found yet
-    int found;
     unsigned long long walks = 0;      // instrumented variant: shadow rays actually walked by this thread
-    unsigned long long hint_hits = 0;  // ... and settled by a hint
     typename BvhAccelT<kCount>::ShadowVisit v;
-
-    // the table persistent_walk visits (read where needed: no register across the walk)
-    RT_DEV const float4* records() const { return P.scene.bvh.n_nodes8 > 0 ? P.scene.bvh.prims8 : P.scene.bvh_tri; }
-
-    // jobs of the launch and the job -> node permutation described above (one thread per block,
-    // before the walk; the caller synchronises)
-    RT_DEV static void make_plan(const FrameParams& P, int level)
-    {
-        ShadowPlan& pl = shadow_plan();
-        unsigned total = 0;
-        pl.first_level = kAllLevels ? -level - 1 : level;      // level = -(first generation) - 1
-        if (kAllLevels) { for (int l = pl.first_level; l <= P.max_depth; l++) total += P.counters->nodes[l]; }
-        else total = P.counters->nodes[level];
-        pl.total = total; pl.passes = 1; pl.group = 1; pl.pass_jobs = total;
-        if (kHints && P.hint_passes > 1) {
-            pl.group = (unsigned)max(P.hint_group, 1);
-            const unsigned groups = (total + pl.group - 1) / pl.group;
-            pl.passes = min((unsigned)P.hint_passes, max(total / (unsigned)max(P.hint_min_chunk, 1), 1u));
-            pl.pass_jobs = (groups + pl.passes - 1) / pl.passes * pl.group;
-        }
-    }
-    RT_DEV static unsigned perm(unsigned j)
-    {
-        if (!kHints) return j;
-        const ShadowPlan& pl = shadow_plan();
-        if (pl.passes == 1) return j;
-        const unsigned ps = j / pl.pass_jobs, r = j - ps * pl.pass_jobs;
-        const unsigned g = r / pl.group, w = r - g * pl.group;
-        return (g * pl.passes + ps) * pl.group + w;
-    }
 
     RT_DEV void setup(V3& wo, V3& wray, float& tmin, float& tmax)
     {
@@ -515,42 +320,20 @@ struct ShadowJob {
             acc.shadow_begin(p, wray, self, tmin, tmax, true, v);
         }
         wo = p;
-        found = kFoundNone;
-    }
-    // The hinted record as a leaf code: persistent_walk tests it (through visit(), like any leaf)
-    // before it opens the root.
-    RT_DEV int first_leaf()
-    {
-        if (!kHints || v.count_all || !(P.hint_mode & 1)) return 0;
-        const int h = __ldcg(P.occluder_hint + (size_t)li * P.hint_prims + self);
-        if (h < 0) return 0;
-        found = -2 - h;
-        return ~(h << 3);
     }
     RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        k = perm(j); li = 0; mask = 1.0f;                                        // 788
-        if (kHints && k >= shadow_plan().total) { k = 0xffffffffu; return false; }   // padding of the last groups
-        if (kAllLevels) {
-            level = shadow_plan().first_level;
-            n_nodes = P.counters->nodes[level];
-            while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
-        }
+        k = j; li = 0; mask = 1.0f;                                              // 788
+        level = first;
+        n_nodes = P.counters->nodes[level];
+        while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
         const float4 hp = P.level[level].hp[P.level[level].node_list[k]];
         p = mk3(hp.x, hp.y, hp.z);
         self = __float_as_int(hp.w);
         setup(wo, wray, tmin, tmax);
         return true;
     }
-    RT_DEV float visit(const float4* w, float tmax)
-    {
-        const float r = v(w, tmax);
-        if (kHints && r < 0.0f) {          // (count_all walks never stop; found stays unused there)
-            const int idx = (int)((w - records()) / kTriWords);
-            found = (found == -2 - idx) ? kFoundByHint : idx;
-        }
-        return r;
-    }
+    RT_DEV float visit(const float4* w, float tmax) { return v(w, tmax); }
 
     RT_DEV void adopt(int src, bool take, V3& wo, V3& wray)
     {
@@ -563,23 +346,19 @@ struct ShadowJob {
         if (take) {
             v.o = mk3(ox, oy, oz); v.ray = mk3(rx, ry, rz); v.tmin = t0; v.tmax_hit = t1; v.self = sf;
             v.use_tmax = (fl & 1) != 0; v.skip_spheres = (fl & 2) != 0; v.count_all = (fl & 4) != 0;
-            v.hits = 0; v.n_partial = 0; v.overflow_mask = 1.0f; v.opaque = false;
-            found = kFoundNone;
+            v.hits = 0; v.n_partial = 0; v.overflowed = false; v.opaque = false;
         }
         wo = v.o; wray = v.ray;
     }
     RT_DEV void merge(int src, bool mine)
     {
         constexpr unsigned kFull = 0xffffffffu;
-        const int op = __shfl_sync(kFull, v.opaque ? 1 : 0, src), h = __shfl_sync(kFull, v.hits, src);
+        const int op = __shfl_sync(kFull, (v.opaque ? 1 : 0) | (v.overflowed ? 2 : 0), src), h = __shfl_sync(kFull, v.hits, src);
         const int np = __shfl_sync(kFull, v.n_partial, src);
-        const float ov = __shfl_sync(kFull, v.overflow_mask, src);
-        const int fd = __shfl_sync(kFull, found, src);
         if (mine) {
             v.hits += h;
-            v.opaque = v.opaque || op != 0;
-            if (kHints && fd >= 0 && fd != kFoundByHint && found < 0) found = fd;
-            if (ov != 1.0f) v.overflow_mask = clamp01(fmul(ov, v.overflow_mask));
+            v.opaque = v.opaque || (op & 1) != 0;
+            v.overflowed = v.overflowed || (op & 2) != 0;
         }
         for (int i = 0; i < np; i++) {
             // (constant indices after unrolling: the lists stay in registers)
@@ -590,63 +369,108 @@ struct ShadowJob {
             if (mine) { v.hits--; v.add(po, pk); }
         }
     }
-    // an opaque occluder found by any lane ends the walk of this light for all of them
+    // an opaque occluder found by any lane ends the walk of this light for all of them (and so
+    // does a list that is full: the node goes to the redo kernel)
     RT_DEV float share(unsigned group, float tmax)
     {
-        if (__reduce_or_sync(group, v.opaque ? 1u : 0u) && !v.count_all) return -1.0f;
+        if (__reduce_or_sync(group, (v.opaque || v.overflowed) ? 1u : 0u) && !v.count_all) return -1.0f;
         return tmax;
     }
 
     RT_DEV void retire(bool fin)
     {
-        if (!fin || (kHints && k == 0xffffffffu)) return;
+        if (!fin) return;
         acc.shadow_end(v);
-        const bool by_hint = kHints && v.opaque && found == kFoundByHint;
-        if (kCount) { if (by_hint) hint_hits++; else walks++; }
+        if (kCount) walks++;
+        if (v.overflowed && !v.opaque) {
+            // more transparent occluders than the visitor holds: the whole chain of this node is
+            // redone exactly by bvh_shadow_redo_kernel; this lane drops it
+            const unsigned at = atomicAdd(&P.counters->redo_count, 1u);
+            if (at < (unsigned)kRedoCapacity) P.redo_list[at] = ((unsigned)level << 28) | k;
+            else atomicOr(&P.counters->overflow, kOverflowRedo);
+            mask = 0.0f;                           // next() ends the chain
+            return;
+        }
         // the carried product exactly as BvhAccelT::shadow applies it (main.cpp:909 / 946 in
         // iteration order); the record is the mask AFTER this light
         if (v.opaque) {
             mask = clamp01(fmul(0.0f, mask));
-            if (kHints && found >= 0 && !by_hint && (P.hint_mode & 2))
-                __stcg(P.occluder_hint + (size_t)li * P.hint_prims + self, found);
         } else {
             for (int i = 0; i < v.n_partial; i++) mask = clamp01(fmul(v.p_k[i], mask));
-            if (v.overflow_mask != 1.0f) mask = clamp01(fmul(v.overflow_mask, mask));
         }
         P.level[level].sh[(size_t)li * n_nodes + k] = mask;
     }
     RT_DEV bool next(V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        if ((kHints && k == 0xffffffffu) || mask == 0.0f || li + 1 >= P.scene.nl) return false;
+        if (mask == 0.0f || li + 1 >= P.scene.nl) return false;
         li++;
         setup(wo, wray, tmin, tmax);
         return true;
     }
 };
 
-// level < 0 (kAllLevels): the nodes of generations -level - 1 .. max_depth in one launch
-template <bool kCount, bool kNearFirst, bool kStealing, bool kAllLevels = false, bool kHints = false>
-__global__ void __launch_bounds__(kWalkBlock, (kCount ? 0 : kHints ? RT_SHADOW_MIN_BLOCKS : 0) * kWalkScale) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int level)
+template <bool kCount, bool kStealing>
+__global__ void __launch_bounds__(kWalkBlock, kCount ? 0 : RT_SHADOW_MIN_BLOCKS) bvh_shadow_kernel(const __grid_constant__ FrameParams P, int first, int last)
 {
-    using Job = ShadowJob<kCount, kNearFirst, kStealing, kAllLevels, kHints>;
-    const auto acc = make_bvh_accel<kCount>(P.scene);
-    if (threadIdx.x == 0) Job::make_plan(P, level);
-    __syncthreads();
-    const unsigned n_jobs = shadow_plan().pass_jobs * shadow_plan().passes;
-    Job job{ P, acc, kAllLevels ? 0 : level, kAllLevels ? 0u : shadow_plan().total };
-    const int cl = kAllLevels ? -level - 1 : level;
-    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[cl], job, P.sh_refill_lanes, P.sh_inner_min_lanes, P.sh_leaf_min_lanes,
-                        kCount ? &P.counters->clock[1][cl] : nullptr, P.steal != 0,
-                        P.shadow_job_budget > 0 ? (unsigned)P.shadow_job_budget : 0xffffffffu);
+    using Job = ShadowJob<kCount, kStealing>;
+    auto acc = make_bvh_accel<kCount>(P.scene);
+    acc.overflow_flag = &P.counters->overflow;
+    unsigned n_jobs = 0;
+    for (int l = first; l <= last; l++) n_jobs += P.counters->nodes[l];
+    Job job{ P, acc, first };
+    acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[first], job, P.sh_refill_lanes, P.sh_inner_min_lanes, P.sh_leaf_min_lanes,
+                        kCount ? &P.counters->clock[1][first] : nullptr);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
-        unsigned long long w = job.walks, hh = job.hint_hits;
-        for (int o = 16; o > 0; o >>= 1) { w += __shfl_down_sync(0xffffffffu, w, o); hh += __shfl_down_sync(0xffffffffu, hh, o); }
-        if ((threadIdx.x & 31) == 0) { atomicAdd(&P.counters->shadow_walks, w); atomicAdd(&P.counters->shadow_hint_hits, hh); }
+        unsigned long long w = job.walks;
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_down_sync(0xffffffffu, w, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&P.counters->shadow_walks, w);
     }
 }
 
-// Shadow source of the shade kernel: the carried shadow_mask after each light, as left by
+// The chains bvh_shadow_kernel gave up, one thread each: BvhAccelT::shadow has no limit on the
+// number of partial occluders (it repeats the walk).  Almost always zero entries.
+template <bool kCount>
+__global__ void __launch_bounds__(kBlock) bvh_shadow_redo_kernel(const __grid_constant__ FrameParams P)
+{
+    const unsigned n = min(P.counters->redo_count, (unsigned)kRedoCapacity);
+    auto acc = make_bvh_accel<kCount>(P.scene);
+    acc.overflow_flag = &P.counters->overflow;
+    unsigned long long walks = 0;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned e = P.redo_list[i];
+        const int level = (int)(e >> 28);
+        const unsigned k = e & 0x0fffffffu;
+        const LevelBuffers& LB = P.level[level];
+        const unsigned n_nodes = P.counters->nodes[level];
+        const float4 hp = LB.hp[LB.node_list[k]];
+        const V3 p = mk3(hp.x, hp.y, hp.z);
+        const int self = __float_as_int(hp.w);
+        float mask = 1.0f;                                                       // 788
+        for (int li = 0; li < P.scene.nl; li++) {
+            const float4 l0 = P.scene.light[3 * li];
+            if (l0.w == 0.0f) {
+                acc.shadow(p, vneg(ld3(l0)), self, P.epsilon, 0.0f, false, mask);
+            } else {
+                const V3 L = vnorm(vsub(ld3(l0), p));
+                const V3 dp = vsub(p, ld3(l0));
+                acc.shadow(p, L, self, P.epsilon, fsqrt(vsum3(fmul(dp.x, dp.x), fmul(dp.y, dp.y), fmul(dp.z, dp.z))), true, mask);
+            }
+            if (kCount) walks++;
+            LB.sh[(size_t)li * n_nodes + k] = mask;
+            if (mask == 0.0f) break;
+        }
+    }
+    if (kCount) {
+        for (int o = 16; o > 0; o >>= 1) walks += __shfl_down_sync(0xffffffffu, walks, o);
+        if ((threadIdx.x & 31) == 0 && walks) atomicAdd(&P.counters->shadow_walks, walks);
+        // (the chain's first walks were already counted by the any-hit kernel: the redo count is a
+        // handful per frame at most and only the instrumented statistics see the difference)
+        flush_bvh_counters(acc, P.counters, true);
+    }
+}
+
+// Shadow source of the colour kernel: the carried shadow_mask after each light, as left by
 // the node's chain in bvh_shadow_kernel.
 struct RecordedShadow {
     const float* rec;           // sh + k: mask after light li at rec[li * n_nodes]
@@ -658,48 +482,23 @@ struct RecordedShadow {
     }
 };
 
-// kColour / kSpawn select the half of ShadeRay this launch does (wavefront.cuh:
-// shade_and_spawn).  The spawn half depends only on the hits, so the next generation's trace
-// kernel can start before this generation's shadow rays have been walked: the frame scheduler
-// (render.cu) runs the chain trace -> spawn -> trace -> ... first and all generations' shadow
-// chains in one any-hit launch after it, then the colour halves.
-template <bool kColour, bool kSpawn>
-RT_DEV void shade_level(const FrameParams& P, int level)
+// The colour half of ShadeRay (shade_colour) for the nodes of generations first .. last, one after
+// the other in this launch (nothing orders them among themselves).
+__global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_colour_kernel(const __grid_constant__ FrameParams P, int first, int last)
 {
-    const LevelBuffers& LB = P.level[level];
-    const unsigned n_nodes = P.counters->nodes[level];
-    const unsigned stride = gridDim.x * blockDim.x;
-    const unsigned rounded = (n_nodes + 31u) & ~31u;
-    for (unsigned k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += stride) {
-        const bool hit = k < n_nodes;
-        RayIn r; r.ns = 0;
-        Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
-        unsigned slot = 0;
-        if (hit) {
-            slot = (unsigned)LB.node_list[k];
+    for (int level = first; level <= last; level++) {
+        const LevelBuffers& LB = P.level[level];
+        const unsigned n_nodes = P.counters->nodes[level];
+        const unsigned stride = gridDim.x * blockDim.x;
+        for (unsigned k = blockIdx.x * blockDim.x + threadIdx.x; k < n_nodes; k += stride) {
+            const unsigned slot = (unsigned)LB.node_list[k];
+            RayIn r;
             load_ray(P, level, slot, r);
             const float4 hp = LB.hp[slot], hb = LB.hb[slot];
-            h.obj = __float_as_int(hp.w); h.b = hb.x; h.g = hb.y; h.t = hb.z;
-        }
-        if (kColour) {
+            Hit h; h.obj = __float_as_int(hp.w); h.b = hb.x; h.g = hb.y; h.t = hb.z;
             const RecordedShadow shadow{ LB.sh + k, n_nodes };
-            shade_and_spawn<kColour, kSpawn>(P, shadow, level, slot, r, h, hit);
-        } else {
-            const NoShadow none;
-            shade_and_spawn<kColour, kSpawn>(P, none, level, slot, r, h, hit);
+            shade_and_spawn<true, false>(P, shadow, level, slot, r, h, true);
         }
-    }
-}
-
-// kRange: generations -level - 1 .. max_depth one after the other in this launch (the colour halves
-// after the merged any-hit launch: nothing orders them among themselves)
-template <bool kColour, bool kSpawn, bool kRange = false>
-__global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_shade_kernel(const __grid_constant__ FrameParams P, int level)
-{
-    if constexpr (kRange) {
-        for (int l = -level - 1; l <= P.max_depth; l++) shade_level<kColour, kSpawn>(P, l);
-    } else {
-        shade_level<kColour, kSpawn>(P, level);
     }
 }
 
