@@ -91,7 +91,7 @@ struct PinnedBuf {
 // travels with the Workspace.
 struct ChainStreams {
     cudaStream_t main[kMaxSubframes] = { nullptr }, side[kMaxSubframes] = { nullptr };
-    cudaEvent_t fork[kMaxSubframes][kMaxLevels] = { { nullptr } };
+    cudaEvent_t fork[kMaxSubframes] = { nullptr };
     cudaEvent_t side_done[kMaxSubframes] = { nullptr }, main_done[kMaxSubframes] = { nullptr }, begin = nullptr;
     int chains = 0;      // chains whose streams / events exist
     ChainStreams() = default;
@@ -113,7 +113,7 @@ private:
         for (int j = 0; j < kMaxSubframes; j++) {
             main[j] = o.main[j]; side[j] = o.side[j]; side_done[j] = o.side_done[j]; main_done[j] = o.main_done[j];
             o.main[j] = o.side[j] = nullptr; o.side_done[j] = o.main_done[j] = nullptr;
-            for (int l = 0; l < kMaxLevels; l++) { fork[j][l] = o.fork[j][l]; o.fork[j][l] = nullptr; }
+            fork[j] = o.fork[j]; o.fork[j] = nullptr;
         }
         begin = o.begin; o.begin = nullptr;
         chains = o.chains; o.chains = 0;
@@ -127,9 +127,7 @@ struct Workspace {
     DevBuf counters;
     DevBuf tiles;          // RGBA8 [local_tile][row][col]
     DevBuf primary_ids;
-    DevBuf hit_order;      // ... and its hit list (hits waiting for the spawn half of ShadeRay)
-    DevBuf work_order;     // fused trace kernel: the work list (one entry per spawned ray)
-    DevBuf hints;          // occluder hints of the any-hit kernel: (nf + ns) * nl ints
+    DevBuf redo_list;      // shadow chains for the slow exact path: kRedoCapacity entries per sub-frame
     DevBuf rgb24, flags8;  // scanline-order planes for rt_download_framebuffer
     ChainStreams chains;
     PinnedBuf h_counters;  // one Counters per sub-frame
@@ -153,6 +151,7 @@ struct SceneHost {
     DevBuf bvh_nodes, bvh_tri, bvh_sph;
     DevBuf bvh8_nodes, bvh8_prims;      // the 8-wide tree of the any-hit walk (bvh.cu: collapse8_kernel)
     int bvh_n_nodes = 0, bvh_root = 0, bvh8_n_nodes = 0;
+    int bvh_levels4 = 0, bvh_levels8 = 0;   // depth of the two trees (build_bvh checks them against the walk stacks)
     bool bvh_built = false;
 
     CameraView cam{};
@@ -192,8 +191,9 @@ TileLayout tile_layout(int height, int width, int world, int tile_rows);
 int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cudaStream_t stream, int* launches);
 int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* demand /* per level or null */);
 // Reads the counters of the last frame (stream must be idle): sums the sub-frames into `total`,
-// returns true when some queue overflowed and then fills `demand` with what to grow to.
-bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels]);
+// returns the frame's kOverflow* bits (0 = complete); with kOverflowQueue `demand` says what to grow to.
+unsigned frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels]);
+int overflow_error(unsigned bits);      // RT_OK, or RT_E_LIMIT + message for the bits no regrow cures
 void stash_workspace(Workspace&& ws);
 
 // ppm_device.cu

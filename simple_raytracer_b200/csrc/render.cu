@@ -80,28 +80,76 @@ void stash_workspace(Workspace&& ws)
     g_ws_cache_valid = true;
 }
 
-static size_t level_bytes(int level, size_t cap, bool bvh, int nl)
+// Bytes of one queue slot of generation `level` (fill_levels lays the arrays out).
+static size_t slot_bytes(int level, bool bvh, int nl)
 {
     // level 0 has no ray queue (primary rays are generated in place)
     size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16 + 8;
     if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 4;    // hp, hb, node_list, sh (wavefront_bvh.cuh)
-    // slop: every sub-frame's slice starts on a 256-byte boundary
-    return cap * per_slot + 512 * (kMaxSubframes + 1);
+    return per_slot;
 }
 
-// Launch chains of a frame.  Sub-frames only pay when the per-kernel tails are a large part
-// of the frame (few pixels per GPU); profiled / instrumented frames and the brute-force
-// path run as one serial chain.
+// One sub-frame's slice of a generation's memory: its arrays, the slice rounded up to 256 bytes.
+static size_t slice_bytes(int level, size_t cap, bool bvh, int nl)
+{
+    return (cap * slot_bytes(level, bvh, nl) + 64 + 255) / 256 * 256;
+}
+
+// ... and the whole generation: enough for any split into 1..kMaxSubframes slices of cap / K slots
+// (K slices of cap / K slots need at most cap * per_slot + K * (64 + 255) bytes).
+static size_t level_bytes(int level, size_t cap, bool bvh, int nl)
+{
+    return cap * slot_bytes(level, bvh, nl) + (size_t)kMaxSubframes * (64 + 256);
+}
+
+// Tuning of the LBVH pipeline.  These are the measured optima on B200 (sweeps under
+// profiles/); a product build has no other source for them.  A lab build (-DRT_TUNING_ENV) lets the
+// environment override each one for sweeps (RT_<NAME>).
+struct Tuning {
+    int refill_lanes = 6;            // a warp fetches new rays when this many lanes are idle
+    int inner_min_lanes = 8;         // closest hit: leave the inner-node loop below this many descending lanes
+    int leaf_min_lanes = 8;          // ... and the leaf loop below this many leaf holders
+    int sh_refill_lanes = 6, sh_inner_min_lanes = 6, sh_leaf_min_lanes = 6;   // the same for the any-hit kernel
+    int grid_mult = 16;              // persistent grids: blocks per SM asked for (the hardware keeps 7-8 resident)
+    int subframes = 0;               // launch chains per frame: 0 = 2 from subframe_min_kpixels on, 1 below
+    int subframe_min_kpixels = 3000;
+    int steal_max_krays = 1500;      // closest-hit launches of at most this many thousand slots share work in their tail
+    int steal_shadow_max_kpixels = 2500;   // ... the any-hit launch of chains of at most this many thousand pixels
+    int colour_merge_max_kpixels = 2500;   // ... whose colour halves then also run as one launch
+};
+
+static const Tuning& tuning()
+{
+    static const Tuning t = [] {
+        Tuning v;
+#ifdef RT_TUNING_ENV
+        v.refill_lanes = tuning_int("RT_REFILL_LANES", v.refill_lanes, 1, 32);
+        v.inner_min_lanes = tuning_int("RT_INNER_MIN_LANES", v.inner_min_lanes, 1, 32);
+        v.leaf_min_lanes = tuning_int("RT_LEAF_MIN_LANES", v.leaf_min_lanes, 1, 32);
+        v.sh_refill_lanes = tuning_int("RT_SHADOW_REFILL_LANES", v.sh_refill_lanes, 1, 32);
+        v.sh_inner_min_lanes = tuning_int("RT_SHADOW_INNER_MIN_LANES", v.sh_inner_min_lanes, 1, 32);
+        v.sh_leaf_min_lanes = tuning_int("RT_SHADOW_LEAF_MIN_LANES", v.sh_leaf_min_lanes, 1, 32);
+        v.grid_mult = tuning_int("RT_GRID_MULT", v.grid_mult, 1, 64);
+        v.subframes = tuning_int("RT_SUBFRAMES", v.subframes, 0, kMaxSubframes);
+        v.subframe_min_kpixels = tuning_int("RT_SUBFRAME_MIN_KPIXELS", v.subframe_min_kpixels, 0, 1 << 30);
+        v.steal_max_krays = tuning_int("RT_STEAL_MAX_KRAYS", v.steal_max_krays, 0, 1 << 30);
+        v.steal_shadow_max_kpixels = tuning_int("RT_STEAL_SHADOW_MAX_KPIXELS", v.steal_shadow_max_kpixels, 0, 1 << 30);
+        v.colour_merge_max_kpixels = tuning_int("RT_COLOUR_MERGE_MAX_KPIXELS", v.colour_merge_max_kpixels, 0, 1 << 30);
+#endif
+        return v;
+    }();
+    return t;
+}
+
+// Launch chains of a frame.  Two interleaved chains pay when one chain's kernel tails are a small
+// part of its launches (many pixels per GPU: the other chain's blocks fill them); below that one
+// chain is faster.  Profiled frames and the brute-force path run one serial chain.
 static int pick_subframes(const RtRenderParams& p, int accel, const TileLayout& tl)
 {
-    if (accel != RT_ACCEL_LBVH || p.profile || p.instrument) return 1;
-    static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
-    if (!overlap_knob) return 1;
-    static const int knob = tuning_int("RT_SUBFRAMES", 0, 0, kMaxSubframes);
-    int k = p.subframes ? p.subframes : knob;
-    // measured (tools/merge_sweep2.sh, two-phase frame): two interleaved chains pay from about 3 M pixels
-    // per rank on (4K: 40.1 -> 39.3 ms whole, 21.2 -> 20.5 ms half), one chain below; see DESIGN.md 5.4
-    if (k == 0) k = tl.n_local_pixels >= 3000000 ? 2 : 1;
+    if (accel != RT_ACCEL_LBVH || p.profile) return 1;
+    const Tuning& T = tuning();
+    int k = p.subframes ? p.subframes : T.subframes;
+    if (k == 0) k = (long long)tl.n_local_pixels >= 1000LL * T.subframe_min_kpixels ? 2 : 1;
     return std::max(1, std::min(k, tl.n_local_tiles));
 }
 
@@ -114,9 +162,8 @@ bool ChainStreams::ensure(int n)
         if (!cuda_ok(cudaDeviceGetStreamPriorityRange(&lo, &hi), "cudaDeviceGetStreamPriorityRange")) return false;
         if (!cuda_ok(cudaStreamCreateWithPriority(&main[j], cudaStreamNonBlocking, hi), "cudaStreamCreate")) return false;
         if (!cuda_ok(cudaStreamCreateWithPriority(&side[j], cudaStreamNonBlocking, lo), "cudaStreamCreate")) return false;
-        for (int l = 0; l < kMaxLevels; l++)
-            if (!cuda_ok(cudaEventCreateWithFlags(&fork[j][l], cudaEventDisableTiming), "cudaEventCreate")) return false;
-        if (!cuda_ok(cudaEventCreateWithFlags(&side_done[j], cudaEventDisableTiming), "cudaEventCreate") ||
+        if (!cuda_ok(cudaEventCreateWithFlags(&fork[j], cudaEventDisableTiming), "cudaEventCreate") ||
+            !cuda_ok(cudaEventCreateWithFlags(&side_done[j], cudaEventDisableTiming), "cudaEventCreate") ||
             !cuda_ok(cudaEventCreateWithFlags(&main_done[j], cudaEventDisableTiming), "cudaEventCreate")) return false;
         chains = j + 1;
     }
@@ -138,11 +185,8 @@ void ChainStreams::release()
         if (side[j]) cudaStreamDestroy(side[j]);
         if (side_done[j]) cudaEventDestroy(side_done[j]);
         if (main_done[j]) cudaEventDestroy(main_done[j]);
-        main[j] = side[j] = nullptr; side_done[j] = main_done[j] = nullptr;
-        for (int l = 0; l < kMaxLevels; l++) {
-            if (fork[j][l]) cudaEventDestroy(fork[j][l]);
-            fork[j][l] = nullptr;
-        }
+        if (fork[j]) cudaEventDestroy(fork[j]);
+        main[j] = side[j] = nullptr; side_done[j] = main_done[j] = fork[j] = nullptr;
     }
     if (begin) cudaEventDestroy(begin);
     begin = nullptr;
@@ -176,7 +220,7 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
     s->h_counters = static_cast<Counters*>(ws.h_counters.p);
     if (!ws.counters.reserve(sizeof(Counters) * kMaxSubframes) || !ws.tiles.reserve(npx * sizeof(uchar4))) return RT_E_NOMEM;
     if (p.instrument && !ws.primary_ids.reserve(npx * sizeof(int))) return RT_E_NOMEM;
-    if (bvh && s->nl > 0 && !ws.hints.reserve((size_t)(s->nf + s->ns) * s->nl * sizeof(int))) return RT_E_NOMEM;
+    if (bvh && !ws.redo_list.reserve((size_t)kRedoCapacity * kMaxSubframes * sizeof(unsigned))) return RT_E_NOMEM;
     for (int l = 0; l <= p.max_depth; l++) {
         size_t want;
         // level 0: one slot per pixel; the sub-frames' virtual layouts pad up to one tile each
@@ -187,20 +231,12 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
             static const double guess[kMaxLevels] = { 1.0, 1.25, 0.75, 0.5, 0.5, 0.5, 0.5, 0.5 };
             want = std::max<size_t>((size_t)ws.capacity[l], (size_t)(npx * guess[l]) + 1024);
         }
-        if (want > 0x7ffffff0u) { set_error("wavefront queue would exceed 2^31 slots"); return RT_E_NOMEM; }
+        if (want > 0x0ffffff0u) { set_error("wavefront queue would exceed 2^28 slots"); return RT_E_NOMEM; }
         want = std::max<size_t>(want, (size_t)ws.capacity[l]);
         if ((size_t)ws.capacity[l] < want || ws.level_mem[l].bytes < level_bytes(l, want, bvh, s->nl)) {
             if (!ws.level_mem[l].reserve(level_bytes(l, want, bvh, s->nl))) return RT_E_NOMEM;
             ws.capacity[l] = (int)want;
         }
-    }
-    if (bvh) {
-        size_t entries = 0;
-        for (int l = 1; l <= p.max_depth; l++) entries += (size_t)ws.capacity[l];
-        if (!ws.work_order.reserve(std::max<size_t>(entries, 1) * sizeof(unsigned))) return RT_E_NOMEM;
-        size_t hits = 0;
-        for (int l = 0; l < p.max_depth; l++) hits += l == 0 ? npx + (size_t)kMaxSubframes * p.tile_rows * s->width : (size_t)ws.capacity[l];
-        if (!ws.hit_order.reserve(std::max<size_t>(hits, 1) * sizeof(unsigned))) return RT_E_NOMEM;
     }
     return RT_OK;
 }
@@ -219,8 +255,7 @@ static void fill_levels(const SceneHost* s, int max_depth, bool bvh, int K, int 
         std::memset(&L, 0, sizeof L);
         if (l > max_depth) continue;
         const size_t cap = chain_capacity(s, l, K, chain_pixels);
-        const size_t slice = (level_bytes(l, cap, bvh, s->nl) - 512 * kMaxSubframes + 255) / 256 * 256;
-        char* base = ws.level_mem[l].as<char>() + (size_t)j * slice;
+        char* base = ws.level_mem[l].as<char>() + (size_t)j * slice_bytes(l, cap, bvh, s->nl);
         L.capacity = (int)cap;
         if (l > 0) {
             L.rq_o = (float4*)base; base += cap * 16;
@@ -250,25 +285,46 @@ static void launch_level(const FrameParams& P, int level, int grid, size_t smem,
     level_kernel<Factory><<<grid, kBlock, smem, st>>>(P, level);
 }
 
-// ... of a walk kernel (blocks of kWalkBlock threads; mult counts 128-thread blocks per SM)
-static int walk_grid(long long work, int sms, int mult)
+// Persistent grids: whole waves of resident blocks, never more blocks than there is work.
+static int persistent_grid(long long work, int sms, int mult, int block = kBlock)
 {
-    return (int)std::max<long long>(1, std::min<long long>((work + kWalkBlock - 1) / kWalkBlock, (long long)sms * mult * kWalkScale));
+    return (int)std::max<long long>(1, std::min<long long>((work + block - 1) / block, (long long)sms * mult));
 }
 
-static int persistent_grid(long long work, int sms, int mult)
+template <bool kCount>
+static void launch_trace(const FrameParams& P, int level, bool sharing, int grid, cudaStream_t st)
 {
-    return (int)std::max<long long>(1, std::min<long long>((work + kBlock - 1) / kBlock, (long long)sms * mult));
+    if (sharing) bvh_trace_kernel<kCount, true><<<grid, kWalkBlock, 0, st>>>(P, level);
+    else bvh_trace_kernel<kCount, false><<<grid, kWalkBlock, 0, st>>>(P, level);
+}
+
+template <bool kCount>
+static void launch_shadow(const FrameParams& P, int first, int last, bool sharing, int grid, cudaStream_t st)
+{
+    if (sharing) bvh_shadow_kernel<kCount, true><<<grid, kWalkBlock, 0, st>>>(P, first, last);
+    else bvh_shadow_kernel<kCount, false><<<grid, kWalkBlock, 0, st>>>(P, first, last);
+    // the chains it gave up (a handful at most): a few blocks that find the list empty otherwise
+    bvh_shadow_redo_kernel<kCount><<<8, kBlock, 0, st>>>(P);
 }
 
 // Enqueues one frame on `stream`.  The queues must already be sized (ensure_workspace).
 //
-// LBVH pipeline: the rank's tiles are dealt out to K sub-frames (tile t of the rank's buffer
-// -> sub-frame t % K), each a complete, independent chain of generation launches with its own
-// queues and counters: trace(g) -> spawn(g) -> trace(g+1) ... on one stream and
-// shadow(g) -> colour(g) on a second one.  A persistent walk kernel ends with a tail in which
-// a few long rays keep a few warps busy; with 2K streams the other chains' blocks fill the
-// SMs during that tail (the frame of a 1/8 shard is otherwise half tails).
+// Brute force (scenes of at most 48 primitives): one fused level_kernel per generation, then the
+// bottom-up combine passes.
+//
+// LBVH pipeline: the rank's tiles are dealt out to K sub-frames (tile t of the rank's buffer ->
+// sub-frame t % K), each a complete, independent chain with its own queues and counters.  A chain
+// runs in two phases:
+//   1. trace(0) -> spawn(0) -> trace(1) -> ... -> trace(D) -> spawn(D)  (spawn(D) only lists the hits)
+//      on the chain's main stream: the closest-hit rays do not depend on the shadow rays;
+//   2. ONE any-hit launch over the nodes of all generations, the redo of what it gave up, the colour
+//      halves (one launch for small chains, one per generation otherwise) on the chain's side stream,
+//      then the bottom-up combine passes on the main stream again.
+// A persistent walk kernel ends with a tail in which a few long rays keep a few warps busy; with
+// two chains (large frames) the other chain's blocks fill the SMs during that tail.
+// Instrumented frames (params.instrument) run the very same schedule with the counting builds of
+// the walk kernels; profiled frames (params.profile) run one chain serially, shadow and colour
+// kernels per generation, with events between the kernels.
 int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cudaStream_t stream, int* launches)
 {
     const TileLayout tl = tile_layout(s->height, s->width, p.world_size, p.tile_rows);
@@ -278,105 +334,34 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         if (rc != RT_OK) return rc;
     }
     const bool lbvh = accel == RT_ACCEL_LBVH;
-    // Fused trace: every generation's closest-hit rays in ONE persistent launch that spawns as it goes
-    // (wavefront_bvh.cuh: bvh_trace_all_kernel), then every generation's shadow chains in one launch
-    static const int fused_env = tuning_int("RT_FUSED", 0, 0, 1);
-    static const int spawn_every = tuning_int("RT_SPAWN_EVERY", 8, 2, 64);
-    const bool fused = lbvh && (p.fused_trace == 1 || (p.fused_trace == 0 && fused_env)) && p.subframes <= 1;
-    const int K = fused ? 1 : pick_subframes(p, accel, tl);
-    static const int overlap_knob = tuning_int("RT_OVERLAP", 1, 0, 1);
-    const bool overlap = lbvh && overlap_knob && !p.profile && !p.instrument && !fused;
+    const Tuning& T = tuning();
+    const int K = pick_subframes(p, accel, tl);
+    const bool overlap = lbvh && !p.profile;
+    const bool count = p.instrument != 0;
     // sub-frame j is virtual rank (rank + world*j) of (world*K): the same interleaved-tile arithmetic
     const TileLayout vl = tile_layout(s->height, s->width, p.world_size * K, p.tile_rows);
+    const int D = p.max_depth;
 
-    static const int refill = tuning_int("RT_REFILL_LANES", 6, 1, 32);
-    static const int grid_mult = tuning_int("RT_GRID_MULT", 16, 1, 64);
-    static const int inner_min = tuning_int("RT_INNER_MIN_LANES", 8, 1, 32);
-    static const int leaf_min = tuning_int("RT_LEAF_MIN_LANES", 8, 1, 32);
-    // ... of the any-hit kernel (0 = as the closest-hit kernel)
-    static const int sh_refill = tuning_int("RT_SHADOW_REFILL_LANES", 0, 0, 32);
-    static const int sh_inner_min = tuning_int("RT_SHADOW_INNER_MIN_LANES", 6, 0, 32);
-    static const int sh_leaf_min = tuning_int("RT_SHADOW_LEAF_MIN_LANES", 6, 0, 32);
-    static const int near_first = tuning_int("RT_SHADOW_NEAR_FIRST", 0, 0, 1);
-    // Work sharing in the walk kernels' tails.  0: never, 1: always, 2: for launches of at most
-    // RT_STEAL_MAX_KRAYS thousand queue slots.  Measured on the 4K stress frame (tools/steal_sweep.sh):
-    // 1/8 shard 7.43 -> 7.00 ms, 1/4 shard 12.34 -> 12.22, whole frame 42.3 -> 44.5 (the sharing
-    // build's main loop carries more state), hence the size rule.
-    static const int steal_env = tuning_int("RT_STEAL", 2, 0, 2);
-    static const int steal_shadow_env = tuning_int("RT_STEAL_SHADOW", 2, 0, 2);
-    static const long long steal_max_work = 1000LL * tuning_int("RT_STEAL_MAX_KRAYS", 1500, 0, 2000000);
-    static const long long steal_shadow_max_work = 1000LL * tuning_int("RT_STEAL_SHADOW_MAX_KRAYS", 2500, 0, 2000000);   // merged any-hit launch: by the chain's pixels
-    const int steal = p.work_sharing == 1 ? 1 : p.work_sharing == 2 ? 0 : steal_env;
-    const int steal_shadow = p.work_sharing == 1 ? 1 : p.work_sharing == 2 ? 0 : steal_shadow_env;
-    // Any-hit blocks that end after a bounded number of jobs + a high-priority trace chain: a trace
-    // launch that becomes ready gets SM slots at once instead of waiting behind persistent shadow blocks
-    static const int shadow_budget = tuning_int("RT_SHADOW_JOB_BUDGET", 0, 0, 1 << 20);
-    static const int shadow_mult = tuning_int("RT_SHADOW_GRID_MULT", 0, 0, 64);   // 0: same as RT_GRID_MULT
-    // Occluder hints of the any-hit kernel (wavefront_bvh.cuh: ShadowJob) and the interleaved passes
-    // that make them available in time
-    // Generations from this one on share ONE any-hit launch after the last trace (fewer kernel tails,
-    // less overlap with the trace chain); 99 = every generation has its own
-    static const int merge_env = tuning_int("RT_SHADOW_MERGE_FROM", 0, 0, 99);
-    static const int colour_merge = tuning_int("RT_COLOUR_MERGE", 1, 0, 1);   // ... and one launch for their colour halves
-    static const long long merge_max_work = 1000LL * tuning_int("RT_SHADOW_MERGE_MAX_KRAYS", 2000000, 0, 2000000);
-    static const int hint_env = tuning_int("RT_HINT", 0, 0, 1);
-    static const int hint_passes = tuning_int("RT_HINT_PASSES", 16, 1, 256);
-    static const int hint_group = tuning_int("RT_HINT_GROUP", 32, 1, 4096);
-    static const int hint_min_chunk = 1024 * tuning_int("RT_HINT_MIN_CHUNK_K", 256, 1, 1 << 20);
-    static const int hint_mode = tuning_int("RT_HINT_MODE", 3, 0, 3);
-    static const int hint_keep = tuning_int("RT_HINT_KEEP", 0, 0, 1);      // experiments only: hints survive the frame
-    const bool hints = lbvh && s->nl > 0 && (p.occluder_hints == 1 || (p.occluder_hints == 0 && hint_env));
-
-    // L1 / shared-memory split of the walk kernels (percent of the maximum shared memory; -1 = the driver's choice)
-    static const int carveout = tuning_int("RT_CARVEOUT", -1, -1, 100);
-    static bool carveout_set = false;
-    if (carveout >= 0 && !carveout_set) {
-        carveout_set = true;
-        cudaFuncSetAttribute(bvh_trace_kernel<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
-        cudaFuncSetAttribute(bvh_trace_kernel<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
-        cudaFuncSetAttribute(bvh_shadow_kernel<false, false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
-        cudaFuncSetAttribute(bvh_shadow_kernel<false, false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
-    }
     static thread_local FrameParams PS[kMaxSubframes];
     for (int j = 0; j < K; j++) {
         FrameParams& P = PS[j];
         std::memset(&P, 0, sizeof P);
         P.scene = scene_view(s);
         P.cam = s->cam;
-        fill_levels(s, p.max_depth, lbvh, K, j, (size_t)vl.n_local_pixels, &P);
+        fill_levels(s, D, lbvh, K, j, (size_t)vl.n_local_pixels, &P);
         P.counters = s->ws.counters.as<Counters>() + j;
         P.tiles = tiles_out ? tiles_out : s->ws.tiles.as<uchar4>();
         P.primary_ids = p.instrument ? s->ws.primary_ids.as<int>() : nullptr;
-        P.max_depth = p.max_depth; P.epsilon = p.epsilon;
+        P.max_depth = D; P.epsilon = p.epsilon;
         P.rank = p.rank + p.world_size * j; P.world = p.world_size * K; P.tile_rows = p.tile_rows;
         P.n_local_rows = vl.n_local_rows; P.n_local_pixels = vl.n_local_pixels;
         P.out_mul = K; P.out_add = j; P.out_tiles = tl.n_local_tiles;
-        P.refill_lanes = refill; P.inner_min_lanes = inner_min; P.leaf_min_lanes = leaf_min;
-        P.sh_refill_lanes = sh_refill ? sh_refill : refill;
-        P.sh_inner_min_lanes = sh_inner_min ? sh_inner_min : inner_min;
-        P.sh_leaf_min_lanes = sh_leaf_min ? sh_leaf_min : leaf_min;
-        P.steal = 1;
-        P.shadow_job_budget = overlap ? shadow_budget : 0;
-        P.occluder_hint = hints ? s->ws.hints.as<int>() : nullptr;
-        P.hint_prims = s->nf + s->ns;
-        P.hint_passes = hint_passes; P.hint_group = hint_group; P.hint_min_chunk = hint_min_chunk;
-        P.hint_mode = hint_mode;
-        if (fused) {
-            size_t entries = 0;
-            for (int l = 1; l <= p.max_depth; l++) entries += (size_t)s->ws.capacity[l];
-            P.work_order = s->ws.work_order.as<unsigned>();
-            P.work_capacity = (unsigned)std::min<size_t>(entries, 0xffffffffu);
-            size_t hits = 0;
-            for (int l = 0; l < p.max_depth; l++) hits += (size_t)P.level[l].capacity;
-            P.hit_order = s->ws.hit_order.as<unsigned>();
-            P.hit_capacity = (unsigned)std::min<size_t>(hits, 0xffffffffu);
-            P.spawn_every = spawn_every;
-        }
+        P.refill_lanes = T.refill_lanes; P.inner_min_lanes = T.inner_min_lanes; P.leaf_min_lanes = T.leaf_min_lanes;
+        P.sh_refill_lanes = T.sh_refill_lanes; P.sh_inner_min_lanes = T.sh_inner_min_lanes; P.sh_leaf_min_lanes = T.sh_leaf_min_lanes;
+        P.redo_list = lbvh ? s->ws.redo_list.as<unsigned>() + (size_t)j * kRedoCapacity : nullptr;
     }
 
     RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
-    // every frame starts without hints: a frame never depends on an earlier one
-    if (hints && !(hint_keep && s->rendered)) RT_CUDA(cudaMemsetAsync(s->ws.hints.p, 0xff, (size_t)(s->nf + s->ns) * s->nl * sizeof(int), stream));
     const int sms = sm_count(s->device);
     const size_t smem = (size_t)(s->nf * kTriWords + s->ns * kSphWords) * sizeof(float4);
     const bool stage = accel == RT_ACCEL_BRUTE && smem <= 48 * 1024;
@@ -396,120 +381,74 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         RT_CUDA(cudaEventRecord(cs.begin, stream));        // the counters are cleared
         for (int j = 0; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
     }
-    if (fused) {
+    const int steal = p.work_sharing;      // 0: by launch size, 1: always, 2: never
+
+    if (!lbvh) {
+        for (int l = 0; l <= D; l++) {
+            if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
+            const FrameParams& P = PS[0];
+            const int grid = persistent_grid(P.level[l].capacity, sms, T.grid_mult);
+            if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
+            else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
+            n++;
+        }
+    } else if (p.profile) {
+        // one serial chain, every kernel on its own between events (bench.py's per-kernel times)
         const FrameParams& P = PS[0];
-        if (P.work_capacity) RT_CUDA(cudaMemsetAsync(P.work_order, 0xff, (size_t)P.work_capacity * sizeof(unsigned), stream));
-        if (P.hit_capacity) RT_CUDA(cudaMemsetAsync(P.hit_order, 0xff, (size_t)P.hit_capacity * sizeof(unsigned), stream));
-        // exactly the blocks that are resident at once: a block only ends when the frame is traced
-        static int resident[2] = { 0, 0 };
-        const int ri = p.instrument ? 1 : 0;
-        if (!resident[ri]) {
-            int nb = 0;
-            if (p.instrument) RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, bvh_trace_all_kernel<true>, kWalkBlock, 0));
-            else RT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, bvh_trace_all_kernel<false>, kWalkBlock, 0));
-            resident[ri] = std::max(nb, 1);
-        }
-        // (at least one spawner warp: warp w spawns when w % spawn_every == spawn_every - 1)
-        const int grid = std::max((int)std::min<long long>(((long long)P.n_local_pixels + kWalkBlock - 1) / kWalkBlock, (long long)sms * resident[ri]), (spawn_every * 32 + kWalkBlock - 1) / kWalkBlock);
-        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[0], stream));
-        if (p.instrument) bvh_trace_all_kernel<true><<<grid, kWalkBlock, 0, stream>>>(P);
-        else bvh_trace_all_kernel<false><<<grid, kWalkBlock, 0, stream>>>(P);
-        n++;
-        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[0][0], stream));
-        if (s->nl) {
-            long long work = 0;
-            for (int l = 0; l <= p.max_depth; l++) work += P.level[l].capacity;
-            const int sh_grid = walk_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
-            if (p.instrument) { if (hints) bvh_shadow_kernel<true, false, false, true, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); else bvh_shadow_kernel<true, false, false, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); }
-            else { if (hints) bvh_shadow_kernel<false, false, false, true, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); else bvh_shadow_kernel<false, false, false, true><<<sh_grid, kWalkBlock, 0, stream>>>(P, -1); }
+        for (int l = 0; l <= D; l++) {
+            const long long work = P.level[l].capacity;
+            const bool sharing = steal == 1 || (steal == 0 && work <= 1000LL * T.steal_max_krays);
+            RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
+            if (count) launch_trace<true>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
+            else launch_trace<false>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
+            bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l);
+            n += 2;
+            RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
+            if (s->nl) {
+                const int sh_grid = persistent_grid(work * s->nl, sms, T.grid_mult, kWalkBlock);
+                if (count) launch_shadow<true>(P, l, l, sharing, sh_grid, stream);
+                else launch_shadow<false>(P, l, l, sharing, sh_grid, stream);
+                n += 2;
+            }
+            RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
+            bvh_colour_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l, l);
             n++;
         }
-        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[0][1], stream));
-        for (int l = 0; l <= p.max_depth; l++) {
-            const int cgrid = persistent_grid(P.level[l].capacity, sms, grid_mult);
-            bvh_shade_kernel<true, false><<<cgrid, kBlock, 0, stream>>>(P, l);
-            n++;
-        }
-    }
-    for (int l = 0; l <= p.max_depth && !fused; l++) {
-        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
+    } else {
         for (int j = 0; j < K; j++) {
             const FrameParams& P = PS[j];
-            // persistent grid: whole waves of resident blocks; generation 0 has one slot per pixel
-            const long long work = P.level[l].capacity;
-            const int grid = persistent_grid(work, sms, grid_mult);
-            const int wgrid = walk_grid(work, sms, grid_mult);
-            if (!lbvh) {
-                if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
-                else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
-                n++;
-                continue;
+            cudaStream_t ms = cs.main[j], side = cs.side[j];
+            long long all_work = 0;
+            for (int l = 0; l <= D; l++) {
+                const long long work = P.level[l].capacity;
+                all_work += work;
+                const bool sharing = steal == 1 || (steal == 0 && work <= 1000LL * T.steal_max_krays);
+                const int wgrid = persistent_grid(work, sms, T.grid_mult, kWalkBlock);
+                if (count) launch_trace<true>(P, l, sharing, wgrid, ms);
+                else launch_trace<false>(P, l, sharing, wgrid, ms);
+                bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, ms>>>(P, l);
+                n += 2;
             }
-            // trace: one thread per ray; shadow: one chain per node; colour / spawn: one thread per node
-            cudaStream_t ms = overlap ? cs.main[j] : stream;
-            int sh_grid = walk_grid(work * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
-            if (overlap && shadow_budget > 0)   // bounded blocks: as many as the queue may need (surplus blocks end at once)
-                sh_grid = (int)std::max<long long>(sh_grid, std::min<long long>((work + 4LL * shadow_budget - 1) / (4LL * shadow_budget) + 1, 1 << 20));
-            const bool sharing = steal == 1 || (steal == 2 && work <= steal_max_work);
-            if (p.instrument) {
-                if (sharing) bvh_trace_kernel<true, true><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
-                else bvh_trace_kernel<true, false><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
-            } else {
-                if (sharing) bvh_trace_kernel<false, true><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
-                else bvh_trace_kernel<false, false><<<wgrid, kWalkBlock, 0, ms>>>(P, l);
-            }
-            n++;
-            // shadow -> colour depends only on this generation's hits, spawn -> next trace too:
-            // two chains on two streams (profiled / instrumented frames stay serial)
-            cudaStream_t side = ms;
-            if (overlap) {
-                RT_CUDA(cudaEventRecord(cs.fork[j][l], ms));
-                RT_CUDA(cudaStreamWaitEvent(cs.side[j], cs.fork[j][l], 0));
-                side = cs.side[j];
-                // the critical chain first: spawn feeds the next generation's trace
-                if (l < p.max_depth) { bvh_shade_kernel<false, true><<<grid, kBlock, 0, ms>>>(P, l); n++; }
-            }
-            if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
-            const bool merged = overlap && s->nl && l >= merge_env && (long long)P.level[0].capacity <= merge_max_work;
-            if (merged) {
-                // this generation's shadow chains wait for the merged launch after the last trace
-                if (l == p.max_depth) {
-                    long long mwork = 0;
-                    for (int m = merge_env; m <= p.max_depth; m++) mwork += P.level[m].capacity;
-                    const int mgrid = walk_grid(mwork * std::max(1, s->nl), sms, shadow_mult ? shadow_mult : grid_mult);
-                    // (work sharing by the size of the chain's frame, like the per-generation launches: measured, 1/8 shard 6.09 -> 5.96 ms)
-                    const bool msharing = steal_shadow == 1 || (steal_shadow == 2 && (long long)P.level[0].capacity <= steal_shadow_max_work);
-                    if (msharing) bvh_shadow_kernel<false, false, true, true, false><<<mgrid, kWalkBlock, 0, side>>>(P, -merge_env - 1);
-                    else bvh_shadow_kernel<false, false, false, true, false><<<mgrid, kWalkBlock, 0, side>>>(P, -merge_env - 1);
-                    n++;
-                    // (measured: whole 4K frame 37.5 -> 37.9 ms, 1/8 shard 5.92 -> 5.86 ms: small frames only)
-                    if (colour_merge && (long long)P.level[0].capacity <= steal_shadow_max_work) {
-                        bvh_shade_kernel<true, false, true><<<persistent_grid(mwork, sms, grid_mult), kBlock, 0, side>>>(P, -merge_env - 1);
-                        n++;
-                    } else for (int m = merge_env; m <= p.max_depth; m++) {
-                        bvh_shade_kernel<true, false><<<persistent_grid(P.level[m].capacity, sms, grid_mult), kBlock, 0, side>>>(P, m);
-                        n++;
-                    }
-                }
-                continue;
-            }
+            RT_CUDA(cudaEventRecord(cs.fork[j], ms));
+            RT_CUDA(cudaStreamWaitEvent(side, cs.fork[j], 0));
+            const long long chain_pixels = P.level[0].capacity;
             if (s->nl) {
-                const bool sh_sharing = steal_shadow == 1 || (steal_shadow == 2 && work <= steal_max_work);
-                if (p.instrument) {
-                    if (sh_sharing) { if (hints) bvh_shadow_kernel<true, false, true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
-                    else { if (hints) bvh_shadow_kernel<true, false, false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<true, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
-                } else if (near_first) bvh_shadow_kernel<false, true, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l);
-                else if (sh_sharing) { if (hints) bvh_shadow_kernel<false, false, true, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
-                else { if (hints) bvh_shadow_kernel<false, false, false, false, true><<<sh_grid, kWalkBlock, 0, side>>>(P, l); else bvh_shadow_kernel<false, false, false><<<sh_grid, kWalkBlock, 0, side>>>(P, l); }
+                const bool sharing = steal == 1 || (steal == 0 && chain_pixels <= 1000LL * T.steal_shadow_max_kpixels);
+                const int sh_grid = persistent_grid(all_work * s->nl, sms, T.grid_mult, kWalkBlock);
+                if (count) launch_shadow<true>(P, 0, D, sharing, sh_grid, side);
+                else launch_shadow<false>(P, 0, D, sharing, sh_grid, side);
+                n += 2;
+            }
+            if (chain_pixels <= 1000LL * T.colour_merge_max_kpixels) {
+                bvh_colour_kernel<<<persistent_grid(all_work, sms, T.grid_mult), kBlock, 0, side>>>(P, 0, D);
+                n++;
+            } else for (int l = 0; l <= D; l++) {
+                bvh_colour_kernel<<<persistent_grid(P.level[l].capacity, sms, T.grid_mult), kBlock, 0, side>>>(P, l, l);
                 n++;
             }
-            if (p.profile) RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
-            if (overlap) bvh_shade_kernel<true, false><<<grid, kBlock, 0, side>>>(P, l);
-            else bvh_shade_kernel<true, true><<<grid, kBlock, 0, ms>>>(P, l);
-            n++;
         }
     }
-    const int prof_n = fused ? 1 : p.max_depth + 1;      // a fused frame is profiled as one "generation"
+    const int prof_n = D + 1;
     if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[prof_n], stream));
     // bottom-up combine per chain, on the chain's main stream once its colour kernels are done
     for (int j = 0; j < K; j++) {
@@ -519,7 +458,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             RT_CUDA(cudaEventRecord(cs.side_done[j], cs.side[j]));
             RT_CUDA(cudaStreamWaitEvent(ms, cs.side_done[j], 0));
         }
-        for (int l = std::max(p.max_depth - 1, 0); l >= 0; l--) {
+        for (int l = std::max(D - 1, 0); l >= 0; l--) {
             // (max_depth == 0: no backward pass, but generation 0 still has to be quantised)
             const long long work = P.level[l].capacity;
             const int grid = (int)std::max<long long>(1, std::min<long long>((work + 255) / 256, (long long)sms * 8));
@@ -550,27 +489,26 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
 
 // Sums the sub-frames' counters of the last frame and checks every queue against the slice
 // it had.  demand: what the whole generation would have needed had every slice been as full
-// as the fullest one.
-bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels])
+// as the fullest one.  Returns the kOverflow* bits of the frame (0 = complete).
+unsigned frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels])
 {
     const int K = s->last_subframes;
     const RtRenderParams& p = s->last;
     Counters t;
     std::memset(&t, 0, sizeof t);
-    bool overflow = false;
+    unsigned overflow = 0;
     double factor = 1.0;
     unsigned fullest[kMaxLevels] = { 0 };
     for (int j = 0; j < K; j++) {
         const Counters& c = s->h_counters[j];
-        overflow = overflow || c.overflow != 0;
-        t.overflow |= c.overflow;
+        overflow |= c.overflow;
         for (int l = 0; l < kMaxLevels; l++) {
             t.rays[l] += c.rays[l]; t.nodes[l] += c.nodes[l]; t.rays_reflect[l] += c.rays_reflect[l];
             fullest[l] = std::max(fullest[l], c.rays[l]);
             if (l >= 1 && l <= p.max_depth) {
                 const unsigned cap = (unsigned)(s->ws.capacity[l] / K);
                 if (c.rays[l] > cap) {
-                    overflow = true;
+                    overflow |= kOverflowQueue;
                     // a truncated generation under-reports what the deeper ones need: scale those up with it
                     factor = std::max(factor, (double)c.rays[l] / (double)std::max(1u, cap));
                 }
@@ -578,15 +516,29 @@ bool frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxL
         }
         t.bvh_nodes += c.bvh_nodes; t.prim_tests += c.prim_tests; t.texels += c.texels;
         t.shadow_boxes += c.shadow_boxes; t.shadow_prims += c.shadow_prims; t.shadow_walks += c.shadow_walks;
-        t.shadow_hint_hits += c.shadow_hint_hits;
-        t.work.stalled |= c.work.stalled;
-        if (j == 0) std::memcpy(t.clock, c.clock, sizeof t.clock);      // instrumented frames have one chain
+        t.redo_count += c.redo_count;
+        if (j == 0) std::memcpy(t.clock, c.clock, sizeof t.clock);      // (the first chain's)
     }
+    t.overflow = overflow;
     if (total) *total = t;
     if (demand)
         for (int l = 0; l < kMaxLevels; l++)
-            demand[l] = (unsigned)std::min(2.0e9, (double)fullest[l] * K * factor + 64.0 * K);
+            demand[l] = (unsigned)std::min(2.0e8, (double)fullest[l] * K * factor + 64.0 * K);
     return overflow;
+}
+
+// What rt_render / rt_async_frame_status make of a frame's overflow bits other than kOverflowQueue.
+int overflow_error(unsigned bits)
+{
+    if (bits & kOverflowStack) {
+        set_error("a BVH traversal stack overflowed (degenerate tree): the frame is incomplete");
+        return RT_E_LIMIT;
+    }
+    if (bits & kOverflowRedo) {
+        set_error("more than 65536 shadow chains with over 12 transparent occluders on one ray in a launch chain: the frame is incomplete");
+        return RT_E_LIMIT;
+    }
+    return RT_OK;
 }
 
 int launch_split_planes(SceneHost* s, cudaStream_t st)
