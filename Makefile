@@ -29,9 +29,17 @@ $(LIB)/librt_host.so: $(HOST_SRCS) $(CSRC)/host/host_common.h include/rt_host.h 
 	@mkdir -p $(LIB)
 	$(CXX) $(HOSTFLAGS) -shared -o $@ $(HOST_SRCS)
 
-$(LIB)/librt_b200.so: $(CU_SRCS) $(CU_HDRS)
+# one object per .cu so that `make -j` compiles them side by side (render.cu alone is most of the time)
+CU_OBJS   := $(patsubst $(CSRC)/%.cu,build/%.o,$(CU_SRCS))
+
+build/%.o: $(CSRC)/%.cu $(CU_HDRS)
+	@mkdir -p build $(LIB)
+	$(NVCC) $(NVCCFLAGS) $(EXTRA) -Xptxas -v -c -o $@ $< 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; exit 1)
+
+$(LIB)/librt_b200.so: $(CU_OBJS)
 	@mkdir -p $(LIB)
-	$(NVCC) $(NVCCFLAGS) -Xptxas -v -shared -o $@ $(CU_SRCS) 2> $(LIB)/ptxas.log || (cat $(LIB)/ptxas.log; exit 1)
+	$(NVCC) $(ARCH) -cudart static -shared -o $@ $(CU_OBJS)
+	@cat build/*.ptxas.log > $(LIB)/ptxas.log
 
 bin/raytracer: $(CSRC)/host/raytracer_main.cpp $(LIB)/librt_host.so $(LIB)/librt_b200.so
 	@mkdir -p bin

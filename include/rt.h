@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RT_ABI_VERSION 3
+#define RT_ABI_VERSION 4
 
 /* ---- status codes ------------------------------------------------------ */
 #define RT_OK            0
@@ -42,6 +42,8 @@ extern "C" {
 #define RT_E_STATE      -4   /* call order (e.g. download before render)      */
 #define RT_E_PARSE      -5   /* scene / texture file could not be parsed      */
 #define RT_E_IO         -6   /* file could not be opened / written            */
+#define RT_E_LIMIT      -7   /* a stated limit of the implementation was hit: the
+                                frame (or the LBVH) is refused, never returned wrong */
 
 /* ---- scene description (what `environment` + main()'s locals hold) ------ */
 
@@ -114,6 +116,7 @@ typedef struct RtSceneDesc {
 #define RT_ACCEL_AUTO   0   /* brute force for small scenes, LBVH otherwise */
 #define RT_ACCEL_BRUTE  1
 #define RT_ACCEL_LBVH   2
+#define RT_ACCEL_LBVH8  3   /* rt_trace_shadow only: the 8-wide tree the any-hit kernel walks */
 
 typedef struct RtRenderParams {
     int32_t max_depth;     /* environment.other["recursion_depth"], default 4 */
@@ -122,10 +125,12 @@ typedef struct RtRenderParams {
     int32_t rank;          /* row-tile sharding: this process renders tiles   */
     int32_t world_size;    /*   t with t % world_size == rank; default 0 / 1  */
     int32_t tile_rows;     /* rows per tile (default 8)                       */
-    int32_t instrument;    /* 1: count BVH work / texels, keep primary hit ids
-                              (slower; never use for timing)                  */
-    int32_t profile;       /* 1: CUDA events around every generation's kernel;
-                              rt_render reports RtStats.level_ms / combine_ms */
+    int32_t instrument;    /* 1: count BVH work / texels, keep primary hit ids: the
+                              same launch schedule with the counting builds of the
+                              walk kernels (slower; never use for timing)       */
+    int32_t profile;       /* 1: one serial launch chain with CUDA events around every
+                              kernel; rt_render reports RtStats.level_ms / trace_ms /
+                              shadow_ms / shade_ms / combine_ms                 */
     int32_t subframes;     /* LBVH pipeline: independent launch chains the rank's
                               tiles are dealt out to (1..8; 0 = choose).  Never
                               changes a pixel, only how kernel tails overlap. */
@@ -133,20 +138,6 @@ typedef struct RtRenderParams {
                               idle lanes take subtrees off the stacks of the lanes
                               still walking.  0 = for short launches (default),
                               1 = always, 2 = never.  Never changes a pixel.   */
-    int32_t occluder_hints;/* LBVH any-hit kernel: a shadow walk that ends at an opaque
-                              occluder leaves that primitive as a hint for later shadow
-                              rays from the same surface primitive to the same light,
-                              which test it first (exactly) and skip the walk when it
-                              blocks them too.  0 = off (default: the extra state costs
-                              the kernel more than the skipped walks save on B200,
-                              DESIGN.md 5.5), 1 = on, 2 = off.  Never changes a pixel. */
-    int32_t fused_trace;   /* LBVH pipeline: the closest-hit rays of ALL generations in one
-                              persistent launch that spawns the next generation's rays as
-                              it goes (one kernel tail per frame instead of one per
-                              generation), then all shadow chains in one launch.
-                              0 = off (default: one launch chain per generation; measured
-                              faster on B200), 1 = on, 2 = off.  Never
-                              changes a pixel.                                   */
 } RtRenderParams;
 
 /* Filled by rt_render when a non-NULL pointer is passed.  The ray counts
@@ -186,8 +177,9 @@ typedef struct RtStats {
        dry, the lanes active in such a pass, and the subtrees handed to idle lanes. */
     double   trace_drain_steps[8], trace_drain_lanes[8], trace_drain_steals[8];
     double   shadow_drain_steps[8], shadow_drain_lanes[8];
-    uint64_t shadow_hint_hits;   /* instrument, LBVH: shadow rays settled by an occluder hint (not walked,
-                                    not counted in shadow_rays_walked) */
+    uint64_t shadow_chains_redone; /* LBVH: nodes whose shadow chain met more than 12 transparent occluders on
+                                    one ray and went through the exact slow path (bvh_shadow_redo_kernel) */
+    int32_t  bvh_levels4, bvh_levels8; /* LBVH: depth of the closest-hit (4-wide) and any-hit (8-wide) trees */
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

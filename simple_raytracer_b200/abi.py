@@ -13,12 +13,12 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_DIR = os.path.join(_HERE, "lib")
 
 RT_OK = 0
-RT_E_INVALID, RT_E_CUDA, RT_E_NOMEM, RT_E_STATE, RT_E_PARSE, RT_E_IO = -1, -2, -3, -4, -5, -6
-RT_ACCEL_AUTO, RT_ACCEL_BRUTE, RT_ACCEL_LBVH = 0, 1, 2
+RT_E_INVALID, RT_E_CUDA, RT_E_NOMEM, RT_E_STATE, RT_E_PARSE, RT_E_IO, RT_E_LIMIT = -1, -2, -3, -4, -5, -6, -7
+RT_ACCEL_AUTO, RT_ACCEL_BRUTE, RT_ACCEL_LBVH, RT_ACCEL_LBVH8 = 0, 1, 2, 3
 
 _ERR_NAMES = {
     RT_E_INVALID: "RT_E_INVALID", RT_E_CUDA: "RT_E_CUDA", RT_E_NOMEM: "RT_E_NOMEM",
-    RT_E_STATE: "RT_E_STATE", RT_E_PARSE: "RT_E_PARSE", RT_E_IO: "RT_E_IO",
+    RT_E_STATE: "RT_E_STATE", RT_E_PARSE: "RT_E_PARSE", RT_E_IO: "RT_E_IO", RT_E_LIMIT: "RT_E_LIMIT",
 }
 
 
@@ -67,8 +67,7 @@ class RtRenderParams(C.Structure):
     _fields_ = [("max_depth", C.c_int32), ("epsilon", C.c_float), ("accel", C.c_int32),
                 ("rank", C.c_int32), ("world_size", C.c_int32), ("tile_rows", C.c_int32),
                 ("instrument", C.c_int32), ("profile", C.c_int32), ("subframes", C.c_int32),
-                ("work_sharing", C.c_int32), ("occluder_hints", C.c_int32),
-                ("fused_trace", C.c_int32)]
+                ("work_sharing", C.c_int32)]
 
 
 class RtStats(C.Structure):
@@ -85,7 +84,8 @@ class RtStats(C.Structure):
                 ("shadow_warp_drain_ms", C.c_double * 8),
                 ("trace_drain_steps", C.c_double * 8), ("trace_drain_lanes", C.c_double * 8),
                 ("trace_drain_steals", C.c_double * 8), ("shadow_drain_steps", C.c_double * 8),
-                ("shadow_drain_lanes", C.c_double * 8), ("shadow_hint_hits", C.c_uint64)]
+                ("shadow_drain_lanes", C.c_double * 8), ("shadow_chains_redone", C.c_uint64),
+                ("bvh_levels4", C.c_int32), ("bvh_levels8", C.c_int32)]
 
     def as_dict(self) -> dict:
         d = {}

@@ -42,9 +42,7 @@ int check_params(const RtRenderParams* in, RtRenderParams* out)
     if (out->tile_rows < 1) { set_error("tile_rows must be >= 1"); return RT_E_INVALID; }
     if (out->subframes < 0 || out->subframes > kMaxSubframes) { set_error("subframes must be in 0..8"); return RT_E_INVALID; }
     if (out->work_sharing < 0 || out->work_sharing > 2) { set_error("work_sharing must be 0, 1 or 2"); return RT_E_INVALID; }
-    if (out->fused_trace < 0 || out->fused_trace > 2) { set_error("fused_trace must be 0, 1 or 2"); return RT_E_INVALID; }
-    if (out->occluder_hints < 0 || out->occluder_hints > 2) { set_error("occluder_hints must be 0, 1 or 2"); return RT_E_INVALID; }
-    if (out->accel < RT_ACCEL_AUTO || out->accel > RT_ACCEL_LBVH) { set_error("bad accel"); return RT_E_INVALID; }
+    if (out->accel < RT_ACCEL_AUTO || out->accel > RT_ACCEL_LBVH) { set_error("bad accel"); return RT_E_INVALID; }   // (RT_ACCEL_LBVH8: probes only)
     return RT_OK;
 }
 
@@ -83,6 +81,19 @@ __global__ void probe_shadow_kernel(SceneView S, Accel acc, int n, const float* 
     out_mask[i] = mask; out_hits[i] = hits;
 }
 
+// ... through the 8-wide tree of the any-hit kernel
+__global__ void probe_shadow8_kernel(SceneView S, BvhAccel acc, int n, const float* __restrict__ o, const float* __restrict__ d,
+                                     const int* __restrict__ self_order, float tmin, const float* __restrict__ tmax,
+                                     float* __restrict__ out_mask, int* __restrict__ out_hits)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 ro = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    float mask = 1.0f;
+    const int hits = acc.shadow(ro, rd, self_order[i], tmin, tmax ? tmax[i] : 0.0f, tmax != nullptr, mask, true);
+    out_mask[i] = mask; out_hits[i] = hits;
+}
+
 __global__ void ids_to_order_kernel(SceneView S, int n, const int* __restrict__ ids, int* __restrict__ order)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -98,7 +109,7 @@ __global__ void ids_to_order_kernel(SceneView S, int n, const int* __restrict__ 
 int probe_accel(SceneHost* s, int accel)
 {
     if (accel == RT_ACCEL_AUTO) accel = (s->nf + s->ns) > 48 ? RT_ACCEL_LBVH : RT_ACCEL_BRUTE;
-    if (accel == RT_ACCEL_LBVH && !s->bvh_built) {
+    if ((accel == RT_ACCEL_LBVH || accel == RT_ACCEL_LBVH8) && !s->bvh_built) {
         const int rc = build_bvh(s);
         if (rc != RT_OK) return rc;
     }
@@ -213,8 +224,11 @@ int rt_async_frame_status(RtScene* scene)
     RT_CUDA(cudaSetDevice(s->device));
     RT_CUDA(cudaMemcpy(s->h_counters, s->ws.counters.p, sizeof(Counters) * s->last_subframes, cudaMemcpyDeviceToHost));
     unsigned demand[kMaxLevels];
-    if (!frame_overflowed(s, nullptr, demand)) return RT_OK;
-    const int rc = ensure_workspace(s, s->last, demand);
+    const unsigned bits = frame_overflowed(s, nullptr, demand);
+    if (!bits) return RT_OK;
+    int rc = overflow_error(bits);
+    if (rc != RT_OK) return rc;
+    rc = ensure_workspace(s, s->last, demand);
     if (rc != RT_OK) return rc;
     set_error("the last asynchronous frame overflowed a wavefront queue (queues grown: render it again)");
     return RT_E_NOMEM;
@@ -241,9 +255,9 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         RT_CUDA(cudaStreamSynchronize(s->stream));
         RT_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
         unsigned demand[kMaxLevels];
-        const bool again = frame_overflowed(s, &total, demand);
-        if (total.work.stalled) { set_error("fused trace kernel: a warp waited 2 s for work that never came (frame invalid)"); return RT_E_CUDA; }
-        if (!again) break;
+        const unsigned bits = frame_overflowed(s, &total, demand);
+        if ((rc = overflow_error(bits)) != RT_OK) return rc;
+        if (!bits) break;
         if (++regrows > 16) { set_error("wavefront queues still overflow after 16 regrows"); return RT_E_NOMEM; }
         if ((rc = ensure_workspace(s, p, demand)) != RT_OK) return rc;
     }
@@ -268,7 +282,9 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->bvh_nodes_visited = c.bvh_nodes; stats->prim_tests = c.prim_tests; stats->texel_fetches = c.texels;
         stats->shadow_boxes_tested = c.shadow_boxes; stats->shadow_prim_tests = c.shadow_prims;
         stats->shadow_rays_walked = (s->last_accel == RT_ACCEL_LBVH && p.instrument) ? c.shadow_walks : stats->rays_shadow;
-        stats->shadow_hint_hits = c.shadow_hint_hits;
+        stats->shadow_chains_redone = c.redo_count;
+        stats->bvh_levels4 = s->last_accel == RT_ACCEL_LBVH ? s->bvh_levels4 : 0;
+        stats->bvh_levels8 = s->last_accel == RT_ACCEL_LBVH ? s->bvh_levels8 : 0;
         stats->accel_used = s->last_accel; stats->kernel_launches = launches; stats->queue_regrows = regrows;
         if (p.instrument && s->last_accel == RT_ACCEL_LBVH) {
             for (int l = 0; l <= p.max_depth; l++)
@@ -387,8 +403,9 @@ int rt_trace_closest(RtScene* scene, int32_t accel, int32_t n, const float* orig
     RT_CUDA(cudaMemcpyAsync(d.p, dirs, N * 12, cudaMemcpyHostToDevice, s->stream));
     const SceneView S = scene_view(s);
     const int B = 128, G = (n + B - 1) / B;
+    if (accel == RT_ACCEL_LBVH8) { set_error("rt_trace_closest: closest hits walk the 4-wide tree (RT_ACCEL_LBVH)"); return RT_E_INVALID; }
     if (accel == RT_ACCEL_LBVH) {
-        BvhAccel a{}; a.nodes = S.bvh.nodes; a.prims = S.bvh_tri; a.tri = S.tri; a.sph = S.sph; a.nf = S.nf; a.ns = S.ns; a.root = S.bvh.root; a.n_nodes = S.bvh.n_nodes;
+        BvhAccel a = make_bvh_accel<false>(S);
         probe_closest_kernel<<<G, B, 0, s->stream>>>(S, a, n, o.as<float>(), d.as<float>(), tmin, id.as<int>(), t.as<float>(), nn.as<float>(), bb.as<float>());
     } else {
         BruteAccel a; a.tri = S.tri; a.sph = S.sph; a.nf = S.nf; a.ns = S.ns;
@@ -423,9 +440,12 @@ int rt_trace_shadow(RtScene* scene, int32_t accel, int32_t n, const float* origi
     const int B = 128, G = (n + B - 1) / B;
     ids_to_order_kernel<<<G, B, 0, s->stream>>>(S, n, sid.as<int>(), sord.as<int>());
     const float* tmp = tmax ? tm.as<float>() : nullptr;
-    if (accel == RT_ACCEL_LBVH) {
-        BvhAccel a{}; a.nodes = S.bvh.nodes; a.prims = S.bvh_tri; a.tri = S.tri; a.sph = S.sph; a.nf = S.nf; a.ns = S.ns; a.root = S.bvh.root; a.n_nodes = S.bvh.n_nodes; a.count_all = true;
-        probe_shadow_kernel<<<G, B, 0, s->stream>>>(S, a, n, o.as<float>(), d.as<float>(), sord.as<int>(), tmin, tmp, mask.as<float>(), hits.as<int>());
+    if (accel == RT_ACCEL_LBVH8 && S.bvh.n_nodes8 == 0) { set_error("rt_trace_shadow: the scene has no 8-wide tree (8 primitives or fewer)"); return RT_E_STATE; }
+    if (accel == RT_ACCEL_LBVH || accel == RT_ACCEL_LBVH8) {
+        BvhAccel a = make_bvh_accel<false>(S);
+        a.count_all = true;
+        if (accel == RT_ACCEL_LBVH8) probe_shadow8_kernel<<<G, B, 0, s->stream>>>(S, a, n, o.as<float>(), d.as<float>(), sord.as<int>(), tmin, tmp, mask.as<float>(), hits.as<int>());
+        else probe_shadow_kernel<<<G, B, 0, s->stream>>>(S, a, n, o.as<float>(), d.as<float>(), sord.as<int>(), tmin, tmp, mask.as<float>(), hits.as<int>());
     } else {
         BruteAccel a; a.tri = S.tri; a.sph = S.sph; a.nf = S.nf; a.ns = S.ns;
         probe_shadow_kernel<<<G, B, 0, s->stream>>>(S, a, n, o.as<float>(), d.as<float>(), sord.as<int>(), tmin, tmp, mask.as<float>(), hits.as<int>());

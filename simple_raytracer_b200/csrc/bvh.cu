@@ -280,17 +280,6 @@ __global__ void refit_kernel(int n, const unsigned* __restrict__ sorted_vals, co
 }
 
 // ---- 4-wide quantised traversal nodes (layout: bvh.cuh) ---------------------------------
-// depth of every binary inner node (root = 0): nodes of even depth become 4-wide nodes, nodes
-// of odd depth are absorbed by their parent
-__global__ void depth_kernel(int n, const int* __restrict__ parent_internal, unsigned char* __restrict__ odd)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
-    int d = 0;
-    for (int p = parent_internal[i]; p >= 0; p = parent_internal[p]) d++;
-    odd[i] = (unsigned char)(d & 1);
-}
-
 // Writes one node from up to four (box, code) entries.  Per axis: quantum q = 2^e with e the
 // smallest exponent that spans the node box in 250 steps (but never below 64 ulp of the
 // coordinates, so that fp32 rounding in the decode stays far below one quantum); origin =
@@ -347,49 +336,6 @@ __device__ void write_node4(float4* out, int n_e, const float4* lo, const float4
     w[3] = make_uint4(bytes[2][0], bytes[2][1], bytes[3][0], bytes[3][1]);
 }
 
-// one thread per binary inner node of even depth: its (grand)children become the 4 entries;
-// subtrees of <= leaf_max primitives collapse into one leaf
-__global__ void emit_nodes4_kernel(int n, const unsigned* __restrict__ sorted_vals, const float4* __restrict__ prim_lo,
-                                   const float4* __restrict__ prim_hi, const int2* __restrict__ children,
-                                   const int2* __restrict__ range, const float4* __restrict__ node_lo,
-                                   const float4* __restrict__ node_hi, const unsigned char* __restrict__ odd,
-                                   float4* __restrict__ nodes, int leaf_max)
-{
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1 || odd[i]) return;
-    float4 lo[4], hi[4];
-    int code[4];
-    int n_e = 0;
-    // returns true when child c became an entry, false when it is an inner node to be absorbed
-    auto entry = [&](int c, bool may_absorb) {
-        if (c < 0) {
-            const int slot = ~c;
-            const unsigned p = sorted_vals[slot];
-            lo[n_e] = prim_lo[p]; hi[n_e] = prim_hi[p]; code[n_e] = ~(slot << 3); n_e++;
-            return true;
-        }
-        const int2 r = range[c];
-        const int size = r.y - r.x + 1;
-        if (size <= leaf_max) {
-            lo[n_e] = node_lo[c]; hi[n_e] = node_hi[c]; code[n_e] = ~((r.x << 3) | (size - 1)); n_e++;
-            return true;
-        }
-        if (may_absorb) return false;
-        lo[n_e] = node_lo[c]; hi[n_e] = node_hi[c]; code[n_e] = c; n_e++;
-        return true;
-    };
-    const int2 ch = children[i];
-    const int c2[2] = { ch.x, ch.y };
-    for (int c = 0; c < 2; c++) {
-        if (!entry(c2[c], true)) {
-            const int2 g = children[c2[c]];
-            entry(g.x, false);
-            entry(g.y, false);
-        }
-    }
-    write_node4(nodes + (size_t)i * 4, n_e, lo, hi, code, ~(n << 3));
-}
-
 // scenes of <= kLeafMax (4) primitives: one node with one leaf per primitive
 __global__ void emit_tiny_kernel(int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi,
                                  const unsigned* __restrict__ sorted_vals, float4* __restrict__ nodes)
@@ -442,11 +388,11 @@ __device__ float box_area(float4 lo, float4 hi)
     return dx * dy + dy * dz + dz * dx;
 }
 
-// The 4-wide tree by greedy collapse (instead of "every other level", emit_nodes4_kernel): one
-// thread per 4-wide node of the current level takes its binary node, opens the entry with the
-// largest surface area until it holds four, writes the node at the binary node's own index and
-// queues its inner entries for the next level.  Fuller nodes and fewer levels than the fixed
-// two-level collapse; same node format, so the walk does not change.
+// The 4-wide tree by greedy collapse: one thread per 4-wide node of the current level takes its
+// binary node, opens the entry with the largest surface area until it holds four, writes the node
+// at the binary node's own index and queues its inner entries for the next level.  (Fuller nodes
+// and fewer levels than collapsing every other level of the binary tree: closest-hit kernels 21.3
+// -> 21.1 ms on the 4K stress frame, round 1.)
 // counts[l] = nodes of level l (level 0: the binary root, not stored): the host launches a fixed
 // number of levels back to back without reading anything back.
 constexpr int kCollapseLevels = 128;     // entries of the level-count arrays
@@ -620,15 +566,14 @@ int build_bvh(SceneHost* s)
     }
     bb.scale = scale;
 
-    const int leaf_max = tuning_int("RT_LEAF_MAX", kLeafDefault, 1, 8);
     const int n_internal = n > kLeafMax ? n - 1 : 1;
     const int nblocks = (n + kSortTile - 1) / kSortTile;
-    DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals, odd;
+    DevBuf box_lo, box_hi, keys_a, keys_b, vals_a, vals_b, hist, children, range, par_i, par_l, node_lo, node_hi, arrivals;
     const size_t N = (size_t)n;
     if (!box_lo.reserve(N * 16) || !box_hi.reserve(N * 16) || !keys_a.reserve(N * 4) || !keys_b.reserve(N * 4) ||
         !vals_a.reserve(N * 4) || !vals_b.reserve(N * 4) || !hist.reserve((size_t)256 * (nblocks + 1) * 4) ||
         !children.reserve(N * 8) || !range.reserve(N * 8) || !par_i.reserve(N * 4) || !par_l.reserve(N * 4) ||
-        !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4) || !odd.reserve(N))
+        !node_lo.reserve(N * 16) || !node_hi.reserve(N * 16) || !arrivals.reserve(N * 4))
         return RT_E_NOMEM;
     if (!s->bvh_nodes.reserve((size_t)n_internal * 64) || !s->bvh_tri.reserve((N + 1) * kTriWords * 16)) return RT_E_NOMEM;
 
@@ -645,13 +590,13 @@ int build_bvh(SceneHost* s)
         std::swap(kin, kout); std::swap(vin, vout);
     }
     // 4 passes: the sorted data is back in keys_a / vals_a
+    int levels4 = 1, levels8 = 0;
     if (n > kLeafMax) {
         RT_CUDA(cudaMemsetAsync(arrivals.p, 0, N * 4, st));
         hierarchy_kernel<<<G, B, 0, st>>>(kin, n, children.as<int2>(), range.as<int2>(), par_i.as<int>(), par_l.as<int>());
         refit_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(), par_i.as<int>(),
                                       par_l.as<int>(), node_lo.as<float4>(), node_hi.as<float4>(), arrivals.as<unsigned>());
-        static const int greedy4 = tuning_int("RT_BVH4_GREEDY", 1, 0, 1);
-        if (greedy4 && leaf_max == 1) {
+        {
             DevBuf queue_a, queue_b, counts;
             PinnedBuf h_counts;
             const size_t cbytes = (size_t)kCollapseLevels * sizeof(unsigned);
@@ -661,7 +606,8 @@ int build_bvh(SceneHost* s)
             const int cgrid = std::min((n + B - 1) / B, 148 * 8);
             const unsigned* hc = static_cast<const unsigned*>(h_counts.p);
             // a batch of levels without a word from the device, then a look at where it stands
-            for (int level = 0, batch = 24;; batch = 8) {
+            int level = 0;
+            for (int batch = 24;; batch = 8) {
                 for (int k = 0; k < batch && level < kCollapseLevels - 1; k++, level++) {
                     collapse4_kernel<<<cgrid, B, 0, st>>>(n, level, counts.as<unsigned>(), qc, qn, vin, box_lo.as<float4>(),
                                                          box_hi.as<float4>(), children.as<int2>(), node_lo.as<float4>(),
@@ -672,13 +618,11 @@ int build_bvh(SceneHost* s)
                 RT_CUDA(cudaMemcpyAsync(h_counts.p, counts.p, cbytes, cudaMemcpyDeviceToHost, st));
                 RT_CUDA(cudaStreamSynchronize(st));
                 if (hc[level] == 0) break;
-                if (level >= kCollapseLevels - 1) { set_error("collapse4: tree deeper than 127 levels"); return RT_E_CUDA; }
+                if (level >= kCollapseLevels - 1) { set_error("collapse4: tree deeper than 127 levels"); return RT_E_LIMIT; }
             }
-        } else {
-            depth_kernel<<<G, B, 0, st>>>(n, par_i.as<int>(), odd.as<unsigned char>());
-            emit_nodes4_kernel<<<G, B, 0, st>>>(n, vin, box_lo.as<float4>(), box_hi.as<float4>(), children.as<int2>(),
-                                                range.as<int2>(), node_lo.as<float4>(), node_hi.as<float4>(),
-                                                odd.as<unsigned char>(), s->bvh_nodes.as<float4>(), leaf_max);
+            // levels of the tree = the root's + those that received nodes
+            levels4 = 1;
+            while (levels4 < level && hc[levels4] != 0) levels4++;
         }
     } else {
         emit_tiny_kernel<<<1, 32, 0, st>>>(n, box_lo.as<float4>(), box_hi.as<float4>(), vin, s->bvh_nodes.as<float4>());
@@ -687,8 +631,7 @@ int build_bvh(SceneHost* s)
     RT_CUDA(cudaGetLastError());
     // the 8-wide tree of the any-hit walk (scenes with a binary tree worth collapsing)
     s->bvh8_n_nodes = 0;
-    static const int use8 = tuning_int("RT_BVH8", 1, 0, 1);
-    if (use8 && n > 8) {
+    if (n > 8) {
         DevBuf queue_a, queue_b, counts;
         PinnedBuf h_counts;
         const size_t cbytes = (size_t)(kCollapseLevels + 1) * sizeof(unsigned);      // [kCollapseLevels] = primitives placed
@@ -712,14 +655,26 @@ int build_bvh(SceneHost* s)
             RT_CUDA(cudaMemcpyAsync(h_counts.p, counts.p, cbytes, cudaMemcpyDeviceToHost, st));
             RT_CUDA(cudaStreamSynchronize(st));
             if (hc[level] == 0) break;
-            if (level >= kCollapseLevels - 1) { set_error("collapse8: tree deeper than 127 levels"); return RT_E_CUDA; }
+            if (level >= kCollapseLevels - 1) { set_error("collapse8: tree deeper than 127 levels"); return RT_E_LIMIT; }
         }
+        levels8 = 1;
+        while (levels8 < level && hc[levels8] != 0) levels8++;
         if (hc[kCollapseLevels] != (unsigned)n) { set_error("collapse8: primitive count mismatch"); return RT_E_CUDA; }
         unsigned total = 1;
         for (int l = 1; l < level; l++) total += hc[l];
         s->bvh8_n_nodes = (int)total;
     }
     RT_CUDA(cudaStreamSynchronize(st));
+    // The walks' stacks hold kSmemStack + kBvhStack entries (and the parity probes' kBvhStack): a tree
+    // that could need more is refused here rather than walked with a chance of a dropped subtree.
+    // (Karras trees over 30-bit Morton codes + index tie-breaks are at most ~50 binary levels deep;
+    // the stress scene's trees have about a dozen levels.)
+    s->bvh_levels4 = levels4; s->bvh_levels8 = levels8;
+    if (kStackNeed4(levels4) > kBvhStack || kStackNeed8(levels8) > kSmemStack + kBvhStack) {
+        set_error("LBVH too deep for the traversal stacks (" + std::to_string(levels4) + " / " + std::to_string(levels8) +
+                  " levels): degenerate primitive distribution");
+        return RT_E_LIMIT;
+    }
     s->bvh_n_nodes = n_internal; s->bvh_root = 0; s->bvh_built = true;
     return RT_OK;
 }

@@ -22,10 +22,9 @@ def _ptr(a: Optional[np.ndarray]):
 
 def make_params(max_depth: int = 4, epsilon: float = 1.0e-3, accel: int = abi.RT_ACCEL_AUTO, rank: int = 0,
                 world_size: int = 1, tile_rows: int = 8, instrument: bool = False, profile: bool = False,
-                subframes: int = 0, work_sharing: int = 0, occluder_hints: int = 0,
-                fused_trace: int = 0) -> abi.RtRenderParams:
+                subframes: int = 0, work_sharing: int = 0) -> abi.RtRenderParams:
     return abi.RtRenderParams(max_depth, epsilon, accel, rank, world_size, tile_rows, 1 if instrument else 0,
-                              1 if profile else 0, subframes, work_sharing, occluder_hints, fused_trace)
+                              1 if profile else 0, subframes, work_sharing)
 
 
 class DeviceScene:
