@@ -50,7 +50,7 @@ def scene_text(name: str) -> str:
     return _scene_table()[name]["text"]
 
 
-def materialise(name: str, workdir: str) -> str:
+def materialise(name: str, workdir: str, tex_scale: int = 1) -> str:
     """Writes the scene file and the stand-in textures it names; returns the scene path."""
     entry = _scene_table()[name]
     os.makedirs(os.path.join(workdir, "textures"), exist_ok=True)
@@ -58,7 +58,7 @@ def materialise(name: str, workdir: str) -> str:
         for p in (os.path.join(workdir, "textures", t), os.path.join(workdir, t)):
             if not os.path.exists(p):
                 with open(p, "w") as f:
-                    f.write(scenegen.p3_text(scenegen.standin_texture(t)))
+                    f.write(scenegen.p3_text(scenegen.standin_texture(t, tex_scale)))
     path = os.path.join(workdir, name.replace("/", "__") + ".txt")
     with open(path, "w") as f:
         f.write(entry["text"])
@@ -66,10 +66,11 @@ def materialise(name: str, workdir: str) -> str:
 
 
 @functools.lru_cache(maxsize=None)
-def example_scene(name: str) -> Scene:
-    """The example scene parsed by OUR host front-end at its own imsize."""
+def example_scene(name: str, tex_scale: int = 1) -> Scene:
+    """The example scene parsed by OUR host front-end at its own imsize (tex_scale: the seeded
+    stand-in textures that many times larger than the 128-wide ones the fixtures were made with)."""
     with tempfile.TemporaryDirectory() as tmp:
-        return Scene.from_file(materialise(name, tmp), texture_dir=tmp)
+        return Scene.from_file(materialise(name, tmp, tex_scale), texture_dir=tmp)
 
 
 def golden_frame(name: str):

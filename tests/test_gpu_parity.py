@@ -279,92 +279,6 @@ def test_work_sharing_in_the_walk_tails_never_changes_a_pixel():
             assert np.array_equal(ids_lbvh, ds.download_primary_ids())
 
 
-def test_occluder_hints_never_change_a_pixel():
-    """Shadow rays that test a hinted occluder before (instead of) walking the tree (ShadowJob::
-    first_leaf): frames with hints on / off equal the brute-force frame; the instrumented frame
-    reports hint hits, and walked + hinted shadow rays never exceed the reference's count."""
-    for scene in (scenegen.coverage_scene(128, 96), scenegen.stress_scene(8000, 100, 160, 120)):
-        with DeviceScene(scene) as ds:
-            ds.render(accel=abi.RT_ACCEL_BRUTE)
-            want = ds.download()
-            want = (want[0].copy(), want[1].copy())
-            stats = []
-            for mode in (2, 1, 0):
-                stats.append(ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=mode))
-                got = ds.download()
-                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), mode
-            assert list(stats[0].nodes_per_level) == list(stats[1].nodes_per_level) == list(stats[2].nodes_per_level)
-            off = ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=2, instrument=True)
-            on = ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=1, instrument=True)
-            got = ds.download()
-            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
-            assert off.shadow_hint_hits == 0
-            assert on.shadow_rays_walked + on.shadow_hint_hits <= on.rays_shadow
-            # a hint replaces a walk one for one: the chains stop at the same light either way
-            assert on.shadow_rays_walked + on.shadow_hint_hits == off.shadow_rays_walked
-    assert on.shadow_hint_hits > 0          # the dense stress scene does produce hits
-
-
-def test_interleaved_shadow_passes_never_change_a_pixel():
-    """The any-hit kernel takes the node list in interleaved passes so that hints are there in time
-    (ShadowJob::perm).  The knobs are process-wide, so a child process renders with 1024-node
-    passes and ragged groups; its frames must equal this process's brute-force frames."""
-    import subprocess, sys, tempfile
-    code = (
-        "import sys, numpy as np\n"
-        "sys.path.insert(0, %r)\n"
-        "from simple_raytracer_b200 import abi, scenegen\n"
-        "from simple_raytracer_b200.renderer import DeviceScene\n"
-        "out = {}\n"
-        "for name, sc in (('cov', scenegen.coverage_scene(128, 96)), ('stress', scenegen.stress_scene(8000, 100, 160, 120))):\n"
-        "    with DeviceScene(sc) as ds:\n"
-        "        ds.render(accel=abi.RT_ACCEL_LBVH, occluder_hints=1)\n"
-        "        rgb, fl = ds.download()\n"
-        "        out[name + '_rgb'] = rgb.copy(); out[name + '_fl'] = fl.copy()\n"
-        "np.savez(sys.argv[1], **out)\n" % os.path.dirname(common.HERE))
-    want = {}
-    for name, sc in (("cov", scenegen.coverage_scene(128, 96)), ("stress", scenegen.stress_scene(8000, 100, 160, 120))):
-        with DeviceScene(sc) as ds:
-            ds.render(accel=abi.RT_ACCEL_BRUTE)
-            rgb, fl = ds.download()
-            want[name] = (rgb.copy(), fl.copy())
-    for group in ("1", "3", "32"):
-        with tempfile.TemporaryDirectory() as td:
-            path = os.path.join(td, "frames.npz")
-            env = dict(os.environ, RT_HINT_MIN_CHUNK_K="1", RT_HINT_PASSES="7", RT_HINT_GROUP=group)
-            subprocess.run([sys.executable, "-c", code, path], check=True, env=env, timeout=600)
-            got = np.load(path)
-            for name in want:
-                assert np.array_equal(got[name + "_rgb"], want[name][0]), (group, name)
-                assert np.array_equal(got[name + "_fl"], want[name][1]), (group, name)
-
-
-@pytest.mark.parametrize("depth", [0, 1, 4])
-def test_fused_trace_kernel_never_changes_a_pixel(depth):
-    """All generations' closest-hit rays in one persistent launch whose spawner warps feed its own
-    work list (bvh_trace_all_kernel), then all shadow chains in one launch: frames, node and ray
-    counts and primary hit ids equal those of the per-generation launch chains and of brute force —
-    also for frames of a few pixels (fewer rays than lanes) and at depth 0 (nothing to spawn)."""
-    scenes = (scenegen.coverage_scene(128, 96), scenegen.stress_scene(8000, 100, 160, 120), scenegen.coverage_scene(16, 2))
-    for scene in scenes:
-        with DeviceScene(scene) as ds:
-            ds.render(accel=abi.RT_ACCEL_BRUTE, max_depth=depth)
-            want = ds.download()
-            want = (want[0].copy(), want[1].copy())
-            stats = {}
-            for mode in (2, 1):
-                stats[mode] = ds.render(accel=abi.RT_ACCEL_LBVH, fused_trace=mode, max_depth=depth)
-                got = ds.download()
-                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1]), (mode, scene.width)
-            assert list(stats[1].nodes_per_level) == list(stats[2].nodes_per_level)
-            assert stats[1].rays_reflect == stats[2].rays_reflect and stats[1].rays_transmit == stats[2].rays_transmit
-            assert stats[1].kernel_launches < stats[2].kernel_launches or depth == 0
-            ds.render(accel=abi.RT_ACCEL_LBVH, fused_trace=1, instrument=True, max_depth=depth)
-            ids_fused = ds.download_primary_ids().copy()
-            ds.render(accel=abi.RT_ACCEL_BRUTE, instrument=True, max_depth=depth)
-            assert np.array_equal(ids_fused, ds.download_primary_ids())
-
-
 def test_device_formatted_ppm_equals_the_host_formatter():
     """rt_format_ppm_device against rt_host_format_ppm on the downloaded frame: NaN
     channels (Test1 has them), primary misses with an out-of-range bkgcolor, 1/2/3-digit values,

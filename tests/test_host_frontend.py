@@ -32,14 +32,14 @@ def test_every_declared_symbol_is_exported():
         assert getattr(rt, n) is not None
     for n in names_host:
         assert getattr(host, n) is not None
-    assert rt.rt_abi_version() == 3
+    assert rt.rt_abi_version() == 4
 
 
 def test_struct_layouts_match_the_header():
     # sizes implied by include/rt.h on LP64
     assert C.sizeof(abi.RtMaterial) == 48 and C.sizeof(abi.RtSphere) == 28
     assert C.sizeof(abi.RtFace) == 112 and C.sizeof(abi.RtLight) == 28 and C.sizeof(abi.RtTexture) == 16
-    assert C.sizeof(abi.RtRenderParams) == 48
+    assert C.sizeof(abi.RtRenderParams) == 40
     assert C.sizeof(abi.RtSceneDesc) == 8 + 12 * 3 + 4 + 12 + 4 + 5 * 16
 
 
@@ -343,13 +343,13 @@ def test_ctypes_mirror_has_the_sizes_the_c_compiler_sees(tmp_path):
         '#include <stdio.h>\n#include <stddef.h>\n#include "rt.h"\n'
         "int main(void) {\n"
         '  printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(RtRenderParams), sizeof(RtStats), sizeof(RtSceneDesc),\n'
-        "         sizeof(RtMaterial), sizeof(RtFace), offsetof(RtStats, shadow_hint_hits), offsetof(RtRenderParams, fused_trace),\n"
+        "         sizeof(RtMaterial), sizeof(RtFace), offsetof(RtStats, bvh_levels8), offsetof(RtRenderParams, work_sharing),\n"
         "         offsetof(RtStats, shadow_rays_walked));\n"
         "  return 0; }\n")
     exe = tmp_path / "sizes"
     subprocess.run([cc, "-std=c11", "-I", os.path.join(root, "include"), "-o", str(exe), str(src)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [C.sizeof(abi.RtRenderParams), C.sizeof(abi.RtStats), C.sizeof(abi.RtSceneDesc), C.sizeof(abi.RtMaterial),
-            C.sizeof(abi.RtFace), abi.RtStats.shadow_hint_hits.offset, abi.RtRenderParams.fused_trace.offset,
+            C.sizeof(abi.RtFace), abi.RtStats.bvh_levels8.offset, abi.RtRenderParams.work_sharing.offset,
             abi.RtStats.shadow_rays_walked.offset]
     assert got == want

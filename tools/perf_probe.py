@@ -43,7 +43,7 @@ def main():
         if not a.no_instrument:
             si = ds.render(instrument=True, **kw)
             out.update(boxes_per_ray=round(si.bvh_nodes_visited / rays, 1), prims_per_ray=round(si.prim_tests / rays, 2),
-                       texels=int(si.texel_fetches), shadow_walked=int(si.shadow_rays_walked), hint_hits=int(si.shadow_hint_hits), shadow_ref=int(si.rays_shadow), instr_ms=round(si.render_ms, 2))
+                       texels=int(si.texel_fetches), shadow_walked=int(si.shadow_rays_walked), shadow_ref=int(si.rays_shadow), instr_ms=round(si.render_ms, 2))
             for name in ("trace_span_ms", "trace_drain_ms", "trace_warp_drain_ms", "shadow_span_ms", "shadow_drain_ms", "shadow_warp_drain_ms",
                          "trace_drain_steps", "trace_drain_lanes", "trace_drain_steals", "shadow_drain_steps", "shadow_drain_lanes"):
                 out[name] = [round(x, 3) for x in list(getattr(si, name))[:a.depth + 1]]
