@@ -233,15 +233,13 @@ def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
             # 64 B per 4-wide node visited + 80 B per primitive record tested + the ray read and the hit written
             "bvh_trace_kernel": 64 * tb + 80 * tp + 64 * closest_rays,
             # (the any-hit walk uses the 8-wide tree: 80 B loaded per node visited)
-            # (+ per hint-settled ray: the 4-byte hint and the 20 B of the chain; its record test is in sp)
-            "bvh_shadow_kernel": 80 * sb + 80 * sp + 20 * walked + 24 * int(st.shadow_hint_hits),
+            "bvh_shadow_kernel": 80 * sb + 80 * sp + 20 * walked,
             # 64 B per shaded hit + 4 B per texel
             "bvh_shade_kernel": 64 * nodes + 4 * int(st.texel_fetches),
         }
         return {"bound": "hbm", "per_frame": sum(per_kernel.values()), "per_kernel": per_kernel, "unit": "GB/s",
                 "detail": {"trace_nodes_visited": tb, "trace_prim_tests": tp, "shadow_nodes_visited": sb,
                            "shadow_prim_tests": sp, "closest_hit_rays": closest_rays, "shadow_rays_walked": walked,
-                           "shadow_rays_settled_by_hint": int(st.shadow_hint_hits),
                            "shadow_rays_reference": int(st.rays_shadow), "nodes_shaded": nodes,
                            "texels": int(st.texel_fetches)}}
     fl = rays * (19 * len(scene.spheres) + 42 * len(scene.faces)) + nodes * (64 + 52 * L)
