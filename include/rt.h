@@ -257,6 +257,30 @@ size_t rt_release_cached_memory(void);
  * terminating NUL. */
 int rt_format_ppm_device(RtScene* scene, const void* dev_rgba, const char** text, size_t* len);
 
+/* rt_format_ppm_device without a single allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  Needs no scene handle: the caller passes
+ * the frame and receives the text, both in DEVICE memory of the current device.
+ *   dev_rgba      : width*height RGBA8 in scanline order, A = flags (as rt_deinterleave_tiles leaves it,
+ *                   or the tile buffer of a world_size == 1 rt_render_async)
+ *   bkg           : RtSceneDesc.bkg (primary-miss pixels print the un-clamped (int)(bkg*255))
+ *   dev_text      : receives "P3 \n" "W H \n" "255 \n" + one "r g b \n" line per pixel, byte for byte
+ *                   what rt_format_ppm_device / rt_host_format_ppm produce; text_capacity bytes.
+ *                   41 + 64 * width * height always suffices; 12 * width * height + 64 does when
+ *                   no channel is NaN and bkg is in range
+ *   dev_len       : receives the file's length in bytes (8 bytes, device).  *dev_len > text_capacity
+ *                   means the buffer was too small: whole 256-pixel blocks are missing from the text
+ * Enqueues three kernels on cuda_stream (NULL = the legacy default stream) and returns; it calls no
+ * cudaMalloc / cudaFree / allocating routine and does not synchronise.  LIMIT: width * height <=
+ * 33,177,600 pixels (7680 x 4320), RT_E_LIMIT beyond: the per-block scratch is a static __device__
+ * array of 1.56 MB that every GPU loading this library holds until the process exits.  All calls on
+ * a device SHARE that array and it keeps the last call's contents (each call rewrites every entry
+ * it reads, nothing needs clearing): calls that overlap on the GPU — different streams without an
+ * ordering between them — race.  Calls on one stream, or ordered by events, are safe. */
+int rt_format_ppm_noalloc(const void* dev_rgba, int32_t width, int32_t height, const float bkg[3],
+                          char* dev_text, size_t text_capacity, unsigned long long* dev_len,
+                          void* cuda_stream);
+
 /* After an allgather of every rank's tile buffer ([rank][local_tile][row][col]
  * RGBA8, device memory) puts the pixels in scanline order:
  * dev_rgba_out[height][width] RGBA8. Asynchronous on cuda_stream. */

@@ -12,6 +12,8 @@
 
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 namespace rt {
 
@@ -202,3 +204,125 @@ int format_ppm_device(SceneHost* s, const uchar4* px, const char** text, size_t*
 }
 
 }  // namespace rt
+
+// ---- rt_format_ppm_noalloc: the same text without a single allocation ---------------------------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The formatter's scratch — one byte count and one offset per 256-pixel block — lives in a
+// file-scope __device__ array sized for the largest frame BASELINE.json names (7680 x 4320);
+// every GPU that loads the library holds these 1.56 MB until the process exits.  All calls on a
+// device share the array: calls that overlap on the GPU (different streams) race.  Nothing in it
+// has to start at zero — the length kernel rewrites every count the later kernels read, so a
+// call never sees what the last call left.
+namespace rt {
+namespace {
+
+constexpr unsigned kNoAllocMaxPixels = 7680u * 4320u;
+constexpr unsigned kNoAllocMaxBlocks = (kNoAllocMaxPixels + kPpmBlock - 1) / kPpmBlock;
+
+struct PpmScratch {
+    unsigned long long offset[kNoAllocMaxBlocks + 1];   // [n_blocks] = bytes of all pixel lines
+    unsigned bytes[kNoAllocMaxBlocks];
+};
+static __device__ __align__(256) PpmScratch g_ppm_scratch;
+
+// In host code `g_ppm_scratch` is a stand-in, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+std::mutex g_scratch_mutex;
+PpmScratch* g_scratch_addr[64] = { nullptr };
+
+int scratch_address(PpmScratch** out)
+{
+    int dev = -1;
+    RT_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { set_error("rt_format_ppm_noalloc: device index out of range"); return RT_E_CUDA; }
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_addr[dev]) {
+        void* p = nullptr;
+        RT_CUDA(cudaGetSymbolAddress(&p, g_ppm_scratch));
+        g_scratch_addr[dev] = static_cast<PpmScratch*>(p);
+    }
+    *out = g_scratch_addr[dev];
+    return RT_OK;
+}
+
+struct PpmHeader {
+    char text[64];
+    int len;
+};
+
+// Variant of ppm_write_kernel: the body starts behind the header (which block 0 writes), nothing is
+// stored past `capacity`, and the file's length goes to *len_out (device memory).
+__global__ void __launch_bounds__(kPpmBlock) ppm_write_noalloc_kernel(const uchar4* __restrict__ px, unsigned n, PpmTokens T,
+                                                                     PpmHeader H, const PpmScratch* __restrict__ scratch,
+                                                                     unsigned n_blocks, char* __restrict__ out,
+                                                                     unsigned long long capacity,
+                                                                     unsigned long long* __restrict__ len_out)
+{
+    __shared__ char text[kPpmBlock * kLineMax];
+    const unsigned k = blockIdx.x * kPpmBlock + threadIdx.x;
+    uchar4 p = make_uchar4(0, 0, 0, 0);
+    unsigned len = 0;
+    if (k < n) { p = px[k]; len = (unsigned)line_len(p, T); }
+    unsigned total;
+    const unsigned at = block_exclusive_scan(len, &total);
+    if (k < n) {
+        char* o = text + at;
+        o = put_token(o, p.x, p.w, 0, T);
+        o = put_token(o, p.y, p.w, 1, T);
+        o = put_token(o, p.z, p.w, 2, T);
+        *o = '\n';
+    }
+    __syncthreads();
+    const unsigned long long begin = (unsigned long long)H.len + scratch->offset[blockIdx.x];
+    if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) *len_out = (unsigned long long)H.len + scratch->offset[n_blocks];
+        if ((unsigned long long)H.len <= capacity)
+            for (unsigned i = threadIdx.x; i < (unsigned)H.len; i += kPpmBlock) out[i] = H.text[i];
+    }
+    if (begin + total > capacity) return;          // the caller sees *len_out > capacity: the text is incomplete
+    char* dst = out + begin;
+    for (unsigned i = threadIdx.x; i < total; i += kPpmBlock) dst[i] = text[i];
+}
+
+}  // namespace
+}  // namespace rt
+
+extern "C" int rt_format_ppm_noalloc(const void* dev_rgba, int32_t width, int32_t height, const float bkg[3],
+                                     char* dev_text, size_t text_capacity, unsigned long long* dev_len,
+                                     void* cuda_stream)
+{
+    using namespace rt;
+    if (!dev_rgba || !bkg || !dev_text || !dev_len || width < 1 || height < 1) {
+        set_error("rt_format_ppm_noalloc: bad argument");
+        return RT_E_INVALID;
+    }
+    const unsigned long long n = (unsigned long long)width * (unsigned long long)height;
+    if (n > kNoAllocMaxPixels) {
+        set_error("rt_format_ppm_noalloc: " + std::to_string(n) + " pixels exceed the built-in scratch (33177600 pixels = 7680 x 4320); use rt_format_ppm_device");
+        return RT_E_LIMIT;
+    }
+    PpmScratch* scratch = nullptr;
+    const int rc = scratch_address(&scratch);
+    if (rc != RT_OK) return rc;
+    const unsigned n_blocks = (unsigned)((n + kPpmBlock - 1) / kPpmBlock);
+    PpmTokens T;
+    std::memset(&T, 0, sizeof T);
+    std::memcpy(T.nan, "18446744071562067968", kTokMax);
+    for (int c = 0; c < 3; c++) {
+        char tmp[32];
+        T.bkg_len[c] = std::snprintf(tmp, sizeof tmp, "%llu", quantise_like_reference(bkg[c]));
+        std::memcpy(T.bkg[c], tmp, (size_t)T.bkg_len[c]);
+    }
+    PpmHeader H;
+    std::memset(&H, 0, sizeof H);
+    H.len = std::snprintf(H.text, sizeof H.text, "P3 \n%d %d \n255 \n", width, height);   // main.cpp:628-630
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    const uchar4* px = static_cast<const uchar4*>(dev_rgba);
+    ppm_len_kernel<<<n_blocks, kPpmBlock, 0, st>>>(px, (unsigned)n, T, scratch->bytes);
+    ppm_scan_kernel<<<1, 1024, 0, st>>>(scratch->bytes, n_blocks, scratch->offset, scratch->offset + n_blocks);
+    ppm_write_noalloc_kernel<<<n_blocks, kPpmBlock, 0, st>>>(px, (unsigned)n, T, H, scratch, n_blocks, dev_text,
+                                                            (unsigned long long)text_capacity, dev_len);
+    RT_CUDA(cudaGetLastError());
+    return RT_OK;
+}
