@@ -208,7 +208,9 @@ struct BvhAccelT {
     // bit patterns order like unsigned integers: the child index rides in the two lowest
     // mantissa bits and the four keys go through a five-comparator network of integer min / max
     // (order is only a heuristic here: every accepted hit comes from the exact primitive test).
-    // No branch depends on how many children were hit, so the lanes of a warp stay together.
+    // No branch depends on how many children were hit, so the lanes of a warp stay together
+    // (A/B against round 1's float compare-and-swap network with a branch per push, 4K stress frame:
+    // 37.50 -> 37.03 ms, 1/8 shard 5.98 -> 5.88 ms; profiles/r2_ab_sort_tiles.txt).
     template <class Stack>
     RT_DEV int step(const float4* __restrict__ nd, int node, const RayQ& r, float tmin, float tmax, Stack& st) const
     {
