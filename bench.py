@@ -40,9 +40,9 @@ L2_BYTES = 126 << 20
 
 
 # ---- workloads (BASELINE.json configs) ------------------------------------------
-def _example(name, w, h):
+def _example(name, w, h, tex_scale=1):
     from tests import common
-    return common.example_scene(name).with_size(w, h)
+    return common.example_scene(name, tex_scale).with_size(w, h)
 
 
 WORKLOADS = {
@@ -55,6 +55,8 @@ WORKLOADS = {
     # configs[2] / configs[3]: the reference's own reflection / refraction demo scene
     "test7_1080p": lambda: _example("reflection_transparency_tests/test7", 1920, 1080),
     "test7_4k": lambda: _example("reflection_transparency_tests/test7", 3840, 2160),
+    # configs[3] (ii): the showcase scene with its four textures (seeded 1024-wide stand-ins)
+    "house_4k": lambda: _example("showcases/house", 3840, 2160, tex_scale=8),
     # configs[0]
     "four_spheres_512": lambda: _example("basic_geometry_tests/four_spheres", 512, 512),
     # small variant for quick checks of this script
@@ -151,6 +153,11 @@ def cpu_reference(scene: Scene, budget_s: float, procs: int) -> dict:
     import multiprocessing as mp
     from tests import oracle_lib as O
     kind = "reference" if O.have_ref() else "port"
+    if kind == "reference":
+        # the forked workers trace through oracle/_ref/libref.so; one pixel in this process as well, so that
+        # the library is mapped here too (the driver records the libraries of the bench process itself)
+        O.load_ref()
+        O.ref_render_pixels(scene, cpu_sample_pixels(scene, 1))
     # calibrate on a few pixels with the (much faster) port, then size the sample
     probe = cpu_sample_pixels(scene, 4)
     t0 = time.perf_counter()
@@ -218,6 +225,13 @@ def pin_scene(scene: Scene):
     return sc
 
 
+# SURVEY 8(d) "Algorithmic work per unit": 32 B per node visited, 48 B per primitive tested, 64 B per ray /
+# closest hit shaded, 4 B per texel.  (The trees here have 64-byte 4-wide and 96-byte 8-wide nodes and 80-byte
+# primitive records, so the bytes that actually move per visit are larger; this line's figure is the
+# implementation-independent one the survey fixed.)
+B_NODE, B_PRIM, B_RAY, B_TEXEL = 32, 48, 64, 4
+
+
 def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
     """algorithmic bytes (LBVH) or flops (brute force) of one frame, from the
     instrumented frame's device counters, split by kernel for the LBVH pipeline."""
@@ -230,20 +244,35 @@ def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
         closest_rays = int(st.rays_primary + st.rays_transmit + st.rays_reflect)
         walked = int(st.shadow_rays_walked)
         per_kernel = {
-            # 64 B per 4-wide node visited + 80 B per primitive record tested + the ray read and the hit written
-            "bvh_trace_kernel": 64 * tb + 80 * tp + 64 * closest_rays,
-            # (the any-hit walk uses the 8-wide tree: 80 B loaded per node visited)
-            "bvh_shadow_kernel": 80 * sb + 80 * sp + 20 * walked,
-            # 64 B per shaded hit + 4 B per texel
-            "bvh_shade_kernel": 64 * nodes + 4 * int(st.texel_fetches),
+            "bvh_trace_kernel": B_NODE * tb + B_PRIM * tp + B_RAY * closest_rays,
+            "bvh_shadow_kernel": B_NODE * sb + B_PRIM * sp,
+            "bvh_colour_kernel": B_RAY * nodes + B_TEXEL * int(st.texel_fetches),
         }
         return {"bound": "hbm", "per_frame": sum(per_kernel.values()), "per_kernel": per_kernel, "unit": "GB/s",
                 "detail": {"trace_nodes_visited": tb, "trace_prim_tests": tp, "shadow_nodes_visited": sb,
                            "shadow_prim_tests": sp, "closest_hit_rays": closest_rays, "shadow_rays_walked": walked,
                            "shadow_rays_reference": int(st.rays_shadow), "nodes_shaded": nodes,
-                           "texels": int(st.texel_fetches)}}
+                           "texels": int(st.texel_fetches), "shadow_chains_redone": int(st.shadow_chains_redone),
+                           "bvh_levels": [int(st.bvh_levels4), int(st.bvh_levels8)]}}
     fl = rays * (19 * len(scene.spheres) + 42 * len(scene.faces)) + nodes * (64 + 52 * L)
     return {"bound": "fp32", "per_frame": fl, "unit": "TFLOP/s", "detail": {"rays": rays, "nodes_shaded": nodes}}
+
+
+def ncu_summary(workload: str) -> dict:
+    """What the committed `ncu --set full` capture of this workload's dominant kernels says
+    (profiles/r2_ncu_summary.json, written by tools/ncu_summary.py from the .ncu-rep): issue-slot use,
+    lanes per instruction, DRAM bytes per launch.  A profiler cannot run inside the timed run, so these
+    are the one part of the line that is not live; the file they come from is named beside them."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_ncu_summary.json")) as f:
+            return json.load(f).get(workload, {})
+    except (OSError, ValueError):
+        return {}
+
+
+def frame_sha256(t) -> str:
+    import hashlib
+    return hashlib.sha256(t.cpu().numpy().tobytes()).hexdigest()
 
 
 # ---- our arm ---------------------------------------------------------------------------------
@@ -286,9 +315,11 @@ def run_ours(args) -> dict:
     st_plain = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS)
     st_p = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS, profile=True)
     level_ms = [float(x) for x in list(st_p.level_ms)[:5]]
+    # (profiled frames: one serial chain; trace_ms = bvh_trace_kernel + bvh_spawn_kernel of the generation,
+    # shadow_ms = bvh_shadow_kernel (+ the empty redo launch), shade_ms = bvh_colour_kernel)
     kernel_ms = {"bvh_trace_kernel": [float(x) for x in list(st_p.trace_ms)[:5]],
                  "bvh_shadow_kernel": [float(x) for x in list(st_p.shadow_ms)[:5]],
-                 "bvh_shade_kernel": [float(x) for x in list(st_p.shade_ms)[:5]]}
+                 "bvh_colour_kernel": [float(x) for x in list(st_p.shade_ms)[:5]]}
     # (kernels of a plain frame as the timed loop runs it; the profiled frame is a serial chain per generation)
     launches_per_frame = int(st_plain.kernel_launches)
 
@@ -316,13 +347,41 @@ def run_ours(args) -> dict:
     total_ms = sum(a.elapsed_time(b) for a, b in ev)
     clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([total_ms, float(rays_local)], dtype=torch.float64, device="cuda")
+    # ---- the frame the timed loop left behind: complete (no queue overflow on any rank), the same bytes on
+    # every rank, and the bytes of an untimed single-GPU rt_render of the whole frame on rank 0
+    complete = ds.async_frame_ok()
+    my_hash = frame_sha256(df.frame)
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (bool(complete), my_hash))
+    else:
+        gathered = [(bool(complete), my_hash)]
+    frame_check = None
+    if rank == 0:
+        ds.render(rank=0, world_size=1, tile_rows=TILE_ROWS)
+        rgb1, flg1 = ds.download()
+        import hashlib
+        single = hashlib.sha256(np.concatenate([rgb1, flg1[..., None]], axis=2).tobytes()).hexdigest()
+        if not all(c for c, _ in gathered):
+            frame_check = "INCOMPLETE: a wavefront queue overflowed on rank(s) " + str([k for k, (c, _) in enumerate(gathered) if not c])
+        elif any(h != single for _, h in gathered):
+            frame_check = "MISMATCH against the single-GPU frame on rank(s) " + str([k for k, (_, h) in enumerate(gathered) if h != single])
+        else:
+            frame_check = "byte-identical"
+        frame_check = {"result": frame_check, "sha256": single, "ranks": world,
+                       "what": "sha256 of every rank's assembled RGBA8 frame after the timed loop vs an untimed "
+                               "single-GPU rt_render + rt_download_framebuffer on rank 0; rt_async_frame_status on every rank"}
+
+    # rays the pipeline actually walks (the LBVH pipeline skips shadow rays whose result cannot matter)
+    rays_walked_local = (work["detail"].get("closest_hit_rays", 0) + work["detail"].get("shadow_rays_walked", 0)) \
+        if "closest_hit_rays" in work["detail"] else rays_local
+    t = torch.tensor([total_ms, float(rays_local), float(rays_walked_local)], dtype=torch.float64, device="cuda")
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        total_ms, rays_frame = float(tmax[0]), int(tsum[1])
+        total_ms, rays_frame, rays_walked_frame = float(tmax[0]), int(tsum[1]), int(tsum[2])
     else:
-        rays_frame = rays_local
+        rays_frame, rays_walked_frame = rays_local, int(rays_walked_local)
     ms_per_step = total_ms / args.steps
     value = rays_frame / (ms_per_step * 1e-3) / 1e6
 
@@ -337,12 +396,22 @@ def run_ours(args) -> dict:
         rgb, flg = rgb_t.numpy(), flg_t.numpy()
         n_e2e = max(1, min(args.steps, args.e2e_steps))
 
+        split = {"upload_ms": 0.0, "build_plus_render_ms": 0.0, "download_ms": 0.0}
+
         def e2e_step():
-            with DeviceScene(pinned) as d2:
-                d2.render(prm)
-                d2.download(rgb, flg)
+            t0 = time.perf_counter()
+            with DeviceScene(pinned) as d2:                 # rt_upload_scene: H2D of the description + SoA packing
+                t1 = time.perf_counter()
+                d2.render(prm)                              # rt_render: LBVH build (first frame of a scene) + the frame
+                t2 = time.perf_counter()
+                d2.download(rgb, flg)                       # rt_download_framebuffer: split planes + D2H
+                t3 = time.perf_counter()
+            split["upload_ms"] += (t1 - t0) * 1e3; split["build_plus_render_ms"] += (t2 - t1) * 1e3
+            split["download_ms"] += (t3 - t2) * 1e3
 
         e2e_step()      # warm-up (first-touch of the pinned buffers, workspace cache)
+        for k in split:
+            split[k] = 0.0
         barrier()
         t0 = time.perf_counter()
         for _ in range(n_e2e):
@@ -356,6 +425,7 @@ def run_ours(args) -> dict:
         e2e = {"value": rays_frame * n_e2e / dt / 1e6, "unit": "Mrays/s", "ms_per_step": dt / n_e2e * 1e3,
                "steps": n_e2e, "h2d_bytes_per_step": pinned.h2d_bytes(),
                "d2h_bytes_per_step": int(H * W * 4 / world),
+               "split_ms": {k: v / n_e2e for k, v in split.items()} | {"build_ms_est": max(0.0, split["build_plus_render_ms"] / n_e2e - ms_per_step)},
                "what": "rt_upload_scene(host RtSceneDesc, pinned) + rt_render + rt_download_framebuffer per step, "
                        "host wall clock, max over ranks"}
     else:
@@ -368,53 +438,68 @@ def run_ours(args) -> dict:
 
     peaks = measured_peaks()
     n_levels = 5
+    ncu = ncu_summary(args.workload) if world == 1 else {}
     if work["bound"] == "hbm":
         # the dominant kernel of the LBVH pipeline: whichever tree-walk kernel takes longer
         dom = max(("bvh_trace_kernel", "bvh_shadow_kernel"), key=lambda k: sum(kernel_ms[k]))
         dom_ms = sum(kernel_ms[dom])
         achieved = work["per_kernel"][dom] / (dom_ms * 1e-3) / 1e9
         peak = peaks["hbm_gbs"]
-        traffic = None
-        try:      # dram__bytes_read + dram__bytes_write per launch from the committed ncu --set full capture
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-                traffic = json.load(f)[dom]["dram_bytes_per_launch"] if args.workload == DEFAULT_WORKLOAD and world == 1 else None
-        except (OSError, KeyError, ValueError):
-            pass
+        nk = ncu.get(dom, {})
         roof = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peaks["source"], "kernel": dom,
+                "traffic": nk.get("dram_bytes_per_launch"), "peak_source": peaks["source"], "kernel": dom,
                 "algorithmic_bytes_per_launch": work["per_kernel"][dom] / n_levels,
+                "per_unit_bytes": {"node_visit": B_NODE, "primitive_test": B_PRIM, "ray_or_shaded_hit": B_RAY, "texel": B_TEXEL,
+                                   "source": "SURVEY.md 8(d)"},
+                # what actually limits the kernel, from the committed ncu --set full capture of this workload
+                "binding": {"unit": "issue slots at the SIMT efficiency of incoherent tree walks (not HBM)",
+                            "issue_active_pct": nk.get("issue_active_pct"), "lanes_per_inst": nk.get("lanes_per_inst"),
+                            "useful_lane_issue_frac": (nk["issue_active_pct"] / 100.0 * nk["lanes_per_inst"] / 32.0)
+                            if nk.get("issue_active_pct") and nk.get("lanes_per_inst") else None,
+                            "dram_gbs_measured": nk.get("dram_gbs"), "dram_pct_of_peak": nk.get("dram_pct"),
+                            "l1_hit_pct": nk.get("l1_hit_pct"), "source": ncu.get("source")},
                 "kernels": {k: {"ms_per_frame": sum(v), "ms_by_generation": v,
                                 "algorithmic_bytes_per_frame": work["per_kernel"][k],
                                 "achieved_gbs": work["per_kernel"][k] / (sum(v) * 1e-3) / 1e9 if sum(v) else None}
                             for k, v in kernel_ms.items()},
-                "note": "algorithmic bytes = 64 B per 4-wide node visit (closest hit) / 80 B per 8-wide node visit (any hit) + 80 B per primitive test; they are mostly served by "
-                        "L1/L2 (the tree is shared by all rays): the walk is bound by the L1/TEX gather pipe and SIMT "
-                        "divergence, not by HBM - see DESIGN.md 6 and profiles/"}
+                "note": "frac = SURVEY 8(d) algorithmic bytes / kernel time / measured HBM copy bandwidth: the figure the survey "
+                        "fixed for comparison.  Most of those bytes are served by L1/L2 (the upper tree is shared by all rays): "
+                        "measured DRAM traffic is `traffic` per launch, a few percent of peak, and the kernel is bound by "
+                        "instruction issue at ~18-20 of 32 lanes (`binding`), see DESIGN.md 6"}
     else:
         dom_ms = sum(level_ms)
         clk = (clocks or {}).get("sm_mhz") or peaks["sm_max_mhz"]
         peak = fp32_peak_tflops(clk)
         achieved = work["per_frame"] / (dom_ms * 1e-3) / 1e12
+        nk = ncu.get("level_kernel", {})
         roof = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": f"148 SM x 128 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)",
-                "kernel": "level_kernel (fused closest hit + shadow rays + shade + spawn)"}
+                "traffic": nk.get("dram_bytes_per_launch"),
+                "peak_source": f"148 SM x 128 lanes x 2 x {clk:.0f} MHz (clock sampled during the run)",
+                "kernel": "level_kernel (fused closest hit + shadow rays + shade + spawn)",
+                "binding": {"unit": "exact-rounding FP32 divisions / FP64 conversions and libm (XU + FP64 pipes), launch latency on small frames",
+                            "issue_active_pct": nk.get("issue_active_pct"), "lanes_per_inst": nk.get("lanes_per_inst"),
+                            "xu_pipe_pct": nk.get("xu_pipe_pct"), "fp64_pipe_pct": nk.get("fp64_pipe_pct"),
+                            "fma_pipe_pct": nk.get("fma_pipe_pct"), "source": ncu.get("source")}}
     roof.update({"launches_per_frame": n_levels, "ms_per_launch_avg": dom_ms / n_levels, "level_ms": level_ms,
                  "algorithmic_per_frame": work["per_frame"], "counters": work["detail"],
+                 "frame_frac": work["per_frame"] / (float(st_p.render_ms) * 1e-3) / (1e9 if work["bound"] == "hbm" else 1e12) / peak
+                 if st_p.render_ms else None,
                  "share_of_frame": dom_ms / float(st_p.render_ms) if st_p.render_ms else None,
                  "scope": "rank 0's shard" if world > 1 else "whole frame"})
-
     out = {"metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": args.workload, "width": W, "height": H, "triangles": len(scene.faces),
-                      "spheres": len(scene.spheres), "lights": len(scene.lights), "max_depth": 4,
-                      "accel": "lbvh" if accel_used == abi.RT_ACCEL_LBVH else "brute",
-                      "rays_per_frame": rays_frame,
-                      "rays_traced": (work["detail"].get("closest_hit_rays", 0) + work["detail"].get("shadow_rays_walked", 0))
-                      if world == 1 and "closest_hit_rays" in work["detail"] else None,
-                      "sharding": f"interleaved tiles of {TILE_ROWS} rows, "
-                      f"{'NCCL allgather of RGBA8 tiles + ' if world > 1 else ''}device de-interleave",
-                      "l2": "flushed between timed iterations (252 MiB memset, untimed)"},
+                      "spheres": len(scene.spheres), "lights": len(scene.lights), "max_depth": 4},
+           "config_note": {"accel": "lbvh" if accel_used == abi.RT_ACCEL_LBVH else "brute",
+                           "rays_per_frame": rays_frame, "rays_walked_per_frame": rays_walked_frame,
+                           "sharding": f"interleaved tiles of {TILE_ROWS} rows, "
+                           f"{'NCCL allgather of RGBA8 tiles + ' if world > 1 else ''}device de-interleave",
+                           "l2": "flushed between timed iterations (252 MiB memset, untimed)"},
+           "rays_walked_per_s": rays_walked_frame / (ms_per_step * 1e-3),
+           "value_note": "value counts the reference's TraceRay calls (primary + one shadow ray per light per shaded hit + "
+                         "transmission + reflection); rays_walked_per_s counts the rays this pipeline had to walk",
+           "frame_check": frame_check,
            "clocks": clocks, "gpu_launches": (launches_per_frame + 1) * args.steps, "roofline": roof}
     if e2e:
         out["e2e"] = e2e
@@ -449,7 +534,9 @@ def run_reference(args) -> dict:
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "width": scene.width, "height": scene.height,
                        "triangles": len(scene.faces), "spheres": len(scene.spheres), "lights": len(scene.lights),
-                       "max_depth": 4, "accel": "brute force (the reference has no acceleration structure)"},
+                       "max_depth": 4},
+            "config_note": "the reference has no acceleration structure: brute force over all primitives per ray, "
+                           "a bounded pixel sample of the frame per step",
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": base["cores"], "kind": base["kind"],
                              "sample": "each step: " + base["sample"]},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
