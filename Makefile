@@ -45,7 +45,7 @@ bin/raytracer: $(CSRC)/host/raytracer_main.cpp $(LIB)/librt_host.so $(LIB)/librt
 	@mkdir -p bin
 	$(CXX) -std=c++17 -O2 -Iinclude -o $@ $< -L$(LIB) -lrt_b200 -lrt_host -Wl,-rpath,'$$ORIGIN/../$(LIB)'
 
-oracle:
+oracle: $(LIB)/librt_b200.so
 	$(MAKE) -C oracle all
 
 clean:

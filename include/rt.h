@@ -110,6 +110,10 @@ typedef struct RtSceneDesc {
     int32_t n_spheres;    const RtSphere*   spheres;   /* file order */
     int32_t n_faces;      const RtFace*     faces;     /* file order */
     int32_t n_lights;     const RtLight*    lights;    /* file order */
+    int32_t camera_normalised;    /* 0: viewdir / updir are the scene file's raw vectors and are normalised
+                                     inside (what main.cpp:607 does at the call site); 1: they are what
+                                     create_view_window_and_ray_trace RECEIVES, i.e. already normalised,
+                                     and are used bit for bit (the drop-in binding) */
 } RtSceneDesc;
 
 /* ---- render parameters (environment.other, main.cpp:100-101) ------------ */

@@ -468,9 +468,10 @@ typedef struct { V3 eye, ul, delta_h, delta_v; } OCamera;
 static void make_camera(const RtSceneDesc* d, OCamera* cam)
 {
     V3 view_origin = v3(d->eye[0], d->eye[1], d->eye[2]);
-    /* the caller normalises both (main.cpp:607) */
-    V3 view_direction = vnorm(v3(d->viewdir[0], d->viewdir[1], d->viewdir[2]));
-    V3 view_up = vnorm(v3(d->updir[0], d->updir[1], d->updir[2]));
+    /* the caller normalises both (main.cpp:607); camera_normalised: they already are what the callee receives */
+    V3 view_direction = v3(d->viewdir[0], d->viewdir[1], d->viewdir[2]);
+    V3 view_up = v3(d->updir[0], d->updir[1], d->updir[2]);
+    if (!d->camera_normalised) { view_direction = vnorm(view_direction); view_up = vnorm(view_up); }
     float res_h = (float)d->height, res_w = (float)d->width;         /* passed as float, 670 */
     V3 u = vnorm(vcross(view_direction, view_up));                   /* 677 */
     V3 v = vcross(u, view_direction);                                /* 684 */

@@ -60,7 +60,8 @@ class RtSceneDesc(C.Structure):
                 ("n_textures", C.c_int32), ("textures", C.POINTER(RtTexture)),
                 ("n_spheres", C.c_int32), ("spheres", C.POINTER(RtSphere)),
                 ("n_faces", C.c_int32), ("faces", C.POINTER(RtFace)),
-                ("n_lights", C.c_int32), ("lights", C.POINTER(RtLight))]
+                ("n_lights", C.c_int32), ("lights", C.POINTER(RtLight)),
+                ("camera_normalised", C.c_int32)]
 
 
 class RtRenderParams(C.Structure):

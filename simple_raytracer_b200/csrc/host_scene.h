@@ -176,7 +176,7 @@ struct SceneHost {
 // upload.cu
 int build_scene(const RtSceneDesc* d, SceneHost* s);
 void make_camera(const float eye[3], const float viewdir[3], const float updir[3], float hfov_deg, int width,
-                 int height, CameraView* cam);
+                 int height, CameraView* cam, bool normalised = false);
 SceneView scene_view(const SceneHost* s);
 
 // bvh.cu

@@ -172,7 +172,7 @@ int upload_array(DevBuf& buf, const T* host, size_t n, cudaStream_t st)
 // glibc's, exactly as in the reference.  Host float arithmetic is IEEE single with
 // no contraction (-ffp-contract=off, no -march).
 void make_camera(const float eye[3], const float viewdir[3], const float updir[3], float hfov_deg, int width,
-                 int height, CameraView* cam)
+                 int height, CameraView* cam, bool normalised)
 {
     struct H3 { float x, y, z; };
     auto add = [](H3 a, H3 b) { return H3{ a.x + b.x, a.y + b.y, a.z + b.z }; };
@@ -190,8 +190,9 @@ void make_camera(const float eye[3], const float viewdir[3], const float updir[3
         return H3{ x1 - x2, y1 - y2, z1 - z2 };
     };
     const H3 origin{ eye[0], eye[1], eye[2] };
-    const H3 vd = norm(H3{ viewdir[0], viewdir[1], viewdir[2] });   // main.cpp:607
-    const H3 vu = norm(H3{ updir[0], updir[1], updir[2] });
+    const H3 vd_raw{ viewdir[0], viewdir[1], viewdir[2] }, vu_raw{ updir[0], updir[1], updir[2] };
+    const H3 vd = normalised ? vd_raw : norm(vd_raw);                // main.cpp:607
+    const H3 vu = normalised ? vu_raw : norm(vu_raw);
     const float res_h = (float)height, res_w = (float)width;
     const H3 u = norm(cross(vd, vu));                                // 677
     const H3 v = cross(u, vd);                                       // 684
@@ -245,7 +246,7 @@ int build_scene(const RtSceneDesc* d, SceneHost* s)
     for (int i = 0; i < d->n_lights; i++)
         for (int c = 0; c < 3; c++) tame = tame && std::isfinite(d->lights[i].rgb[c]) && std::isfinite(d->lights[i].xyz[c]);
     s->zero_mask_exit = tame;
-    make_camera(d->eye, d->viewdir, d->updir, d->hfov_deg, d->width, d->height, &s->cam);
+    make_camera(d->eye, d->viewdir, d->updir, d->hfov_deg, d->width, d->height, &s->cam, d->camera_normalised != 0);
 
     cudaStream_t st = s->stream;
     DevBuf raw_faces, raw_spheres, raw_mats, raw_lights, raw_tex;

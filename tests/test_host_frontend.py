@@ -40,7 +40,7 @@ def test_struct_layouts_match_the_header():
     assert C.sizeof(abi.RtMaterial) == 48 and C.sizeof(abi.RtSphere) == 28
     assert C.sizeof(abi.RtFace) == 112 and C.sizeof(abi.RtLight) == 28 and C.sizeof(abi.RtTexture) == 16
     assert C.sizeof(abi.RtRenderParams) == 40
-    assert C.sizeof(abi.RtSceneDesc) == 8 + 12 * 3 + 4 + 12 + 4 + 5 * 16
+    assert C.sizeof(abi.RtSceneDesc) == 8 + 12 * 3 + 4 + 12 + 4 + 5 * 16 + 8
 
 
 def _write(tmp_path, text, name="s.txt"):
