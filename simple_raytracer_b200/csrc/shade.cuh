@@ -157,9 +157,25 @@ RT_DEV void shade_spawn(const SceneView& S, V3 incidence_ray, int obj, const Sur
     if (cosi < 0.0f && is_sphere) { N = vneg(N); cosi = vdot(N, I); }            // 869-872
 
     const float snell = fdiv(n_i, n_t);                                          // 961
-    const float critical = ref_asinf(fdiv(n_t, n_i));                            // 962
-    const float incidence = ref_acosf(cosi);                                     // 963
-    const bool tir = (critical < incidence) && ((double)incidence < (90.0 * 3.14159265358979323846 / 180.0));   // 964
+    // 962-964: critical = asinf(n_t / n_i); incidence = acosf(cos); tir = critical < incidence && incidence < pi/2.
+    // Two double libm calls per node, decided without them unless the node sits within 1e-4 of a boundary:
+    // asin(x) < acos(c)  <=>  x < 0, or x^2 + c^2 < 1 (x in [0,1], c in [0,1]); NaN (|x| > 1, c > 1) compares false;
+    // the two float roundings move the angles by < 1.3e-7, |x^2 + c^2 - 1| >= 1e-4 keeps them >= 1e-4 apart.
+    const float xq = fdiv(n_t, n_i);
+    bool tir;
+    {
+        const float sq = fmaf(xq, xq, fmaf(cosi, cosi, -1.0f));
+        const bool c_clear = cosi > 1.0e-4f && cosi <= 1.0f;            // incidence < pi/2 for sure, and defined
+        if (!(cosi >= -1.0f && cosi <= 1.0f) || !(xq >= -1.0f && xq <= 1.0f)) tir = false;       // an angle is NaN
+        else if (cosi < -1.0e-4f) tir = false;                                                    // incidence > pi/2
+        else if (c_clear && xq < -1.0e-4f) tir = true;
+        else if (c_clear && xq > 1.0e-4f && fabsf(sq) >= 1.0e-4f) tir = sq < 0.0f;
+        else {
+            const float critical = ref_asinf(xq);                                // 962
+            const float incidence = ref_acosf(cosi);                             // 963
+            tir = (critical < incidence) && ((double)incidence < (90.0 * 3.14159265358979323846 / 180.0));   // 964
+        }
+    }
     const float F0t = ref_pow2f(fdiv(fsub(n_t, n_i), fadd(n_t, n_i)));           // 965
     const float Ft = schlick(F0t, cosi);                                         // 966
 

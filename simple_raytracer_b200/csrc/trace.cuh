@@ -57,6 +57,15 @@ RT_DEV int sphere_roots(const float4& w0, V3 o, V3 ray, float& t_far, float& t_n
     const float dot = vsum3(fmul(ray.x, dir.x), fmul(ray.y, dir.y), fmul(ray.z, dir.z));
     const float B = fmul(2.0f, dot);                                             // 1233: exact doubling
     const float ss = vsum3(fmul(dir.x, dir.x), fmul(dir.y, dir.y), fmul(dir.z, dir.z));
+    {
+        // Screening (culls only): most tests are clear misses, and the exact discriminant below costs six
+        // float<->double conversions and three FP64 operations.  e approximates B^2 - 4C within a few ulp of
+        // m = B^2 + 4(ss + r^2); when e < -1e-6 m (16 times that error) the exact det is negative and not
+        // -0: no root.  NaN / inf operands fail the comparison and take the exact path.
+        const float rr = w0.w * w0.w;
+        const float e = fmaf(B, B, -4.0f * (ss - rr)), m = fmaf(B, B, 4.0f * (ss + rr));
+        if (e < -1.0e-6f * m) return 0;
+    }
     const double r = (double)w0.w;
     const float C = (float)dsub((double)ss, dmul(r, r));                         // 1234: pow(r, 2.0) is exact
     const float det = (float)dsub(dmul((double)B, (double)B), dmul(4.0, (double)C));   // 1242
