@@ -184,6 +184,10 @@ typedef struct RtStats {
     uint64_t shadow_chains_redone; /* LBVH: nodes whose shadow chain met more than 12 transparent occluders on
                                     one ray and went through the exact slow path (bvh_shadow_redo_kernel) */
     int32_t  bvh_levels4, bvh_levels8; /* LBVH: depth of the closest-hit (4-wide) and any-hit (8-wide) trees */
+    int32_t  graph_replays;      /* frames of this scene so far that were issued as ONE CUDA-graph launch: a frame
+                                    whose buffers, camera, sharding and parameters equal the previous frame's is
+                                    captured on its second sighting and replayed afterwards */
+    int32_t  reserved2;
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

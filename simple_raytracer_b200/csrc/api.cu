@@ -158,6 +158,7 @@ void rt_free_scene(RtScene* scene)
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     s->ws.chains.sync();
+    if (s->graph.exec) { cudaGraphExecDestroy(s->graph.exec); s->graph.exec = nullptr; }
     if (s->ws.device >= 0) stash_workspace(std::move(s->ws));
     if (s->ev0) cudaEventDestroy(s->ev0);
     if (s->ev1) cudaEventDestroy(s->ev1);
@@ -285,6 +286,7 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->shadow_chains_redone = c.redo_count;
         stats->bvh_levels4 = s->last_accel == RT_ACCEL_LBVH ? s->bvh_levels4 : 0;
         stats->bvh_levels8 = s->last_accel == RT_ACCEL_LBVH ? s->bvh_levels8 : 0;
+        stats->graph_replays = s->graph_replays;
         stats->accel_used = s->last_accel; stats->kernel_launches = launches; stats->queue_regrows = regrows;
         if (p.instrument && s->last_accel == RT_ACCEL_LBVH) {
             for (int l = 0; l <= p.max_depth; l++)

@@ -137,6 +137,13 @@ struct Workspace {
     int device = -1;
 };
 
+// The captured launch sequence of a frame and the FrameParams it was captured for (render.cu: enqueue_frame).
+struct FrameGraph {
+    cudaGraphExec_t exec = nullptr;
+    FrameParams ps[kMaxSubframes];
+    int K = 0, accel = 0, launches = 0;
+};
+
 struct SceneHost {
     int device = 0;
     int width = 0, height = 0;
@@ -171,6 +178,8 @@ struct SceneHost {
     int last_local_rows = 0, last_local_pixels = 0, last_accel = 0, last_launches = 0;
     int last_subframes = 1;             // launch chains of the last frame (its queues were cut that many ways)
     bool have_primary_ids = false;
+    FrameGraph graph;
+    int graph_replays = 0;              // frames of this scene that were graph launches
 };
 
 // upload.cu

@@ -346,7 +346,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     for (int j = 0; j < K; j++) {
         FrameParams& P = PS[j];
         std::memset(&P, 0, sizeof P);
-        P.scene = scene_view(s);
+        { const SceneView sv = scene_view(s); std::memcpy(&P.scene, &sv, sizeof sv); }     // (bytewise: padding stays defined)
         P.cam = s->cam;
         fill_levels(s, D, lbvh, K, j, (size_t)vl.n_local_pixels, &P);
         P.counters = s->ws.counters.as<Counters>() + j;
@@ -361,123 +361,170 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         P.redo_list = lbvh ? s->ws.redo_list.as<unsigned>() + (size_t)j * kRedoCapacity : nullptr;
     }
 
-    RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
-    const int sms = sm_count(s->device);
-    const size_t smem = (size_t)(s->nf * kTriWords + s->ns * kSphWords) * sizeof(float4);
-    const bool stage = accel == RT_ACCEL_BRUTE && smem <= 48 * 1024;
-    int n = 0;
-    s->prof_levels = 0;
-    if (p.profile) {
-        for (int k = 0; k < kMaxLevels + 2; k++)
-            if (!s->prof_ev[k]) RT_CUDA(cudaEventCreate(&s->prof_ev[k]));
-        for (int k = 0; k < kMaxLevels; k++)
-            for (int j = 0; j < 2; j++)
-                if (!s->prof_mid[k][j]) RT_CUDA(cudaEventCreate(&s->prof_mid[k][j]));
-    }
-    s->prof_split = p.profile && lbvh;
     ChainStreams& cs = s->ws.chains;
-    if (overlap) {
-        if (!cs.ensure(K)) return RT_E_CUDA;
-        RT_CUDA(cudaEventRecord(cs.begin, stream));        // the counters are cleared
-        for (int j = 0; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
-    }
-    const int steal = p.work_sharing;      // 0: by launch size, 1: always, 2: never
+    if (overlap && !cs.ensure(K)) return RT_E_CUDA;
+    int n = 0;
+    // The launch sequence of the frame on `stream` (directly, or under stream capture: see below).
+    auto issue = [&](cudaStream_t stream) -> int {
+        RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
+        const int sms = sm_count(s->device);
+        const size_t smem = (size_t)(s->nf * kTriWords + s->ns * kSphWords) * sizeof(float4);
+        const bool stage = accel == RT_ACCEL_BRUTE && smem <= 48 * 1024;
+        s->prof_levels = 0;
+        if (p.profile) {
+            for (int k = 0; k < kMaxLevels + 2; k++)
+                if (!s->prof_ev[k]) RT_CUDA(cudaEventCreate(&s->prof_ev[k]));
+            for (int k = 0; k < kMaxLevels; k++)
+                for (int j = 0; j < 2; j++)
+                    if (!s->prof_mid[k][j]) RT_CUDA(cudaEventCreate(&s->prof_mid[k][j]));
+        }
+        s->prof_split = p.profile && lbvh;
+        if (overlap) {
+            RT_CUDA(cudaEventRecord(cs.begin, stream));        // the counters are cleared
+            for (int j = 0; j < K; j++) RT_CUDA(cudaStreamWaitEvent(cs.main[j], cs.begin, 0));
+        }
+        const int steal = p.work_sharing;      // 0: by launch size, 1: always, 2: never
 
-    if (!lbvh) {
-        for (int l = 0; l <= D; l++) {
-            if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
-            const FrameParams& P = PS[0];
-            const int grid = persistent_grid(P.level[l].capacity, sms, T.grid_mult);
-            if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
-            else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
-            n++;
-        }
-    } else if (p.profile) {
-        // one serial chain, every kernel on its own between events (bench.py's per-kernel times)
-        const FrameParams& P = PS[0];
-        for (int l = 0; l <= D; l++) {
-            const long long work = P.level[l].capacity;
-            const bool sharing = steal == 1 || (steal == 0 && work <= 1000LL * T.steal_max_krays);
-            RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
-            if (count) launch_trace<true>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
-            else launch_trace<false>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
-            bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l);
-            n += 2;
-            RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
-            if (s->nl) {
-                const int sh_grid = persistent_grid(work * s->nl, sms, T.grid_mult, kWalkBlock);
-                if (count) launch_shadow<true>(P, l, l, sharing, sh_grid, stream);
-                else launch_shadow<false>(P, l, l, sharing, sh_grid, stream);
-                n += 2;
+        if (!lbvh) {
+            for (int l = 0; l <= D; l++) {
+                if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
+                const FrameParams& P = PS[0];
+                const int grid = persistent_grid(P.level[l].capacity, sms, T.grid_mult);
+                if (stage) launch_level<BruteSmemFactory>(P, l, grid, smem, stream);
+                else launch_level<BruteGlobalFactory>(P, l, grid, 0, stream);
+                n++;
             }
-            RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
-            bvh_colour_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l, l);
-            n++;
-        }
-    } else {
-        for (int j = 0; j < K; j++) {
-            const FrameParams& P = PS[j];
-            cudaStream_t ms = cs.main[j], side = cs.side[j];
-            long long all_work = 0;
+        } else if (p.profile) {
+            // one serial chain, every kernel on its own between events (bench.py's per-kernel times)
+            const FrameParams& P = PS[0];
             for (int l = 0; l <= D; l++) {
                 const long long work = P.level[l].capacity;
-                all_work += work;
                 const bool sharing = steal == 1 || (steal == 0 && work <= 1000LL * T.steal_max_krays);
-                const int wgrid = persistent_grid(work, sms, T.grid_mult, kWalkBlock);
-                if (count) launch_trace<true>(P, l, sharing, wgrid, ms);
-                else launch_trace<false>(P, l, sharing, wgrid, ms);
-                bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, ms>>>(P, l);
+                RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
+                if (count) launch_trace<true>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
+                else launch_trace<false>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
+                bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l);
                 n += 2;
-            }
-            RT_CUDA(cudaEventRecord(cs.fork[j], ms));
-            RT_CUDA(cudaStreamWaitEvent(side, cs.fork[j], 0));
-            const long long chain_pixels = P.level[0].capacity;
-            if (s->nl) {
-                const bool sharing = steal == 1 || (steal == 0 && chain_pixels <= 1000LL * T.steal_shadow_max_kpixels);
-                const int sh_grid = persistent_grid(all_work * s->nl, sms, T.grid_mult, kWalkBlock);
-                if (count) launch_shadow<true>(P, 0, D, sharing, sh_grid, side);
-                else launch_shadow<false>(P, 0, D, sharing, sh_grid, side);
-                n += 2;
-            }
-            if (chain_pixels <= 1000LL * T.colour_merge_max_kpixels) {
-                bvh_colour_kernel<<<persistent_grid(all_work, sms, T.grid_mult), kBlock, 0, side>>>(P, 0, D);
-                n++;
-            } else for (int l = 0; l <= D; l++) {
-                bvh_colour_kernel<<<persistent_grid(P.level[l].capacity, sms, T.grid_mult), kBlock, 0, side>>>(P, l, l);
+                RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
+                if (s->nl) {
+                    const int sh_grid = persistent_grid(work * s->nl, sms, T.grid_mult, kWalkBlock);
+                    if (count) launch_shadow<true>(P, l, l, sharing, sh_grid, stream);
+                    else launch_shadow<false>(P, l, l, sharing, sh_grid, stream);
+                    n += 2;
+                }
+                RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
+                bvh_colour_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l, l);
                 n++;
             }
+        } else {
+            for (int j = 0; j < K; j++) {
+                const FrameParams& P = PS[j];
+                cudaStream_t ms = cs.main[j], side = cs.side[j];
+                long long all_work = 0;
+                for (int l = 0; l <= D; l++) {
+                    const long long work = P.level[l].capacity;
+                    all_work += work;
+                    const bool sharing = steal == 1 || (steal == 0 && work <= 1000LL * T.steal_max_krays);
+                    const int wgrid = persistent_grid(work, sms, T.grid_mult, kWalkBlock);
+                    if (count) launch_trace<true>(P, l, sharing, wgrid, ms);
+                    else launch_trace<false>(P, l, sharing, wgrid, ms);
+                    bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, ms>>>(P, l);
+                    n += 2;
+                }
+                RT_CUDA(cudaEventRecord(cs.fork[j], ms));
+                RT_CUDA(cudaStreamWaitEvent(side, cs.fork[j], 0));
+                const long long chain_pixels = P.level[0].capacity;
+                if (s->nl) {
+                    const bool sharing = steal == 1 || (steal == 0 && chain_pixels <= 1000LL * T.steal_shadow_max_kpixels);
+                    const int sh_grid = persistent_grid(all_work * s->nl, sms, T.grid_mult, kWalkBlock);
+                    if (count) launch_shadow<true>(P, 0, D, sharing, sh_grid, side);
+                    else launch_shadow<false>(P, 0, D, sharing, sh_grid, side);
+                    n += 2;
+                }
+                if (chain_pixels <= 1000LL * T.colour_merge_max_kpixels) {
+                    bvh_colour_kernel<<<persistent_grid(all_work, sms, T.grid_mult), kBlock, 0, side>>>(P, 0, D);
+                    n++;
+                } else for (int l = 0; l <= D; l++) {
+                    bvh_colour_kernel<<<persistent_grid(P.level[l].capacity, sms, T.grid_mult), kBlock, 0, side>>>(P, l, l);
+                    n++;
+                }
+            }
         }
+        const int prof_n = D + 1;
+        if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[prof_n], stream));
+        // bottom-up combine per chain, on the chain's main stream once its colour kernels are done
+        for (int j = 0; j < K; j++) {
+            const FrameParams& P = PS[j];
+            cudaStream_t ms = overlap ? cs.main[j] : stream;
+            if (overlap) {
+                RT_CUDA(cudaEventRecord(cs.side_done[j], cs.side[j]));
+                RT_CUDA(cudaStreamWaitEvent(ms, cs.side_done[j], 0));
+            }
+            for (int l = std::max(D - 1, 0); l >= 0; l--) {
+                // (max_depth == 0: no backward pass, but generation 0 still has to be quantised)
+                const long long work = P.level[l].capacity;
+                const int grid = (int)std::max<long long>(1, std::min<long long>((work + 255) / 256, (long long)sms * 8));
+                combine_kernel<<<grid, 256, 0, ms>>>(P, l);
+                n++;
+            }
+            if (overlap) {
+                RT_CUDA(cudaEventRecord(cs.main_done[j], ms));
+                RT_CUDA(cudaStreamWaitEvent(stream, cs.main_done[j], 0));
+            }
+        }
+        RT_CUDA(cudaGetLastError());
+        if (p.profile) {
+            RT_CUDA(cudaEventRecord(s->prof_ev[prof_n + 1], stream));
+            s->prof_levels = prof_n;
+        }
+        if (tiles_out && tiles_out != s->ws.tiles.as<uchar4>())
+            RT_CUDA(cudaMemcpyAsync(s->ws.tiles.p, tiles_out, (size_t)tl.n_local_pixels * sizeof(uchar4),
+                                    cudaMemcpyDeviceToDevice, stream));
+        return RT_OK;
+    };
+
+    // CUDA-graph replay (SURVEY 8b "captured in a CUDA Graph for replays", 8f-4): a frame is fully described by
+    // the FrameParams its kernels receive, so a frame whose FrameParams equal the previous frame's (same
+    // buffers, camera, sharding, parameters) is captured once — on its second sighting, so that a
+    // load-render-free sequence never pays for an instantiation — and replayed from then on: one graph launch
+    // instead of 11-30 kernel launches + event traffic.  Profiled / instrumented frames and frames enqueued on a
+    // stream the caller is capturing are issued directly.
+    FrameGraph& G = s->graph;
+    if (!p.profile) { s->prof_levels = 0; s->prof_split = false; }
+    bool graphable = !p.profile && !p.instrument;
+    if (graphable) {
+        cudaStreamCaptureStatus cst = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cst) != cudaSuccess || cst != cudaStreamCaptureStatusNone) { cudaGetLastError(); graphable = false; }
     }
-    const int prof_n = D + 1;
-    if (p.profile) RT_CUDA(cudaEventRecord(s->prof_ev[prof_n], stream));
-    // bottom-up combine per chain, on the chain's main stream once its colour kernels are done
-    for (int j = 0; j < K; j++) {
-        const FrameParams& P = PS[j];
-        cudaStream_t ms = overlap ? cs.main[j] : stream;
-        if (overlap) {
-            RT_CUDA(cudaEventRecord(cs.side_done[j], cs.side[j]));
-            RT_CUDA(cudaStreamWaitEvent(ms, cs.side_done[j], 0));
+    const bool same = graphable && G.K == K && G.accel == accel && std::memcmp(G.ps, PS, sizeof(FrameParams) * K) == 0;
+    if (same && G.exec) {
+        RT_CUDA(cudaGraphLaunch(G.exec, stream));
+        n = G.launches;
+        s->graph_replays++;
+    } else if (same) {
+        cudaGraph_t graph = nullptr;
+        RT_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+        const int rc = issue(stream);
+        const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+        if (rc != RT_OK || ce != cudaSuccess || !graph) {
+            if (graph) cudaGraphDestroy(graph);
+            cudaGetLastError();
+            if (rc != RT_OK) return rc;
+            set_error(std::string("cudaStreamEndCapture: ") + cudaGetErrorString(ce));
+            return RT_E_CUDA;
         }
-        for (int l = std::max(D - 1, 0); l >= 0; l--) {
-            // (max_depth == 0: no backward pass, but generation 0 still has to be quantised)
-            const long long work = P.level[l].capacity;
-            const int grid = (int)std::max<long long>(1, std::min<long long>((work + 255) / 256, (long long)sms * 8));
-            combine_kernel<<<grid, 256, 0, ms>>>(P, l);
-            n++;
-        }
-        if (overlap) {
-            RT_CUDA(cudaEventRecord(cs.main_done[j], ms));
-            RT_CUDA(cudaStreamWaitEvent(stream, cs.main_done[j], 0));
-        }
+        const cudaError_t ci = cudaGraphInstantiate(&G.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ci != cudaSuccess) { G.exec = nullptr; set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(ci)); return RT_E_CUDA; }
+        G.launches = n;
+        RT_CUDA(cudaGraphLaunch(G.exec, stream));
+    } else {
+        if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+        G.K = graphable ? K : 0; G.accel = accel;
+        if (graphable) std::memcpy(G.ps, PS, sizeof(FrameParams) * K);
+        const int rc = issue(stream);
+        if (rc != RT_OK) return rc;
     }
-    RT_CUDA(cudaGetLastError());
-    if (p.profile) {
-        RT_CUDA(cudaEventRecord(s->prof_ev[prof_n + 1], stream));
-        s->prof_levels = prof_n;
-    }
-    if (tiles_out && tiles_out != s->ws.tiles.as<uchar4>())
-        RT_CUDA(cudaMemcpyAsync(s->ws.tiles.p, tiles_out, (size_t)tl.n_local_pixels * sizeof(uchar4),
-                                cudaMemcpyDeviceToDevice, stream));
     s->rendered = true;
     s->last = p;
     s->last_local_rows = tl.n_local_rows; s->last_local_pixels = tl.n_local_pixels;

@@ -330,7 +330,8 @@ int build_scene(const RtSceneDesc* d, SceneHost* s)
 
 SceneView scene_view(const SceneHost* s)
 {
-    SceneView v{};
+    SceneView v;
+    std::memset(&v, 0, sizeof v);      // padding too: enqueue_frame compares FrameParams bytewise (graph replay)
     v.nf = s->nf; v.ns = s->ns; v.nl = s->nl; v.ntex = s->ntex;
     v.tri = s->tri.as<float4>(); v.sph = s->sph.as<float4>(); v.face_attr = s->face_attr.as<float4>();
     v.obj = s->obj.as<int4>(); v.mat = s->mat.as<float4>(); v.light = s->light.as<float4>();

@@ -263,8 +263,12 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
 }
 
 // AccelFactory builds the per-block accelerator view (stages shared memory if any).
+// blocks per SM the fused kernel is compiled for (0 = the compiler's choice: 96 registers, 5 blocks)
+#ifndef RT_LEVEL_MIN_BLOCKS
+#define RT_LEVEL_MIN_BLOCKS 0
+#endif
 template <class AccelFactory>
-__global__ void __launch_bounds__(kBlock) level_kernel(const __grid_constant__ FrameParams P, int level)
+__global__ void __launch_bounds__(kBlock, RT_LEVEL_MIN_BLOCKS) level_kernel(const __grid_constant__ FrameParams P, int level)
 {
     extern __shared__ float4 smem[];
     const auto acc = AccelFactory::make(P.scene, smem);

@@ -416,3 +416,46 @@ def test_invalid_arguments_are_reported():
     with pytest.raises(abi.RtError) as e:
         DeviceScene(bad)
     assert e.value.code == abi.RT_E_INVALID
+
+
+@pytest.mark.parametrize("accel", [abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH])
+def test_graph_replay_of_repeated_frames_never_changes_a_pixel(accel):
+    """A frame identical to the previous one is captured into a CUDA graph on its second sighting and
+    replayed from the third (render.cu: enqueue_frame).  Replays give the bytes of the directly issued
+    frame; anything that changes the frame (camera, sharding, depth) drops the graph."""
+    scene = scenegen.coverage_scene(120, 90)
+    moved = scene.copy(eye=(1.0, 2.5, -3.0), viewdir=(-0.1, -0.2, 1.0), hfov_deg=50.0)
+    with DeviceScene(moved) as ds:
+        ds.render(accel=accel)
+        want_moved = ds.download()
+        want_moved = (want_moved[0].copy(), want_moved[1].copy())
+    with DeviceScene(scene) as ds:
+        first = ds.render(accel=accel)
+        want = ds.download()
+        want = (want[0].copy(), want[1].copy())
+        replays = [first.graph_replays]
+        for _ in range(4):
+            st = ds.render(accel=accel)
+            got = ds.download()
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+            assert list(st.nodes_per_level) == list(first.nodes_per_level)
+            replays.append(st.graph_replays)
+        assert replays[0] == 0 and replays[-1] >= 2, replays          # direct, capture, replay, replay
+        # a shard of the frame, then the whole frame again: each its own graph, same bytes
+        ds.render(accel=accel, rank=1, world_size=2, tile_rows=5)
+        st = ds.render(accel=accel)
+        got = ds.download()
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        # another camera: the frame of a fresh upload with that camera, also when replayed
+        ds.set_camera(moved.eye, moved.viewdir, moved.updir, moved.hfov_deg)
+        for _ in range(3):
+            ds.render(accel=accel)
+            got = ds.download()
+            assert np.array_equal(got[0], want_moved[0]) and np.array_equal(got[1], want_moved[1])
+        # depth 1 and back
+        ds.render(accel=accel, max_depth=1)
+        ds.set_camera(scene.eye, scene.viewdir, scene.updir, scene.hfov_deg)
+        for _ in range(3):
+            ds.render(accel=accel)
+            got = ds.download()
+            assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
