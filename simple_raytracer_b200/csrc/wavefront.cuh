@@ -263,9 +263,11 @@ RT_DEV void process_slot(const FrameParams& P, const Accel& acc, int level, unsi
 }
 
 // AccelFactory builds the per-block accelerator view (stages shared memory if any).
-// blocks per SM the fused kernel is compiled for (0 = the compiler's choice: 96 registers, 5 blocks)
+// blocks per SM the fused kernel is compiled for: 8 (64 registers, ~250 B of spills) against the compiler's own
+// 96 registers / 5 blocks: test7 at 4K 1.67 -> 1.56 ms (6 blocks: 1.62); the kernel waits on dependent exact-rounding
+// chains, more resident warps hide them (profiles/r2_level_kernel_test7_ncu_full.txt: issue 51 %, 28 % occupancy before)
 #ifndef RT_LEVEL_MIN_BLOCKS
-#define RT_LEVEL_MIN_BLOCKS 0
+#define RT_LEVEL_MIN_BLOCKS 8
 #endif
 template <class AccelFactory>
 __global__ void __launch_bounds__(kBlock, RT_LEVEL_MIN_BLOCKS) level_kernel(const __grid_constant__ FrameParams P, int level)
