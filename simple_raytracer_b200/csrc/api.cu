@@ -18,8 +18,6 @@ bool cuda_ok(cudaError_t e, const char* what)
     return false;
 }
 
-int launch_split_planes(SceneHost* s, cudaStream_t st);
-int launch_deinterleave(const SceneHost* s, const void* gathered, void* out, int world, int tile_rows, cudaStream_t st);
 
 namespace {
 
@@ -117,6 +115,9 @@ int probe_accel(SceneHost* s, int accel)
 }
 
 }  // namespace
+
+int checked_params(const RtRenderParams* in, RtRenderParams* out) { return check_params(in, out); }
+
 }  // namespace rt
 
 using namespace rt;

@@ -205,6 +205,12 @@ unsigned frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[k
 int overflow_error(unsigned bits);      // RT_OK, or RT_E_LIMIT + message for the bits no regrow cures
 void stash_workspace(Workspace&& ws);
 
+int launch_split_planes(SceneHost* s, cudaStream_t st, const uchar4* src = nullptr, int n_pixels = 0);   // src: null = the last frame's tiles
+int launch_deinterleave(const SceneHost* s, const void* gathered, void* out, int world, int tile_rows, cudaStream_t st);
+
+// api.cu
+int checked_params(const RtRenderParams* in, RtRenderParams* out);     // defaults + validation of RtRenderParams
+
 // ppm_device.cu
 int format_ppm_device(SceneHost* s, const uchar4* px, const char** text, size_t* len, cudaStream_t st);
 

@@ -588,11 +588,11 @@ int overflow_error(unsigned bits)
     return RT_OK;
 }
 
-int launch_split_planes(SceneHost* s, cudaStream_t st)
+int launch_split_planes(SceneHost* s, cudaStream_t st, const uchar4* src, int n_pixels)
 {
-    const int n = s->last_local_pixels;
+    const int n = src ? n_pixels : s->last_local_pixels;
     if (!s->ws.rgb24.reserve((size_t)n * 3) || !s->ws.flags8.reserve((size_t)n)) return RT_E_NOMEM;
-    split_planes_kernel<<<(n + 255) / 256, 256, 0, st>>>(s->ws.tiles.as<uchar4>(), n, s->ws.rgb24.as<unsigned char>(),
+    split_planes_kernel<<<(n + 255) / 256, 256, 0, st>>>(src ? src : s->ws.tiles.as<uchar4>(), n, s->ws.rgb24.as<unsigned char>(),
                                                         s->ws.flags8.as<unsigned char>());
     RT_CUDA(cudaGetLastError());
     return RT_OK;
