@@ -38,7 +38,7 @@ build/%.o: $(CSRC)/%.cu $(CU_HDRS)
 
 $(LIB)/librt_b200.so: $(CU_OBJS)
 	@mkdir -p $(LIB)
-	$(NVCC) $(ARCH) -cudart static -shared -o $@ $(CU_OBJS)
+	$(NVCC) $(ARCH) -cudart static -shared -o $@ $(CU_OBJS) -ldl
 	@cat build/*.ptxas.log > $(LIB)/ptxas.log
 
 bin/raytracer: $(CSRC)/host/raytracer_main.cpp $(LIB)/librt_host.so $(LIB)/librt_b200.so

@@ -296,6 +296,24 @@ int rt_deinterleave_tiles(const RtScene* scene, const void* dev_gathered,
                           void* dev_rgba_out, int32_t world_size,
                           int32_t tile_rows, void* cuda_stream);
 
+/* ---- N GPUs of one node behind the same three calls ------------------------------
+ * One process, one host thread: the handle owns the scene replicas of all devices, their streams and
+ * the NCCL communicators (ncclCommInitAll; NCCL is dlopen'ed at the first multi-GPU upload, RT_NCCL_LIB
+ * overrides the library name).  The scene is uploaded, packed and its LBVH built once on the first
+ * device and broadcast to the others over NVLink; a frame is rendered as interleaved row tiles (tile t
+ * on device t % N), exchanged with ONE ncclAllGather of the RGBA8 tiles and de-interleaved on the first
+ * device.  The frame is byte-identical for every N (main.cpp:718-763 has no cross-pixel state).
+ *   device_ids : num_gpus CUDA device ordinals, or NULL for 0 .. num_gpus-1
+ *   params     : as rt_render; rank / world_size are ignored, tile_rows 0 = 10 when height % 10 == 0, else 8
+ *   stats      : sums over the devices; render_ms = first device's stream, enqueue to de-interleaved frame */
+typedef struct RtMultiScene RtMultiScene;
+int  rt_upload_scene_multi(const RtSceneDesc* desc, int32_t num_gpus, const int32_t* device_ids, RtMultiScene** out);
+int  rt_render_multi(RtMultiScene* scene, const RtRenderParams* params, RtStats* stats_or_null);
+int  rt_download_framebuffer_multi(RtMultiScene* scene, uint8_t* rgb, uint8_t* flags);
+int  rt_format_ppm_multi(RtMultiScene* scene, const char** text, size_t* len);   /* as rt_format_ppm_device */
+int  rt_num_gpus_multi(const RtMultiScene* scene);
+void rt_free_scene_multi(RtMultiScene* scene);
+
 /* Re-render API: replace the camera without re-uploading. */
 int rt_set_camera(RtScene* scene, const float eye[3], const float viewdir[3],
                   const float updir[3], float hfov_deg);

@@ -102,6 +102,8 @@ RT_SYMBOLS = [
     "rt_upload_scene", "rt_render", "rt_download_framebuffer", "rt_free_scene", "rt_last_error",
     "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_async_frame_status", "rt_release_cached_memory", "rt_format_ppm_device", "rt_deinterleave_tiles", "rt_set_camera",
     "rt_trace_closest", "rt_trace_shadow", "rt_download_primary_ids", "rt_tile_layout", "rt_format_ppm_noalloc",
+    "rt_upload_scene_multi", "rt_render_multi", "rt_download_framebuffer_multi", "rt_format_ppm_multi", "rt_num_gpus_multi",
+    "rt_free_scene_multi",
 ]
 RT_HOST_SYMBOLS = [
     "rt_host_parse_scene_file", "rt_host_free_scene_desc", "rt_host_read_texture_p3", "rt_host_free",
@@ -151,6 +153,18 @@ def load_rt() -> C.CDLL:
     lib.rt_format_ppm_device.restype = C.c_int
     lib.rt_format_ppm_noalloc.argtypes = [vp, i32, i32, _p(f32), vp, C.c_size_t, vp, vp]
     lib.rt_format_ppm_noalloc.restype = C.c_int
+    lib.rt_upload_scene_multi.argtypes = [_p(RtSceneDesc), i32, _p(i32), _p(vp)]
+    lib.rt_upload_scene_multi.restype = C.c_int
+    lib.rt_render_multi.argtypes = [vp, _p(RtRenderParams), _p(RtStats)]
+    lib.rt_render_multi.restype = C.c_int
+    lib.rt_download_framebuffer_multi.argtypes = [vp, vp, vp]
+    lib.rt_download_framebuffer_multi.restype = C.c_int
+    lib.rt_format_ppm_multi.argtypes = [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+    lib.rt_format_ppm_multi.restype = C.c_int
+    lib.rt_num_gpus_multi.argtypes = [vp]
+    lib.rt_num_gpus_multi.restype = C.c_int
+    lib.rt_free_scene_multi.argtypes = [vp]
+    lib.rt_free_scene_multi.restype = None
     lib.rt_release_cached_memory.argtypes = []
     lib.rt_release_cached_memory.restype = C.c_size_t
     lib.rt_async_frame_status.argtypes = [vp]

@@ -145,3 +145,56 @@ def render_scene(scene: Scene, **kw) -> Tuple[np.ndarray, np.ndarray, abi.RtStat
         st = ds.render(**kw)
         rgb, flags = ds.download()
     return rgb, flags, st
+
+
+class MultiDeviceScene:
+    """A scene resident on N GPUs of this node, driven by ONE process through rt_*_multi
+    (NCCL communicator, broadcast of the built scene, allgather of the tiles inside the library)."""
+
+    def __init__(self, scene: Scene, num_gpus: int, device_ids=None):
+        self._lib = abi.load_rt()
+        self.scene = scene
+        self._h = C.c_void_p()
+        ids = None if device_ids is None else (C.c_int32 * num_gpus)(*device_ids)
+        abi.check(self._lib.rt_upload_scene_multi(C.byref(scene.desc()), num_gpus, ids, C.byref(self._h)),
+                  "rt_upload_scene_multi")
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.rt_free_scene_multi(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def num_gpus(self) -> int:
+        return int(self._lib.rt_num_gpus_multi(self._h))
+
+    def render(self, params: Optional[abi.RtRenderParams] = None, **kw) -> abi.RtStats:
+        kw.setdefault("tile_rows", 0)
+        p = params if params is not None else make_params(**kw)
+        st = abi.RtStats()
+        abi.check(self._lib.rt_render_multi(self._h, C.byref(p), C.byref(st)), "rt_render_multi")
+        return st
+
+    def download(self) -> Tuple[np.ndarray, np.ndarray]:
+        H, W = self.scene.height, self.scene.width
+        rgb = np.zeros((H, W, 3), dtype=np.uint8)
+        flags = np.zeros((H, W), dtype=np.uint8)
+        abi.check(self._lib.rt_download_framebuffer_multi(self._h, _ptr(rgb), _ptr(flags)), "rt_download_framebuffer_multi")
+        return rgb, flags
+
+    def ppm_text(self) -> bytes:
+        text = C.c_void_p(); n = C.c_size_t()
+        abi.check(self._lib.rt_format_ppm_multi(self._h, C.byref(text), C.byref(n)), "rt_format_ppm_multi")
+        return C.string_at(text, n.value)
