@@ -66,8 +66,8 @@ def test_cli_gpus_n_writes_the_same_file(tmp_path, n):
     if not os.path.exists(cli):
         pytest.skip("bin/raytracer not built")
     outs = []
-    for g in (1, n):
-        d = tmp_path / f"g{g}"
+    for k, g in enumerate((1, n)):
+        d = tmp_path / f"run{k}_g{g}"
         d.mkdir()
         path = common.materialise("showcases/house", str(d))
         os.rename(path, str(d / "scene.txt"))
