@@ -79,6 +79,32 @@ bool nccl_ok(ncclResult_t r, const char* what)
 }
 #define RT_NCCL(call) do { if (!nccl_ok((call), #call)) return RT_E_CUDA; } while (0)
 
+// Communicators are kept for the life of the process, one set per device list: ncclCommInitAll costs
+// about a second on an 8-GPU node, a scene upload a few milliseconds.  (One host thread drives a multi
+// scene at a time — the handle is not thread-safe — so sharing them between scenes is safe.)
+struct CommSet {
+    std::vector<int> dev;
+    std::vector<ncclComm_t> comm;
+};
+std::vector<CommSet>& comm_cache()
+{
+    static std::vector<CommSet>* c = new std::vector<CommSet>();     // leaked on purpose, like the device-memory cache
+    return *c;
+}
+
+int get_comms(const std::vector<int>& dev, std::vector<ncclComm_t>* out)
+{
+    for (const CommSet& c : comm_cache())
+        if (c.dev == dev) { *out = c.comm; return RT_OK; }
+    CommSet c;
+    c.dev = dev;
+    c.comm.assign(dev.size(), nullptr);
+    RT_NCCL(g_nccl.CommInitAll(c.comm.data(), (int)dev.size(), dev.data()));
+    comm_cache().push_back(c);
+    *out = c.comm;
+    return RT_OK;
+}
+
 }  // namespace
 }  // namespace rt
 
@@ -87,7 +113,7 @@ struct RtMultiScene {
     int n = 0;
     std::vector<int> dev;
     std::vector<RtScene*> sc;               // sc[0]: the uploaded scene; sc[1..]: replicas filled by broadcast
-    std::vector<ncclComm_t> comm;           // empty when n == 1
+    std::vector<ncclComm_t> comm;           // empty when n == 1; owned by the process-wide cache (get_comms)
     std::vector<rt::DevBuf> send, gathered; // per device: its tiles / everybody's tiles
     rt::DevBuf frame;                       // first device: the assembled frame, RGBA8 in scanline order
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -185,7 +211,6 @@ void rt_free_scene_multi(RtMultiScene* m)
             if (m->ev0) cudaEventDestroy(m->ev0);
             if (m->ev1) cudaEventDestroy(m->ev1);
         }
-        if (i < (int)m->comm.size() && m->comm[i]) g_nccl.CommDestroy(m->comm[i]);
         rt_free_scene(m->sc[i]);
     }
     if (!m->dev.empty()) cudaSetDevice(m->dev[0]);
@@ -215,8 +240,7 @@ int rt_upload_scene_multi(const RtSceneDesc* desc, int32_t num_gpus, const int32
     int rc = RT_OK;
     if (num_gpus > 1) {
         if (!load_nccl()) { rt_free_scene_multi(m); return RT_E_CUDA; }
-        m->comm.assign(num_gpus, nullptr);
-        if (!nccl_ok(g_nccl.CommInitAll(m->comm.data(), num_gpus, m->dev.data()), "ncclCommInitAll")) { rt_free_scene_multi(m); return RT_E_CUDA; }
+        if ((rc = get_comms(m->dev, &m->comm)) != RT_OK) { rt_free_scene_multi(m); return rc; }
     }
     // the scene itself: once, on the first device (LBVH included when the scene is large)
     if (!cuda_ok(cudaSetDevice(m->dev[0]), "cudaSetDevice")) rc = RT_E_CUDA;
