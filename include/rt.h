@@ -233,10 +233,14 @@ size_t rt_tile_buffer_bytes(const RtScene* scene, int32_t world_size, int32_t ti
 int rt_tile_layout(int32_t height, int32_t width, int32_t world_size,
                    int32_t tile_rows, int32_t out[4]);
 
-/* Like rt_render, but asynchronous on `cuda_stream` (a cudaStream_t, may be
- * NULL for the default stream) and with the RGBA8 tile buffer written to
- * caller-provided DEVICE memory (e.g. the send buffer of an NCCL allgather).
- * dev_tiles may be NULL to render into the scene's own buffer only. */
+/* Like rt_render, but asynchronous on `cuda_stream` (a cudaStream_t) and with the RGBA8 tile buffer
+ * written to caller-provided DEVICE memory (e.g. the send buffer of an NCCL allgather).
+ *   cuda_stream : NULL = the scene's OWN non-blocking stream (the one rt_render uses) — NOT the legacy
+ *                 default stream: work a caller enqueues on the default stream is not ordered against
+ *                 the frame; pass your stream explicitly when something of yours follows the frame.
+ *   dev_tiles   : may be NULL to render into the scene's own buffer only.
+ * A frame equal to the previous one (same buffers, camera, sharding, parameters) is replayed as one
+ * CUDA-graph launch from its third sighting on; a stream the caller is capturing is enqueued into directly. */
 int rt_render_async(RtScene* scene, const RtRenderParams* params,
                     void* dev_tiles, void* cuda_stream);
 

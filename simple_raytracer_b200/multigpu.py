@@ -103,10 +103,14 @@ class DistributedFrame:
         self.frame = torch.empty(sc.height * sc.width * 4, dtype=torch.uint8, device="cuda")
 
     def step(self, stream_ptr: int) -> None:
-        """Enqueue one frame: render this rank's tiles, allgather, de-interleave."""
+        """Enqueue one frame on the CUDA stream `stream_ptr`: render this rank's tiles, allgather, de-interleave.
+        The collective is issued with that stream current (torch orders NCCL work against the CURRENT stream),
+        so the three steps are stream-ordered whatever stream the caller had current."""
+        import torch
         self.ds.render_async(self.params, self.send.data_ptr(), stream_ptr)
         if self.world > 1:
-            allgather_tiles(self.send, self.gathered)
+            with torch.cuda.stream(torch.cuda.ExternalStream(stream_ptr)):
+                allgather_tiles(self.send, self.gathered)
         self.ds.deinterleave(self.gathered.data_ptr(), self.frame.data_ptr(), self.world, self.tile_rows, stream_ptr)
 
     def frame_host(self) -> np.ndarray:
