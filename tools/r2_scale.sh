@@ -8,7 +8,7 @@ run() { # workload N extra-args
   echo "$1 N=$2 rc=$?"
 }
 for n in 1 2 4 8; do run stress_1M_4k $n; done
-for n in 1 2 4 8; do run test7_4k $n --no-e2e; run house_4k $n --no-e2e; done
-for n in 1 8; do run stress_1M_8k $n --no-e2e; done
-for n in 2 4 8; do python tools/multi_probe.py $n > gpurun_out/r2_multi_probe_${n}gpu.json 2> gpurun_out/r2_multi_probe_${n}gpu.err; done
+# (N = 1 of these three: tools/r2_measure.sh, same hardware)
+run test7_4k 8 --no-e2e; run house_4k 8 --no-e2e; run stress_1M_8k 8 --no-e2e
+python tools/multi_probe.py 8 > gpurun_out/r2_multi_probe_8gpu.json 2> gpurun_out/r2_multi_probe_8gpu.err
 python tools/multi_probe.py 8 7680 4320 > gpurun_out/r2_multi_probe_8gpu_8k.json 2>> gpurun_out/r2_multi_probe_8gpu.err
