@@ -346,6 +346,16 @@ int rt_trace_shadow(RtScene* scene, int32_t accel, int32_t n,
                     const int32_t* self_id, float tmin, const float* tmax,
                     float* out_mask, int32_t* out_hits);
 
+/* Identity of the SECONDARY hits and of shadow occlusion (north star: "hit primitive IDs and shadow occlusion
+ * must be identical"; SURVEY 8c "oracle B": hit ids at main.cpp:745 / 1008 / 1120, occlusion at 909 / 946), of the
+ * last frame of the LBVH pipeline (this rank's tiles):
+ *   hits  [8][n_faces + n_spheres]  ShadeRay invocations of generation g on object o (order: faces in file
+ *                                   order, then spheres)
+ *   shadow[8][n_lights][3]          nodes of generation g whose carried shadow_mask after light l was exactly 0 /
+ *                                   in (0,1) / exactly 1
+ * Compared with the same histograms of the CPU oracle in tests/test_gpu_parity.py. */
+int rt_download_hit_histograms(RtScene* scene, uint64_t* hits, uint64_t* shadow);
+
 /* Primary-hit object id per pixel of the last render (height*width int32,
  * 0 = miss); available when the last render had instrument != 0. */
 int rt_download_primary_ids(RtScene* scene, int32_t* ids);

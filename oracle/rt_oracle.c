@@ -265,6 +265,16 @@ static Col texel(const OScene* S, int tex, int x, int y)
     return c;
 }
 
+/* Identity dumps (SURVEY 8c "oracle B"): what ShadeRay was called FOR, beyond the pixels it produced.
+ *   hits  [level][object order]      ShadeRay invocations of generation `level` on that object — the hit ids
+ *                                    chosen at main.cpp:745 (level 0), 1008 (transmission), 1120 (reflection)
+ *   shadow[level][light][class]      the carried shadow_mask after that light's TraceRay (main.cpp:909 / 946):
+ *                                    class 0: exactly 0 (an opaque occluder so far), 1: in (0,1), 2: exactly 1
+ * Filled when rto_set_histograms() was given arrays (caller-sized: 8 x n_objects, 8 x n_lights x 3). */
+static uint64_t* g_hist_hits = NULL;
+static uint64_t* g_hist_shadow = NULL;
+void rto_set_histograms(uint64_t* hits, uint64_t* shadow) { g_hist_hits = hits; g_hist_shadow = shadow; }
+
 static Col shade_ray(const OScene* S, V3 incidence_ray, int obj, const OHit* hit,
                      float n_i, float n_t, const int* stack, int nstack,
                      int ray_state, int depth, int level, Col bkg)
@@ -284,6 +294,7 @@ static Col shade_ray(const OScene* S, V3 incidence_ray, int obj, const OHit* hit
 
     S->st->nodes_total++;
     if (level < 8) S->st->nodes_per_level[level]++;
+    if (g_hist_hits && level < 8) g_hist_hits[(size_t)level * (size_t)(S->nf + S->ns) + (size_t)obj]++;
 
     /* diffuse colour / texture, main.cpp:800-867 */
     int tex = obj_tex(S, obj);
@@ -339,6 +350,8 @@ static Col shade_ray(const OScene* S, V3 incidence_ray, int obj, const OHit* hit
             trace_ray(S, hit->p, L, visit_shadow, &sc);              /* 928 */
         }
         shadow_mask = sc.mask;
+        if (g_hist_shadow && level < 8)
+            g_hist_shadow[((size_t)level * (size_t)S->d->n_lights + (size_t)li) * 3 + (shadow_mask == 0.0f ? 0 : shadow_mask == 1.0f ? 2 : 1)]++;
         V3 H = vnorm(vadd(L, I));                                    /* 952 */
         float ndl = vdot(N, L), ndh = vdot(N, H);
         float mdl = (0.0f < ndl) ? ndl : 0.0f;                       /* std::max(0.0f, x): NaN -> 0 */

@@ -51,6 +51,11 @@ int rto_render(const RtSceneDesc* desc, const RtoParams* params,
                int32_t* out_raw, int32_t* out_primary_id, RtoStats* stats);
 
 /* Primary rays of the given pixels (main.cpp:677-728): n*3 floats each. */
+/* Identity dumps for the next rto_render calls (NULL, NULL to stop): hits[8][n_faces + n_spheres] counts the
+ * ShadeRay invocations per generation and object (order: faces in file order, then spheres), shadow[8][n_lights][3]
+ * the carried shadow_mask after each light per generation (0: == 0, 1: in between, 2: == 1). */
+void rto_set_histograms(uint64_t* hits, uint64_t* shadow);
+
 int rto_primary_rays(const RtSceneDesc* desc, int64_t n_pixels, const int64_t* pixel_index,
                      float* out_origins, float* out_dirs);
 

@@ -103,7 +103,7 @@ RT_SYMBOLS = [
     "rt_abi_version", "rt_tile_buffer_bytes", "rt_render_async", "rt_async_frame_status", "rt_release_cached_memory", "rt_format_ppm_device", "rt_deinterleave_tiles", "rt_set_camera",
     "rt_trace_closest", "rt_trace_shadow", "rt_download_primary_ids", "rt_tile_layout", "rt_format_ppm_noalloc",
     "rt_upload_scene_multi", "rt_render_multi", "rt_download_framebuffer_multi", "rt_format_ppm_multi", "rt_num_gpus_multi",
-    "rt_free_scene_multi",
+    "rt_free_scene_multi", "rt_download_hit_histograms",
 ]
 RT_HOST_SYMBOLS = [
     "rt_host_parse_scene_file", "rt_host_free_scene_desc", "rt_host_read_texture_p3", "rt_host_free",
@@ -165,6 +165,8 @@ def load_rt() -> C.CDLL:
     lib.rt_num_gpus_multi.restype = C.c_int
     lib.rt_free_scene_multi.argtypes = [vp]
     lib.rt_free_scene_multi.restype = None
+    lib.rt_download_hit_histograms.argtypes = [vp, vp, vp]
+    lib.rt_download_hit_histograms.restype = C.c_int
     lib.rt_release_cached_memory.argtypes = []
     lib.rt_release_cached_memory.restype = C.c_size_t
     lib.rt_async_frame_status.argtypes = [vp]

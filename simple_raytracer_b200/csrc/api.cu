@@ -390,6 +390,28 @@ int rt_download_primary_ids(RtScene* scene, int32_t* ids)
     return RT_OK;
 }
 
+int rt_download_hit_histograms(RtScene* scene, uint64_t* hits, uint64_t* shadow)
+{
+    if (!scene || !hits || !shadow) { set_error("rt_download_hit_histograms: null argument"); return RT_E_INVALID; }
+    SceneHost* s = &scene->h;
+    if (!s->rendered || s->last_accel != RT_ACCEL_LBVH) {
+        set_error("hit histograms need a previous frame of the LBVH pipeline (params.accel = RT_ACCEL_LBVH)");
+        return RT_E_STATE;
+    }
+    RT_CUDA(cudaSetDevice(s->device));
+    const size_t nh = (size_t)kMaxLevels * (size_t)(s->nf + s->ns), nsw = (size_t)kMaxLevels * (size_t)std::max(s->nl, 1) * 3;
+    DevBuf dh, dsw;
+    if (!dh.reserve(nh * 8) || !dsw.reserve(nsw * 8)) return RT_E_NOMEM;
+    RT_CUDA(cudaMemsetAsync(dh.p, 0, nh * 8, s->stream));
+    RT_CUDA(cudaMemsetAsync(dsw.p, 0, nsw * 8, s->stream));
+    const int rc = launch_hit_histograms(s, dh.as<unsigned long long>(), dsw.as<unsigned long long>(), s->stream);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(cudaMemcpyAsync(hits, dh.p, nh * 8, cudaMemcpyDeviceToHost, s->stream));
+    RT_CUDA(cudaMemcpyAsync(shadow, dsw.p, (size_t)kMaxLevels * (size_t)s->nl * 3 * 8, cudaMemcpyDeviceToHost, s->stream));
+    RT_CUDA(cudaStreamSynchronize(s->stream));
+    return RT_OK;
+}
+
 int rt_trace_closest(RtScene* scene, int32_t accel, int32_t n, const float* origins, const float* dirs, float tmin,
                      int32_t* out_id, float* out_t, float* out_normal, float* out_bary)
 {

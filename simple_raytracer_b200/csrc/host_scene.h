@@ -180,6 +180,7 @@ struct SceneHost {
     bool have_primary_ids = false;
     FrameGraph graph;
     int graph_replays = 0;              // frames of this scene that were graph launches
+    FrameParams last_ps[kMaxSubframes]; // the FrameParams of the last frame's launch chains (rt_download_hit_histograms)
 };
 
 // upload.cu
@@ -202,6 +203,7 @@ int ensure_workspace(SceneHost* s, const RtRenderParams& p, const unsigned* dema
 // Reads the counters of the last frame (stream must be idle): sums the sub-frames into `total`,
 // returns the frame's kOverflow* bits (0 = complete); with kOverflowQueue `demand` says what to grow to.
 unsigned frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[kMaxLevels]);
+int launch_hit_histograms(const SceneHost* s, unsigned long long* dev_hits, unsigned long long* dev_shadow, cudaStream_t st);
 int overflow_error(unsigned bits);      // RT_OK, or RT_E_LIMIT + message for the bits no regrow cures
 void stash_workspace(Workspace&& ws);
 

@@ -525,6 +525,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         const int rc = issue(stream);
         if (rc != RT_OK) return rc;
     }
+    std::memcpy(s->last_ps, PS, sizeof(FrameParams) * K);
     s->rendered = true;
     s->last = p;
     s->last_local_rows = tl.n_local_rows; s->last_local_pixels = tl.n_local_pixels;
@@ -585,6 +586,35 @@ int overflow_error(unsigned bits)
         set_error("more than 65536 shadow chains with over 12 transparent occluders on one ray in a launch chain: the frame is incomplete");
         return RT_E_LIMIT;
     }
+    return RT_OK;
+}
+
+// Identity dump of the last LBVH frame (include/rt.h: rt_download_hit_histograms): per generation, which objects
+// ShadeRay was invoked on, and in which class (== 0, in between, == 1) the carried shadow_mask was after each light.
+__global__ void hit_histogram_kernel(const __grid_constant__ FrameParams P, int n_obj, unsigned long long* __restrict__ hits,
+                                     unsigned long long* __restrict__ shadow)
+{
+    const int nl = P.scene.nl;
+    for (int level = 0; level <= P.max_depth; level++) {
+        const LevelBuffers& LB = P.level[level];
+        const unsigned n = P.counters->nodes[level];
+        for (unsigned k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+            const int obj = __float_as_int(LB.hp[LB.node_list[k]].w);
+            atomicAdd(&hits[(size_t)level * n_obj + obj], 1ull);
+            float mask = 1.0f;                                   // 788
+            for (int li = 0; li < nl; li++) {
+                if (mask != 0.0f) mask = LB.sh[(size_t)li * n + k];   // a chain stops once the mask is 0 (and 0 stays 0)
+                atomicAdd(&shadow[((size_t)level * nl + li) * 3 + (mask == 0.0f ? 0 : mask == 1.0f ? 2 : 1)], 1ull);
+            }
+        }
+    }
+}
+
+int launch_hit_histograms(const SceneHost* s, unsigned long long* dev_hits, unsigned long long* dev_shadow, cudaStream_t st)
+{
+    for (int j = 0; j < s->last_subframes; j++)
+        hit_histogram_kernel<<<148 * 4, 256, 0, st>>>(s->last_ps[j], s->nf + s->ns, dev_hits, dev_shadow);
+    RT_CUDA(cudaGetLastError());
     return RT_OK;
 }
 

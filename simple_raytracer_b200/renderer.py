@@ -104,6 +104,13 @@ class DeviceScene:
         abi.check(self._lib.rt_download_primary_ids(self._h, _ptr(ids)), "rt_download_primary_ids")
         return ids
 
+    def hit_histograms(self) -> Tuple[np.ndarray, np.ndarray]:
+        """-> (hits uint64 [8][n_objects], shadow uint64 [8][n_lights][3]) of the last LBVH frame (rt_download_hit_histograms)."""
+        hits = np.zeros((8, self.scene.n_prims), dtype=np.uint64)
+        shadow = np.zeros((8, max(len(self.scene.lights), 1), 3), dtype=np.uint64)
+        abi.check(self._lib.rt_download_hit_histograms(self._h, _ptr(hits), _ptr(shadow)), "rt_download_hit_histograms")
+        return hits, shadow[:, :len(self.scene.lights)]
+
     def tile_buffer_bytes(self, world_size: int, tile_rows: int) -> int:
         return int(self._lib.rt_tile_buffer_bytes(self._h, world_size, tile_rows))
 

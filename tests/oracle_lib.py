@@ -111,6 +111,23 @@ def oracle_render(scene: Scene, max_depth: int = 4, epsilon: float = 1.0e-3, pix
     return raw, ids, st
 
 
+def oracle_hit_histograms(scene: Scene, max_depth: int = 4, epsilon: float = 1.0e-3):
+    """-> (hits uint64 [8][n_objects], shadow uint64 [8][n_lights][3]) of a whole-frame oracle render:
+    which objects ShadeRay was invoked on per generation, and the class of the carried shadow_mask after
+    each light (== 0 / in between / == 1); see oracle/rt_oracle.c: rto_set_histograms."""
+    lib = load_oracle()
+    lib.rto_set_histograms.argtypes = [C.c_void_p, C.c_void_p]
+    lib.rto_set_histograms.restype = None
+    hits = np.zeros((8, scene.n_prims), dtype=np.uint64)
+    shadow = np.zeros((8, max(len(scene.lights), 1), 3), dtype=np.uint64)
+    lib.rto_set_histograms(_ptr(hits), _ptr(shadow))
+    try:
+        oracle_render(scene, max_depth, epsilon)
+    finally:
+        lib.rto_set_histograms(None, None)
+    return hits, shadow[:, :len(scene.lights)]
+
+
 def primary_rays(scene: Scene, rows):
     """Primary rays of whole image rows -> (origins [n,3], dirs [n,3]) float32."""
     lib = load_oracle()

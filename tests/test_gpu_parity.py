@@ -459,3 +459,30 @@ def test_graph_replay_of_repeated_frames_never_changes_a_pixel(accel):
             ds.render(accel=accel)
             got = ds.download()
             assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+
+
+@pytest.mark.parametrize("make", [lambda n=n: common.golden_frame(n)[0] for n in common.ALL_SCENES] + [
+    lambda: scenegen.coverage_scene(200, 150),
+    lambda: scenegen.random_soup(300, 20, 1, 96, 72),
+    lambda: scenegen.random_soup(60, 6, 5, 96, 72),
+    lambda: scenegen.stress_scene(8000, 100, 160, 120),
+])
+def test_secondary_hit_ids_and_shadow_occlusion_are_identical(make):
+    """North star: "hit primitive IDs and shadow occlusion must be identical".  Beyond the primary ids per pixel:
+    per generation, the objects ShadeRay was invoked on (the hit ids chosen at main.cpp:745 / 1008 / 1120) and the
+    class of the carried shadow_mask after every light (main.cpp:909 / 946: exactly 0, in between, exactly 1),
+    as histograms of the production LBVH frame against the CPU oracle's — zero differences demanded."""
+    scene = make()
+    if scene.n_prims == 0:
+        pytest.skip("empty scene")
+    want_hits, want_shadow = O.oracle_hit_histograms(scene)
+    with DeviceScene(scene) as ds:
+        st = ds.render(accel=abi.RT_ACCEL_LBVH)
+        hits, shadow = ds.hit_histograms()
+        for k in (2, 3):                       # and with the tiles dealt out to several launch chains
+            ds.render(accel=abi.RT_ACCEL_LBVH, subframes=k)
+            h2, s2 = ds.hit_histograms()
+            assert np.array_equal(h2, hits) and np.array_equal(s2, shadow), k
+    assert int(want_hits.sum()) == st.nodes_total
+    assert np.array_equal(hits, want_hits), np.argwhere(hits != want_hits)[:5]
+    assert np.array_equal(shadow, want_shadow), (shadow[:5].tolist(), want_shadow[:5].tolist())
