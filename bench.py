@@ -247,6 +247,7 @@ def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
             "bvh_trace_kernel": B_NODE * tb + B_PRIM * tp + B_RAY * closest_rays,
             "bvh_shadow_kernel": B_NODE * sb + B_PRIM * sp,
             "bvh_colour_kernel": B_RAY * nodes + B_TEXEL * int(st.texel_fetches),
+            "bvh_spawn_kernel": B_RAY * (nodes + closest_rays - int(st.rays_primary)),      # hits read, child rays written
         }
         return {"bound": "hbm", "per_frame": sum(per_kernel.values()), "per_kernel": per_kernel, "unit": "GB/s",
                 "detail": {"trace_nodes_visited": tb, "trace_prim_tests": tp, "shadow_nodes_visited": sb,
@@ -315,9 +316,10 @@ def run_ours(args) -> dict:
     st_plain = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS)
     st_p = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS, profile=True)
     level_ms = [float(x) for x in list(st_p.level_ms)[:5]]
-    # (profiled frames: one serial chain; trace_ms = bvh_trace_kernel + bvh_spawn_kernel of the generation,
-    # shadow_ms = bvh_shadow_kernel (+ the empty redo launch), shade_ms = bvh_colour_kernel)
+    # (profiled frames: one serial chain with an event after every kernel; shadow_ms = bvh_shadow_kernel + the
+    # empty redo launch, shade_ms = bvh_colour_kernel)
     kernel_ms = {"bvh_trace_kernel": [float(x) for x in list(st_p.trace_ms)[:5]],
+                 "bvh_spawn_kernel": [float(x) for x in list(st_p.spawn_ms)[:5]],
                  "bvh_shadow_kernel": [float(x) for x in list(st_p.shadow_ms)[:5]],
                  "bvh_colour_kernel": [float(x) for x in list(st_p.shade_ms)[:5]]}
     # (kernels of a plain frame as the timed loop runs it; the profiled frame is a serial chain per generation)

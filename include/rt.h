@@ -188,6 +188,7 @@ typedef struct RtStats {
                                     whose buffers, camera, sharding and parameters equal the previous frame's is
                                     captured on its second sighting and replayed afterwards */
     int32_t  reserved2;
+    double   spawn_ms[8];        /* params.profile, LBVH: bvh_spawn_kernel of each generation (trace_ms is the walk alone) */
 } RtStats;
 
 typedef struct RtScene RtScene;   /* opaque: all device state of one scene */

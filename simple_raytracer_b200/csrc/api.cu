@@ -166,7 +166,7 @@ void rt_free_scene(RtScene* scene)
     for (int k = 0; k < kMaxLevels + 2; k++)
         if (s->prof_ev[k]) cudaEventDestroy(s->prof_ev[k]);
     for (int k = 0; k < kMaxLevels; k++)
-        for (int j = 0; j < 2; j++)
+        for (int j = 0; j < 3; j++)
             if (s->prof_mid[k][j]) cudaEventDestroy(s->prof_mid[k][j]);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete scene;
@@ -310,7 +310,8 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
                 RT_CUDA(cudaEventElapsedTime(&t, s->prof_ev[l], s->prof_ev[l + 1]));
                 stats->level_ms[l] = t;
                 if (s->prof_split) {
-                    RT_CUDA(cudaEventElapsedTime(&t, s->prof_ev[l], s->prof_mid[l][0]));      stats->trace_ms[l] = t;
+                    RT_CUDA(cudaEventElapsedTime(&t, s->prof_ev[l], s->prof_mid[l][2]));      stats->trace_ms[l] = t;
+                    RT_CUDA(cudaEventElapsedTime(&t, s->prof_mid[l][2], s->prof_mid[l][0])); stats->spawn_ms[l] = t;
                     RT_CUDA(cudaEventElapsedTime(&t, s->prof_mid[l][0], s->prof_mid[l][1])); stats->shadow_ms[l] = t;
                     RT_CUDA(cudaEventElapsedTime(&t, s->prof_mid[l][1], s->prof_ev[l + 1])); stats->shade_ms[l] = t;
                 }

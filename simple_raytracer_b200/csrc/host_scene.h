@@ -167,7 +167,7 @@ struct SceneHost {
     cudaStream_t stream = nullptr;      // owned
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaEvent_t prof_ev[kMaxLevels + 2] = { nullptr };   // params.profile: boundaries of the generations
-    cudaEvent_t prof_mid[kMaxLevels][2] = { { nullptr } };   // LBVH pipeline: after trace, after shadow
+    cudaEvent_t prof_mid[kMaxLevels][3] = { { nullptr } };   // LBVH pipeline: after trace + spawn, after shadow, after trace
     bool prof_split = false;
     int prof_levels = 0;                                 // events recorded by the last frame (0 = none)
     Counters* h_counters = nullptr;     // = ws.h_counters (pinned, one per sub-frame), set by ensure_workspace

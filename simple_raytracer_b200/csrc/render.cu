@@ -375,7 +375,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
             for (int k = 0; k < kMaxLevels + 2; k++)
                 if (!s->prof_ev[k]) RT_CUDA(cudaEventCreate(&s->prof_ev[k]));
             for (int k = 0; k < kMaxLevels; k++)
-                for (int j = 0; j < 2; j++)
+                for (int j = 0; j < 3; j++)
                     if (!s->prof_mid[k][j]) RT_CUDA(cudaEventCreate(&s->prof_mid[k][j]));
         }
         s->prof_split = p.profile && lbvh;
@@ -403,6 +403,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 RT_CUDA(cudaEventRecord(s->prof_ev[l], stream));
                 if (count) launch_trace<true>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
                 else launch_trace<false>(P, l, sharing, persistent_grid(work, sms, T.grid_mult, kWalkBlock), stream);
+                RT_CUDA(cudaEventRecord(s->prof_mid[l][2], stream));
                 bvh_spawn_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l);
                 n += 2;
                 RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));

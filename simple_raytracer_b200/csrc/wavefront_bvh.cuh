@@ -253,10 +253,20 @@ __global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_spawn_kernel(
     const unsigned stride = gridDim.x * blockDim.x;
     const unsigned rounded = (count + 31u) & ~31u;
     const bool lane0 = (threadIdx.x & 31) == 0;
+    const bool spawning = level < P.max_depth;
     for (unsigned slot = blockIdx.x * blockDim.x + threadIdx.x; slot < rounded; slot += stride) {
         RayIn r; r.ns = 0;
         Hit h; h.obj = -1; h.t = 0.f; h.b = h.g = 0.f;
-        if (slot < count) h.obj = __float_as_int(__ldcg(&LB.hp[slot].w));
+        // every record of the slot is asked for at once (most slots of a dense scene hold a hit): one memory
+        // round trip per slot instead of hit -> ray -> barycentrics one after the other
+        if (slot < count) {
+            h.obj = __float_as_int(__ldcg(&LB.hp[slot].w));
+            if (spawning) {
+                const float4 hb = __ldcg(LB.hb + slot);
+                load_ray(P, level, slot, r);
+                h.b = hb.x; h.g = hb.y; h.t = hb.z;
+            }
+        }
         const bool hit = h.obj >= 0;
         const unsigned hm = __ballot_sync(0xffffffffu, hit);
         if (!hm) continue;                            // warp-uniform
@@ -264,12 +274,7 @@ __global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_spawn_kernel(
         if (lane0) base = atomicAdd(&P.counters->nodes[level], (unsigned)__popc(hm));
         base = __shfl_sync(0xffffffffu, base, 0);
         if (hit) LB.node_list[base + __popc(hm & lanemask_lt())] = (int)slot;
-        if (level == P.max_depth) continue;
-        if (hit) {
-            load_ray(P, level, slot, r);
-            const float4 hb = __ldcg(LB.hb + slot);
-            h.b = hb.x; h.g = hb.y; h.t = hb.z;
-        }
+        if (!spawning) continue;
         const NoShadow none;
         shade_and_spawn<false, true>(P, none, level, slot, r, h, hit);
     }

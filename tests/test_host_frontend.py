@@ -343,13 +343,13 @@ def test_ctypes_mirror_has_the_sizes_the_c_compiler_sees(tmp_path):
         '#include <stdio.h>\n#include <stddef.h>\n#include "rt.h"\n'
         "int main(void) {\n"
         '  printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(RtRenderParams), sizeof(RtStats), sizeof(RtSceneDesc),\n'
-        "         sizeof(RtMaterial), sizeof(RtFace), offsetof(RtStats, bvh_levels8), offsetof(RtRenderParams, work_sharing),\n"
+        "         sizeof(RtMaterial), sizeof(RtFace), offsetof(RtStats, spawn_ms), offsetof(RtRenderParams, work_sharing),\n"
         "         offsetof(RtStats, shadow_rays_walked));\n"
         "  return 0; }\n")
     exe = tmp_path / "sizes"
     subprocess.run([cc, "-std=c11", "-I", os.path.join(root, "include"), "-o", str(exe), str(src)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     want = [C.sizeof(abi.RtRenderParams), C.sizeof(abi.RtStats), C.sizeof(abi.RtSceneDesc), C.sizeof(abi.RtMaterial),
-            C.sizeof(abi.RtFace), abi.RtStats.bvh_levels8.offset, abi.RtRenderParams.work_sharing.offset,
+            C.sizeof(abi.RtFace), abi.RtStats.spawn_ms.offset, abi.RtRenderParams.work_sharing.offset,
             abi.RtStats.shadow_rays_walked.offset]
     assert got == want

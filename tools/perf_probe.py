@@ -38,7 +38,7 @@ def main():
                 best = s
         out = dict(upload_s=round(up, 3), first_render_s=round(first, 3), ms=round(best.render_ms, 3), rays=int(rays),
                    mrays_s=round(rays / best.render_ms / 1e3, 1), nodes=list(best.nodes_per_level)[:a.depth + 1],
-                   level_ms=[round(x, 3) for x in list(best.level_ms)[:a.depth + 1]], combine_ms=round(best.combine_ms, 3), trace_ms=[round(x, 3) for x in list(best.trace_ms)[:a.depth + 1]], shadow_ms=[round(x, 3) for x in list(best.shadow_ms)[:a.depth + 1]], shade_ms=[round(x, 3) for x in list(best.shade_ms)[:a.depth + 1]],
+                   level_ms=[round(x, 3) for x in list(best.level_ms)[:a.depth + 1]], combine_ms=round(best.combine_ms, 3), trace_ms=[round(x, 3) for x in list(best.trace_ms)[:a.depth + 1]], spawn_ms=[round(x, 3) for x in list(best.spawn_ms)[:a.depth + 1]], shadow_ms=[round(x, 3) for x in list(best.shadow_ms)[:a.depth + 1]], shade_ms=[round(x, 3) for x in list(best.shade_ms)[:a.depth + 1]],
                    launches=best.kernel_launches, subframes=a.subframes)
         if not a.no_instrument:
             si = ds.render(instrument=True, **kw)
