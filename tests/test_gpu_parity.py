@@ -486,3 +486,41 @@ def test_secondary_hit_ids_and_shadow_occlusion_are_identical(make):
     assert int(want_hits.sum()) == st.nodes_total
     assert np.array_equal(hits, want_hits), np.argwhere(hits != want_hits)[:5]
     assert np.array_equal(shadow, want_shadow), (shadow[:5].tolist(), want_shadow[:5].tolist())
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_random_scenes_fuzz_against_the_oracle(seed):
+    """Seeded random scenes through both accelerators against the CPU oracle: primitive counts from a handful to a
+    few hundred, 1-5 lights of both kinds (every third scene with a NON-unit directional light: the reference's
+    sphere test then accepts an unbounded region), transparent materials, bkgcolor with and without eta,
+    recursion depths 1-5, odd image sizes.  Pixels (NaN set included), primary ids, ShadeRay / TraceRay counts per
+    generation, secondary hit histograms and shadow-mask classes must all be identical."""
+    rng = np.random.default_rng(1000 + seed)
+    n_tris = int(rng.choice([3, 12, 60, 250, 700]))
+    n_sph = int(rng.choice([0, 2, 9, 40]))
+    w, h = int(rng.integers(33, 90)), int(rng.integers(17, 70))
+    scene = scenegen.random_soup(n_tris, n_sph, 500 + seed, w, h, n_lights=int(rng.integers(1, 6)))
+    if seed % 3 == 0:
+        d = np.where(scene.lights["w"] == 0)[0]
+        if len(d):
+            scene.lights["xyz"][d[0]] *= np.float32(rng.uniform(0.3, 3.0))      # un-normalised direction
+    kw = {}
+    if seed % 4 == 1:
+        kw["bkg_eta"] = 0.0                                                       # bkgcolor without a 4th argument
+    if seed % 5 == 2:
+        kw["eye"] = (float(rng.uniform(-3, 3)), float(rng.uniform(-3, 3)), 6.0)  # camera inside the soup
+    scene = scene.copy(**kw)
+    depth = int(rng.integers(1, 6))
+    raw, ids, ost = O.oracle_render(scene, max_depth=depth)
+    want_hits, want_shadow = O.oracle_hit_histograms(scene, max_depth=depth)
+    for accel in (abi.RT_ACCEL_BRUTE, abi.RT_ACCEL_LBVH):
+        cmp, st = _render_and_compare(scene, raw, ids, ost, accel, depth=depth)
+        assert cmp["exact"] == cmp["pixels"], (seed, accel, cmp)
+        with DeviceScene(scene) as ds:
+            ds.render(accel=accel, max_depth=depth)                               # the production schedule
+            rgb, flags = ds.download()
+            c2 = common.compare_frames(raw, rgb, flags)
+            assert c2["exact"] == c2["pixels"] and c2["nan_mismatch"] == 0, (seed, accel, c2)
+            if accel == abi.RT_ACCEL_LBVH:
+                hits, shadow = ds.hit_histograms()
+                assert np.array_equal(hits, want_hits) and np.array_equal(shadow, want_shadow), seed
