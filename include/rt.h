@@ -187,7 +187,9 @@ typedef struct RtStats {
     int32_t  graph_replays;      /* frames of this scene so far that were issued as ONE CUDA-graph launch: a frame
                                     whose buffers, camera, sharding and parameters equal the previous frame's is
                                     captured on its second sighting and replayed afterwards */
-    int32_t  reserved2;
+    int32_t  shadow_map_hits;    /* instrumented LBVH frames: shadow rays settled by a directional light's occluder map
+                                    (the exact test against the map's candidate found an opaque occluder: no walk);
+                                    saturates at INT32_MAX */
     double   spawn_ms[8];        /* params.profile, LBVH: bvh_spawn_kernel of each generation (trace_ms is the walk alone) */
 } RtStats;
 

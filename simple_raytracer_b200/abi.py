@@ -87,7 +87,7 @@ class RtStats(C.Structure):
                 ("trace_drain_steals", C.c_double * 8), ("shadow_drain_steps", C.c_double * 8),
                 ("shadow_drain_lanes", C.c_double * 8), ("shadow_chains_redone", C.c_uint64),
                 ("bvh_levels4", C.c_int32), ("bvh_levels8", C.c_int32), ("graph_replays", C.c_int32),
-                ("reserved2", C.c_int32), ("spawn_ms", C.c_double * 8)]
+                ("shadow_map_hits", C.c_int32), ("spawn_ms", C.c_double * 8)]
 
     def as_dict(self) -> dict:
         d = {}

@@ -285,6 +285,7 @@ int rt_render(RtScene* scene, const RtRenderParams* params, RtStats* stats)
         stats->shadow_boxes_tested = c.shadow_boxes; stats->shadow_prim_tests = c.shadow_prims;
         stats->shadow_rays_walked = (s->last_accel == RT_ACCEL_LBVH && p.instrument) ? c.shadow_walks : stats->rays_shadow;
         stats->shadow_chains_redone = c.redo_count;
+        stats->shadow_map_hits = (int32_t)std::min<unsigned long long>(c.shadow_map_hits, 0x7fffffffull);
         stats->bvh_levels4 = s->last_accel == RT_ACCEL_LBVH ? s->bvh_levels4 : 0;
         stats->bvh_levels8 = s->last_accel == RT_ACCEL_LBVH ? s->bvh_levels8 : 0;
         stats->graph_replays = s->graph_replays;

@@ -550,6 +550,207 @@ __global__ void collapse8_kernel(int n_prims, int nf, int level, unsigned* __res
     (void)n_prims;
 }
 
+// ---- occluder maps of directional lights (scene_device.h: ShadowMapView) -----------------------------------
+//
+// An orthographic id buffer seen from the light: one thread per primitive slot of the array the any-hit walk
+// reads rasterises an OPAQUE primitive (shadow factor 1 - opacity == 0) over the cells whose centres it covers and
+// keeps, per cell, the one nearest to the light (64-bit atomicMin on depth | slot).  Plain float arithmetic: the
+// map is a guess that the exact test confirms or not.  Primitives covering more than kSmapThreadCells cells go
+// to a list that a second kernel rasterises one block per primitive.
+struct SmapBuild {
+    float dir[3], ub[3], vb[3];
+    float u0, v0, inv_cell, cell;
+    int R;
+};
+constexpr int kSmapThreadCells = 1024;
+
+RT_DEV unsigned long long smap_key(float depth, int slot)
+{
+    unsigned b = __float_as_uint(depth);
+    b = (b & 0x80000000u) ? ~b : (b | 0x80000000u);            // floats in unsigned order
+    return ((unsigned long long)b << 32) | (unsigned)slot;
+}
+
+struct SmapPrim {
+    bool ok, is_tri;
+    float x[3], y[3], d[3];      // triangle: vertices in cell units, depth along the light; sphere: [0] = centre
+    float r;                     // sphere radius (world units)
+    int x0, y0, wx, wy;          // the cells whose centres its bounding box holds
+};
+
+RT_DEV SmapPrim smap_setup(const float4* w, const SmapBuild& m)
+{
+    SmapPrim q;
+    q.ok = false;
+    const float4 w4 = w[4];
+    if (w4.y != 0.0f) return q;                                  // not opaque (or NaN)
+    q.is_tri = __float_as_int(w4.w) == 0;
+    float lo_x, hi_x, lo_y, hi_y;
+    if (q.is_tri) {
+        const float4 v0 = w[1], e1 = w[2], e2 = w[3];
+        const float p[3][3] = { { v0.x, v0.y, v0.z }, { v0.x + e1.x, v0.y + e1.y, v0.z + e1.z }, { v0.x + e2.x, v0.y + e2.y, v0.z + e2.z } };
+        for (int k = 0; k < 3; k++) {
+            q.x[k] = (p[k][0] * m.ub[0] + p[k][1] * m.ub[1] + p[k][2] * m.ub[2] - m.u0) * m.inv_cell;
+            q.y[k] = (p[k][0] * m.vb[0] + p[k][1] * m.vb[1] + p[k][2] * m.vb[2] - m.v0) * m.inv_cell;
+            q.d[k] = p[k][0] * m.dir[0] + p[k][1] * m.dir[1] + p[k][2] * m.dir[2];
+        }
+        lo_x = fminf(q.x[0], fminf(q.x[1], q.x[2])); hi_x = fmaxf(q.x[0], fmaxf(q.x[1], q.x[2]));
+        lo_y = fminf(q.y[0], fminf(q.y[1], q.y[2])); hi_y = fmaxf(q.y[0], fmaxf(q.y[1], q.y[2]));
+        q.r = 0.0f;
+    } else {
+        const float4 c = w[0];
+        q.x[0] = (c.x * m.ub[0] + c.y * m.ub[1] + c.z * m.ub[2] - m.u0) * m.inv_cell;
+        q.y[0] = (c.x * m.vb[0] + c.y * m.vb[1] + c.z * m.vb[2] - m.v0) * m.inv_cell;
+        q.d[0] = c.x * m.dir[0] + c.y * m.dir[1] + c.z * m.dir[2];
+        q.r = fabsf(c.w);
+        const float rc = q.r * m.inv_cell;
+        lo_x = q.x[0] - rc; hi_x = q.x[0] + rc; lo_y = q.y[0] - rc; hi_y = q.y[0] + rc;
+    }
+    if (!(isfinite(lo_x) && isfinite(hi_x) && isfinite(lo_y) && isfinite(hi_y))) return q;
+    // cell i has its centre at i + 0.5
+    const float R = (float)m.R;
+    const int x0 = (int)fmaxf(ceilf(lo_x - 0.5f), 0.0f), x1 = (int)fminf(floorf(hi_x - 0.5f), R - 1.0f);
+    const int y0 = (int)fmaxf(ceilf(lo_y - 0.5f), 0.0f), y1 = (int)fminf(floorf(hi_y - 0.5f), R - 1.0f);
+    if (x1 < x0 || y1 < y0) return q;
+    q.x0 = x0; q.y0 = y0; q.wx = x1 - x0 + 1; q.wy = y1 - y0 + 1;
+    q.ok = true;
+    return q;
+}
+
+RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, unsigned long long* cells, int start, int stride)
+{
+    const int total = q.wx * q.wy;
+    float den = 0.0f;
+    if (q.is_tri) {
+        den = (q.x[1] - q.x[0]) * (q.y[2] - q.y[0]) - (q.x[2] - q.x[0]) * (q.y[1] - q.y[0]);
+        if (!(fabsf(den) > 1.0e-12f)) return;                   // edge-on
+    }
+    for (int i = start; i < total; i += stride) {
+        const int ix = q.x0 + i % q.wx, iy = q.y0 + i / q.wx;
+        const float cx = (float)ix + 0.5f, cy = (float)iy + 0.5f;
+        float depth;
+        if (q.is_tri) {
+            const float b1 = ((cx - q.x[0]) * (q.y[2] - q.y[0]) - (q.x[2] - q.x[0]) * (cy - q.y[0])) / den;
+            const float b2 = ((q.x[1] - q.x[0]) * (cy - q.y[0]) - (cx - q.x[0]) * (q.y[1] - q.y[0])) / den;
+            const float b0 = 1.0f - b1 - b2;
+            if (!(b0 >= 0.0f && b1 >= 0.0f && b2 >= 0.0f)) continue;
+            depth = b0 * q.d[0] + b1 * q.d[1] + b2 * q.d[2];
+        } else {
+            const float dx = (cx - q.x[0]) * m.cell, dy = (cy - q.y[0]) * m.cell;
+            const float h2 = q.r * q.r - (dx * dx + dy * dy);
+            if (!(h2 >= 0.0f)) continue;
+            depth = q.d[0] - sqrtf(h2);
+        }
+        if (!isfinite(depth)) continue;
+        atomicMin(cells + (size_t)iy * m.R + ix, smap_key(depth, slot));
+    }
+}
+
+__global__ void smap_prims_kernel(const float4* __restrict__ prims, int n, SmapBuild m, unsigned long long* __restrict__ cells,
+                                  int* __restrict__ big, unsigned* __restrict__ n_big)
+{
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n) return;
+    const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m);
+    if (!q.ok) return;
+    if ((long long)q.wx * q.wy > kSmapThreadCells) { big[atomicAdd(n_big, 1u)] = slot; return; }
+    smap_raster(q, slot, m, cells, 0, 1);
+}
+
+__global__ void smap_big_kernel(const float4* __restrict__ prims, SmapBuild m, unsigned long long* __restrict__ cells,
+                                const int* __restrict__ big, const unsigned* __restrict__ n_big)
+{
+    const unsigned n = *n_big;
+    for (unsigned b = blockIdx.x; b < n; b += gridDim.x) {
+        const int slot = big[b];
+        const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m);
+        if (q.ok) smap_raster(q, slot, m, cells, (int)threadIdx.x, (int)blockDim.x);
+    }
+}
+
+__global__ void smap_finish_kernel(const unsigned long long* __restrict__ cells, int n_cells, int* __restrict__ out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_cells) return;
+    const unsigned long long k = cells[i];
+    out[i] = k == ~0ull ? -1 : (int)(unsigned)(k & 0xffffffffull);
+}
+
+// Maps for the directional ones among the first kMaxShadowMaps lights, over the primitive array the any-hit walk
+// reads (prims: n records of kTriWords words).  Lights whose direction is not finite, and scenes without finite
+// bounds, get none.
+static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const BuildBounds& bb, cudaStream_t st)
+{
+    for (int k = 0; k < kMaxShadowMaps; k++) s->smap[k] = SceneHost::SmapHost();
+    const int nl = std::min(s->nl, kMaxShadowMaps);
+    if (nl <= 0 || n <= 0) return RT_OK;
+    for (int c = 0; c < 3; c++) if (!std::isfinite(bb.lo[c]) || !std::isfinite(bb.hi[c])) return RT_OK;
+    float4 lights[kMaxShadowMaps * 3];
+    RT_CUDA(cudaMemcpyAsync(lights, s->light.p, (size_t)nl * 3 * sizeof(float4), cudaMemcpyDeviceToHost, st));
+    RT_CUDA(cudaStreamSynchronize(st));
+    // twice as many cells per axis as the square root of the primitive count: cells a good deal smaller than the
+    // typical primitive, so that a point in a cell is usually behind the primitive that covers the cell's centre
+    int R = 64;
+    while (R < 2048 && (double)R < 2.0 * std::sqrt((double)n)) R *= 2;
+    const size_t n_cells = (size_t)R * R;
+    int want[kMaxShadowMaps], n_maps = 0;
+    for (int k = 0; k < nl; k++) {
+        const float4 l0 = lights[3 * k];
+        const double len = std::sqrt((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z);
+        if (l0.w == 0.0f && std::isfinite(len) && len > 1.0e-30) want[n_maps++] = k;
+    }
+    if (n_maps == 0) return RT_OK;
+    DevBuf keys, big, n_big;
+    if (!s->smap_cells.reserve(n_cells * n_maps * sizeof(int)) || !keys.reserve(n_cells * 8) || !big.reserve((size_t)n * 4) ||
+        !n_big.reserve(4))
+        return RT_E_NOMEM;
+    for (int j = 0; j < n_maps; j++) {
+        const int k = want[j];
+        const float4 l0 = lights[3 * k];
+        const double len = std::sqrt((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z);
+        const double d[3] = { l0.x / len, l0.y / len, l0.z / len };
+        // an axis the direction is least aligned with, then an orthonormal pair
+        int a = 0;
+        if (std::fabs(d[1]) < std::fabs(d[a])) a = 1;
+        if (std::fabs(d[2]) < std::fabs(d[a])) a = 2;
+        double ax[3] = { 0, 0, 0 }; ax[a] = 1.0;
+        double u[3] = { d[1] * ax[2] - d[2] * ax[1], d[2] * ax[0] - d[0] * ax[2], d[0] * ax[1] - d[1] * ax[0] };
+        const double ul = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+        for (int c = 0; c < 3; c++) u[c] /= ul;
+        const double v[3] = { d[1] * u[2] - d[2] * u[1], d[2] * u[0] - d[0] * u[2], d[0] * u[1] - d[1] * u[0] };
+        double umin = 1e300, umax = -1e300, vmin = 1e300, vmax = -1e300;
+        for (int corner = 0; corner < 8; corner++) {
+            double pu = 0, pv = 0;
+            for (int c = 0; c < 3; c++) {
+                const double x = (corner >> c) & 1 ? bb.hi[c] : bb.lo[c];
+                pu += x * u[c]; pv += x * v[c];
+            }
+            umin = std::min(umin, pu); umax = std::max(umax, pu); vmin = std::min(vmin, pv); vmax = std::max(vmax, pv);
+        }
+        const double extent = std::max(umax - umin, vmax - vmin) * 1.0001 + 1.0e-20;
+        if (!std::isfinite(extent) || !(extent > 0.0)) continue;
+        SmapBuild m;
+        for (int c = 0; c < 3; c++) { m.dir[c] = (float)d[c]; m.ub[c] = (float)u[c]; m.vb[c] = (float)v[c]; }
+        m.cell = (float)(extent / R); m.inv_cell = (float)(R / extent);
+        m.u0 = (float)(0.5 * (umin + umax) - 0.5 * extent); m.v0 = (float)(0.5 * (vmin + vmax) - 0.5 * extent);
+        m.R = R;
+        if (!std::isfinite(m.inv_cell) || !std::isfinite(m.u0) || !std::isfinite(m.v0)) continue;
+        RT_CUDA(cudaMemsetAsync(keys.p, 0xff, n_cells * 8, st));
+        RT_CUDA(cudaMemsetAsync(n_big.p, 0, 4, st));
+        smap_prims_kernel<<<(n + 255) / 256, 256, 0, st>>>(prims, n, m, keys.as<unsigned long long>(), big.as<int>(), n_big.as<unsigned>());
+        smap_big_kernel<<<1024, 256, 0, st>>>(prims, m, keys.as<unsigned long long>(), big.as<int>(), n_big.as<unsigned>());
+        smap_finish_kernel<<<(unsigned)((n_cells + 255) / 256), 256, 0, st>>>(keys.as<unsigned long long>(), (int)n_cells,
+                                                                             s->smap_cells.as<int>() + (size_t)j * n_cells);
+        RT_CUDA(cudaGetLastError());
+        SceneHost::SmapHost& h = s->smap[k];
+        h.offset_plus_1 = (size_t)j * n_cells + 1;
+        for (int c = 0; c < 3; c++) { h.ub[c] = m.ub[c]; h.vb[c] = m.vb[c]; }
+        h.u0 = m.u0; h.v0 = m.v0; h.inv_cell = m.inv_cell; h.R = R;
+    }
+    RT_CUDA(cudaStreamSynchronize(st));      // (the temporaries go out of scope)
+    return RT_OK;
+}
+
 }  // namespace
 
 int build_bvh(SceneHost* s)
@@ -676,7 +877,8 @@ int build_bvh(SceneHost* s)
         return RT_E_LIMIT;
     }
     s->bvh_n_nodes = n_internal; s->bvh_root = 0; s->bvh_built = true;
-    return RT_OK;
+    // the any-hit walk reads the 8-wide tree's primitive records when there is one (bvh.cuh: make_bvh_accel)
+    return build_shadow_maps(s, s->bvh8_n_nodes > 0 ? s->bvh8_prims.as<float4>() : s->bvh_tri.as<float4>(), n, bb, st);
 }
 
 }  // namespace rt

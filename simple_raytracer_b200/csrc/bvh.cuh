@@ -541,7 +541,7 @@ struct BvhAccelT {
                 if (fin) {
                     // a job may be a chain of rays (the lights of one node): go on in this lane
                     V3 o, ray;
-                    if (job.next(o, ray, tmin, tmax)) start(true, o, ray);
+                    if (job.next(o, ray, tmin, tmax)) start(job.walk_needed(), o, ray);
                     else alive = false;
                 }
             }

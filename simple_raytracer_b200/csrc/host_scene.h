@@ -160,6 +160,11 @@ struct SceneHost {
     int bvh_n_nodes = 0, bvh_root = 0, bvh8_n_nodes = 0;
     int bvh_levels4 = 0, bvh_levels8 = 0;   // depth of the two trees (build_bvh checks them against the walk stacks)
     bool bvh_built = false;
+    // occluder maps of the first kMaxShadowMaps lights (directional ones; bvh.cu: build_shadow_maps): all maps in one
+    // buffer, smap[k].cells holds the map's OFFSET (in ints) + 1 as an integer (0 = no map) until scene_view() adds the base
+    DevBuf smap_cells;
+    struct SmapHost { size_t offset_plus_1 = 0; float ub[3] = { 0, 0, 0 }, vb[3] = { 0, 0, 0 }; float u0 = 0, v0 = 0, inv_cell = 0; int R = 0; };
+    SmapHost smap[kMaxShadowMaps];
 
     CameraView cam{};
     Workspace ws;

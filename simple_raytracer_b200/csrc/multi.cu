@@ -128,7 +128,7 @@ namespace {
 DevBuf SceneHost::* const kSceneBuffers[] = {
     &SceneHost::tri, &SceneHost::sph, &SceneHost::face_attr, &SceneHost::obj, &SceneHost::mat, &SceneHost::light,
     &SceneHost::tex_desc, &SceneHost::texels, &SceneHost::bvh_nodes, &SceneHost::bvh_tri, &SceneHost::bvh_sph,
-    &SceneHost::bvh8_nodes, &SceneHost::bvh8_prims,
+    &SceneHost::bvh8_nodes, &SceneHost::bvh8_prims, &SceneHost::smap_cells,
 };
 
 // An RtScene without contents on the current device (what rt_upload_scene creates before build_scene).
@@ -156,6 +156,7 @@ void copy_scalars(const SceneHost* a, SceneHost* b)
     b->zero_mask_exit = a->zero_mask_exit; b->nonunit_directional = a->nonunit_directional;
     b->bvh_n_nodes = a->bvh_n_nodes; b->bvh_root = a->bvh_root; b->bvh8_n_nodes = a->bvh8_n_nodes;
     b->bvh_levels4 = a->bvh_levels4; b->bvh_levels8 = a->bvh_levels8; b->bvh_built = a->bvh_built;
+    for (int k = 0; k < kMaxShadowMaps; k++) b->smap[k] = a->smap[k];
     b->cam = a->cam;
 }
 
@@ -335,6 +336,7 @@ int rt_render_multi(RtMultiScene* m, const RtRenderParams* params, RtStats* stat
             stats->bvh_nodes_visited += c.bvh_nodes; stats->prim_tests += c.prim_tests; stats->texel_fetches += c.texels;
             stats->shadow_boxes_tested += c.shadow_boxes; stats->shadow_prim_tests += c.shadow_prims;
             stats->shadow_rays_walked += c.shadow_walks; stats->shadow_chains_redone += c.redo_count;
+            stats->shadow_map_hits = (int32_t)std::min<unsigned long long>((unsigned long long)stats->shadow_map_hits + c.shadow_map_hits, 0x7fffffffull);
             stats->graph_replays += m->sc[i]->h.graph_replays;
         }
         stats->rays_primary = (uint64_t)W * (uint64_t)H;

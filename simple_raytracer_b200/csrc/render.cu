@@ -565,6 +565,7 @@ unsigned frame_overflowed(const SceneHost* s, Counters* total, unsigned demand[k
         }
         t.bvh_nodes += c.bvh_nodes; t.prim_tests += c.prim_tests; t.texels += c.texels;
         t.shadow_boxes += c.shadow_boxes; t.shadow_prims += c.shadow_prims; t.shadow_walks += c.shadow_walks;
+        t.shadow_map_hits += c.shadow_map_hits;
         t.redo_count += c.redo_count;
         if (j == 0) std::memcpy(t.clock, c.clock, sizeof t.clock);      // (the first chain's)
     }

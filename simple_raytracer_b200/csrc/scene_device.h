@@ -55,6 +55,19 @@ struct BvhView {
     int n_nodes8;
 };
 
+// Occluder maps (bvh.cu: build_shadow_maps): for a directional light, an orthographic id buffer seen from the
+// light — per cell the OPAQUE primitive nearest to the light that covers the cell's centre, as its slot in the
+// primitive array the any-hit walk reads.  A shadow ray first runs the reference's exact test against the
+// primitive of its cell (ShadowJob::setup): if that accepts, the carried product is exactly 0 and the walk is
+// skipped; if not, the ray is walked as before.  The map only guesses; nothing it holds can change a result.
+constexpr int kMaxShadowMaps = 4;      // the first four lights (94 % of the stress scene's chains end at light 0)
+struct ShadowMapView {
+    const int* cells;                  // [R * R], -1 = none; nullptr = this light has no map
+    float ub[3], vb[3];                // orthonormal basis of the light's plane
+    float u0, v0, inv_cell;
+    int R;
+};
+
 struct SceneView {
     int nf, ns, nl, ntex;
     const float4* tri;        // nf * kTriWords, file order
@@ -72,6 +85,7 @@ struct SceneView {
     float bkg[3];
     float bkg_eta;
     int zero_mask_exit;       // shade_node may leave the light loop once shadow_mask == 0 (see there)
+    ShadowMapView smap[kMaxShadowMaps];
 };
 
 struct CameraView {          // main.cpp:677-710, computed on the host in rt_upload_scene / rt_set_camera
@@ -143,6 +157,7 @@ struct Counters {
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
     unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
+    unsigned long long shadow_map_hits;                 // ... shadow rays settled by the occluder map's candidate (no walk)
     WalkClock clock[2][kMaxLevels];                     // instrumented LBVH frames: [0] trace, [1] shadow kernels
 };
 

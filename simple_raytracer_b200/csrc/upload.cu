@@ -342,6 +342,14 @@ SceneView scene_view(const SceneHost* s)
     for (int k = 0; k < 3; k++) v.bkg[k] = s->bkg[k];
     v.bkg_eta = s->bkg_eta;
     v.zero_mask_exit = s->zero_mask_exit ? 1 : 0;
+    for (int k = 0; k < kMaxShadowMaps; k++) {
+        const SceneHost::SmapHost& m = s->smap[k];
+        if (!m.offset_plus_1 || !s->smap_cells.p) continue;
+        ShadowMapView& d = v.smap[k];
+        d.cells = s->smap_cells.as<int>() + (m.offset_plus_1 - 1);
+        for (int c = 0; c < 3; c++) { d.ub[c] = m.ub[c]; d.vb[c] = m.vb[c]; }
+        d.u0 = m.u0; d.v0 = m.v0; d.inv_cell = m.inv_cell; d.R = m.R;
+    }
     return v;
 }
 

@@ -144,6 +144,7 @@ struct TraceJob {
     }
 
     RT_DEV bool next(V3&, V3&, float&, float&) { return false; }
+    RT_DEV bool walk_needed() const { return true; }
 
     // work sharing at the end of a launch (persistent_walk): a helper lane walks a subtree
     // for the ray of lane src with a copy of its state ...
@@ -307,17 +308,38 @@ struct ShadowJob {
     int li;
     V3 p; int self;
     float mask;
+    bool settled;                      // this light's ray needs no walk: the occluder map's candidate is an opaque hit
     unsigned long long walks = 0;      // instrumented variant: shadow rays actually walked by this thread
+    unsigned long long map_hits = 0;   // ... and those the occluder map settled
     typename BvhAccelT<kCount>::ShadowVisit v;
 
     RT_DEV void setup(V3& wo, V3& wray, float& tmin, float& tmax)
     {
         const float4 l0 = P.scene.light[3 * li];
         tmin = P.epsilon;
+        settled = false;
         if (l0.w == 0.0f) {
             wray = vneg(ld3(l0));                                                // 895: un-normalised ray
             tmax = 3.402823466e+38f;
             acc.shadow_begin(p, wray, self, tmin, 0.0f, false, v);
+            // the occluder map's guess (scene_device.h: ShadowMapView): the reference's own test of this ray against
+            // the opaque primitive that covers the ray's cell nearest to the light.  Accepted: the product is
+            // exactly 0 whatever else the ray meets (every factor lies in [0,1]), no walk.  Not accepted: forget
+            // the attempt and walk.
+            if (li < kMaxShadowMaps && P.scene.smap[li].cells != nullptr) {
+                const ShadowMapView& m = P.scene.smap[li];
+                const float fu = (p.x * m.ub[0] + p.y * m.ub[1] + p.z * m.ub[2] - m.u0) * m.inv_cell;
+                const float fv = (p.x * m.vb[0] + p.y * m.vb[1] + p.z * m.vb[2] - m.v0) * m.inv_cell;
+                if (fu >= 0.0f && fv >= 0.0f && fu < (float)m.R && fv < (float)m.R) {
+                    const int slot = __ldg(m.cells + (size_t)(int)fv * m.R + (int)fu);
+                    if (slot >= 0) {
+                        const float4* pr = acc.nodes8 != nullptr ? acc.prims8 : acc.prims;
+                        v(pr + (size_t)slot * kTriWords, tmax);
+                        if (v.opaque) settled = true;
+                        else acc.shadow_begin(p, wray, self, tmin, 0.0f, false, v);
+                    }
+                }
+            }
         } else {
             wray = vnorm(vsub(ld3(l0), p));                                      // 921
             const V3 dp = vsub(p, ld3(l0));
@@ -336,8 +358,9 @@ struct ShadowJob {
         p = mk3(hp.x, hp.y, hp.z);
         self = __float_as_int(hp.w);
         setup(wo, wray, tmin, tmax);
-        return true;
+        return !settled;
     }
+    RT_DEV bool walk_needed() const { return !settled; }
     RT_DEV float visit(const float4* w, float tmax) { return v(w, tmax); }
 
     RT_DEV void adopt(int src, bool take, V3& wo, V3& wray)
@@ -386,7 +409,7 @@ struct ShadowJob {
     {
         if (!fin) return;
         acc.shadow_end(v);
-        if (kCount) walks++;
+        if (kCount) { if (settled) map_hits++; else walks++; }
         if (v.overflowed && !v.opaque) {
             // more transparent occluders than the visitor holds: the whole chain of this node is
             // redone exactly by bvh_shadow_redo_kernel; this lane drops it
@@ -427,9 +450,9 @@ __global__ void __launch_bounds__(kWalkBlock, kCount ? 0 : RT_SHADOW_MIN_BLOCKS)
                         kCount ? &P.counters->clock[1][first] : nullptr);
     flush_bvh_counters(acc, P.counters, true);
     if (kCount) {
-        unsigned long long w = job.walks;
-        for (int o = 16; o > 0; o >>= 1) w += __shfl_down_sync(0xffffffffu, w, o);
-        if ((threadIdx.x & 31) == 0) atomicAdd(&P.counters->shadow_walks, w);
+        unsigned long long w = job.walks, mh = job.map_hits;
+        for (int o = 16; o > 0; o >>= 1) { w += __shfl_down_sync(0xffffffffu, w, o); mh += __shfl_down_sync(0xffffffffu, mh, o); }
+        if ((threadIdx.x & 31) == 0) { atomicAdd(&P.counters->shadow_walks, w); atomicAdd(&P.counters->shadow_map_hits, mh); }
     }
 }
 
