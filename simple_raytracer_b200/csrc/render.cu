@@ -85,7 +85,7 @@ static size_t slot_bytes(int level, bool bvh, int nl)
 {
     // level 0 has no ray queue (primary rays are generated in place)
     size_t per_slot = (level == 0 ? 0 : 4 * 16) + 3 * 16 + 8;
-    if (bvh) per_slot += 2 * 16 + 4 + (size_t)nl * 4;    // hp, hb, node_list, sh (wavefront_bvh.cuh)
+    if (bvh) per_slot += 2 * 16 + 4 + 4 + (size_t)nl * 4;    // hp, hb, node_list, walk_list, sh (wavefront_bvh.cuh)
     return per_slot;
 }
 
@@ -274,7 +274,8 @@ static void fill_levels(const SceneHost* s, int max_depth, bool bvh, int K, int 
         L.nr_c = (int2*)base;   base += cap * 8;
         if (bvh) {
             L.sh = (float*)base;  base += cap * 4 * (size_t)s->nl;
-            L.node_list = (int*)base;
+            L.node_list = (int*)base; base += cap * 4;
+            L.walk_list = (int*)base;
         }
     }
 }
@@ -301,6 +302,8 @@ static void launch_trace(const FrameParams& P, int level, bool sharing, int grid
 template <bool kCount>
 static void launch_shadow(const FrameParams& P, int first, int last, bool sharing, int grid, cudaStream_t st)
 {
+    // light 0's occluder map first: what it settles never enters the walk kernel
+    if (P.settled_first) bvh_shadow_settle_kernel<kCount><<<std::max(1, std::min(grid, 148 * 16)), 256, 0, st>>>(P, first, last);
     if (sharing) bvh_shadow_kernel<kCount, true><<<grid, kWalkBlock, 0, st>>>(P, first, last);
     else bvh_shadow_kernel<kCount, false><<<grid, kWalkBlock, 0, st>>>(P, first, last);
     // the chains it gave up (a handful at most): a few blocks that find the list empty otherwise
@@ -359,6 +362,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         P.refill_lanes = T.refill_lanes; P.inner_min_lanes = T.inner_min_lanes; P.leaf_min_lanes = T.leaf_min_lanes;
         P.sh_refill_lanes = T.sh_refill_lanes; P.sh_inner_min_lanes = T.sh_inner_min_lanes; P.sh_leaf_min_lanes = T.sh_leaf_min_lanes;
         P.redo_list = lbvh ? s->ws.redo_list.as<unsigned>() + (size_t)j * kRedoCapacity : nullptr;
+        P.settled_first = (lbvh && P.scene.smap[0].cells != nullptr) ? 1 : 0;
     }
 
     ChainStreams& cs = s->ws.chains;
@@ -411,7 +415,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                     const int sh_grid = persistent_grid(work * s->nl, sms, T.grid_mult, kWalkBlock);
                     if (count) launch_shadow<true>(P, l, l, sharing, sh_grid, stream);
                     else launch_shadow<false>(P, l, l, sharing, sh_grid, stream);
-                    n += 2;
+                    n += 2 + P.settled_first;
                 }
                 RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
                 bvh_colour_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l, l);
@@ -440,7 +444,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                     const int sh_grid = persistent_grid(all_work * s->nl, sms, T.grid_mult, kWalkBlock);
                     if (count) launch_shadow<true>(P, 0, D, sharing, sh_grid, side);
                     else launch_shadow<false>(P, 0, D, sharing, sh_grid, side);
-                    n += 2;
+                    n += 2 + P.settled_first;
                 }
                 if (chain_pixels <= 1000LL * T.colour_merge_max_kpixels) {
                     bvh_colour_kernel<<<persistent_grid(all_work, sms, T.grid_mult), kBlock, 0, side>>>(P, 0, D);

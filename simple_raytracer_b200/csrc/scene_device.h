@@ -122,6 +122,8 @@ struct LevelBuffers {
     float4* hp;     // hit point.xyz, as_float(object order); w = as_float(-1) for a slot without a hit
     float4* hb;     // b, g, t, 0
     int*    node_list;
+    int*    walk_list;  // the nodes (indices into node_list) whose shadow chain has to be walked: all of them, or those
+                        // bvh_shadow_settle_kernel could not settle with light 0's occluder map
     float*  sh;
     int capacity;
 };
@@ -154,6 +156,7 @@ struct Counters {
     unsigned int redo_count;              // entries of FrameParams::redo_list ((generation << 28) | node index)
     unsigned int fetch_trace[kMaxLevels];   // LBVH pipeline: next job of the persistent trace / shadow kernels
     unsigned int fetch_shadow[kMaxLevels];
+    unsigned int walk_nodes[kMaxLevels];    // entries of LevelBuffers::walk_list
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
     unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out
@@ -184,6 +187,8 @@ struct FrameParams {
     // Shadow chains the any-hit kernel could not finish exactly (more than BvhAccelT::kMaxPartial
     // transparent occluders on one ray): redone by bvh_shadow_redo_kernel.  kRedoCapacity entries.
     unsigned int* redo_list;
+    int settled_first;    // the any-hit kernel's jobs come from the walk lists (bvh_shadow_settle_kernel ran): light 0 is
+                          // not looked up in its occluder map again
 };
 
 }  // namespace rt

@@ -290,6 +290,72 @@ __global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_spawn_kernel(
 // One launch covers the nodes of generations first .. last (the frame scheduler passes all of
 // them at once: one kernel tail per frame instead of one per generation): job j counts through
 // generation `first`'s node list, then the next one's, ...
+// The occluder map's guess for the shadow ray (p, ray) of directional light li (scene_device.h: ShadowMapView): the
+// reference's own test of this ray against the opaque primitive that covers the ray's cell nearest to the light.
+// Accepted (-> true, v.opaque set): the product is exactly 0 whatever else the ray meets (every factor lies in
+// [0,1]), no walk.  Not accepted: the attempt is forgotten (v as shadow_begin left it) and the ray has to be walked.
+template <bool kCount>
+RT_DEV bool occluder_map_settles(const FrameParams& P, const BvhAccelT<kCount>& acc, int li, V3 p, V3 ray, int self,
+                                 typename BvhAccelT<kCount>::ShadowVisit& v)
+{
+    if (li >= kMaxShadowMaps || P.scene.smap[li].cells == nullptr) return false;
+    const ShadowMapView& m = P.scene.smap[li];
+    const float fu = (p.x * m.ub[0] + p.y * m.ub[1] + p.z * m.ub[2] - m.u0) * m.inv_cell;
+    const float fv = (p.x * m.vb[0] + p.y * m.vb[1] + p.z * m.vb[2] - m.v0) * m.inv_cell;
+    if (!(fu >= 0.0f && fv >= 0.0f && fu < (float)m.R && fv < (float)m.R)) return false;
+    const int slot = __ldg(m.cells + (size_t)(int)fv * m.R + (int)fu);
+    if (slot < 0) return false;
+    const float4* pr = acc.nodes8 != nullptr ? acc.prims8 : acc.prims;
+    v(pr + (size_t)slot * kTriWords, 3.402823466e+38f);
+    if (v.opaque) return true;
+    acc.shadow_begin(p, ray, self, P.epsilon, 0.0f, false, v);
+    return false;
+}
+
+// Before the any-hit walks of a chain's nodes: one thread per node tries light 0's occluder map.  Settled nodes get
+// their record (the carried product after light 0 is 0: the chain ends there) and never enter the persistent walk
+// kernel; the others are listed (LevelBuffers::walk_list) as that kernel's jobs.  Launched only when light 0 has a map.
+template <bool kCount>
+__global__ void __launch_bounds__(256) bvh_shadow_settle_kernel(const __grid_constant__ FrameParams P, int first, int last)
+{
+    auto acc = make_bvh_accel<kCount>(P.scene);
+    const float4 l0 = P.scene.light[0];
+    const V3 ray = vneg(ld3(l0));                                            // 895: un-normalised ray
+    unsigned long long hits = 0;
+    for (int level = first; level <= last; level++) {
+        const LevelBuffers& LB = P.level[level];
+        const unsigned n = P.counters->nodes[level];
+        const unsigned rounded = (n + 31u) & ~31u;
+        for (unsigned k = blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += gridDim.x * blockDim.x) {
+            bool walk = false;
+            if (k < n) {
+                const float4 hp = LB.hp[LB.node_list[k]];
+                const V3 p = mk3(hp.x, hp.y, hp.z);
+                const int self = __float_as_int(hp.w);
+                typename BvhAccelT<kCount>::ShadowVisit v;
+                acc.shadow_begin(p, ray, self, P.epsilon, 0.0f, false, v);
+                if (occluder_map_settles(P, acc, 0, p, ray, self, v)) {
+                    LB.sh[k] = clamp01(fmul(0.0f, 1.0f));                    // 909 with shadow_mask == 1 (788)
+                    if (kCount) hits++;
+                } else {
+                    walk = true;
+                }
+            }
+            const unsigned wm = __ballot_sync(0xffffffffu, walk);
+            if (wm) {
+                unsigned base = 0;
+                if ((threadIdx.x & 31) == 0) base = atomicAdd(&P.counters->walk_nodes[level], (unsigned)__popc(wm));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (walk) LB.walk_list[base + __popc(wm & lanemask_lt())] = (int)k;
+            }
+        }
+    }
+    if (kCount) {
+        for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xffffffffu, hits, o);
+        if ((threadIdx.x & 31) == 0 && hits) atomicAdd(&P.counters->shadow_map_hits, hits);
+    }
+}
+
 template <bool kCount, bool kStealing>
 struct ShadowJob {
     // One light's walk is a fold in any order too: "an opaque occluder exists" is an OR and the
@@ -322,24 +388,7 @@ struct ShadowJob {
             wray = vneg(ld3(l0));                                                // 895: un-normalised ray
             tmax = 3.402823466e+38f;
             acc.shadow_begin(p, wray, self, tmin, 0.0f, false, v);
-            // the occluder map's guess (scene_device.h: ShadowMapView): the reference's own test of this ray against
-            // the opaque primitive that covers the ray's cell nearest to the light.  Accepted: the product is
-            // exactly 0 whatever else the ray meets (every factor lies in [0,1]), no walk.  Not accepted: forget
-            // the attempt and walk.
-            if (li < kMaxShadowMaps && P.scene.smap[li].cells != nullptr) {
-                const ShadowMapView& m = P.scene.smap[li];
-                const float fu = (p.x * m.ub[0] + p.y * m.ub[1] + p.z * m.ub[2] - m.u0) * m.inv_cell;
-                const float fv = (p.x * m.vb[0] + p.y * m.vb[1] + p.z * m.vb[2] - m.v0) * m.inv_cell;
-                if (fu >= 0.0f && fv >= 0.0f && fu < (float)m.R && fv < (float)m.R) {
-                    const int slot = __ldg(m.cells + (size_t)(int)fv * m.R + (int)fu);
-                    if (slot >= 0) {
-                        const float4* pr = acc.nodes8 != nullptr ? acc.prims8 : acc.prims;
-                        v(pr + (size_t)slot * kTriWords, tmax);
-                        if (v.opaque) settled = true;
-                        else acc.shadow_begin(p, wray, self, tmin, 0.0f, false, v);
-                    }
-                }
-            }
+            if (!(li == 0 && P.settled_first)) settled = occluder_map_settles(P, acc, li, p, wray, self, v);
         } else {
             wray = vnorm(vsub(ld3(l0), p));                                      // 921
             const V3 dp = vsub(p, ld3(l0));
@@ -352,8 +401,15 @@ struct ShadowJob {
     {
         k = j; li = 0; mask = 1.0f;                                              // 788
         level = first;
-        n_nodes = P.counters->nodes[level];
-        while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
+        if (P.settled_first) {
+            unsigned n_walk = P.counters->walk_nodes[level];
+            while (k >= n_walk) { k -= n_walk; level++; n_walk = P.counters->walk_nodes[level]; }
+            k = (unsigned)P.level[level].walk_list[k];
+            n_nodes = P.counters->nodes[level];
+        } else {
+            n_nodes = P.counters->nodes[level];
+            while (k >= n_nodes) { k -= n_nodes; level++; n_nodes = P.counters->nodes[level]; }
+        }
         const float4 hp = P.level[level].hp[P.level[level].node_list[k]];
         p = mk3(hp.x, hp.y, hp.z);
         self = __float_as_int(hp.w);
@@ -444,7 +500,7 @@ __global__ void __launch_bounds__(kWalkBlock, kCount ? 0 : RT_SHADOW_MIN_BLOCKS)
     auto acc = make_bvh_accel<kCount>(P.scene);
     acc.overflow_flag = &P.counters->overflow;
     unsigned n_jobs = 0;
-    for (int l = first; l <= last; l++) n_jobs += P.counters->nodes[l];
+    for (int l = first; l <= last; l++) n_jobs += P.settled_first ? P.counters->walk_nodes[l] : P.counters->nodes[l];
     Job job{ P, acc, first };
     acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[first], job, P.sh_refill_lanes, P.sh_inner_min_lanes, P.sh_leaf_min_lanes,
                         kCount ? &P.counters->clock[1][first] : nullptr);
