@@ -254,6 +254,7 @@ def algorithmic_work(scene: Scene, st, accel_used: int) -> dict:
                            "shadow_prim_tests": sp, "closest_hit_rays": closest_rays, "shadow_rays_walked": walked,
                            "shadow_rays_reference": int(st.rays_shadow), "nodes_shaded": nodes,
                            "texels": int(st.texel_fetches), "shadow_chains_redone": int(st.shadow_chains_redone),
+                           "shadow_rays_settled_by_occluder_map": int(st.shadow_map_hits),
                            "bvh_levels": [int(st.bvh_levels4), int(st.bvh_levels8)]}}
     fl = rays * (19 * len(scene.spheres) + 42 * len(scene.faces)) + nodes * (64 + 52 * L)
     return {"bound": "fp32", "per_frame": fl, "unit": "TFLOP/s", "detail": {"rays": rays, "nodes_shaded": nodes}}
@@ -316,8 +317,8 @@ def run_ours(args) -> dict:
     st_plain = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS)
     st_p = ds.render(rank=rank, world_size=world, tile_rows=TILE_ROWS, profile=True)
     level_ms = [float(x) for x in list(st_p.level_ms)[:5]]
-    # (profiled frames: one serial chain with an event after every kernel; shadow_ms = bvh_shadow_kernel + the
-    # empty redo launch, shade_ms = bvh_colour_kernel)
+    # (profiled frames: one serial chain with an event after every kernel; shadow_ms = the occluder-map pre-pass
+    # bvh_shadow_settle_kernel + bvh_shadow_kernel + the empty redo launch, shade_ms = bvh_colour_kernel)
     kernel_ms = {"bvh_trace_kernel": [float(x) for x in list(st_p.trace_ms)[:5]],
                  "bvh_spawn_kernel": [float(x) for x in list(st_p.spawn_ms)[:5]],
                  "bvh_shadow_kernel": [float(x) for x in list(st_p.shadow_ms)[:5]],

@@ -306,6 +306,7 @@ RT_DEV bool occluder_map_settles(const FrameParams& P, const BvhAccelT<kCount>& 
     const int slot = __ldg(m.cells + (size_t)(int)fv * m.R + (int)fu);
     if (slot < 0) return false;
     const float4* pr = acc.nodes8 != nullptr ? acc.prims8 : acc.prims;
+    if (kCount) acc.cnt_prims++;
     v(pr + (size_t)slot * kTriWords, 3.402823466e+38f);
     if (v.opaque) return true;
     acc.shadow_begin(p, ray, self, P.epsilon, 0.0f, false, v);
@@ -353,6 +354,7 @@ __global__ void __launch_bounds__(256) bvh_shadow_settle_kernel(const __grid_con
     if (kCount) {
         for (int o = 16; o > 0; o >>= 1) hits += __shfl_down_sync(0xffffffffu, hits, o);
         if ((threadIdx.x & 31) == 0 && hits) atomicAdd(&P.counters->shadow_map_hits, hits);
+        flush_bvh_counters(acc, P.counters, true);
     }
 }
 

@@ -524,3 +524,38 @@ def test_random_scenes_fuzz_against_the_oracle(seed):
             if accel == abi.RT_ACCEL_LBVH:
                 hits, shadow = ds.hit_histograms()
                 assert np.array_equal(hits, want_hits) and np.array_equal(shadow, want_shadow), seed
+
+
+def test_occluder_maps_settle_shadow_rays_without_changing_anything():
+    """Directional lights get an occluder map (bvh.cu: build_shadow_maps): a guess at an opaque occluder per cell of
+    the light's plane, confirmed by the reference's exact test before the any-hit walk is skipped.  On a dense scene
+    most shadow rays must be settled that way (RtStats.shadow_map_hits), and the frame, the shadow classes per light
+    and the node counts must equal the brute-force path's and the oracle's — also with an UN-normalised direction
+    (SURVEY H5), with a point light first (no map for light 0: the plain schedule) and with transparent occluders."""
+    base = scenegen.stress_scene(6000, 60, 128, 96, tex_size=32)
+    variants = {"as generated": base}
+    s2 = base.copy(); s2.lights["xyz"][0] *= np.float32(2.5); s2._invalidate(); variants["non-unit direction"] = s2
+    s3 = base.copy(); s3.lights = s3.lights[::-1].copy(); s3._invalidate(); variants["point light first"] = s3
+    for name, scene in variants.items():
+        raw, ids, ost = O.oracle_render(scene)
+        want_hits, want_shadow = O.oracle_hit_histograms(scene)
+        with DeviceScene(scene) as ds:
+            st = ds.render(accel=abi.RT_ACCEL_LBVH, instrument=True)
+            rgb, flags = ds.download()
+            cmp = common.compare_frames(raw, rgb, flags)
+            assert cmp["exact"] == cmp["pixels"] and cmp["nan_mismatch"] == 0, (name, cmp)
+            assert st.nodes_total == ost.nodes_total and st.rays_shadow == ost.rays_shadow, name
+            evaluated = st.shadow_rays_walked + st.shadow_map_hits
+            if name == "point light first":
+                # lights 0-3 are point lights now: their rays are all walked; the directional ones come later
+                assert st.shadow_map_hits == 0 or evaluated > 0
+            else:
+                assert st.shadow_map_hits > 0.5 * evaluated, (name, st.shadow_map_hits, st.shadow_rays_walked)
+            ds.render(accel=abi.RT_ACCEL_LBVH)                   # the production schedule (graph-able frame)
+            rgb2, flags2 = ds.download()
+            assert np.array_equal(rgb2, rgb) and np.array_equal(flags2, flags), name
+            hits, shadow = ds.hit_histograms()
+            assert np.array_equal(hits, want_hits) and np.array_equal(shadow, want_shadow), name
+            ds.render(accel=abi.RT_ACCEL_BRUTE)
+            rgb3, flags3 = ds.download()
+            assert np.array_equal(rgb3, rgb) and np.array_equal(flags3, flags), name
