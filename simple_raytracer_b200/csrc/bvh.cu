@@ -550,17 +550,20 @@ __global__ void collapse8_kernel(int n_prims, int nf, int level, unsigned* __res
     (void)n_prims;
 }
 
-// ---- occluder maps of directional lights (scene_device.h: ShadowMapView) -----------------------------------
+// ---- occluder maps (scene_device.h: ShadowMapView) ------------------------------------------------------------
 //
-// An orthographic id buffer seen from the light: one thread per primitive slot of the array the any-hit walk
-// reads rasterises an OPAQUE primitive (shadow factor 1 - opacity == 0) over the cells whose centres it covers and
-// keeps, per cell, the one nearest to the light (64-bit atomicMin on depth | slot).  Plain float arithmetic: the
-// map is a guess that the exact test confirms or not.  Primitives covering more than kSmapThreadCells cells go
-// to a list that a second kernel rasterises one block per primitive.
+// An id buffer seen from the light — orthographic for a directional light, the six 90-degree faces of a cube around
+// a point light: one thread per primitive slot of the array the any-hit walk reads rasterises an OPAQUE primitive
+// (shadow factor 1 - opacity == 0) over the cells whose centres it covers and keeps, per cell, the one nearest to
+// the light (64-bit atomicMin on depth | slot).  Plain float arithmetic: the map is a guess that the exact test
+// confirms or not, so a triangle that reaches behind a cube face's plane is simply left out of that face.
+// Primitives covering more than kSmapThreadCells cells go to a list that a second kernel rasterises one block each.
 struct SmapBuild {
-    float dir[3], ub[3], vb[3];
+    float dir[3], ub[3], vb[3];          // directional: light travel direction, basis of its plane
     float u0, v0, inv_cell, cell;
+    float origin[3];                     // point: position
     int R;
+    int cube;
 };
 constexpr int kSmapThreadCells = 1024;
 
@@ -571,44 +574,85 @@ RT_DEV unsigned long long smap_key(float depth, int slot)
     return ((unsigned long long)b << 32) | (unsigned)slot;
 }
 
+// A primitive as one view (the light's plane, or one cube face) sees it, in cell units (cell i has its centre at i + 0.5).
 struct SmapPrim {
     bool ok, is_tri;
-    float x[3], y[3], d[3];      // triangle: vertices in cell units, depth along the light; sphere: [0] = centre
-    float r;                     // sphere radius (world units)
+    float x[3], y[3], d[3];      // triangle: projected vertices, and what orders hits along a cell's ray (below)
+    float c[3], r;               // sphere: centre in the view's frame (x, y, depth axis), radius, world units
+    float pl[4];                 // point light, triangle: plane n . q = pl[3] in the face's frame (q relative to the light)
     int x0, y0, wx, wy;          // the cells whose centres its bounding box holds
 };
 
-RT_DEV SmapPrim smap_setup(const float4* w, const SmapBuild& m)
+// view: -1 = the directional light's plane, 0..5 = cube face (axis = view / 2, negative side if view & 1)
+RT_DEV SmapPrim smap_setup(const float4* w, const SmapBuild& m, int view)
 {
     SmapPrim q;
     q.ok = false;
     const float4 w4 = w[4];
     if (w4.y != 0.0f) return q;                                  // not opaque (or NaN)
     q.is_tri = __float_as_int(w4.w) == 0;
+    const float R = (float)m.R;
     float lo_x, hi_x, lo_y, hi_y;
-    if (q.is_tri) {
-        const float4 v0 = w[1], e1 = w[2], e2 = w[3];
-        const float p[3][3] = { { v0.x, v0.y, v0.z }, { v0.x + e1.x, v0.y + e1.y, v0.z + e1.z }, { v0.x + e2.x, v0.y + e2.y, v0.z + e2.z } };
-        for (int k = 0; k < 3; k++) {
-            q.x[k] = (p[k][0] * m.ub[0] + p[k][1] * m.ub[1] + p[k][2] * m.ub[2] - m.u0) * m.inv_cell;
-            q.y[k] = (p[k][0] * m.vb[0] + p[k][1] * m.vb[1] + p[k][2] * m.vb[2] - m.v0) * m.inv_cell;
-            q.d[k] = p[k][0] * m.dir[0] + p[k][1] * m.dir[1] + p[k][2] * m.dir[2];
+    if (view < 0) {
+        if (q.is_tri) {
+            const float4 v0 = w[1], e1 = w[2], e2 = w[3];
+            const float p[3][3] = { { v0.x, v0.y, v0.z }, { v0.x + e1.x, v0.y + e1.y, v0.z + e1.z }, { v0.x + e2.x, v0.y + e2.y, v0.z + e2.z } };
+            for (int k = 0; k < 3; k++) {
+                q.x[k] = (p[k][0] * m.ub[0] + p[k][1] * m.ub[1] + p[k][2] * m.ub[2] - m.u0) * m.inv_cell;
+                q.y[k] = (p[k][0] * m.vb[0] + p[k][1] * m.vb[1] + p[k][2] * m.vb[2] - m.v0) * m.inv_cell;
+                q.d[k] = p[k][0] * m.dir[0] + p[k][1] * m.dir[1] + p[k][2] * m.dir[2];
+            }
+        } else {
+            const float4 c = w[0];
+            q.x[0] = (c.x * m.ub[0] + c.y * m.ub[1] + c.z * m.ub[2] - m.u0) * m.inv_cell;
+            q.y[0] = (c.x * m.vb[0] + c.y * m.vb[1] + c.z * m.vb[2] - m.v0) * m.inv_cell;
+            q.d[0] = c.x * m.dir[0] + c.y * m.dir[1] + c.z * m.dir[2];
+            q.r = fabsf(c.w);
+            const float rc = q.r * m.inv_cell;
+            q.x[1] = q.x[0] - rc; q.x[2] = q.x[0] + rc; q.y[1] = q.y[0] - rc; q.y[2] = q.y[0] + rc;
         }
+    } else {
+        // the face's frame: z = the face's axis (pointing away from the light), x / y the other two axes; a point
+        // (x, y, z) projects to (x / z, y / z) in [-1, 1]^2, cell coordinate (x / z + 1) * R / 2
+        const int az = view >> 1, ax = (az + 1) % 3, ay = (az + 2) % 3;
+        const float sgn = (view & 1) ? -1.0f : 1.0f;
+        const float half = 0.5f * R;
+        if (q.is_tri) {
+            const float4 v0 = w[1], e1 = w[2], e2 = w[3];
+            const float p[3][3] = { { v0.x, v0.y, v0.z }, { v0.x + e1.x, v0.y + e1.y, v0.z + e1.z }, { v0.x + e2.x, v0.y + e2.y, v0.z + e2.z } };
+            float f[3][3];
+            for (int k = 0; k < 3; k++) {
+                f[k][0] = p[k][ax] - m.origin[ax]; f[k][1] = p[k][ay] - m.origin[ay]; f[k][2] = sgn * (p[k][az] - m.origin[az]);
+                if (!(f[k][2] > 1.0e-6f * (fabsf(f[k][0]) + fabsf(f[k][1])) && f[k][2] > 0.0f)) return q;   // reaches behind the face's plane
+                q.x[k] = (f[k][0] / f[k][2] + 1.0f) * half;
+                q.y[k] = (f[k][1] / f[k][2] + 1.0f) * half;
+            }
+            // plane through the three points (light at the origin): a cell's ray (cx, cy, 1) * t meets it at
+            // t = pl[3] / (n . (cx, cy, 1)); t orders the hits along that ray
+            const float a[3] = { f[1][0] - f[0][0], f[1][1] - f[0][1], f[1][2] - f[0][2] };
+            const float b[3] = { f[2][0] - f[0][0], f[2][1] - f[0][1], f[2][2] - f[0][2] };
+            q.pl[0] = a[1] * b[2] - a[2] * b[1]; q.pl[1] = a[2] * b[0] - a[0] * b[2]; q.pl[2] = a[0] * b[1] - a[1] * b[0];
+            q.pl[3] = q.pl[0] * f[0][0] + q.pl[1] * f[0][1] + q.pl[2] * f[0][2];
+        } else {
+            const float4 c = w[0];
+            const float cc[3] = { c.x, c.y, c.z };
+            q.c[0] = cc[ax] - m.origin[ax]; q.c[1] = cc[ay] - m.origin[ay]; q.c[2] = sgn * (cc[az] - m.origin[az]);
+            q.r = fabsf(c.w);
+            const float zn = q.c[2] - q.r, zf = q.c[2] + q.r;
+            if (!(zn > 1.0e-6f * (fabsf(q.c[0]) + fabsf(q.c[1]) + q.r) && zn > 0.0f)) return q;            // too close to the face's plane
+            // bounds of x / z over the sphere's bounding box (z in [zn, zf], both positive)
+            const float xl = q.c[0] - q.r, xh = q.c[0] + q.r, yl = q.c[1] - q.r, yh = q.c[1] + q.r;
+            q.x[1] = (fminf(xl / zn, xl / zf) + 1.0f) * half; q.x[2] = (fmaxf(xh / zn, xh / zf) + 1.0f) * half;
+            q.y[1] = (fminf(yl / zn, yl / zf) + 1.0f) * half; q.y[2] = (fmaxf(yh / zn, yh / zf) + 1.0f) * half;
+        }
+    }
+    if (q.is_tri) {
         lo_x = fminf(q.x[0], fminf(q.x[1], q.x[2])); hi_x = fmaxf(q.x[0], fmaxf(q.x[1], q.x[2]));
         lo_y = fminf(q.y[0], fminf(q.y[1], q.y[2])); hi_y = fmaxf(q.y[0], fmaxf(q.y[1], q.y[2]));
-        q.r = 0.0f;
     } else {
-        const float4 c = w[0];
-        q.x[0] = (c.x * m.ub[0] + c.y * m.ub[1] + c.z * m.ub[2] - m.u0) * m.inv_cell;
-        q.y[0] = (c.x * m.vb[0] + c.y * m.vb[1] + c.z * m.vb[2] - m.v0) * m.inv_cell;
-        q.d[0] = c.x * m.dir[0] + c.y * m.dir[1] + c.z * m.dir[2];
-        q.r = fabsf(c.w);
-        const float rc = q.r * m.inv_cell;
-        lo_x = q.x[0] - rc; hi_x = q.x[0] + rc; lo_y = q.y[0] - rc; hi_y = q.y[0] + rc;
+        lo_x = q.x[1]; hi_x = q.x[2]; lo_y = q.y[1]; hi_y = q.y[2];
     }
     if (!(isfinite(lo_x) && isfinite(hi_x) && isfinite(lo_y) && isfinite(hi_y))) return q;
-    // cell i has its centre at i + 0.5
-    const float R = (float)m.R;
     const int x0 = (int)fmaxf(ceilf(lo_x - 0.5f), 0.0f), x1 = (int)fminf(floorf(hi_x - 0.5f), R - 1.0f);
     const int y0 = (int)fmaxf(ceilf(lo_y - 0.5f), 0.0f), y1 = (int)fminf(floorf(hi_y - 0.5f), R - 1.0f);
     if (x1 < x0 || y1 < y0) return q;
@@ -617,7 +661,7 @@ RT_DEV SmapPrim smap_setup(const float4* w, const SmapBuild& m)
     return q;
 }
 
-RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, unsigned long long* cells, int start, int stride)
+RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int view, unsigned long long* cells, int start, int stride)
 {
     const int total = q.wx * q.wy;
     float den = 0.0f;
@@ -625,24 +669,37 @@ RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, unsigne
         den = (q.x[1] - q.x[0]) * (q.y[2] - q.y[0]) - (q.x[2] - q.x[0]) * (q.y[1] - q.y[0]);
         if (!(fabsf(den) > 1.0e-12f)) return;                   // edge-on
     }
+    unsigned long long* face = cells + (view < 0 ? 0 : (size_t)view * m.R * m.R);
+    const float to_dir = 2.0f / (float)m.R;
     for (int i = start; i < total; i += stride) {
         const int ix = q.x0 + i % q.wx, iy = q.y0 + i / q.wx;
         const float cx = (float)ix + 0.5f, cy = (float)iy + 0.5f;
         float depth;
         if (q.is_tri) {
+            // (a projective map keeps lines straight: inside the projected triangle <=> the cell's ray hits it)
             const float b1 = ((cx - q.x[0]) * (q.y[2] - q.y[0]) - (q.x[2] - q.x[0]) * (cy - q.y[0])) / den;
             const float b2 = ((q.x[1] - q.x[0]) * (cy - q.y[0]) - (cx - q.x[0]) * (q.y[1] - q.y[0])) / den;
             const float b0 = 1.0f - b1 - b2;
             if (!(b0 >= 0.0f && b1 >= 0.0f && b2 >= 0.0f)) continue;
-            depth = b0 * q.d[0] + b1 * q.d[1] + b2 * q.d[2];
-        } else {
+            if (view < 0) depth = b0 * q.d[0] + b1 * q.d[1] + b2 * q.d[2];
+            else depth = q.pl[3] / (q.pl[0] * (cx * to_dir - 1.0f) + q.pl[1] * (cy * to_dir - 1.0f) + q.pl[2]);
+        } else if (view < 0) {
             const float dx = (cx - q.x[0]) * m.cell, dy = (cy - q.y[0]) * m.cell;
             const float h2 = q.r * q.r - (dx * dx + dy * dy);
             if (!(h2 >= 0.0f)) continue;
             depth = q.d[0] - sqrtf(h2);
+        } else {
+            // ray (dx, dy, 1) * t against the sphere: the nearer root
+            const float dx = cx * to_dir - 1.0f, dy = cy * to_dir - 1.0f;
+            const float dd = dx * dx + dy * dy + 1.0f;
+            const float bq = dx * q.c[0] + dy * q.c[1] + q.c[2];
+            const float cq = q.c[0] * q.c[0] + q.c[1] * q.c[1] + q.c[2] * q.c[2] - q.r * q.r;
+            const float disc = bq * bq - dd * cq;
+            if (!(disc >= 0.0f)) continue;
+            depth = (bq - sqrtf(disc)) / dd;
         }
-        if (!isfinite(depth)) continue;
-        atomicMin(cells + (size_t)iy * m.R + ix, smap_key(depth, slot));
+        if (!(isfinite(depth)) || (view >= 0 && !(depth > 0.0f))) continue;
+        atomicMin(face + (size_t)iy * m.R + ix, smap_key(depth, slot));
     }
 }
 
@@ -651,10 +708,12 @@ __global__ void smap_prims_kernel(const float4* __restrict__ prims, int n, SmapB
 {
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     if (slot >= n) return;
-    const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m);
-    if (!q.ok) return;
-    if ((long long)q.wx * q.wy > kSmapThreadCells) { big[atomicAdd(n_big, 1u)] = slot; return; }
-    smap_raster(q, slot, m, cells, 0, 1);
+    for (int view = m.cube ? 0 : -1; view < (m.cube ? 6 : 0); view++) {
+        const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m, view);
+        if (!q.ok) continue;
+        if ((long long)q.wx * q.wy > kSmapThreadCells) { big[atomicAdd(n_big, 1u)] = slot * 8 + (view + 1); continue; }
+        smap_raster(q, slot, m, view, cells, 0, 1);
+    }
 }
 
 __global__ void smap_big_kernel(const float4* __restrict__ prims, SmapBuild m, unsigned long long* __restrict__ cells,
@@ -662,28 +721,27 @@ __global__ void smap_big_kernel(const float4* __restrict__ prims, SmapBuild m, u
 {
     const unsigned n = *n_big;
     for (unsigned b = blockIdx.x; b < n; b += gridDim.x) {
-        const int slot = big[b];
-        const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m);
-        if (q.ok) smap_raster(q, slot, m, cells, (int)threadIdx.x, (int)blockDim.x);
+        const int slot = big[b] >> 3, view = (big[b] & 7) - 1;
+        const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m, view);
+        if (q.ok) smap_raster(q, slot, m, view, cells, (int)threadIdx.x, (int)blockDim.x);
     }
 }
 
-__global__ void smap_finish_kernel(const unsigned long long* __restrict__ cells, int n_cells, int* __restrict__ out)
+__global__ void smap_finish_kernel(const unsigned long long* __restrict__ cells, size_t n_cells, int* __restrict__ out)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_cells) return;
     const unsigned long long k = cells[i];
     out[i] = k == ~0ull ? -1 : (int)(unsigned)(k & 0xffffffffull);
 }
 
-// Maps for the directional ones among the first kMaxShadowMaps lights, over the primitive array the any-hit walk
-// reads (prims: n records of kTriWords words).  Lights whose direction is not finite, and scenes without finite
-// bounds, get none.
+// Maps for the first kMaxShadowMaps lights, over the primitive array the any-hit walk reads (prims: n records of
+// kTriWords words).  Lights whose direction / position is not finite, and scenes without finite bounds, get none.
 static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const BuildBounds& bb, cudaStream_t st)
 {
     for (int k = 0; k < kMaxShadowMaps; k++) s->smap[k] = SceneHost::SmapHost();
     const int nl = std::min(s->nl, kMaxShadowMaps);
-    if (nl <= 0 || n <= 0) return RT_OK;
+    if (nl <= 0 || n <= 0 || n >= (1 << 28)) return RT_OK;
     for (int c = 0; c < 3; c++) if (!std::isfinite(bb.lo[c]) || !std::isfinite(bb.hi[c])) return RT_OK;
     float4 lights[kMaxShadowMaps * 3];
     RT_CUDA(cudaMemcpyAsync(lights, s->light.p, (size_t)nl * 3 * sizeof(float4), cudaMemcpyDeviceToHost, st));
@@ -692,7 +750,7 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
     // the typical primitive, so that a point in a cell is usually behind the primitive that covers the cell's centre.
     // Measured on the 1 M-triangle stress scene at 4K (tools/r2_job18.sh): shadow rays left to walk 7.7 / 4.9 / 3.3 /
     // 2.4 M of 23 M with 1024 / 2048 / 4096 / 8192 cells per axis, frame 31.1 / 29.4 / 28.4 / 27.9 ms; 8192 costs
-    // 12 ms more to build (four maps of 268 MB), 4096 nothing measurable.
+    // 12 ms more to build (four maps of 268 MB), 4096 nothing measurable.  A cube face gets half of that per axis.
     int R = 64;
     double per_sqrt = 4.0;
     int r_max = 4096;
@@ -701,60 +759,74 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
     if (const char* e = std::getenv("RT_SMAP_MAX_RES")) r_max = std::atoi(e);
 #endif
     while (R < r_max && (double)R < per_sqrt * std::sqrt((double)n)) R *= 2;
-    const size_t n_cells = (size_t)R * R;
-    int want[kMaxShadowMaps], n_maps = 0;
+    const int Rc = std::max(32, R / 2);
+    struct Want { int light; bool cube; size_t cells; size_t offset; };
+    Want want[kMaxShadowMaps];
+    int n_maps = 0;
+    size_t total = 0, largest = 0;
     for (int k = 0; k < nl; k++) {
         const float4 l0 = lights[3 * k];
-        const double len = std::sqrt((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z);
-        if (l0.w == 0.0f && std::isfinite(len) && len > 1.0e-30) want[n_maps++] = k;
+        if (!std::isfinite(l0.x) || !std::isfinite(l0.y) || !std::isfinite(l0.z)) continue;
+        const bool cube = l0.w != 0.0f;
+        if (!cube && !((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z > 1.0e-60)) continue;
+        const size_t cells = cube ? (size_t)6 * Rc * Rc : (size_t)R * R;
+        want[n_maps++] = Want{ k, cube, cells, total };
+        total += cells;
+        largest = std::max(largest, cells);
     }
     if (n_maps == 0) return RT_OK;
     DevBuf keys, big, n_big;
-    if (!s->smap_cells.reserve(n_cells * n_maps * sizeof(int)) || !keys.reserve(n_cells * 8) || !big.reserve((size_t)n * 4) ||
-        !n_big.reserve(4))
+    if (!s->smap_cells.reserve(total * sizeof(int)) || !keys.reserve(largest * 8) || !big.reserve((size_t)n * 6 * 4) || !n_big.reserve(4))
         return RT_E_NOMEM;
     for (int j = 0; j < n_maps; j++) {
-        const int k = want[j];
+        const int k = want[j].light;
         const float4 l0 = lights[3 * k];
-        const double len = std::sqrt((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z);
-        const double d[3] = { l0.x / len, l0.y / len, l0.z / len };
-        // an axis the direction is least aligned with, then an orthonormal pair
-        int a = 0;
-        if (std::fabs(d[1]) < std::fabs(d[a])) a = 1;
-        if (std::fabs(d[2]) < std::fabs(d[a])) a = 2;
-        double ax[3] = { 0, 0, 0 }; ax[a] = 1.0;
-        double u[3] = { d[1] * ax[2] - d[2] * ax[1], d[2] * ax[0] - d[0] * ax[2], d[0] * ax[1] - d[1] * ax[0] };
-        const double ul = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
-        for (int c = 0; c < 3; c++) u[c] /= ul;
-        const double v[3] = { d[1] * u[2] - d[2] * u[1], d[2] * u[0] - d[0] * u[2], d[0] * u[1] - d[1] * u[0] };
-        double umin = 1e300, umax = -1e300, vmin = 1e300, vmax = -1e300;
-        for (int corner = 0; corner < 8; corner++) {
-            double pu = 0, pv = 0;
-            for (int c = 0; c < 3; c++) {
-                const double x = (corner >> c) & 1 ? bb.hi[c] : bb.lo[c];
-                pu += x * u[c]; pv += x * v[c];
-            }
-            umin = std::min(umin, pu); umax = std::max(umax, pu); vmin = std::min(vmin, pv); vmax = std::max(vmax, pv);
-        }
-        const double extent = std::max(umax - umin, vmax - vmin) * 1.0001 + 1.0e-20;
-        if (!std::isfinite(extent) || !(extent > 0.0)) continue;
         SmapBuild m;
-        for (int c = 0; c < 3; c++) { m.dir[c] = (float)d[c]; m.ub[c] = (float)u[c]; m.vb[c] = (float)v[c]; }
-        m.cell = (float)(extent / R); m.inv_cell = (float)(R / extent);
-        m.u0 = (float)(0.5 * (umin + umax) - 0.5 * extent); m.v0 = (float)(0.5 * (vmin + vmax) - 0.5 * extent);
-        m.R = R;
-        if (!std::isfinite(m.inv_cell) || !std::isfinite(m.u0) || !std::isfinite(m.v0)) continue;
-        RT_CUDA(cudaMemsetAsync(keys.p, 0xff, n_cells * 8, st));
+        std::memset(&m, 0, sizeof m);
+        m.cube = want[j].cube ? 1 : 0;
+        if (m.cube) {
+            m.origin[0] = l0.x; m.origin[1] = l0.y; m.origin[2] = l0.z;
+            m.R = Rc;
+        } else {
+            const double len = std::sqrt((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z);
+            const double d[3] = { l0.x / len, l0.y / len, l0.z / len };
+            // an axis the direction is least aligned with, then an orthonormal pair
+            int a = 0;
+            if (std::fabs(d[1]) < std::fabs(d[a])) a = 1;
+            if (std::fabs(d[2]) < std::fabs(d[a])) a = 2;
+            double ax[3] = { 0, 0, 0 }; ax[a] = 1.0;
+            double u[3] = { d[1] * ax[2] - d[2] * ax[1], d[2] * ax[0] - d[0] * ax[2], d[0] * ax[1] - d[1] * ax[0] };
+            const double ul = std::sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+            for (int c = 0; c < 3; c++) u[c] /= ul;
+            const double v[3] = { d[1] * u[2] - d[2] * u[1], d[2] * u[0] - d[0] * u[2], d[0] * u[1] - d[1] * u[0] };
+            double umin = 1e300, umax = -1e300, vmin = 1e300, vmax = -1e300;
+            for (int corner = 0; corner < 8; corner++) {
+                double pu = 0, pv = 0;
+                for (int c = 0; c < 3; c++) {
+                    const double x = (corner >> c) & 1 ? bb.hi[c] : bb.lo[c];
+                    pu += x * u[c]; pv += x * v[c];
+                }
+                umin = std::min(umin, pu); umax = std::max(umax, pu); vmin = std::min(vmin, pv); vmax = std::max(vmax, pv);
+            }
+            const double extent = std::max(umax - umin, vmax - vmin) * 1.0001 + 1.0e-20;
+            if (!std::isfinite(extent) || !(extent > 0.0)) continue;
+            for (int c = 0; c < 3; c++) { m.dir[c] = (float)d[c]; m.ub[c] = (float)u[c]; m.vb[c] = (float)v[c]; }
+            m.cell = (float)(extent / R); m.inv_cell = (float)(R / extent);
+            m.u0 = (float)(0.5 * (umin + umax) - 0.5 * extent); m.v0 = (float)(0.5 * (vmin + vmax) - 0.5 * extent);
+            m.R = R;
+            if (!std::isfinite(m.inv_cell) || !std::isfinite(m.u0) || !std::isfinite(m.v0)) continue;
+        }
+        RT_CUDA(cudaMemsetAsync(keys.p, 0xff, want[j].cells * 8, st));
         RT_CUDA(cudaMemsetAsync(n_big.p, 0, 4, st));
         smap_prims_kernel<<<(n + 255) / 256, 256, 0, st>>>(prims, n, m, keys.as<unsigned long long>(), big.as<int>(), n_big.as<unsigned>());
         smap_big_kernel<<<1024, 256, 0, st>>>(prims, m, keys.as<unsigned long long>(), big.as<int>(), n_big.as<unsigned>());
-        smap_finish_kernel<<<(unsigned)((n_cells + 255) / 256), 256, 0, st>>>(keys.as<unsigned long long>(), (int)n_cells,
-                                                                             s->smap_cells.as<int>() + (size_t)j * n_cells);
+        smap_finish_kernel<<<(unsigned)((want[j].cells + 255) / 256), 256, 0, st>>>(keys.as<unsigned long long>(), want[j].cells,
+                                                                                   s->smap_cells.as<int>() + want[j].offset);
         RT_CUDA(cudaGetLastError());
         SceneHost::SmapHost& h = s->smap[k];
-        h.offset_plus_1 = (size_t)j * n_cells + 1;
-        for (int c = 0; c < 3; c++) { h.ub[c] = m.ub[c]; h.vb[c] = m.vb[c]; }
-        h.u0 = m.u0; h.v0 = m.v0; h.inv_cell = m.inv_cell; h.R = R;
+        h.offset_plus_1 = want[j].offset + 1;
+        for (int c = 0; c < 3; c++) { h.ub[c] = m.ub[c]; h.vb[c] = m.vb[c]; h.origin[c] = m.origin[c]; }
+        h.u0 = m.u0; h.v0 = m.v0; h.inv_cell = m.inv_cell; h.R = m.R; h.cube = m.cube;
     }
     RT_CUDA(cudaStreamSynchronize(st));      // (the temporaries go out of scope)
     return RT_OK;

@@ -163,7 +163,7 @@ struct SceneHost {
     // occluder maps of the first kMaxShadowMaps lights (directional ones; bvh.cu: build_shadow_maps): all maps in one
     // buffer, smap[k].cells holds the map's OFFSET (in ints) + 1 as an integer (0 = no map) until scene_view() adds the base
     DevBuf smap_cells;
-    struct SmapHost { size_t offset_plus_1 = 0; float ub[3] = { 0, 0, 0 }, vb[3] = { 0, 0, 0 }; float u0 = 0, v0 = 0, inv_cell = 0; int R = 0; };
+    struct SmapHost { size_t offset_plus_1 = 0; float ub[3] = { 0, 0, 0 }, vb[3] = { 0, 0, 0 }; float u0 = 0, v0 = 0, inv_cell = 0; float origin[3] = { 0, 0, 0 }; int R = 0, cube = 0; };
     SmapHost smap[kMaxShadowMaps];
 
     CameraView cam{};

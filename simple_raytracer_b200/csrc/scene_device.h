@@ -55,17 +55,19 @@ struct BvhView {
     int n_nodes8;
 };
 
-// Occluder maps (bvh.cu: build_shadow_maps): for a directional light, an orthographic id buffer seen from the
-// light — per cell the OPAQUE primitive nearest to the light that covers the cell's centre, as its slot in the
-// primitive array the any-hit walk reads.  A shadow ray first runs the reference's exact test against the
+// Occluder maps (bvh.cu: build_shadow_maps): an id buffer seen from the light — orthographic for a directional
+// light, the six faces of a cube around a point light — holding per cell the OPAQUE primitive nearest to the light
+// that covers the cell's centre, as its slot in the primitive array the any-hit walk reads.  A shadow ray first runs the reference's exact test against the
 // primitive of its cell (ShadowJob::setup): if that accepts, the carried product is exactly 0 and the walk is
 // skipped; if not, the ray is walked as before.  The map only guesses; nothing it holds can change a result.
 constexpr int kMaxShadowMaps = 4;      // the first four lights (94 % of the stress scene's chains end at light 0)
 struct ShadowMapView {
-    const int* cells;                  // [R * R], -1 = none; nullptr = this light has no map
-    float ub[3], vb[3];                // orthonormal basis of the light's plane
+    const int* cells;                  // [R * R] (directional) or [6][R * R] (point), -1 = none; nullptr = no map
+    float ub[3], vb[3];                // directional: orthonormal basis of the light's plane
     float u0, v0, inv_cell;
+    float origin[3];                   // point: the light's position; face f = 2 * axis + (that coordinate of p - origin < 0)
     int R;
+    int cube;                          // 0: directional, 1: point
 };
 
 struct SceneView {

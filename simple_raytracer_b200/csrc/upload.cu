@@ -347,8 +347,8 @@ SceneView scene_view(const SceneHost* s)
         if (!m.offset_plus_1 || !s->smap_cells.p) continue;
         ShadowMapView& d = v.smap[k];
         d.cells = s->smap_cells.as<int>() + (m.offset_plus_1 - 1);
-        for (int c = 0; c < 3; c++) { d.ub[c] = m.ub[c]; d.vb[c] = m.vb[c]; }
-        d.u0 = m.u0; d.v0 = m.v0; d.inv_cell = m.inv_cell; d.R = m.R;
+        for (int c = 0; c < 3; c++) { d.ub[c] = m.ub[c]; d.vb[c] = m.vb[c]; d.origin[c] = m.origin[c]; }
+        d.u0 = m.u0; d.v0 = m.v0; d.inv_cell = m.inv_cell; d.R = m.R; d.cube = m.cube;
     }
     return v;
 }

@@ -290,26 +290,58 @@ __global__ void __launch_bounds__(kBlock, RT_SHADE_MIN_BLOCKS) bvh_spawn_kernel(
 // One launch covers the nodes of generations first .. last (the frame scheduler passes all of
 // them at once: one kernel tail per frame instead of one per generation): job j counts through
 // generation `first`'s node list, then the next one's, ...
-// The occluder map's guess for the shadow ray (p, ray) of directional light li (scene_device.h: ShadowMapView): the
-// reference's own test of this ray against the opaque primitive that covers the ray's cell nearest to the light.
-// Accepted (-> true, v.opaque set): the product is exactly 0 whatever else the ray meets (every factor lies in
-// [0,1]), no walk.  Not accepted: the attempt is forgotten (v as shadow_begin left it) and the ray has to be walked.
+// The shadow ray of light li from p as ShadeRay casts it (main.cpp:895 / 921-922): direction, and the light's
+// distance for a point light (hits beyond it do not count).
+RT_DEV void shadow_ray_of_light(const FrameParams& P, int li, V3 p, V3& ray, float& tmax, bool& use_tmax)
+{
+    const float4 l0 = P.scene.light[3 * li];
+    if (l0.w == 0.0f) {
+        ray = vneg(ld3(l0));                                                 // 895: un-normalised ray
+        tmax = 0.0f; use_tmax = false;
+    } else {
+        ray = vnorm(vsub(ld3(l0), p));                                       // 921
+        const V3 dp = vsub(p, ld3(l0));
+        tmax = fsqrt(vsum3(fmul(dp.x, dp.x), fmul(dp.y, dp.y), fmul(dp.z, dp.z)));   // 922
+        use_tmax = true;
+    }
+}
+
+// The occluder map's guess for the shadow ray (p, ray) of light li (scene_device.h: ShadowMapView): the reference's
+// own test of this ray against the opaque primitive that covers the ray's cell nearest to the light.  Accepted
+// (-> true, v.opaque set): the product is exactly 0 whatever else the ray meets (every factor lies in [0,1]), no
+// walk.  Not accepted: the attempt is forgotten (v as shadow_begin left it) and the ray has to be walked.
+// v must come from shadow_begin(p, ray, self, eps, tmax, use_tmax).
 template <bool kCount>
 RT_DEV bool occluder_map_settles(const FrameParams& P, const BvhAccelT<kCount>& acc, int li, V3 p, V3 ray, int self,
-                                 typename BvhAccelT<kCount>::ShadowVisit& v)
+                                 float tmax, bool use_tmax, typename BvhAccelT<kCount>::ShadowVisit& v)
 {
     if (li >= kMaxShadowMaps || P.scene.smap[li].cells == nullptr) return false;
     const ShadowMapView& m = P.scene.smap[li];
-    const float fu = (p.x * m.ub[0] + p.y * m.ub[1] + p.z * m.ub[2] - m.u0) * m.inv_cell;
-    const float fv = (p.x * m.vb[0] + p.y * m.vb[1] + p.z * m.vb[2] - m.v0) * m.inv_cell;
-    if (!(fu >= 0.0f && fv >= 0.0f && fu < (float)m.R && fv < (float)m.R)) return false;
-    const int slot = __ldg(m.cells + (size_t)(int)fv * m.R + (int)fu);
+    const float R = (float)m.R;
+    float fu, fv;
+    size_t face = 0;
+    if (m.cube) {
+        const float d[3] = { p.x - m.origin[0], p.y - m.origin[1], p.z - m.origin[2] };
+        int az = 0;
+        if (fabsf(d[1]) > fabsf(d[az])) az = 1;
+        if (fabsf(d[2]) > fabsf(d[az])) az = 2;
+        const float z = fabsf(d[az]);
+        if (!(z > 0.0f)) return false;
+        face = (size_t)(2 * az + (d[az] < 0.0f ? 1 : 0)) * (size_t)(m.R * m.R);
+        fu = (d[(az + 1) % 3] / z + 1.0f) * (0.5f * R);
+        fv = (d[(az + 2) % 3] / z + 1.0f) * (0.5f * R);
+    } else {
+        fu = (p.x * m.ub[0] + p.y * m.ub[1] + p.z * m.ub[2] - m.u0) * m.inv_cell;
+        fv = (p.x * m.vb[0] + p.y * m.vb[1] + p.z * m.vb[2] - m.v0) * m.inv_cell;
+    }
+    if (!(fu >= 0.0f && fv >= 0.0f && fu < R && fv < R)) return false;
+    const int slot = __ldg(m.cells + face + (size_t)(int)fv * m.R + (int)fu);
     if (slot < 0) return false;
     const float4* pr = acc.nodes8 != nullptr ? acc.prims8 : acc.prims;
     if (kCount) acc.cnt_prims++;
     v(pr + (size_t)slot * kTriWords, 3.402823466e+38f);
     if (v.opaque) return true;
-    acc.shadow_begin(p, ray, self, P.epsilon, 0.0f, false, v);
+    acc.shadow_begin(p, ray, self, P.epsilon, tmax, use_tmax, v);
     return false;
 }
 
@@ -320,8 +352,6 @@ template <bool kCount>
 __global__ void __launch_bounds__(256) bvh_shadow_settle_kernel(const __grid_constant__ FrameParams P, int first, int last)
 {
     auto acc = make_bvh_accel<kCount>(P.scene);
-    const float4 l0 = P.scene.light[0];
-    const V3 ray = vneg(ld3(l0));                                            // 895: un-normalised ray
     unsigned long long hits = 0;
     for (int level = first; level <= last; level++) {
         const LevelBuffers& LB = P.level[level];
@@ -333,10 +363,12 @@ __global__ void __launch_bounds__(256) bvh_shadow_settle_kernel(const __grid_con
                 const float4 hp = LB.hp[LB.node_list[k]];
                 const V3 p = mk3(hp.x, hp.y, hp.z);
                 const int self = __float_as_int(hp.w);
+                V3 ray; float tmax; bool use_tmax;
+                shadow_ray_of_light(P, 0, p, ray, tmax, use_tmax);
                 typename BvhAccelT<kCount>::ShadowVisit v;
-                acc.shadow_begin(p, ray, self, P.epsilon, 0.0f, false, v);
-                if (occluder_map_settles(P, acc, 0, p, ray, self, v)) {
-                    LB.sh[k] = clamp01(fmul(0.0f, 1.0f));                    // 909 with shadow_mask == 1 (788)
+                acc.shadow_begin(p, ray, self, P.epsilon, tmax, use_tmax, v);
+                if (occluder_map_settles(P, acc, 0, p, ray, self, tmax, use_tmax, v)) {
+                    LB.sh[k] = clamp01(fmul(0.0f, 1.0f));                    // 909 / 946 with shadow_mask == 1 (788)
                     if (kCount) hits++;
                 } else {
                     walk = true;
@@ -383,20 +415,13 @@ struct ShadowJob {
 
     RT_DEV void setup(V3& wo, V3& wray, float& tmin, float& tmax)
     {
-        const float4 l0 = P.scene.light[3 * li];
         tmin = P.epsilon;
-        settled = false;
-        if (l0.w == 0.0f) {
-            wray = vneg(ld3(l0));                                                // 895: un-normalised ray
-            tmax = 3.402823466e+38f;
-            acc.shadow_begin(p, wray, self, tmin, 0.0f, false, v);
-            if (!(li == 0 && P.settled_first)) settled = occluder_map_settles(P, acc, li, p, wray, self, v);
-        } else {
-            wray = vnorm(vsub(ld3(l0), p));                                      // 921
-            const V3 dp = vsub(p, ld3(l0));
-            tmax = fsqrt(vsum3(fmul(dp.x, dp.x), fmul(dp.y, dp.y), fmul(dp.z, dp.z)));   // 922
-            acc.shadow_begin(p, wray, self, tmin, tmax, true, v);
-        }
+        float far; bool use_far;
+        shadow_ray_of_light(P, li, p, wray, far, use_far);
+        tmax = use_far ? far : 3.402823466e+38f;
+        acc.shadow_begin(p, wray, self, tmin, far, use_far, v);
+        // (light 0 was looked up by bvh_shadow_settle_kernel when the jobs come from the walk lists)
+        settled = !(li == 0 && P.settled_first) && occluder_map_settles(P, acc, li, p, wray, self, far, use_far, v);
         wo = p;
     }
     RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
