@@ -699,7 +699,10 @@ RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int vie
             depth = (bq - sqrtf(disc)) / dd;
         }
         if (!(isfinite(depth)) || (view >= 0 && !(depth > 0.0f))) continue;
-        atomicMin(face + (size_t)iy * m.R + ix, smap_key(depth, slot));
+        // (most primitives of a dense scene lie behind what the cell already holds: look before the atomic)
+        unsigned long long* cell = face + (size_t)iy * m.R + ix;
+        const unsigned long long key = smap_key(depth, slot);
+        if (key < *(volatile unsigned long long*)cell) atomicMin(cell, key);
     }
 }
 
@@ -739,6 +742,7 @@ __global__ void smap_finish_kernel(const unsigned long long* __restrict__ cells,
 // kTriWords words).  Lights whose direction / position is not finite, and scenes without finite bounds, get none.
 static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const BuildBounds& bb, cudaStream_t st)
 {
+    finish_shadow_maps(s);
     for (int k = 0; k < kMaxShadowMaps; k++) s->smap[k] = SceneHost::SmapHost();
     const int nl = std::min(s->nl, kMaxShadowMaps);
     if (nl <= 0 || n <= 0 || n >= (1 << 28)) return RT_OK;
@@ -759,8 +763,10 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
     if (const char* e = std::getenv("RT_SMAP_MAX_RES")) r_max = std::atoi(e);
 #endif
     while (R < r_max && (double)R < per_sqrt * std::sqrt((double)n)) R *= 2;
-    const int Rc = std::max(32, R / 2);
-    struct Want { int light; bool cube; size_t cells; size_t offset; };
+    // Light 0 decides most chains (94 % of the stress scene's end there): the full resolution for it, a quarter per
+    // axis for the others — a map of 4096 x 4096 cells takes 1.4 ms to build over 1 M triangles, which a map that is
+    // asked for one node in sixteen does not earn back within a frame.  A cube face gets half of its light's figure.
+    struct Want { int light; bool cube; int R; size_t cells; size_t offset; };
     Want want[kMaxShadowMaps];
     int n_maps = 0;
     size_t total = 0, largest = 0;
@@ -769,15 +775,21 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
         if (!std::isfinite(l0.x) || !std::isfinite(l0.y) || !std::isfinite(l0.z)) continue;
         const bool cube = l0.w != 0.0f;
         if (!cube && !((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z > 1.0e-60)) continue;
-        const size_t cells = cube ? (size_t)6 * Rc * Rc : (size_t)R * R;
-        want[n_maps++] = Want{ k, cube, cells, total };
+        const int Rk = std::max(64, k == 0 ? R : R / 4);
+        const int Rm = cube ? std::max(32, Rk / 2) : Rk;
+        const size_t cells = cube ? (size_t)6 * Rm * Rm : (size_t)Rm * Rm;
+        want[n_maps++] = Want{ k, cube, Rm, cells, total };
         total += cells;
         largest = std::max(largest, cells);
     }
     if (n_maps == 0) return RT_OK;
-    DevBuf keys, big, n_big;
+    DevBuf& keys = s->smap_keys; DevBuf& big = s->smap_big; DevBuf& n_big = s->smap_count;
     if (!s->smap_cells.reserve(total * sizeof(int)) || !keys.reserve(largest * 8) || !big.reserve((size_t)n * 6 * 4) || !n_big.reserve(4))
         return RT_E_NOMEM;
+    if (!s->smap_stream) RT_CUDA(cudaStreamCreateWithFlags(&s->smap_stream, cudaStreamNonBlocking));
+    if (!s->smap_ready) RT_CUDA(cudaEventCreateWithFlags(&s->smap_ready, cudaEventDisableTiming));
+    // (the trees are complete: build_bvh has synchronised its stream)
+    st = s->smap_stream;
     for (int j = 0; j < n_maps; j++) {
         const int k = want[j].light;
         const float4 l0 = lights[3 * k];
@@ -786,7 +798,7 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
         m.cube = want[j].cube ? 1 : 0;
         if (m.cube) {
             m.origin[0] = l0.x; m.origin[1] = l0.y; m.origin[2] = l0.z;
-            m.R = Rc;
+            m.R = want[j].R;
         } else {
             const double len = std::sqrt((double)l0.x * l0.x + (double)l0.y * l0.y + (double)l0.z * l0.z);
             const double d[3] = { l0.x / len, l0.y / len, l0.z / len };
@@ -811,9 +823,10 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
             const double extent = std::max(umax - umin, vmax - vmin) * 1.0001 + 1.0e-20;
             if (!std::isfinite(extent) || !(extent > 0.0)) continue;
             for (int c = 0; c < 3; c++) { m.dir[c] = (float)d[c]; m.ub[c] = (float)u[c]; m.vb[c] = (float)v[c]; }
-            m.cell = (float)(extent / R); m.inv_cell = (float)(R / extent);
+            const int Rm = want[j].R;
+            m.cell = (float)(extent / Rm); m.inv_cell = (float)(Rm / extent);
             m.u0 = (float)(0.5 * (umin + umax) - 0.5 * extent); m.v0 = (float)(0.5 * (vmin + vmax) - 0.5 * extent);
-            m.R = R;
+            m.R = Rm;
             if (!std::isfinite(m.inv_cell) || !std::isfinite(m.u0) || !std::isfinite(m.v0)) continue;
         }
         RT_CUDA(cudaMemsetAsync(keys.p, 0xff, want[j].cells * 8, st));
@@ -828,11 +841,30 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
         for (int c = 0; c < 3; c++) { h.ub[c] = m.ub[c]; h.vb[c] = m.vb[c]; h.origin[c] = m.origin[c]; }
         h.u0 = m.u0; h.v0 = m.v0; h.inv_cell = m.inv_cell; h.R = m.R; h.cube = m.cube;
     }
-    RT_CUDA(cudaStreamSynchronize(st));      // (the temporaries go out of scope)
+    RT_CUDA(cudaEventRecord(s->smap_ready, st));
+    s->smap_pending = true;
     return RT_OK;
 }
 
 }  // namespace
+
+void finish_shadow_maps(SceneHost* s)
+{
+    if (s->smap_pending) {
+        cudaEventSynchronize(s->smap_ready);
+        s->smap_pending = false;
+    }
+    s->smap_keys.release(); s->smap_big.release(); s->smap_count.release();
+}
+
+int wait_shadow_maps(SceneHost* s, cudaStream_t stream, bool capturing)
+{
+    if (!s->smap_pending) return RT_OK;
+    if (capturing || cudaEventQuery(s->smap_ready) == cudaSuccess) { finish_shadow_maps(s); return RT_OK; }
+    cudaGetLastError();                          // (cudaErrorNotReady from the query)
+    RT_CUDA(cudaStreamWaitEvent(stream, s->smap_ready, 0));
+    return RT_OK;
+}
 
 int build_bvh(SceneHost* s)
 {

@@ -299,10 +299,18 @@ static void launch_trace(const FrameParams& P, int level, bool sharing, int grid
     else bvh_trace_kernel<kCount, false><<<grid, kWalkBlock, 0, st>>>(P, level);
 }
 
+static bool any_shadow_map(const FrameParams& P)
+{
+    for (int k = 0; k < kMaxShadowMaps; k++) if (P.scene.smap[k].cells != nullptr) return true;
+    return false;
+}
+
 template <bool kCount>
 static void launch_shadow(const FrameParams& P, int first, int last, bool sharing, int grid, cudaStream_t st)
 {
-    // light 0's occluder map first: what it settles never enters the walk kernel
+    // a sample of the nodes against the occluder maps (which of them pay in this frame), then light 0's map for every
+    // node: what it settles never enters the walk kernel
+    if (any_shadow_map(P)) bvh_shadow_probe_kernel<<<32, 256, 0, st>>>(P, first);
     if (P.settled_first) bvh_shadow_settle_kernel<kCount><<<std::max(1, std::min(grid, 148 * 16)), 256, 0, st>>>(P, first, last);
     if (sharing) bvh_shadow_kernel<kCount, true><<<grid, kWalkBlock, 0, st>>>(P, first, last);
     else bvh_shadow_kernel<kCount, false><<<grid, kWalkBlock, 0, st>>>(P, first, last);
@@ -368,6 +376,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     ChainStreams& cs = s->ws.chains;
     if (overlap && !cs.ensure(K)) return RT_E_CUDA;
     int n = 0;
+    bool capturing = false;
     // The launch sequence of the frame on `stream` (directly, or under stream capture: see below).
     auto issue = [&](cudaStream_t stream) -> int {
         RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
@@ -413,9 +422,10 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
                 if (s->nl) {
                     const int sh_grid = persistent_grid(work * s->nl, sms, T.grid_mult, kWalkBlock);
+                    if (wait_shadow_maps(s, stream, capturing) != RT_OK) return RT_E_CUDA;
                     if (count) launch_shadow<true>(P, l, l, sharing, sh_grid, stream);
                     else launch_shadow<false>(P, l, l, sharing, sh_grid, stream);
-                    n += 2 + P.settled_first;
+                    n += 2 + P.settled_first + (any_shadow_map(P) ? 1 : 0);
                 }
                 RT_CUDA(cudaEventRecord(s->prof_mid[l][1], stream));
                 bvh_colour_kernel<<<persistent_grid(work, sms, T.grid_mult), kBlock, 0, stream>>>(P, l, l);
@@ -442,9 +452,10 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 if (s->nl) {
                     const bool sharing = steal == 1 || (steal == 0 && chain_pixels <= 1000LL * T.steal_shadow_max_kpixels);
                     const int sh_grid = persistent_grid(all_work * s->nl, sms, T.grid_mult, kWalkBlock);
+                    if (wait_shadow_maps(s, side, capturing) != RT_OK) return RT_E_CUDA;
                     if (count) launch_shadow<true>(P, 0, D, sharing, sh_grid, side);
                     else launch_shadow<false>(P, 0, D, sharing, sh_grid, side);
-                    n += 2 + P.settled_first;
+                    n += 2 + P.settled_first + (any_shadow_map(P) ? 1 : 0);
                 }
                 if (chain_pixels <= 1000LL * T.colour_merge_max_kpixels) {
                     bvh_colour_kernel<<<persistent_grid(all_work, sms, T.grid_mult), kBlock, 0, side>>>(P, 0, D);
@@ -499,7 +510,11 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     bool graphable = !p.profile && !p.instrument;
     if (graphable) {
         cudaStreamCaptureStatus cst = cudaStreamCaptureStatusNone;
-        if (cudaStreamIsCapturing(stream, &cst) != cudaSuccess || cst != cudaStreamCaptureStatusNone) { cudaGetLastError(); graphable = false; }
+        if (cudaStreamIsCapturing(stream, &cst) != cudaSuccess || cst != cudaStreamCaptureStatusNone) {
+            cudaGetLastError();
+            graphable = false;
+            finish_shadow_maps(s);               // the caller's capture: no waiting for outside events in there either
+        }
     }
     const bool same = graphable && G.K == K && G.accel == accel && std::memcmp(G.ps, PS, sizeof(FrameParams) * K) == 0;
     if (same && G.exec) {
@@ -508,6 +523,8 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         s->graph_replays++;
     } else if (same) {
         cudaGraph_t graph = nullptr;
+        finish_shadow_maps(s);                   // (a captured stream cannot wait for an event from outside)
+        capturing = true;
         RT_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
         const int rc = issue(stream);
         const cudaError_t ce = cudaStreamEndCapture(stream, &graph);

@@ -60,7 +60,10 @@ struct BvhView {
 // that covers the cell's centre, as its slot in the primitive array the any-hit walk reads.  A shadow ray first runs the reference's exact test against the
 // primitive of its cell (ShadowJob::setup): if that accepts, the carried product is exactly 0 and the walk is
 // skipped; if not, the ray is walked as before.  The map only guesses; nothing it holds can change a result.
-constexpr int kMaxShadowMaps = 4;      // the first four lights (94 % of the stress scene's chains end at light 0)
+#ifndef RT_MAX_SHADOW_MAPS
+#define RT_MAX_SHADOW_MAPS 1
+#endif
+constexpr int kMaxShadowMaps = RT_MAX_SHADOW_MAPS;      // lights 0 .. kMaxShadowMaps - 1 may have one
 struct ShadowMapView {
     const int* cells;                  // [R * R] (directional) or [6][R * R] (point), -1 = none; nullptr = no map
     float ub[3], vb[3];                // directional: orthonormal basis of the light's plane
@@ -159,6 +162,9 @@ struct Counters {
     unsigned int fetch_trace[kMaxLevels];   // LBVH pipeline: next job of the persistent trace / shadow kernels
     unsigned int fetch_shadow[kMaxLevels];
     unsigned int walk_nodes[kMaxLevels];    // entries of LevelBuffers::walk_list
+    // bvh_shadow_probe_kernel: a sample of this frame's nodes against each occluder map (tests made, occluders
+    // confirmed): a map that settles fewer than one ray in eight is left alone for the rest of the frame
+    unsigned int smap_tries[kMaxShadowMaps], smap_hits[kMaxShadowMaps];
     unsigned long long bvh_nodes, prim_tests, texels;   // instrumented variant only (all walks)
     unsigned long long shadow_boxes, shadow_prims;      // ... of which in the shadow kernels
     unsigned long long shadow_walks;                    // instrumented LBVH frames: shadow rays not elided by the mask == 0 early-out

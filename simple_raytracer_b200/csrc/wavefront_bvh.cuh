@@ -311,11 +311,18 @@ RT_DEV void shadow_ray_of_light(const FrameParams& P, int li, V3 p, V3& ray, flo
 // (-> true, v.opaque set): the product is exactly 0 whatever else the ray meets (every factor lies in [0,1]), no
 // walk.  Not accepted: the attempt is forgotten (v as shadow_begin left it) and the ray has to be walked.
 // v must come from shadow_begin(p, ray, self, eps, tmax, use_tmax).
-template <bool kCount>
+// What the frame's sample said about light li's map (bvh_shadow_probe_kernel; no sample: use the map).
+RT_DEV bool occluder_map_pays(const FrameParams& P, int li)
+{
+    const unsigned tries = P.counters->smap_tries[li], hits = P.counters->smap_hits[li];
+    return tries == 0u || hits * 8u >= tries;
+}
+
+template <bool kCount, bool kForce = false>
 RT_DEV bool occluder_map_settles(const FrameParams& P, const BvhAccelT<kCount>& acc, int li, V3 p, V3 ray, int self,
                                  float tmax, bool use_tmax, typename BvhAccelT<kCount>::ShadowVisit& v)
 {
-    if (li >= kMaxShadowMaps || P.scene.smap[li].cells == nullptr) return false;
+    if (li >= kMaxShadowMaps || P.scene.smap[li].cells == nullptr || !kForce && !occluder_map_pays(P, li)) return false;
     const ShadowMapView& m = P.scene.smap[li];
     const float R = (float)m.R;
     float fu, fv;
@@ -345,6 +352,43 @@ RT_DEV bool occluder_map_settles(const FrameParams& P, const BvhAccelT<kCount>& 
     return false;
 }
 
+// Does a map pay in THIS frame?  A lookup is one dependent gather per ray; where most rays reach their light (the lit
+// side of a convex mesh seen from the light's side) it settles nothing and costs ~10 % of the any-hit time.  A few
+// thousand nodes of the first generation, spread over the list, are tried against every map; the kernels that follow
+// leave a map alone if it confirmed an occluder for fewer than one sampled node in eight.  (Whatever is decided,
+// the frame is the same: a map only ever replaces a walk whose result it has proved.)
+constexpr unsigned kProbeNodes = 8192;
+__global__ void __launch_bounds__(256) bvh_shadow_probe_kernel(const __grid_constant__ FrameParams P, int first)
+{
+    auto acc = make_bvh_accel<false>(P.scene);
+    const LevelBuffers& LB = P.level[first];
+    const unsigned n = P.counters->nodes[first];
+    const unsigned samples = min(n, kProbeNodes);
+    const unsigned stride = samples ? n / samples : 1u;
+    const int nl = min(P.scene.nl, kMaxShadowMaps);
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < ((samples + 31u) & ~31u); i += gridDim.x * blockDim.x) {
+        for (int li = 0; li < nl; li++) {
+            if (P.scene.smap[li].cells == nullptr) continue;                     // (uniform)
+            bool hit = false;
+            if (i < samples) {
+                const float4 hp = LB.hp[LB.node_list[i * stride]];
+                const V3 p = mk3(hp.x, hp.y, hp.z);
+                const int self = __float_as_int(hp.w);
+                V3 ray; float tmax; bool use_tmax;
+                shadow_ray_of_light(P, li, p, ray, tmax, use_tmax);
+                BvhAccelT<false>::ShadowVisit v;
+                acc.shadow_begin(p, ray, self, P.epsilon, tmax, use_tmax, v);
+                hit = occluder_map_settles<false, true>(P, acc, li, p, ray, self, tmax, use_tmax, v);
+            }
+            const unsigned hm = __ballot_sync(0xffffffffu, hit), tm = __ballot_sync(0xffffffffu, i < samples);
+            if ((threadIdx.x & 31) == 0) {
+                atomicAdd(&P.counters->smap_tries[li], (unsigned)__popc(tm));
+                if (hm) atomicAdd(&P.counters->smap_hits[li], (unsigned)__popc(hm));
+            }
+        }
+    }
+}
+
 // Before the any-hit walks of a chain's nodes: one thread per node tries light 0's occluder map.  Settled nodes get
 // their record (the carried product after light 0 is 0: the chain ends there) and never enter the persistent walk
 // kernel; the others are listed (LevelBuffers::walk_list) as that kernel's jobs.  Launched only when light 0 has a map.
@@ -353,6 +397,7 @@ __global__ void __launch_bounds__(256) bvh_shadow_settle_kernel(const __grid_con
 {
     auto acc = make_bvh_accel<kCount>(P.scene);
     unsigned long long hits = 0;
+    if (!occluder_map_pays(P, 0)) return;                // (the walk kernel then takes the node lists as they are)
     for (int level = first; level <= last; level++) {
         const LevelBuffers& LB = P.level[level];
         const unsigned n = P.counters->nodes[level];
@@ -408,6 +453,7 @@ struct ShadowJob {
     int li;
     V3 p; int self;
     float mask;
+    bool from_lists;                   // the jobs are the walk lists' (bvh_shadow_settle_kernel has dealt with light 0)
     bool settled;                      // this light's ray needs no walk: the occluder map's candidate is an opaque hit
     unsigned long long walks = 0;      // instrumented variant: shadow rays actually walked by this thread
     unsigned long long map_hits = 0;   // ... and those the occluder map settled
@@ -421,14 +467,17 @@ struct ShadowJob {
         tmax = use_far ? far : 3.402823466e+38f;
         acc.shadow_begin(p, wray, self, tmin, far, use_far, v);
         // (light 0 was looked up by bvh_shadow_settle_kernel when the jobs come from the walk lists)
-        settled = !(li == 0 && P.settled_first) && occluder_map_settles(P, acc, li, p, wray, self, far, use_far, v);
+        // (with maps for light 0 only — the default — the pre-pass has asked it already and the walk kernel carries no lookup)
+        settled = false;
+        if (kMaxShadowMaps > 1)
+            settled = !(li == 0 && from_lists) && occluder_map_settles(P, acc, li, p, wray, self, far, use_far, v);
         wo = p;
     }
     RT_DEV bool begin(unsigned j, V3& wo, V3& wray, float& tmin, float& tmax)
     {
         k = j; li = 0; mask = 1.0f;                                              // 788
         level = first;
-        if (P.settled_first) {
+        if (from_lists) {
             unsigned n_walk = P.counters->walk_nodes[level];
             while (k >= n_walk) { k -= n_walk; level++; n_walk = P.counters->walk_nodes[level]; }
             k = (unsigned)P.level[level].walk_list[k];
@@ -526,9 +575,11 @@ __global__ void __launch_bounds__(kWalkBlock, kCount ? 0 : RT_SHADOW_MIN_BLOCKS)
     using Job = ShadowJob<kCount, kStealing>;
     auto acc = make_bvh_accel<kCount>(P.scene);
     acc.overflow_flag = &P.counters->overflow;
+    const bool from_lists = P.settled_first && occluder_map_pays(P, 0);
     unsigned n_jobs = 0;
-    for (int l = first; l <= last; l++) n_jobs += P.settled_first ? P.counters->walk_nodes[l] : P.counters->nodes[l];
+    for (int l = first; l <= last; l++) n_jobs += from_lists ? P.counters->walk_nodes[l] : P.counters->nodes[l];
     Job job{ P, acc, first };
+    job.from_lists = from_lists;
     acc.persistent_walk(n_jobs, &P.counters->fetch_shadow[first], job, P.sh_refill_lanes, P.sh_inner_min_lanes, P.sh_leaf_min_lanes,
                         kCount ? &P.counters->clock[1][first] : nullptr);
     flush_bvh_counters(acc, P.counters, true);

@@ -109,6 +109,8 @@ def test_stress_frame_tiles_by_brute_force(w, h, world, tiles):
         assert np.array_equal(again[0], rgb) and np.array_equal(again[1], flags)
         assert list(si.nodes_per_level) == list(st.nodes_per_level)
         assert 0 < si.shadow_rays_walked <= si.rays_shadow
+        # the occluder maps (bvh.cu: build_shadow_maps) settle most of this dense scene's shadow rays without a walk
+        assert si.shadow_map_hits > 3 * si.shadow_rays_walked, (si.shadow_map_hits, si.shadow_rays_walked)
 
 
 def test_shadow_probe_on_the_8_wide_tree_is_bit_exact():
