@@ -159,9 +159,6 @@ void rt_free_scene(RtScene* scene)
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     s->ws.chains.sync();
-    finish_shadow_maps(s);
-    if (s->smap_stream) cudaStreamDestroy(s->smap_stream);
-    if (s->smap_ready) cudaEventDestroy(s->smap_ready);
     if (s->graph.exec) { cudaGraphExecDestroy(s->graph.exec); s->graph.exec = nullptr; }
     if (s->ws.device >= 0) stash_workspace(std::move(s->ws));
     if (s->ev0) cudaEventDestroy(s->ev0);

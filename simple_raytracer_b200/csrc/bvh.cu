@@ -742,7 +742,6 @@ __global__ void smap_finish_kernel(const unsigned long long* __restrict__ cells,
 // kTriWords words).  Lights whose direction / position is not finite, and scenes without finite bounds, get none.
 static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const BuildBounds& bb, cudaStream_t st)
 {
-    finish_shadow_maps(s);
     for (int k = 0; k < kMaxShadowMaps; k++) s->smap[k] = SceneHost::SmapHost();
     const int nl = std::min(s->nl, kMaxShadowMaps);
     if (nl <= 0 || n <= 0 || n >= (1 << 28)) return RT_OK;
@@ -783,13 +782,11 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
         largest = std::max(largest, cells);
     }
     if (n_maps == 0) return RT_OK;
-    DevBuf& keys = s->smap_keys; DevBuf& big = s->smap_big; DevBuf& n_big = s->smap_count;
+    // (building the maps on a stream of their own while the first frame's closest-hit kernels run was tried: the two
+    // share the SMs and the frame ends no sooner)
+    DevBuf keys, big, n_big;
     if (!s->smap_cells.reserve(total * sizeof(int)) || !keys.reserve(largest * 8) || !big.reserve((size_t)n * 6 * 4) || !n_big.reserve(4))
         return RT_E_NOMEM;
-    if (!s->smap_stream) RT_CUDA(cudaStreamCreateWithFlags(&s->smap_stream, cudaStreamNonBlocking));
-    if (!s->smap_ready) RT_CUDA(cudaEventCreateWithFlags(&s->smap_ready, cudaEventDisableTiming));
-    // (the trees are complete: build_bvh has synchronised its stream)
-    st = s->smap_stream;
     for (int j = 0; j < n_maps; j++) {
         const int k = want[j].light;
         const float4 l0 = lights[3 * k];
@@ -841,30 +838,11 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
         for (int c = 0; c < 3; c++) { h.ub[c] = m.ub[c]; h.vb[c] = m.vb[c]; h.origin[c] = m.origin[c]; }
         h.u0 = m.u0; h.v0 = m.v0; h.inv_cell = m.inv_cell; h.R = m.R; h.cube = m.cube;
     }
-    RT_CUDA(cudaEventRecord(s->smap_ready, st));
-    s->smap_pending = true;
+    RT_CUDA(cudaStreamSynchronize(st));      // (the temporaries go out of scope)
     return RT_OK;
 }
 
 }  // namespace
-
-void finish_shadow_maps(SceneHost* s)
-{
-    if (s->smap_pending) {
-        cudaEventSynchronize(s->smap_ready);
-        s->smap_pending = false;
-    }
-    s->smap_keys.release(); s->smap_big.release(); s->smap_count.release();
-}
-
-int wait_shadow_maps(SceneHost* s, cudaStream_t stream, bool capturing)
-{
-    if (!s->smap_pending) return RT_OK;
-    if (capturing || cudaEventQuery(s->smap_ready) == cudaSuccess) { finish_shadow_maps(s); return RT_OK; }
-    cudaGetLastError();                          // (cudaErrorNotReady from the query)
-    RT_CUDA(cudaStreamWaitEvent(stream, s->smap_ready, 0));
-    return RT_OK;
-}
 
 int build_bvh(SceneHost* s)
 {

@@ -165,12 +165,6 @@ struct SceneHost {
     DevBuf smap_cells;
     struct SmapHost { size_t offset_plus_1 = 0; float ub[3] = { 0, 0, 0 }, vb[3] = { 0, 0, 0 }; float u0 = 0, v0 = 0, inv_cell = 0; float origin[3] = { 0, 0, 0 }; int R = 0, cube = 0; };
     SmapHost smap[kMaxShadowMaps];
-    // The maps are built on a stream of their own, behind the trees: the first frame's closest-hit kernels do not
-    // need them and run meanwhile; whoever does need them waits for smap_ready (render.cu: wait_shadow_maps).
-    cudaStream_t smap_stream = nullptr;
-    cudaEvent_t smap_ready = nullptr;
-    bool smap_pending = false;
-    DevBuf smap_keys, smap_big, smap_count;     // the build's temporaries (released once it is over)
 
     CameraView cam{};
     Workspace ws;
@@ -202,10 +196,6 @@ SceneView scene_view(const SceneHost* s);
 
 // bvh.cu
 int build_bvh(SceneHost* s);
-// The occluder maps' build is over (waits for it if need be) / has to be over before `stream` goes on (capturing: a
-// captured stream cannot wait for an event from outside, the host waits instead).
-void finish_shadow_maps(SceneHost* s);
-int wait_shadow_maps(SceneHost* s, cudaStream_t stream, bool capturing);
 int tuning_int(const char* name, int dflt, int lo, int hi);   // internal tuning knobs (environment)
 
 // render.cu

@@ -174,7 +174,6 @@ int replicate(RtMultiScene* m)
     }
     RT_CUDA(cudaSetDevice(m->dev[0]));
     RT_CUDA(cudaStreamSynchronize(root->stream));
-    finish_shadow_maps(root);
     for (auto mb : kSceneBuffers) {
         const size_t bytes = (root->*mb).bytes;
         if (!bytes) continue;

@@ -376,7 +376,6 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     ChainStreams& cs = s->ws.chains;
     if (overlap && !cs.ensure(K)) return RT_E_CUDA;
     int n = 0;
-    bool capturing = false;
     // The launch sequence of the frame on `stream` (directly, or under stream capture: see below).
     auto issue = [&](cudaStream_t stream) -> int {
         RT_CUDA(cudaMemsetAsync(s->ws.counters.p, 0, sizeof(Counters) * K, stream));
@@ -422,7 +421,6 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 RT_CUDA(cudaEventRecord(s->prof_mid[l][0], stream));
                 if (s->nl) {
                     const int sh_grid = persistent_grid(work * s->nl, sms, T.grid_mult, kWalkBlock);
-                    if (wait_shadow_maps(s, stream, capturing) != RT_OK) return RT_E_CUDA;
                     if (count) launch_shadow<true>(P, l, l, sharing, sh_grid, stream);
                     else launch_shadow<false>(P, l, l, sharing, sh_grid, stream);
                     n += 2 + P.settled_first + (any_shadow_map(P) ? 1 : 0);
@@ -452,7 +450,6 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
                 if (s->nl) {
                     const bool sharing = steal == 1 || (steal == 0 && chain_pixels <= 1000LL * T.steal_shadow_max_kpixels);
                     const int sh_grid = persistent_grid(all_work * s->nl, sms, T.grid_mult, kWalkBlock);
-                    if (wait_shadow_maps(s, side, capturing) != RT_OK) return RT_E_CUDA;
                     if (count) launch_shadow<true>(P, 0, D, sharing, sh_grid, side);
                     else launch_shadow<false>(P, 0, D, sharing, sh_grid, side);
                     n += 2 + P.settled_first + (any_shadow_map(P) ? 1 : 0);
@@ -510,11 +507,7 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
     bool graphable = !p.profile && !p.instrument;
     if (graphable) {
         cudaStreamCaptureStatus cst = cudaStreamCaptureStatusNone;
-        if (cudaStreamIsCapturing(stream, &cst) != cudaSuccess || cst != cudaStreamCaptureStatusNone) {
-            cudaGetLastError();
-            graphable = false;
-            finish_shadow_maps(s);               // the caller's capture: no waiting for outside events in there either
-        }
+        if (cudaStreamIsCapturing(stream, &cst) != cudaSuccess || cst != cudaStreamCaptureStatusNone) { cudaGetLastError(); graphable = false; }
     }
     const bool same = graphable && G.K == K && G.accel == accel && std::memcmp(G.ps, PS, sizeof(FrameParams) * K) == 0;
     if (same && G.exec) {
@@ -523,8 +516,6 @@ int enqueue_frame(SceneHost* s, const RtRenderParams& p, uchar4* tiles_out, cuda
         s->graph_replays++;
     } else if (same) {
         cudaGraph_t graph = nullptr;
-        finish_shadow_maps(s);                   // (a captured stream cannot wait for an event from outside)
-        capturing = true;
         RT_CUDA(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
         const int rc = issue(stream);
         const cudaError_t ce = cudaStreamEndCapture(stream, &graph);
