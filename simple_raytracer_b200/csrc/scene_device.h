@@ -63,7 +63,7 @@ struct BvhView {
 #ifndef RT_MAX_SHADOW_MAPS
 #define RT_MAX_SHADOW_MAPS 1
 #endif
-constexpr int kMaxShadowMaps = RT_MAX_SHADOW_MAPS;      // lights 0 .. kMaxShadowMaps - 1 may have one
+constexpr int kMaxShadowMaps = RT_MAX_SHADOW_MAPS;      // lights 0 .. kMaxShadowMaps - 1 may have one (why 1)
 struct ShadowMapView {
     const int* cells;                  // [R * R] (directional) or [6][R * R] (point), -1 = none; nullptr = no map
     float ub[3], vb[3];                // directional: orthonormal basis of the light's plane
@@ -195,8 +195,8 @@ struct FrameParams {
     // Shadow chains the any-hit kernel could not finish exactly (more than BvhAccelT::kMaxPartial
     // transparent occluders on one ray): redone by bvh_shadow_redo_kernel.  kRedoCapacity entries.
     unsigned int* redo_list;
-    int settled_first;    // the any-hit kernel's jobs come from the walk lists (bvh_shadow_settle_kernel ran): light 0 is
-                          // not looked up in its occluder map again
+    int settled_first;    // light 0 has an occluder map: bvh_shadow_settle_kernel runs before the any-hit kernel, whose
+                          // jobs then come from the walk lists (unless the frame's probe found that the map does not pay)
 };
 
 }  // namespace rt
