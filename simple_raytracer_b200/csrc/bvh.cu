@@ -566,6 +566,10 @@ struct SmapBuild {
     int cube;
 };
 constexpr int kSmapThreadCells = 1024;
+// ... and those big ones share a budget of cell tests per map: a scene of many map-filling primitives (walls behind
+// walls) would otherwise cost primitives x cells.  Over the budget, each of them is rasterised on every stride-th
+// row and column only — holes in a guess cost nothing but guesses.
+constexpr unsigned long long kSmapBigBudget = 1ull << 30;
 
 RT_DEV unsigned long long smap_key(float depth, int slot)
 {
@@ -661,9 +665,12 @@ RT_DEV SmapPrim smap_setup(const float4* w, const SmapBuild& m, int view)
     return q;
 }
 
-RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int view, unsigned long long* cells, int start, int stride)
+// (step: every step-th row and column of the primitive's cells, 1 = all of them)
+RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int view, unsigned long long* cells, int start, int stride,
+                        int step = 1)
 {
-    const int total = q.wx * q.wy;
+    const int nx = (q.wx + step - 1) / step, ny = (q.wy + step - 1) / step;
+    const int total = nx * ny;
     float den = 0.0f;
     if (q.is_tri) {
         den = (q.x[1] - q.x[0]) * (q.y[2] - q.y[0]) - (q.x[2] - q.x[0]) * (q.y[1] - q.y[0]);
@@ -672,7 +679,7 @@ RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int vie
     unsigned long long* face = cells + (view < 0 ? 0 : (size_t)view * m.R * m.R);
     const float to_dir = 2.0f / (float)m.R;
     for (int i = start; i < total; i += stride) {
-        const int ix = q.x0 + i % q.wx, iy = q.y0 + i / q.wx;
+        const int ix = q.x0 + (i % nx) * step, iy = q.y0 + (i / nx) * step;
         const float cx = (float)ix + 0.5f, cy = (float)iy + 0.5f;
         float depth;
         if (q.is_tri) {
@@ -706,6 +713,7 @@ RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int vie
     }
 }
 
+// n_big[0] = entries of `big`, n_big[1..2] = the cells their bounding boxes hold (64 bits)
 __global__ void smap_prims_kernel(const float4* __restrict__ prims, int n, SmapBuild m, unsigned long long* __restrict__ cells,
                                   int* __restrict__ big, unsigned* __restrict__ n_big)
 {
@@ -714,7 +722,11 @@ __global__ void smap_prims_kernel(const float4* __restrict__ prims, int n, SmapB
     for (int view = m.cube ? 0 : -1; view < (m.cube ? 6 : 0); view++) {
         const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m, view);
         if (!q.ok) continue;
-        if ((long long)q.wx * q.wy > kSmapThreadCells) { big[atomicAdd(n_big, 1u)] = slot * 8 + (view + 1); continue; }
+        if ((long long)q.wx * q.wy > kSmapThreadCells) {
+            big[atomicAdd(n_big, 1u)] = slot * 8 + (view + 1);
+            atomicAdd(reinterpret_cast<unsigned long long*>(n_big + 2), (unsigned long long)q.wx * (unsigned long long)q.wy);
+            continue;
+        }
         smap_raster(q, slot, m, view, cells, 0, 1);
     }
 }
@@ -723,10 +735,13 @@ __global__ void smap_big_kernel(const float4* __restrict__ prims, SmapBuild m, u
                                 const int* __restrict__ big, const unsigned* __restrict__ n_big)
 {
     const unsigned n = *n_big;
+    const unsigned long long work = *reinterpret_cast<const unsigned long long*>(n_big + 2);
+    int step = 1;
+    while ((work / ((unsigned long long)step * step)) > kSmapBigBudget) step *= 2;
     for (unsigned b = blockIdx.x; b < n; b += gridDim.x) {
         const int slot = big[b] >> 3, view = (big[b] & 7) - 1;
         const SmapPrim q = smap_setup(prims + (size_t)slot * kTriWords, m, view);
-        if (q.ok) smap_raster(q, slot, m, view, cells, (int)threadIdx.x, (int)blockDim.x);
+        if (q.ok) smap_raster(q, slot, m, view, cells, (int)threadIdx.x, (int)blockDim.x, step);
     }
 }
 
@@ -785,7 +800,7 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
     // (building the maps on a stream of their own while the first frame's closest-hit kernels run was tried: the two
     // share the SMs and the frame ends no sooner)
     DevBuf keys, big, n_big;
-    if (!s->smap_cells.reserve(total * sizeof(int)) || !keys.reserve(largest * 8) || !big.reserve((size_t)n * 6 * 4) || !n_big.reserve(4))
+    if (!s->smap_cells.reserve(total * sizeof(int)) || !keys.reserve(largest * 8) || !big.reserve((size_t)n * 6 * 4) || !n_big.reserve(16))
         return RT_E_NOMEM;
     for (int j = 0; j < n_maps; j++) {
         const int k = want[j].light;
@@ -827,7 +842,7 @@ static int build_shadow_maps(SceneHost* s, const float4* prims, int n, const Bui
             if (!std::isfinite(m.inv_cell) || !std::isfinite(m.u0) || !std::isfinite(m.v0)) continue;
         }
         RT_CUDA(cudaMemsetAsync(keys.p, 0xff, want[j].cells * 8, st));
-        RT_CUDA(cudaMemsetAsync(n_big.p, 0, 4, st));
+        RT_CUDA(cudaMemsetAsync(n_big.p, 0, 16, st));
         smap_prims_kernel<<<(n + 255) / 256, 256, 0, st>>>(prims, n, m, keys.as<unsigned long long>(), big.as<int>(), n_big.as<unsigned>());
         smap_big_kernel<<<1024, 256, 0, st>>>(prims, m, keys.as<unsigned long long>(), big.as<int>(), n_big.as<unsigned>());
         smap_finish_kernel<<<(unsigned)((want[j].cells + 255) / 256), 256, 0, st>>>(keys.as<unsigned long long>(), want[j].cells,
