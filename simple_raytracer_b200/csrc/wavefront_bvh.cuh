@@ -7,7 +7,10 @@
 //                      (the ShadeRay nodes of the generation) and runs the half of ShadeRay that
 //                      depends only on the hit — medium state machine, Fresnel weights, the two
 //                      child rays appended to the next generation's queue.
-//   bvh_shadow_kernel  one job per node: the shadow rays (main.cpp:896 / 928) to light 0, 1, ...
+//   bvh_shadow_probe_kernel / bvh_shadow_settle_kernel   one thread per node, before the walks: light 0's
+//                      occluder map guesses an opaque occluder, the reference's exact test confirms it, and the
+//                      node's shadow chain is over without a walk; the rest are listed for the walk kernel.
+//   bvh_shadow_kernel  one job per listed node: the shadow rays (main.cpp:896 / 928) to light 0, 1, ...
 //                      as a chain of any-hit walks that stops as soon as the carried product is 0.
 //   bvh_shadow_redo_kernel  the few chains the any-hit kernel had to give up (more partial
 //                      occluders on one ray than its registers hold), by the exact slow path.
