@@ -309,11 +309,6 @@ RT_DEV void shadow_ray_of_light(const FrameParams& P, int li, V3 p, V3& ray, flo
     }
 }
 
-// The occluder map's guess for the shadow ray (p, ray) of light li (scene_device.h: ShadowMapView): the reference's
-// own test of this ray against the opaque primitive that covers the ray's cell nearest to the light.  Accepted
-// (-> true, v.opaque set): the product is exactly 0 whatever else the ray meets (every factor lies in [0,1]), no
-// walk.  Not accepted: the attempt is forgotten (v as shadow_begin left it) and the ray has to be walked.
-// v must come from shadow_begin(p, ray, self, eps, tmax, use_tmax).
 // What the frame's sample said about light li's map (bvh_shadow_probe_kernel; no sample: use the map).
 RT_DEV bool occluder_map_pays(const FrameParams& P, int li)
 {
@@ -321,11 +316,17 @@ RT_DEV bool occluder_map_pays(const FrameParams& P, int li)
     return tries == 0u || hits * 8u >= tries;
 }
 
+// The occluder map's guess for the shadow ray (p, ray) of light li (scene_device.h: ShadowMapView): the reference's
+// own test of this ray against the opaque primitive that covers the ray's cell nearest to the light.  Accepted
+// (-> true, v.opaque set): the product is exactly 0 whatever else the ray meets (every factor lies in [0,1]), no
+// walk.  Not accepted: the attempt is forgotten (v as shadow_begin left it) and the ray has to be walked.
+// v must come from shadow_begin(p, ray, self, eps, tmax, use_tmax).  kForce: whatever the frame's sample said
+// (the sampling kernel itself).
 template <bool kCount, bool kForce = false>
 RT_DEV bool occluder_map_settles(const FrameParams& P, const BvhAccelT<kCount>& acc, int li, V3 p, V3 ray, int self,
                                  float tmax, bool use_tmax, typename BvhAccelT<kCount>::ShadowVisit& v)
 {
-    if (li >= kMaxShadowMaps || P.scene.smap[li].cells == nullptr || !kForce && !occluder_map_pays(P, li)) return false;
+    if (li >= kMaxShadowMaps || P.scene.smap[li].cells == nullptr || (!kForce && !occluder_map_pays(P, li))) return false;
     const ShadowMapView& m = P.scene.smap[li];
     const float R = (float)m.R;
     float fu, fv;
