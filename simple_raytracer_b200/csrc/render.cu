@@ -196,6 +196,10 @@ void ChainStreams::release()
 static int pick_accel(const SceneHost* s, int requested)
 {
     if (s->nf + s->ns == 0) return RT_ACCEL_BRUTE;
+    // Non-finite material / light values (a scene file may say "nan"): the tree path's early-outs — a shadow walk ends
+    // at the first opaque occluder, a chain at a carried product of 0, an occluder map settles a ray — all rest on
+    // every shadow factor lying in [0,1].  The brute-force kernel multiplies every factor in the reference's order.
+    if (!s->zero_mask_exit) return RT_ACCEL_BRUTE;
     if (requested == RT_ACCEL_BRUTE || requested == RT_ACCEL_LBVH) return requested;
     return (s->nf + s->ns) > 48 ? RT_ACCEL_LBVH : RT_ACCEL_BRUTE;
 }

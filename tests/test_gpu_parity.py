@@ -569,3 +569,20 @@ def test_occluder_maps_settle_shadow_rays_without_changing_anything():
             ds.render(accel=abi.RT_ACCEL_BRUTE)
             rgb3, flags3 = ds.download()
             assert np.array_equal(rgb3, rgb) and np.array_equal(flags3, flags), name
+
+
+def test_non_finite_material_values_take_the_brute_force_path():
+    """A scene file may say `nan` (std::stof accepts it).  The tree path's early-outs rest on every shadow factor
+    lying in [0,1]; with a NaN opacity the reference's product 0 * NaN = NaN differs from "0 stays 0".  Such scenes are
+    rendered by the brute-force kernel whatever accelerator was asked for — and equal the oracle, NaN pixels included."""
+    scene = scenegen.random_soup(300, 6, 21, 96, 64)
+    scene.materials["opacity"][3] = np.float32("nan")
+    scene._invalidate()
+    raw, ids, ost = O.oracle_render(scene)
+    with DeviceScene(scene) as ds:
+        st = ds.render(accel=abi.RT_ACCEL_LBVH, instrument=True)
+        assert st.accel_used == abi.RT_ACCEL_BRUTE
+        rgb, flags = ds.download()
+        cmp = common.compare_frames(raw, rgb, flags)
+        assert cmp["exact"] == cmp["pixels"] and cmp["nan_mismatch"] == 0, cmp
+        assert st.nodes_total == ost.nodes_total
