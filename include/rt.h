@@ -119,7 +119,8 @@ typedef struct RtSceneDesc {
 /* ---- render parameters (environment.other, main.cpp:100-101) ------------ */
 #define RT_ACCEL_AUTO   0   /* brute force for small scenes, LBVH otherwise */
 #define RT_ACCEL_BRUTE  1
-#define RT_ACCEL_LBVH   2
+#define RT_ACCEL_LBVH   2   /* (a scene with a non-finite material or light value is rendered by brute force all the
+                               same: RtStats.accel_used says which) */
 #define RT_ACCEL_LBVH8  3   /* rt_trace_shadow only: the 8-wide tree the any-hit kernel walks */
 
 typedef struct RtRenderParams {
