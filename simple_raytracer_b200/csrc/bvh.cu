@@ -15,6 +15,7 @@
 //             (rays with | |ray|^2 - 1 | > 1e-5 never use the tree for spheres, bvh.cuh).
 #include "bvh.cuh"
 #include "host_scene.h"
+#include "smap_span.h"
 
 #include <cfloat>
 #include <cmath>
@@ -713,6 +714,40 @@ RT_DEV void smap_raster(const SmapPrim& q, int slot, const SmapBuild& m, int vie
     }
 }
 
+// A triangle by one thread, row by row: the span of cells inside it (smap_span.h — checked against the per-cell test
+// of smap_raster on the CPU, tests/test_smap_span.py) instead of a test per cell of the bounding box, the barycentrics
+// stepped along the row: half the cells of a bounding box lie outside the triangle, and the index arithmetic of the
+// generic loop costs more than its test (1 M triangles into 4096 x 4096 cells: 1.75 -> see DESIGN.md 5.4).
+RT_DEV void smap_raster_rows(const SmapPrim& q, int slot, const SmapBuild& m, int view, unsigned long long* cells)
+{
+    const float den = (q.x[1] - q.x[0]) * (q.y[2] - q.y[0]) - (q.x[2] - q.x[0]) * (q.y[1] - q.y[0]);
+    if (!(fabsf(den) > 1.0e-12f)) return;                       // edge-on
+    const float inv_den = 1.0f / den;
+    unsigned long long* face = cells + (view < 0 ? 0 : (size_t)view * m.R * m.R);
+    const float to_dir = 2.0f / (float)m.R;
+    for (int iy = q.y0; iy < q.y0 + q.wy; iy++) {
+        const float cy = (float)iy + 0.5f;
+        const SmapRow row = smap_row(q.x, q.y, inv_den, cy);
+        int first, last;
+        if (!smap_span(row, q.x0, q.wx, first, last)) continue;
+        unsigned long long* cell = face + (size_t)iy * m.R + first;
+        float cx = (float)first + 0.5f;
+        for (int ix = first; ix <= last; ix++, cell++, cx += 1.0f) {
+            float depth;
+            if (view < 0) {
+                const float b1 = row.a1 * cx + row.c1, b2 = row.a2 * cx + row.c2;
+                depth = (1.0f - b1 - b2) * q.d[0] + b1 * q.d[1] + b2 * q.d[2];
+            } else {
+                depth = q.pl[3] / (q.pl[0] * (cx * to_dir - 1.0f) + q.pl[1] * (cy * to_dir - 1.0f) + q.pl[2]);
+                if (!(depth > 0.0f)) continue;
+            }
+            if (!isfinite(depth)) continue;
+            const unsigned long long key = smap_key(depth, slot);
+            if (key < *(volatile unsigned long long*)cell) atomicMin(cell, key);
+        }
+    }
+}
+
 // n_big[0] = entries of `big`, n_big[1..2] = the cells their bounding boxes hold (64 bits)
 __global__ void smap_prims_kernel(const float4* __restrict__ prims, int n, SmapBuild m, unsigned long long* __restrict__ cells,
                                   int* __restrict__ big, unsigned* __restrict__ n_big)
@@ -727,7 +762,8 @@ __global__ void smap_prims_kernel(const float4* __restrict__ prims, int n, SmapB
             atomicAdd(reinterpret_cast<unsigned long long*>(n_big + 2), (unsigned long long)q.wx * (unsigned long long)q.wy);
             continue;
         }
-        smap_raster(q, slot, m, view, cells, 0, 1);
+        if (q.is_tri) smap_raster_rows(q, slot, m, view, cells);
+        else smap_raster(q, slot, m, view, cells, 0, 1);
     }
 }
 
